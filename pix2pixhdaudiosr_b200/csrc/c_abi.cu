@@ -1,0 +1,12 @@
+// Error slot + version for libp2p_b200.so (include/p2p_b200.h).
+#include "common.cuh"
+
+namespace p2p {
+char* error_slot() {
+    static thread_local char buf[512] = {0};
+    return buf;
+}
+}  // namespace p2p
+
+extern "C" const char* p2p_last_error(void) { return p2p::error_slot(); }
+extern "C" int p2p_abi_version(void) { return 1; }
