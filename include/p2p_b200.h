@@ -34,8 +34,12 @@ int p2p_abi_version(void);
 
 /* ---- MDCT4 / IMDCT4 ------------------------------------------------------------------------
  * M = n_fft/2 bins, L = M/2 = complex FFT length.  n_fft: power of two, 16..4096.
- * Table layout (float32 words): pre[2L] post[2L] roots[2L] perm[L as int32]  -> 7L words.
+ * Table layout (float32 words): pre[2L] post[2L] roots[2L] perm[L as int32] xtw[2L] -> 9L words
+ * (xtw: exchange twiddles of the register-FFT fast path, zero when n_fft < 256).
  */
+/* Testing/benchmark knob: non-zero forces the general shared-memory kernels even where the
+ * register-FFT fast path (win == n_fft, hop == n_fft/2, n_fft >= 256) applies.  Returns the old value. */
+int p2p_mdct4_force_general(int on);
 int p2p_mdct4_table_words(int n_fft);
 /* host_tables: HOST buffer of p2p_mdct4_table_words(n_fft) 4-byte words, computed in double. */
 int p2p_mdct4_fill_tables(int n_fft, void* host_tables);

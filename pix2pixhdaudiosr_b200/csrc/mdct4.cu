@@ -10,6 +10,7 @@
 // A CTA owns a run of consecutive frames of one batch row, so every signal sample is fetched from
 // HBM once (the hop overlap is served from shared memory) and every coefficient is written once.
 #include "common.cuh"
+#include "mdct4_fast.cuh"
 #include <cmath>
 #include <vector>
 
@@ -259,6 +260,47 @@ int check_geometry(int n_fft, int hop, int win) {
 
 constexpr int kMaxSmem = 227 * 1024;
 
+// (V,P) register/lane split of the L-point FFT used by the fast path; 0 when L has no fast path
+void fast_shape(int L, int* V, int* P) {
+    switch (L) {
+        case 64: *V = 8; *P = 8; break;
+        case 128: *V = 16; *P = 8; break;
+        case 256: *V = 16; *P = 16; break;
+        case 512: *V = 32; *P = 16; break;
+        case 1024: *V = 32; *P = 32; break;
+        default: *V = 0; *P = 0;
+    }
+}
+
+int sm_count_and_blocks(const void* kernel, size_t smem, int* blocks_per_sm) {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, kernel, p2p::fast::kThreads, smem) != cudaSuccess)
+        return -1;
+    return sms;
+}
+
+template <class C>
+int launch_analysis_fast(const float* x, float* spec, const float* window, const void* tables, int B, long long T,
+                         int F, long long offset, float scale, cudaStream_t stream) {
+    using namespace p2p;
+    auto kernel = fast::mdct4_analysis_fast<C>;
+    const size_t smem = C::SMEM_BYTES;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail(P2P_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    int bps = 0;
+    const int sms = sm_count_and_blocks((const void*)kernel, smem, &bps);
+    if (sms <= 0 || bps <= 0) { cudaGetLastError(); return fail(P2P_ECUDA, "occupancy query failed (smem %zu)", smem); }
+    const int tiles_per_row = (F + C::FPT - 1) / C::FPT;
+    const long long total = (long long)tiles_per_row * B;
+    const long long grid = total < (long long)sms * bps ? total : (long long)sms * bps;
+    const int aligned = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && (T % 4 == 0) && (offset % 4 == 0);
+    kernel<<<(unsigned)grid, fast::kThreads, smem, stream>>>(x, spec, window, tables, T, F, offset, scale,
+                                                             tiles_per_row, total, aligned);
+    return check_launch("mdct4_analysis_fast");
+}
+
 template <typename K>
 int ensure_smem(K kernel, size_t bytes) {
     if (bytes > (size_t)kMaxSmem) return p2p::fail(P2P_ENOTSUP, "needs %zu B of shared memory", bytes);
@@ -271,10 +313,13 @@ int ensure_smem(K kernel, size_t bytes) {
 
 }  // namespace
 
+static int g_force_general = 0;
+extern "C" int p2p_mdct4_force_general(int on) { const int old = g_force_general; g_force_general = on; return old; }
+
 extern "C" int p2p_mdct4_table_words(int n_fft) {
     if (!p2p::is_pow2(n_fft) || n_fft < 16 || n_fft > 4096)
         return p2p::fail(P2P_ENOTSUP, "n_fft must be a power of two in [16, 4096], got %d", n_fft);
-    return 7 * (n_fft / 4);
+    return 9 * (n_fft / 4);
 }
 
 extern "C" int p2p_mdct4_fill_tables(int n_fft, void* host_tables) {
@@ -299,6 +344,19 @@ extern "C" int p2p_mdct4_fill_tables(int n_fft, void* host_tables) {
         if (S == 2) { k += rem * weight; }
         perm[p] = k;
     }
+    // fast-path exchange twiddles xtw[k1*P + j] = e^{-2 pi j (j*k1)/L} for the (V,P) split of L
+    int V = 0, P = 0;
+    fast_shape(L, &V, &P);
+    float* xt = f + 7 * L;
+    for (int i = 0; i < 2 * L; ++i) xt[i] = 0.f;
+    if (V) {
+        for (int k1 = 0; k1 < V; ++k1)
+            for (int j = 0; j < P; ++j) {
+                const double a = -2.0 * pi * (double)((long long)j * k1 % L) / L;
+                xt[2 * (k1 * P + j)] = (float)cos(a);
+                xt[2 * (k1 * P + j) + 1] = (float)sin(a);
+            }
+    }
     return P2P_OK;
 }
 
@@ -312,6 +370,16 @@ extern "C" int p2p_mdct4_analysis(const float* x, float* spec, const float* wind
     if (!x || !spec || !window || !tables) return fail(P2P_EINVAL, "null pointer argument");
     if (B > 65535) return fail(P2P_ENOTSUP, "B=%d exceeds 65535 rows per launch", B);
     const int M = n_fft / 2, L = n_fft / 4;
+    if (!g_force_general && win == n_fft && hop == M && L >= 64 && (reinterpret_cast<uintptr_t>(spec) & 7) == 0) {
+        cudaStream_t st = (cudaStream_t)stream;
+        switch (L) {
+            case 64: return launch_analysis_fast<fast::Cfg<8, 8>>(x, spec, window, tables, B, T, F, offset, scale, st);
+            case 128: return launch_analysis_fast<fast::Cfg<16, 8>>(x, spec, window, tables, B, T, F, offset, scale, st);
+            case 256: return launch_analysis_fast<fast::Cfg<16, 16>>(x, spec, window, tables, B, T, F, offset, scale, st);
+            case 512: return launch_analysis_fast<fast::Cfg<32, 16>>(x, spec, window, tables, B, T, F, offset, scale, st);
+            case 1024: return launch_analysis_fast<fast::Cfg<32, 32>>(x, spec, window, tables, B, T, F, offset, scale, st);
+        }
+    }
     int fpb = 4096 / M; if (fpb < 1) fpb = 1; if (fpb > 32) fpb = 32; if (fpb > F) fpb = F;
     const int span_max = (fpb - 1) * hop + win;
     const size_t smem = 4ull * (((span_max + 3) & ~3) + ((win + 3) & ~3) + 2 * fpb * L + fpb * M);

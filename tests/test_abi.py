@@ -39,14 +39,20 @@ def test_tables(n_fft):
     lib = _lib.lib()
     L = n_fft // 4
     words = lib.p2p_mdct4_table_words(n_fft)
-    assert words == 7 * L
+    assert words == 9 * L
     buf = np.zeros(words, np.float32)
     assert lib.p2p_mdct4_fill_tables(n_fft, buf.ctypes.data) == 0
     pre, post = FM.tables(n_fft)
     got_pre = buf[0:2 * L].view(np.complex64)
     got_post = buf[2 * L:4 * L].view(np.complex64)
     roots = buf[4 * L:6 * L].view(np.complex64)
-    perm = buf[6 * L:].view(np.int32)
+    perm = buf[6 * L:7 * L].view(np.int32)
+    xtw = buf[7 * L:9 * L].view(np.complex64)
+    VP = {64: (8, 8), 128: (16, 8), 256: (16, 16), 512: (32, 16), 1024: (32, 32)}.get(L)
+    if VP:
+        V, P = VP
+        want = np.exp(-2j * np.pi * np.outer(np.arange(V), np.arange(P)) / L).reshape(-1)
+        assert np.abs(xtw - want).max() < 1e-7
     assert np.abs(got_pre - pre).max() < 1e-7 and np.abs(got_post - post).max() < 1e-7
     assert np.abs(roots - np.exp(-2j * np.pi * np.arange(L) / L)).max() < 1e-7
     assert sorted(perm.tolist()) == list(range(L))

@@ -80,8 +80,9 @@ def test_large_batch_properties():
     x = torch.randn(B, T, device="cuda")
     z = torch.randn(B, T, device="cuda")
     sx, sz = m(x), m(z)
+    assert tuple(sx.shape) == (B, 257, 512)
     # B % hop == 0 and T % hop != 0 -> the reference drops the partial frame (quirk H8a)
-    assert tuple(sx.shape) == (B, 256, 512)
+    assert tuple(m(x.repeat(2, 1)[:512, :1024 * 8 + 5]).shape) == (512, 17, 512)   # 18 with true T-based padding
     lin = m(2.0 * x - 3.0 * z)
     assert relerr(lin.cpu().numpy(), (2.0 * sx - 3.0 * sz).cpu().numpy()) < TOL
     y = im(sx)
@@ -102,10 +103,10 @@ def test_ragged_and_edge_inputs():
     assert tuple(m(torch.zeros(0, 1000, device="cuda")).shape) == (0, 8, 128)      # empty batch
     x = torch.randn(2, 3, 1000)                                                   # extra leading dims, CPU input
     s = m(x)
-    assert s.is_cuda and tuple(s.shape) == (2, 3, 8, 128)
+    assert s.is_cuda and tuple(s.shape) == (2, 3, 9, 128)
     w = O.kbdwin(256)
     ref = O.mdct4_forward(x.numpy().reshape(6, 1000), w, 256, 128, True, signal_len=2)
-    assert relerr(s.reshape(6, 8, 128).cpu().numpy(), ref) < TOL
+    assert relerr(s.reshape(6, 9, 128).cpu().numpy(), ref) < TOL
     one = im(torch.randn(1, 1, 128, device="cuda"))                                # a single frame
     assert tuple(one.shape) == (1, 1, 1, 0)
     with pytest.raises(RuntimeError):        # shorter than one window: unfold's error in the reference
@@ -121,3 +122,29 @@ def test_reflect_pad_mode_and_gradcheck_like():
     assert relerr(s.detach().cpu().numpy(), ref) < TOL
     s.sum().backward()
     assert x.grad is not None and torch.isfinite(x.grad).all()
+
+
+@pytest.mark.parametrize("n_fft", [256, 512, 1024, 2048, 4096])
+def test_fast_and_general_paths_agree(n_fft):
+    """The register-FFT fast path and the general shared-memory kernels compute the same thing."""
+    from pix2pixhdaudiosr_b200 import _lib
+    torch.manual_seed(n_fft)
+    hop = n_fft // 2
+    x = torch.randn(5, 37 * hop + 123, device="cuda")
+    m = MDCT4(n_fft, hop, n_fft, kbdwin, True, device="cuda")
+    im = IMDCT4(n_fft, hop, n_fft, kbdwin, True, device="cuda")
+    fast_s = m(x)
+    fast_y = im(fast_s)
+    old = _lib.lib().p2p_mdct4_force_general(1)
+    try:
+        gen_s = m(x)
+        gen_y = im(fast_s)
+    finally:
+        _lib.lib().p2p_mdct4_force_general(old)
+    assert relerr(fast_s.cpu().numpy(), gen_s.cpu().numpy()) < 2e-6
+    assert relerr(fast_y.cpu().numpy(), gen_y.cpu().numpy()) < 2e-6
+    # unaligned signal pointer / odd T -> the fast path's non-TMA staging
+    xo = torch.randn(3, 20 * hop + 7, device="cuda")[:, 1:]
+    w = O.kbdwin(n_fft)
+    ref = O.mdct4_forward(xo.cpu().numpy(), w, n_fft, hop, True)
+    assert relerr(m(xo).cpu().numpy(), ref) < TOL
