@@ -311,6 +311,30 @@ int ensure_smem(K kernel, size_t bytes) {
     return P2P_OK;
 }
 
+template <class C>
+int launch_synthesis_fast(const float* spec, float* out, const float* window, const void* tables, int B, int F,
+                          long long T_out, long long crop_left, float scale, cudaStream_t stream) {
+    using namespace p2p;
+    using S = fast::SynCfg<C>;
+    auto kernel = fast::mdct4_synthesis_fast<C>;
+    const size_t smem = S::SMEM_BYTES;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail(P2P_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    int bps = 0;
+    const int sms = sm_count_and_blocks((const void*)kernel, smem, &bps);
+    if (sms <= 0 || bps <= 0) { cudaGetLastError(); return fail(P2P_ECUDA, "occupancy query failed (smem %zu)", smem); }
+    const long long hf = crop_left / C::M, hl = (crop_left + T_out - 1) / C::M;
+    if (hl > 2147483000LL) return fail(P2P_ENOTSUP, "T_out too large");
+    const int tiles_per_row = (int)((hl - hf + 1 + C::FPT - 2) / (C::FPT - 1));
+    const long long total = (long long)tiles_per_row * B;
+    const long long grid = total < (long long)sms * bps ? total : (long long)sms * bps;
+    const int aligned_in = (reinterpret_cast<uintptr_t>(spec) & 15) == 0;
+    const int vec_out = ((reinterpret_cast<uintptr_t>(out) & 15) == 0) && (T_out % 4 == 0) && (crop_left % 4 == 0);
+    kernel<<<(unsigned)grid, fast::kThreads, smem, stream>>>(spec, out, window, tables, F, T_out, crop_left, scale,
+                                                             (int)hf, (int)hl, tiles_per_row, total, aligned_in, vec_out);
+    return check_launch("mdct4_synthesis_fast");
+}
+
 }  // namespace
 
 static int g_force_general = 0;
@@ -401,6 +425,16 @@ extern "C" int p2p_mdct4_synthesis(const float* spec, float* out, const float* w
     if (!out || !window || !tables || (!spec && F > 0)) return fail(P2P_EINVAL, "null pointer argument");
     if (B > 65535) return fail(P2P_ENOTSUP, "B=%d exceeds 65535 rows per launch", B);
     const int M = n_fft / 2, L = n_fft / 4;
+    if (!g_force_general && win == n_fft && hop == M && L >= 64 && F > 0) {
+        cudaStream_t st = (cudaStream_t)stream;
+        switch (L) {
+            case 64: return launch_synthesis_fast<fast::Cfg<8, 8>>(spec, out, window, tables, B, F, T_out, crop_left, scale, st);
+            case 128: return launch_synthesis_fast<fast::Cfg<16, 8>>(spec, out, window, tables, B, F, T_out, crop_left, scale, st);
+            case 256: return launch_synthesis_fast<fast::Cfg<16, 16>>(spec, out, window, tables, B, F, T_out, crop_left, scale, st);
+            case 512: return launch_synthesis_fast<fast::Cfg<32, 16>>(spec, out, window, tables, B, F, T_out, crop_left, scale, st);
+            case 1024: return launch_synthesis_fast<fast::Cfg<32, 32>>(spec, out, window, tables, B, F, T_out, crop_left, scale, st);
+        }
+    }
     const int overlap = (win + hop - 1) / hop;            // frames covering one sample
     int nf_target = 8192 / M; if (nf_target < 2) nf_target = 2;
     int hpb = nf_target - overlap; if (hpb < 1) hpb = 1;

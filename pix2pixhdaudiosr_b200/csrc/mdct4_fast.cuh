@@ -254,5 +254,217 @@ mdct4_analysis_fast(const float* __restrict__ x, float* __restrict__ spec, const
     }
 }
 
+// ---- synthesis ------------------------------------------------------------------------------------
+// A tile = FPT consecutive coefficient rows (frames fA .. fA+FPT-1) of one batch row; it produces the
+// FPT-1 output hop slots that lie between them (slot h = first half of frame h + second half of frame
+// h-1), so consecutive tiles overlap by one frame and every output sample is written exactly once.
+template <class C>
+struct SynCfg {
+    static constexpr int ROWS = C::FPT;
+    static constexpr int BUF = ROWS * C::ROW;                       // floats per coefficient buffer
+    static constexpr int OFF_X = 2 * BUF;
+    static constexpr int OFF_TB = OFF_X + kWarps * C::G * C::XREG;
+    static constexpr int OFF_BAR = OFF_TB + (C::TABLES_IN_SMEM ? 4 * C::L : 0);
+    static constexpr size_t SMEM_BYTES = 4ull * OFF_BAR + 16;
+    static constexpr int G4 = C::M / 4;                             // float4 groups per hop slot
+    static constexpr int NQ = G4 > kThreads ? G4 / kThreads : 1;    // window register sets per thread
+    static constexpr int SS = G4 < kThreads ? kThreads / G4 : 1;    // slots covered per pass
+};
+
+template <class C>
+__device__ __forceinline__ void fetch_rows(float* buf, uint64_t* bar, const float* __restrict__ spec_row, int fA,
+                                           int F, bool aligned) {
+    if (threadIdx.x == 0) {
+        uint32_t bytes = 0;
+        for (int r = 0; r < C::FPT; ++r) {
+            const int f = fA + r;
+            if (aligned && f >= 0 && f < F) bytes += C::M * 4;
+        }
+        mbar_expect_tx(bar, bytes);
+        for (int r = 0; r < C::FPT; ++r) {
+            const int f = fA + r;
+            if (aligned && f >= 0 && f < F) bulk_g2s(buf + r * C::ROW, spec_row + (long long)f * C::M, C::M * 4, bar);
+        }
+    }
+    if (!aligned) {
+        for (int r = 0; r < C::FPT; ++r) {
+            const int f = fA + r;
+            if (f < 0 || f >= F) continue;
+            for (int i = threadIdx.x; i < C::M; i += kThreads) buf[r * C::ROW + i] = __ldg(spec_row + (long long)f * C::M + i);
+        }
+    }
+}
+
+// One warp: coefficient rows of its G frames -> DCT-IV -> t rows written back IN PLACE (same rows).
+template <class C>
+__device__ __forceinline__ void synthesis_warp(float* __restrict__ buf, float* __restrict__ ex_warp, const float2* pre,
+                                               const float2* post, const float2* xtw, const float2 (&xr)[C::XV],
+                                               int fA, int F, int warp, int lane) {
+    constexpr int V = C::V, P = C::P, M = C::M;
+    const int j = lane % P, g = lane / P;
+    const bool flip = (lane >> 4) & 1;
+    const int fl = warp * C::G + g;
+    float* row = buf + fl * C::ROW;
+    const bool valid = (fA + fl) >= 0 && (fA + fl) < F;
+    const int step = flip ? -2 * P : 2 * P;
+    const int first = flip ? M - 1 - 2 * j : 2 * j, second = flip ? 2 * j : M - 1 - 2 * j;
+
+    float2 z[V];
+#pragma unroll
+    for (int n1 = 0; n1 < V; ++n1) {
+        const float a = row[first + step * n1], b = row[second - step * n1];
+        z[n1] = cmulf(make_float2(flip ? b : a, flip ? a : b), ldt<C::TABLES_IN_SMEM>(pre + P * n1 + j));
+    }
+    fft_reg<V>(z);
+
+    float2* ex = reinterpret_cast<float2*>(ex_warp + g * C::XREG);
+#pragma unroll
+    for (int k1 = 0; k1 < V; ++k1) {
+        float2 v = z[brev<V>(k1)];
+        if (k1 > 0) {
+            if constexpr (C::XTW_IN_REGS) v = cmulf(v, xr[k1]);
+            else v = cmulf(v, __ldg(xtw + k1 * P + j));
+        }
+        ex[k1 * (P + 1) + j] = v;
+    }
+    __syncwarp();
+
+    float re_[C::Q][P], nim[C::Q][P];
+#pragma unroll
+    for (int m = 0; m < C::Q; ++m) {
+        float2 b[P];
+        const int k1 = j + P * m;
+#pragma unroll
+        for (int n2 = 0; n2 < P; ++n2) b[n2] = ex[k1 * (P + 1) + n2];
+        fft_reg<P>(b);
+#pragma unroll
+        for (int k2 = 0; k2 < P; ++k2) {
+            const float2 y = cmulf(b[brev<P>(k2)], ldt<C::TABLES_IN_SMEM>(post + k1 + V * k2));
+            re_[m][k2] = y.x;
+            nim[m][k2] = -y.y;
+        }
+    }
+    __syncwarp();
+
+#pragma unroll
+    for (int m = 0; m < C::Q; ++m) {
+#pragma unroll
+        for (int k2 = 0; k2 < P; ++k2) {
+            const float other = __shfl_xor_sync(0xffffffffu, nim[C::Q - 1 - m][P - 1 - k2], P - 1);
+            const int k = j + P * m + V * k2;
+            *reinterpret_cast<float2*>(row + 2 * k) = valid ? make_float2(re_[m][k2], other) : make_float2(0.f, 0.f);
+        }
+    }
+}
+
+template <class C>
+__global__ void __launch_bounds__(kThreads)
+mdct4_synthesis_fast(const float* __restrict__ spec, float* __restrict__ out, const float* __restrict__ window,
+                     const void* __restrict__ tables, int F, long long T_out, long long crop_left, float scale,
+                     int h_first, int h_last, int tiles_per_row, long long total_tiles, int aligned_in, int vec_out) {
+    using S = SynCfg<C>;
+    extern __shared__ __align__(128) float smem[];
+    constexpr int L = C::L, M = C::M;
+    float* buf0 = smem;
+    float* exch = smem + S::OFF_X;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::OFF_BAR);
+    const float* gt = reinterpret_cast<const float*>(tables);
+    const float2* pre = reinterpret_cast<const float2*>(gt);
+    const float2* post = reinterpret_cast<const float2*>(gt + 2 * L);
+    const float2* xtw = reinterpret_cast<const float2*>(gt + 7 * L);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_fence_init(); }
+    if constexpr (C::TABLES_IN_SMEM) {
+        float* tb = smem + S::OFF_TB;
+        for (int i = threadIdx.x; i < 2 * L; i += kThreads) { tb[i] = __ldg(gt + i); tb[2 * L + i] = __ldg(gt + 2 * L + i); }
+        pre = reinterpret_cast<const float2*>(tb);
+        post = reinterpret_cast<const float2*>(tb + 2 * L);
+    }
+    float2 xr[C::XV];
+    if constexpr (C::XTW_IN_REGS) {
+#pragma unroll
+        for (int k1 = 0; k1 < C::V; ++k1) xr[k1] = __ldg(xtw + k1 * C::P + (lane % C::P));
+    } else {
+        xr[0] = make_float2(1.f, 0.f);
+    }
+    // overlap-add role of this thread: float4 group(s) q of every SS-th hop slot; window (with the
+    // unfold signs and the output scale folded in) stays in registers
+    const int q0 = threadIdx.x % S::G4;
+    const int sl0 = (S::G4 < kThreads) ? threadIdx.x / S::G4 : 0;
+    float w1[S::NQ][4], w2[S::NQ][4];
+#pragma unroll
+    for (int qi = 0; qi < S::NQ; ++qi) {
+        const int i = 4 * (q0 + kThreads * qi);
+        const bool lo = i < L;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float a = __ldg(window + i + c) * scale, b = __ldg(window + 2 * L + i + c) * scale;
+            w1[qi][c] = lo ? a : -a;
+            w2[qi][c] = -b;
+        }
+    }
+    __syncthreads();
+
+    auto coord = [&](long long w, int& row, int& h0, int& ns) {
+        row = (int)(w / tiles_per_row);
+        h0 = h_first + (int)(w - (long long)row * tiles_per_row) * (C::FPT - 1);
+        ns = min(C::FPT - 1, h_last + 1 - h0);
+    };
+    long long w = blockIdx.x;
+    int row, h0, ns;
+    if (w < total_tiles) {
+        coord(w, row, h0, ns);
+        fetch_rows<C>(buf0, &bars[0], spec + (long long)row * F * M, h0 - 1, F, aligned_in);
+    }
+    __syncthreads();
+    uint32_t phase[2] = {0, 0};
+    int b = 0;
+    for (; w < total_tiles; w += gridDim.x) {
+        coord(w, row, h0, ns);
+        const long long wn = w + gridDim.x;
+        if (wn < total_tiles) {
+            int rown, h0n, nsn;
+            coord(wn, rown, h0n, nsn);
+            fetch_rows<C>(buf0 + (b ^ 1) * S::BUF, &bars[b ^ 1], spec + (long long)rown * F * M, h0n - 1, F, aligned_in);
+        }
+        mbar_wait(&bars[b], phase[b]);
+        phase[b] ^= 1;
+        float* buf = buf0 + b * S::BUF;
+        if (warp * C::G <= ns)       // frames fA .. fA+ns are needed (ns+1 rows)
+            synthesis_warp<C>(buf, exch + warp * C::G * C::XREG, pre, post, xtw, xr, h0 - 1, F, warp, lane);
+        __syncthreads();
+
+        float* orow = out + (long long)row * T_out;
+        for (int sl = sl0; sl < ns; sl += S::SS) {
+            const float* tp = buf + sl * C::ROW;          // frame h-1
+            const float* th = tp + C::ROW;                // frame h
+#pragma unroll
+            for (int qi = 0; qi < S::NQ; ++qi) {
+                const int i = 4 * (q0 + kThreads * qi);
+                const bool lo = i < L;
+                const float4 A = *reinterpret_cast<const float4*>(th + (lo ? L + i : 3 * L - 4 - i));
+                const float4 Bv = *reinterpret_cast<const float4*>(tp + (lo ? L - 4 - i : i - L));
+                float4 o;
+                o.x = w1[qi][0] * (lo ? A.x : A.w) + w2[qi][0] * (lo ? Bv.w : Bv.x);
+                o.y = w1[qi][1] * (lo ? A.y : A.z) + w2[qi][1] * (lo ? Bv.z : Bv.y);
+                o.z = w1[qi][2] * (lo ? A.z : A.y) + w2[qi][2] * (lo ? Bv.y : Bv.z);
+                o.w = w1[qi][3] * (lo ? A.w : A.x) + w2[qi][3] * (lo ? Bv.x : Bv.w);
+                const long long s = (long long)(h0 + sl) * M + i - crop_left;
+                if (vec_out && s >= 0 && s + 3 < T_out) {
+                    *reinterpret_cast<float4*>(orow + s) = o;
+                } else {
+                    if (s >= 0 && s < T_out) orow[s] = o.x;
+                    if (s + 1 >= 0 && s + 1 < T_out) orow[s + 1] = o.y;
+                    if (s + 2 >= 0 && s + 2 < T_out) orow[s + 2] = o.z;
+                    if (s + 3 >= 0 && s + 3 < T_out) orow[s + 3] = o.w;
+                }
+            }
+        }
+        __syncthreads();
+        b ^= 1;
+    }
+}
+
 }  // namespace fast
 }  // namespace p2p
