@@ -33,11 +33,11 @@ struct Cfg {
     static constexpr int XV = XTW_IN_REGS ? V : 1;
     static constexpr int WS = N + ROWPAD;            // signed window, same padded layout as a frame
     static_assert(V >= P && V % P == 0, "V must be a multiple of P");
-    // shared memory layout (floats): sig[2][SIG] | ws[WS] | exch[kWarps*G][XREG] | tables[4L]? | mbar
+    // shared memory layout (floats): sig[2][SIG] | ws[WS] | exch[kWarps*G][XREG] | tables[6L]? (pre, pre_f, post) | mbar
     static constexpr int OFF_WS = 2 * SIG;
     static constexpr int OFF_X = OFF_WS + ((WS + 3) & ~3);
     static constexpr int OFF_TB = OFF_X + kWarps * G * XREG;
-    static constexpr int OFF_BAR = OFF_TB + (TABLES_IN_SMEM ? 4 * L : 0);
+    static constexpr int OFF_BAR = OFF_TB + (TABLES_IN_SMEM ? 6 * L : 0);
     static constexpr size_t SMEM_BYTES = 4ull * OFF_BAR + 16;
 };
 
@@ -84,21 +84,23 @@ __device__ __forceinline__ void fetch_tile(float* sig, uint64_t* bar, const floa
     const float* xb = x + (long long)tc.row * T;
     const long long t_first = (long long)tc.f0 * C::M - offset;
     const int rows = tc.nfr + 1;
-    if (threadIdx.x == 0) {
-        uint32_t bytes = 0;
-        for (int r = 0; r < rows; ++r) {
-            const long long t = t_first + (long long)r * C::M;
-            if (aligned && t >= 0 && t + C::M <= T) bytes += C::M * 4;
-        }
-        mbar_expect_tx(bar, bytes);
-        for (int r = 0; r < rows; ++r) {
-            const long long t = t_first + (long long)r * C::M;
-            if (aligned && t >= 0 && t + C::M <= T) bulk_g2s(sig + r * C::ROW, xb + t, C::M * 4, bar);
-        }
+    // bulk (TMA) rows are [r_lo, r_hi): in range and aligned; the rest is staged by ordinary loads
+    int r_lo = 0, r_hi = 0;
+    if (aligned) {
+        r_lo = t_first >= 0 ? 0 : (int)min((long long)rows, (-t_first + C::M - 1) / C::M);
+        const long long fit = (T - t_first) / C::M;             // rows r < fit end inside [0,T)
+        r_hi = (int)max((long long)r_lo, min((long long)rows, fit));
     }
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(bar, (uint32_t)(r_hi - r_lo) * C::M * 4);
+#pragma unroll 1
+        for (int r = r_lo; r < r_hi; ++r)
+            bulk_g2s(sig + r * C::ROW, xb + t_first + (long long)r * C::M, C::M * 4, bar);
+    }
+#pragma unroll 1
     for (int r = 0; r < rows; ++r) {
+        if (r >= r_lo && r < r_hi) { r = r_hi - 1; continue; }
         const long long t = t_first + (long long)r * C::M;
-        if (aligned && t >= 0 && t + C::M <= T) continue;
         for (int i = threadIdx.x; i < C::M; i += kThreads) {
             const long long tt = t + i;
             sig[r * C::ROW + i] = (tt >= 0 && tt < T) ? __ldg(xb + tt) : 0.f;
@@ -114,84 +116,152 @@ __device__ __forceinline__ float2 ldt(const float2* p) {
 template <int R>
 __device__ __forceinline__ int brev(int k) { return (int)(__brev((unsigned)k) >> (32 - ilog2(R))); }
 
-// One warp transforms its G frames of the current tile: fold + signed window + pre-twiddle ->
-// radix-V -> exchange -> radix-P -> post-twiddle -> pair up (X[2k], X[2k+1]) by one shuffle -> STG.64.
-//   sig : tile signal buffer (rows of C::ROW floats), ws: signed, scaled, padded window
-//   ex  : this warp's exchange regions, pre/post/xtw: twiddle tables (shared or global)
+// ---- lane roles -------------------------------------------------------------------------------------
+// Lane l: j = l % P (column of the L = V*P point FFT), g = l / P (frame of the warp), flip = (l>>4)&1.
+// Fold/de-interleave reads are stride-2 floats, so lanes 0-15 would collide with lanes 16-31 on the same
+// banks.  "Flipped" lanes therefore read the ODD-position operand of every pair first, and - so that all
+// shared-memory offsets stay compile-time immediates - hold their V points in REVERSED order:
+//   register n1 of a flipped lane holds z[P*pi(n1) + j],  pi(n1) = (c - n1) mod V
+// (c = V/2-1 for analysis, V-1 for synthesis).  FFT_V of the reversed sequence is w_V^{c k} Z[-k mod V]; the
+// phase is folded into the lane's exchange twiddle and the row reversal into the stage-2 row pointer.
 template <class C>
-__device__ __forceinline__ void analysis_warp(const float* __restrict__ sig, const float* __restrict__ ws,
-                                              float* __restrict__ ex_warp, const float2* pre, const float2* post,
-                                              const float2* xtw, const float2 (&xr)[C::XV],
-                                              float* __restrict__ spec_tile, int nfr, int warp, int lane) {
-    constexpr int V = C::V, P = C::P, L = C::L, PAD = C::ROWPAD;
-    const int j = lane % P, g = lane / P;
-    const bool flip = (lane >> 4) & 1;
-    const int fl = warp * C::G + g;
-    const float* sf = sig + fl * C::ROW;
-    const int step = flip ? -2 * P : 2 * P;
-    const int e2j = 2 * j;
-    // (first, second) base offsets of the four fold pairs; see DESIGN.md "fold with a signed window"
-    auto b1 = [&](int ce, int co) { return flip ? co - e2j : ce + e2j; };
-    auto b2 = [&](int ce, int co) { return flip ? ce + e2j : co - e2j; };
-    const int aRe1 = b1(3 * L + PAD, 3 * L - 1 + PAD), aRe2 = b2(3 * L + PAD, 3 * L - 1 + PAD);
-    const int aIm1 = b1(L, L - 1), aIm2 = b2(L, L - 1);
-    const int bRe1 = b1(0, 2 * L - 1), bRe2 = b2(0, 2 * L - 1);
-    const int bIm1 = b1(2 * L + PAD, 4 * L - 1 + PAD), bIm2 = b2(2 * L + PAD, 4 * L - 1 + PAD);
-
-    float2 z[V];
-#pragma unroll
-    for (int n1 = 0; n1 < V; ++n1) {
-        const bool caseA = n1 < V / 2;
-        const int i = caseA ? n1 : n1 - V / 2;
-        const int r1 = (caseA ? aRe1 : bRe1) + step * i, r2 = (caseA ? aRe2 : bRe2) - step * i;
-        const int i1 = (caseA ? aIm1 : bIm1) + step * i, i2 = (caseA ? aIm2 : bIm2) - step * i;
-        const float re = ws[r1] * sf[r1] + ws[r2] * sf[r2];
-        const float im = ws[i1] * sf[i1] + ws[i2] * sf[i2];
-        z[n1] = cmulf(make_float2(re, im), ldt<C::TABLES_IN_SMEM>(pre + P * n1 + j));
+struct LaneRole {
+    int j, g;
+    bool flip;
+    __device__ __forceinline__ LaneRole(int lane) : j(lane % C::P), g(lane / C::P), flip((lane >> 4) & 1) {}
+    // index into roots[] (e^{-2 pi i m/L}) of this lane's exchange twiddle for first-stage output slot k1
+    __device__ __forceinline__ int xtw_index(int k1, int c) const {
+        if (!flip) return j * k1;
+        const int kappa = (C::V - k1) % C::V;
+        return (j * kappa - c * k1 * C::P) & (C::L - 1);
     }
-    fft_reg<V>(z);
+};
 
-    float2* ex = reinterpret_cast<float2*>(ex_warp + g * C::XREG);
+template <class C>
+__device__ __forceinline__ int pi_rev(int n1, int c) { return (c - n1 + 2 * C::V) % C::V; }
+
+// stages 1b..2 shared by analysis and synthesis: z (V registers, lane order as above) -> Y[k1 + V k2] * post
+// returns re_[m][k2] = Re, nim[m][k2] = -Im for k = j + P m + V k2.
+template <class C>
+__device__ __forceinline__ void fft_core(float2 (&z)[C::V], float* __restrict__ ex_warp, const float2* post,
+                                         const float2* roots, const float2 (&xr)[C::XV], const LaneRole<C>& ln, int c,
+                                         float (&re_)[C::Q][C::P], float (&nim)[C::Q][C::P]) {
+    constexpr int V = C::V, P = C::P;
+    fft_reg<V>(z);
+    float2* ex = reinterpret_cast<float2*>(ex_warp + ln.g * C::XREG);
+    float2* exw = ex + ln.j;
 #pragma unroll
     for (int k1 = 0; k1 < V; ++k1) {
         float2 v = z[brev<V>(k1)];
         if (k1 > 0) {
             if constexpr (C::XTW_IN_REGS) v = cmulf(v, xr[k1]);
-            else v = cmulf(v, __ldg(xtw + k1 * P + j));
+            else v = cmulf(v, __ldg(roots + ln.xtw_index(k1, c)));
         }
-        ex[k1 * (P + 1) + j] = v;
+        exw[k1 * (P + 1)] = v;          // flipped lanes: physical row k1 holds logical row (V-k1)%V
     }
     __syncwarp();
-
-    float re_[C::Q][P], nim[C::Q][P];
 #pragma unroll
     for (int m = 0; m < C::Q; ++m) {
         float2 b[P];
-        const int k1 = j + P * m;
+        const int k1 = ln.j + P * m;
+        const float2* rowN = ex + k1 * (P + 1);
+        const float2* rowF = ex + ((V - k1) % V) * (P + 1);
+        const float2* rowL = ln.flip ? rowF : rowN;
 #pragma unroll
-        for (int n2 = 0; n2 < P; ++n2) b[n2] = ex[k1 * (P + 1) + n2];
+        for (int n2 = 0; n2 < P; ++n2) {
+            if constexpr (P == 32) b[n2] = (n2 >= 16 ? rowF : rowN)[n2];   // columns 16.. were written by flipped lanes
+            else b[n2] = rowL[n2];
+        }
         fft_reg<P>(b);
+        const float2* pk = post + k1;
 #pragma unroll
         for (int k2 = 0; k2 < P; ++k2) {
-            const float2 y = cmulf(b[brev<P>(k2)], ldt<C::TABLES_IN_SMEM>(post + k1 + V * k2));
+            const float2 y = cmulf(b[brev<P>(k2)], ldt<C::TABLES_IN_SMEM>(pk + V * k2));
             re_[m][k2] = y.x;
             nim[m][k2] = -y.y;
         }
     }
     __syncwarp();   // exchange regions are reused by the next tile
+}
 
-    float* sp = spec_tile + (long long)fl * C::M;
+// One warp transforms its G frames of the current tile: fold + signed window + pre-twiddle ->
+// radix-V -> exchange -> radix-P -> post-twiddle -> pair up (X[2k], X[2k+1]) by one shuffle -> STG.64.
+//   sig : tile signal buffer (rows of C::ROW floats), ws: signed, scaled, padded window
+//   pre : this lane's pre-twiddle row base (pre + j, or the reversed-order copy for flipped lanes)
+template <class C>
+__device__ __forceinline__ void analysis_warp(const float* __restrict__ sig, const float* __restrict__ ws,
+                                              float* __restrict__ ex_warp, const float2* pre_lane, const float2* post,
+                                              const float2* roots, const float2 (&xr)[C::XV],
+                                              float* __restrict__ spec_tile, int nfr, int warp, const LaneRole<C>& ln) {
+    constexpr int V = C::V, P = C::P, L = C::L, PAD = C::ROWPAD, H = V / 2, CREV = V / 2 - 1;
+    const int fl = warp * C::G + ln.g;
+    const float* sf = sig + fl * C::ROW;
+    const int e2j = 2 * ln.j;
+    // pair (Ce, Co): even-position operand at Ce + 2j + 2P i, odd-position operand at Co - 2j - 2P i.
+    // first load = base F + 2P i, second load = base S - 2P i for BOTH lane kinds (see LaneRole).
+    auto F = [&](int ce, int co) { return ln.flip ? co - e2j - 2 * P * (H - 1) : ce + e2j; };
+    auto S = [&](int ce, int co) { return ln.flip ? ce + e2j + 2 * P * (H - 1) : co - e2j; };
+    const int fo[4] = {F(3 * L + PAD, 3 * L - 1 + PAD), F(L, L - 1), F(0, 2 * L - 1), F(2 * L + PAD, 4 * L - 1 + PAD)};
+    const int so[4] = {S(3 * L + PAD, 3 * L - 1 + PAD), S(L, L - 1), S(0, 2 * L - 1), S(2 * L + PAD, 4 * L - 1 + PAD)};
+    const float *sF[4], *sS[4], *wF[4], *wS[4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { sF[t] = sf + fo[t]; sS[t] = sf + so[t]; wF[t] = ws + fo[t]; wS[t] = ws + so[t]; }
+
+    float2 z[V];
+#pragma unroll
+    for (int n1 = 0; n1 < V; ++n1) {
+        constexpr int dummy = 0; (void)dummy;
+        const int tA = n1 < H ? 0 : 2;                 // pair types: A.re, A.im, B.re, B.im
+        const int i = n1 < H ? n1 : n1 - H;
+        const float re = wF[tA][2 * P * i] * sF[tA][2 * P * i] + wS[tA][-2 * P * i] * sS[tA][-2 * P * i];
+        const float im = wF[tA + 1][2 * P * i] * sF[tA + 1][2 * P * i] + wS[tA + 1][-2 * P * i] * sS[tA + 1][-2 * P * i];
+        float2 tw;
+        if constexpr (C::TABLES_IN_SMEM) tw = pre_lane[P * n1];
+        else tw = __ldg(pre_lane + P * (ln.flip ? pi_rev<C>(n1, CREV) : n1));
+        z[n1] = cmulf(make_float2(re, im), tw);
+    }
+    float re_[C::Q][P], nim[C::Q][P];
+    fft_core<C>(z, ex_warp, post, roots, xr, ln, CREV, re_, nim);
+
+    float* sp = spec_tile + (long long)fl * C::M + 2 * ln.j;
     const bool valid = fl < nfr;
 #pragma unroll
     for (int m = 0; m < C::Q; ++m) {
 #pragma unroll
         for (int k2 = 0; k2 < P; ++k2) {
             const float other = __shfl_xor_sync(0xffffffffu, nim[C::Q - 1 - m][P - 1 - k2], P - 1);
-            if (valid) {
-                const int k = j + P * m + V * k2;
-                *reinterpret_cast<float2*>(sp + 2 * k) = make_float2(re_[m][k2], other);
-            }
+            if (valid) *reinterpret_cast<float2*>(sp + 2 * (P * m + V * k2)) = make_float2(re_[m][k2], other);
         }
+    }
+}
+
+// Prologue shared by both kernels: pre / pre_f / post tables into shared memory (when they fit), the lane's
+// pre-twiddle base pointer and its exchange twiddles (registers when V <= 16).
+template <class C>
+__device__ __forceinline__ void setup_tables(float* tb, const float* gt, int c, const LaneRole<C>& ln,
+                                             const float2*& pre_lane, const float2*& post, const float2*& roots,
+                                             float2 (&xr)[C::XV]) {
+    constexpr int L = C::L;
+    const float2* gpre = reinterpret_cast<const float2*>(gt);
+    post = reinterpret_cast<const float2*>(gt + 2 * L);
+    roots = reinterpret_cast<const float2*>(gt + 4 * L);
+    pre_lane = gpre + ln.j;
+    if constexpr (C::TABLES_IN_SMEM) {
+        float2* t2 = reinterpret_cast<float2*>(tb);
+        for (int i = threadIdx.x; i < L; i += kThreads) {
+            const int n1 = i / C::P, jj = i % C::P;
+            t2[i] = __ldg(gpre + i);                                          // pre
+            t2[L + i] = __ldg(gpre + C::P * pi_rev<C>(n1, c) + jj);            // pre_f: reversed register order
+            t2[2 * L + i] = __ldg(post + i);                                  // post
+        }
+        pre_lane = t2 + (ln.flip ? L : 0) + ln.j;
+        post = t2 + 2 * L;
+    }
+    if constexpr (C::XTW_IN_REGS) {
+#pragma unroll
+        for (int k1 = 0; k1 < C::V; ++k1) xr[k1] = __ldg(roots + ln.xtw_index(k1, c));
+    } else {
+        xr[0] = make_float2(1.f, 0.f);
     }
 }
 
@@ -206,32 +276,17 @@ mdct4_analysis_fast(const float* __restrict__ x, float* __restrict__ spec, const
     float* ws = smem + C::OFF_WS;
     float* exch = smem + C::OFF_X;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::OFF_BAR);
-    const float* gt = reinterpret_cast<const float*>(tables);
-    const float2* pre = reinterpret_cast<const float2*>(gt);
-    const float2* post = reinterpret_cast<const float2*>(gt + 2 * L);
-    const float2* xtw = reinterpret_cast<const float2*>(gt + 7 * L);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const LaneRole<C> ln(lane);
 
     if (threadIdx.x == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_fence_init(); }
     for (int p = threadIdx.x; p < N; p += kThreads) {
         const float w = __ldg(window + p) * scale;
         ws[p + (p >= 2 * L ? C::ROWPAD : 0)] = p < L ? w : -w;
     }
-    if constexpr (C::TABLES_IN_SMEM) {
-        float* tb = smem + C::OFF_TB;
-        for (int i = threadIdx.x; i < 2 * L; i += kThreads) {
-            tb[i] = __ldg(gt + i); tb[2 * L + i] = __ldg(gt + 2 * L + i);
-        }
-        pre = reinterpret_cast<const float2*>(tb);
-        post = reinterpret_cast<const float2*>(tb + 2 * L);
-    }
+    const float2 *pre_lane, *post, *roots;
     float2 xr[C::XV];
-    if constexpr (C::XTW_IN_REGS) {
-#pragma unroll
-        for (int k1 = 0; k1 < C::V; ++k1) xr[k1] = __ldg(xtw + k1 * C::P + (lane % C::P));
-    } else {
-        xr[0] = make_float2(1.f, 0.f);
-    }
+    setup_tables<C>(smem + C::OFF_TB, reinterpret_cast<const float*>(tables), C::V / 2 - 1, ln, pre_lane, post, roots, xr);
     __syncthreads();
 
     long long w = blockIdx.x;
@@ -247,8 +302,8 @@ mdct4_analysis_fast(const float* __restrict__ x, float* __restrict__ spec, const
         mbar_wait(&bars[buf], phase[buf]);
         phase[buf] ^= 1;
         if (warp * C::G < tc.nfr)
-            analysis_warp<C>(sig0 + buf * C::SIG, ws, exch + warp * C::G * C::XREG, pre, post, xtw, xr,
-                             spec + ((long long)tc.row * F + tc.f0) * M, tc.nfr, warp, lane);
+            analysis_warp<C>(sig0 + buf * C::SIG, ws, exch + warp * C::G * C::XREG, pre_lane, post, roots, xr,
+                             spec + ((long long)tc.row * F + tc.f0) * M, tc.nfr, warp, ln);
         __syncthreads();
         buf ^= 1;
     }
@@ -264,7 +319,7 @@ struct SynCfg {
     static constexpr int BUF = ROWS * C::ROW;                       // floats per coefficient buffer
     static constexpr int OFF_X = 2 * BUF;
     static constexpr int OFF_TB = OFF_X + kWarps * C::G * C::XREG;
-    static constexpr int OFF_BAR = OFF_TB + (C::TABLES_IN_SMEM ? 4 * C::L : 0);
+    static constexpr int OFF_BAR = OFF_TB + (C::TABLES_IN_SMEM ? 6 * C::L : 0);
     static constexpr size_t SMEM_BYTES = 4ull * OFF_BAR + 16;
     static constexpr int G4 = C::M / 4;                             // float4 groups per hop slot
     static constexpr int NQ = G4 > kThreads ? G4 / kThreads : 1;    // window register sets per thread
@@ -274,85 +329,58 @@ struct SynCfg {
 template <class C>
 __device__ __forceinline__ void fetch_rows(float* buf, uint64_t* bar, const float* __restrict__ spec_row, int fA,
                                            int F, bool aligned) {
-    if (threadIdx.x == 0) {
-        uint32_t bytes = 0;
-        for (int r = 0; r < C::FPT; ++r) {
-            const int f = fA + r;
-            if (aligned && f >= 0 && f < F) bytes += C::M * 4;
+    const int r_lo = max(0, -fA), r_hi = max(r_lo, min(C::FPT, F - fA));     // rows holding real frames
+    if (aligned) {
+        if (threadIdx.x == 0) {
+            mbar_expect_tx(bar, (uint32_t)(r_hi - r_lo) * C::M * 4);
+#pragma unroll 1
+            for (int r = r_lo; r < r_hi; ++r)
+                bulk_g2s(buf + r * C::ROW, spec_row + (long long)(fA + r) * C::M, C::M * 4, bar);
         }
-        mbar_expect_tx(bar, bytes);
-        for (int r = 0; r < C::FPT; ++r) {
-            const int f = fA + r;
-            if (aligned && f >= 0 && f < F) bulk_g2s(buf + r * C::ROW, spec_row + (long long)f * C::M, C::M * 4, bar);
-        }
-    }
-    if (!aligned) {
-        for (int r = 0; r < C::FPT; ++r) {
-            const int f = fA + r;
-            if (f < 0 || f >= F) continue;
-            for (int i = threadIdx.x; i < C::M; i += kThreads) buf[r * C::ROW + i] = __ldg(spec_row + (long long)f * C::M + i);
-        }
+    } else {
+        if (threadIdx.x == 0) mbar_expect_tx(bar, 0);
+#pragma unroll 1
+        for (int r = r_lo; r < r_hi; ++r)
+            for (int i = threadIdx.x; i < C::M; i += kThreads)
+                buf[r * C::ROW + i] = __ldg(spec_row + (long long)(fA + r) * C::M + i);
     }
 }
 
 // One warp: coefficient rows of its G frames -> DCT-IV -> t rows written back IN PLACE (same rows).
 template <class C>
-__device__ __forceinline__ void synthesis_warp(float* __restrict__ buf, float* __restrict__ ex_warp, const float2* pre,
-                                               const float2* post, const float2* xtw, const float2 (&xr)[C::XV],
-                                               int fA, int F, int warp, int lane) {
-    constexpr int V = C::V, P = C::P, M = C::M;
-    const int j = lane % P, g = lane / P;
-    const bool flip = (lane >> 4) & 1;
-    const int fl = warp * C::G + g;
+__device__ __forceinline__ void synthesis_warp(float* __restrict__ buf, float* __restrict__ ex_warp,
+                                               const float2* pre_lane, const float2* post, const float2* roots,
+                                               const float2 (&xr)[C::XV], int fA, int F, int warp,
+                                               const LaneRole<C>& ln) {
+    constexpr int V = C::V, P = C::P, M = C::M, CREV = V - 1;
+    const int fl = warp * C::G + ln.g;
     float* row = buf + fl * C::ROW;
     const bool valid = (fA + fl) >= 0 && (fA + fl) < F;
-    const int step = flip ? -2 * P : 2 * P;
-    const int first = flip ? M - 1 - 2 * j : 2 * j, second = flip ? 2 * j : M - 1 - 2 * j;
+    // z[n] = X[2n] + j X[M-1-2n]: even operand at 2j + 2P n1, odd operand at M-1-2j - 2P n1; flipped lanes
+    // read the odd one first and hold their points in reversed order (LaneRole)
+    const float* pF = row + (ln.flip ? M - 1 - 2 * ln.j - 2 * P * (V - 1) : 2 * ln.j);
+    const float* pS = row + (ln.flip ? 2 * ln.j + 2 * P * (V - 1) : M - 1 - 2 * ln.j);
 
     float2 z[V];
 #pragma unroll
     for (int n1 = 0; n1 < V; ++n1) {
-        const float a = row[first + step * n1], b = row[second - step * n1];
-        z[n1] = cmulf(make_float2(flip ? b : a, flip ? a : b), ldt<C::TABLES_IN_SMEM>(pre + P * n1 + j));
+        const float a = pF[2 * P * n1], b = pS[-2 * P * n1];
+        float2 tw;
+        if constexpr (C::TABLES_IN_SMEM) tw = pre_lane[P * n1];
+        else tw = __ldg(pre_lane + P * (ln.flip ? pi_rev<C>(n1, CREV) : n1));
+        z[n1] = cmulf(make_float2(ln.flip ? b : a, ln.flip ? a : b), tw);
     }
-    fft_reg<V>(z);
-
-    float2* ex = reinterpret_cast<float2*>(ex_warp + g * C::XREG);
-#pragma unroll
-    for (int k1 = 0; k1 < V; ++k1) {
-        float2 v = z[brev<V>(k1)];
-        if (k1 > 0) {
-            if constexpr (C::XTW_IN_REGS) v = cmulf(v, xr[k1]);
-            else v = cmulf(v, __ldg(xtw + k1 * P + j));
-        }
-        ex[k1 * (P + 1) + j] = v;
-    }
-    __syncwarp();
-
     float re_[C::Q][P], nim[C::Q][P];
-#pragma unroll
-    for (int m = 0; m < C::Q; ++m) {
-        float2 b[P];
-        const int k1 = j + P * m;
-#pragma unroll
-        for (int n2 = 0; n2 < P; ++n2) b[n2] = ex[k1 * (P + 1) + n2];
-        fft_reg<P>(b);
-#pragma unroll
-        for (int k2 = 0; k2 < P; ++k2) {
-            const float2 y = cmulf(b[brev<P>(k2)], ldt<C::TABLES_IN_SMEM>(post + k1 + V * k2));
-            re_[m][k2] = y.x;
-            nim[m][k2] = -y.y;
-        }
-    }
-    __syncwarp();
+    fft_core<C>(z, ex_warp, post, roots, xr, ln, CREV, re_, nim);
 
+    float* tp = row + 2 * ln.j;
 #pragma unroll
     for (int m = 0; m < C::Q; ++m) {
 #pragma unroll
         for (int k2 = 0; k2 < P; ++k2) {
             const float other = __shfl_xor_sync(0xffffffffu, nim[C::Q - 1 - m][P - 1 - k2], P - 1);
-            const int k = j + P * m + V * k2;
-            *reinterpret_cast<float2*>(row + 2 * k) = valid ? make_float2(re_[m][k2], other) : make_float2(0.f, 0.f);
+            re_[m][k2] = valid ? re_[m][k2] : 0.f;
+            *reinterpret_cast<float2*>(tp + 2 * (P * m + V * k2)) = make_float2(re_[m][k2], valid ? other : 0.f);
         }
     }
 }
@@ -368,26 +396,13 @@ mdct4_synthesis_fast(const float* __restrict__ spec, float* __restrict__ out, co
     float* buf0 = smem;
     float* exch = smem + S::OFF_X;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::OFF_BAR);
-    const float* gt = reinterpret_cast<const float*>(tables);
-    const float2* pre = reinterpret_cast<const float2*>(gt);
-    const float2* post = reinterpret_cast<const float2*>(gt + 2 * L);
-    const float2* xtw = reinterpret_cast<const float2*>(gt + 7 * L);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const LaneRole<C> ln(lane);
 
     if (threadIdx.x == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_fence_init(); }
-    if constexpr (C::TABLES_IN_SMEM) {
-        float* tb = smem + S::OFF_TB;
-        for (int i = threadIdx.x; i < 2 * L; i += kThreads) { tb[i] = __ldg(gt + i); tb[2 * L + i] = __ldg(gt + 2 * L + i); }
-        pre = reinterpret_cast<const float2*>(tb);
-        post = reinterpret_cast<const float2*>(tb + 2 * L);
-    }
+    const float2 *pre_lane, *post, *roots;
     float2 xr[C::XV];
-    if constexpr (C::XTW_IN_REGS) {
-#pragma unroll
-        for (int k1 = 0; k1 < C::V; ++k1) xr[k1] = __ldg(xtw + k1 * C::P + (lane % C::P));
-    } else {
-        xr[0] = make_float2(1.f, 0.f);
-    }
+    setup_tables<C>(smem + S::OFF_TB, reinterpret_cast<const float*>(tables), C::V - 1, ln, pre_lane, post, roots, xr);
     // overlap-add role of this thread: float4 group(s) q of every SS-th hop slot; window (with the
     // unfold signs and the output scale folded in) stays in registers
     const int q0 = threadIdx.x % S::G4;
@@ -432,7 +447,7 @@ mdct4_synthesis_fast(const float* __restrict__ spec, float* __restrict__ out, co
         phase[b] ^= 1;
         float* buf = buf0 + b * S::BUF;
         if (warp * C::G <= ns)       // frames fA .. fA+ns are needed (ns+1 rows)
-            synthesis_warp<C>(buf, exch + warp * C::G * C::XREG, pre, post, xtw, xr, h0 - 1, F, warp, lane);
+            synthesis_warp<C>(buf, exch + warp * C::G * C::XREG, pre_lane, post, roots, xr, h0 - 1, F, warp, ln);
         __syncthreads();
 
         float* orow = out + (long long)row * T_out;
@@ -443,13 +458,22 @@ mdct4_synthesis_fast(const float* __restrict__ spec, float* __restrict__ out, co
             for (int qi = 0; qi < S::NQ; ++qi) {
                 const int i = 4 * (q0 + kThreads * qi);
                 const bool lo = i < L;
-                const float4 A = *reinterpret_cast<const float4*>(th + (lo ? L + i : 3 * L - 4 - i));
-                const float4 Bv = *reinterpret_cast<const float4*>(tp + (lo ? L - 4 - i : i - L));
                 float4 o;
-                o.x = w1[qi][0] * (lo ? A.x : A.w) + w2[qi][0] * (lo ? Bv.w : Bv.x);
-                o.y = w1[qi][1] * (lo ? A.y : A.z) + w2[qi][1] * (lo ? Bv.z : Bv.y);
-                o.z = w1[qi][2] * (lo ? A.z : A.y) + w2[qi][2] * (lo ? Bv.y : Bv.z);
-                o.w = w1[qi][3] * (lo ? A.w : A.x) + w2[qi][3] * (lo ? Bv.x : Bv.w);
+                if (lo) {
+                    const float4 A = *reinterpret_cast<const float4*>(th + L + i);
+                    const float4 Bv = *reinterpret_cast<const float4*>(tp + L - 4 - i);
+                    o.x = w1[qi][0] * A.x + w2[qi][0] * Bv.w;
+                    o.y = w1[qi][1] * A.y + w2[qi][1] * Bv.z;
+                    o.z = w1[qi][2] * A.z + w2[qi][2] * Bv.y;
+                    o.w = w1[qi][3] * A.w + w2[qi][3] * Bv.x;
+                } else {
+                    const float4 A = *reinterpret_cast<const float4*>(th + 3 * L - 4 - i);
+                    const float4 Bv = *reinterpret_cast<const float4*>(tp + i - L);
+                    o.x = w1[qi][0] * A.w + w2[qi][0] * Bv.x;
+                    o.y = w1[qi][1] * A.z + w2[qi][1] * Bv.y;
+                    o.z = w1[qi][2] * A.y + w2[qi][2] * Bv.z;
+                    o.w = w1[qi][3] * A.x + w2[qi][3] * Bv.w;
+                }
                 const long long s = (long long)(h0 + sl) * M + i - crop_left;
                 if (vec_out && s >= 0 && s + 3 < T_out) {
                     *reinterpret_cast<float4*>(orow + s) = o;
