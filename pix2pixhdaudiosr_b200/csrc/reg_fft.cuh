@@ -34,11 +34,50 @@ __host__ __device__ constexpr float cos32(int i) {
 }
 __host__ __device__ constexpr float sin32(int i) { return cos32(i - 8); }
 
+// Packed fp32x2 arithmetic (Blackwell FADD2 / FMUL2 / FFMA2): one issue slot per complex add, two per
+// complex multiply.  ptxas folds negation / broadcast / half-swap into operand modifiers.
+#ifdef P2P_USE_F32X2   // measured on B200: no gain here (FADD2 is half rate, extra MOVs) -- kept as an option
+__device__ __forceinline__ unsigned long long pk2(float lo, float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ float2 upk2(unsigned long long r) {
+    float2 c;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(c.x), "=f"(c.y) : "l"(r));
+    return c;
+}
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) {
+    unsigned long long r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk2(a.x, a.y)), "l"(pk2(b.x, b.y)));
+    return upk2(r);
+}
+__device__ __forceinline__ float2 csub(float2 a, float2 b) {
+    unsigned long long r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk2(a.x, a.y)), "l"(pk2(b.x, b.y)));
+    return upk2(r);
+}
+// (a.x + j a.y)(b.x + j b.y) = a.x*(b.x, b.y) + a.y*(-b.y, b.x)
+__device__ __forceinline__ float2 cmulf(float2 a, float2 b) {
+    unsigned long long t, r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(t) : "l"(pk2(a.y, a.y)), "l"(pk2(-b.y, b.x)));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pk2(a.x, a.x)), "l"(pk2(b.x, b.y)), "l"(t));
+    return upk2(r);
+}
+// s * (a.x, a.y) for a real scalar pair (sx, sy)
+__device__ __forceinline__ float2 cscale2(float2 a, float sx, float sy) {
+    unsigned long long r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk2(a.x, a.y)), "l"(pk2(sx, sy)));
+    return upk2(r);
+}
+#else
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
 __device__ __forceinline__ float2 cmulf(float2 a, float2 b) {
     return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
 }
+__device__ __forceinline__ float2 cscale2(float2 a, float sx, float sy) { return make_float2(a.x * sx, a.y * sy); }
+#endif
 
 // d * e^{-2 pi j IDX/32}, IDX in [0,16), trivial factors special-cased
 template <int IDX>
@@ -48,14 +87,14 @@ __device__ __forceinline__ float2 twmul32(float2 d) {
     } else if constexpr (IDX == 8) {
         return make_float2(d.y, -d.x);
     } else if constexpr (IDX == 4) {
-        constexpr float c = 0.70710678118654752f;
-        return make_float2((d.x + d.y) * c, (d.y - d.x) * c);
+        constexpr float c = 0.70710678118654752f;          // (1 - j)/sqrt2
+        return cscale2(cadd(d, make_float2(d.y, -d.x)), c, c);
     } else if constexpr (IDX == 12) {
-        constexpr float c = 0.70710678118654752f;
-        return make_float2((d.y - d.x) * c, -(d.x + d.y) * c);
+        constexpr float c = 0.70710678118654752f;          // (-1 - j)/sqrt2
+        return cscale2(cadd(make_float2(d.y, -d.x), make_float2(-d.x, -d.y)), c, c);
     } else {
         constexpr float wr = cos32(IDX), wi = -sin32(IDX);
-        return make_float2(d.x * wr - d.y * wi, d.x * wi + d.y * wr);
+        return cmulf(d, make_float2(wr, wi));
     }
 }
 
