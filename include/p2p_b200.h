@@ -60,6 +60,88 @@ int p2p_mdct4_synthesis(const float* spec, float* out, const float* window, cons
                         int B, int F, int64_t T_out, int n_fft, int hop, int win, int64_t crop_left,
                         float scale, void* stream);
 
+
+/* ---- pix2pixHD conv GAN layers ---------------------------------------------------------------
+ * Replaces the torch.nn / cuDNN calls under models/networks.py:129-383 (GlobalGenerator, LocalEnhancer,
+ * ResnetBlock, NLayerDiscriminator, MultiscaleDiscriminator) and the loss / optimiser arithmetic of
+ * networks.py:68-110, pix2pixHD_model.py:390-398, train.py:155-184.
+ *
+ * Activations are NHWC ("channels last"), dtype P2P_F32 or P2P_BF16; statistics, losses, master weights,
+ * weight gradients and optimiser state are always fp32.  Weights are tap-major: W[tap][row][col] with
+ * tap = kh*KW + kw and (row, col) strides given per call, so Conv2d ([Cout,Cin,KH,KW] logical) and
+ * ConvTranspose2d ([Cin,Cout,KH,KW] logical) share one physical layout [KH][KW][Cout][Cin].
+ */
+#define P2P_F32 0
+#define P2P_BF16 1
+#define P2P_PAD_ZERO 0
+#define P2P_PAD_REFLECT 1
+#define P2P_MAX_TAPS 49
+
+/* One implicit-GEMM pass:  out[n, y*oys+oyo, x*oxs+oxo, j] (+)= bias[j] +
+ *     sum_{t<ntaps} sum_{k<K} in[n, pad(y*sy + dh[t]), pad(x*sx + dw[t]), k] * W[wtap[t]*w_tap + k*w_k + j*w_j]
+ * for n<N, y<gy, x<gx, j<J.  pad(): zero outside [0,H)x[0,W) or reflection (no edge repeat).
+ * A stride-1/2 convolution is one pass; a stride-2 transposed convolution (and the input gradient of a
+ * stride-2 convolution) is four passes, one per output parity, each with its own tap subset. */
+typedef struct {
+    int N, H, W, K;          /* gathered tensor: NHWC with K channels */
+    int OH, OW, J;           /* full extent of the written tensor: NHWC with J channels */
+    int gy, gx;              /* GEMM rows per image */
+    int sy, sx;              /* gather stride */
+    int oys, oyo, oxs, oxo;  /* scatter stride / offset of the written position */
+    int ntaps;
+    int pad_mode;
+    long long w_tap, w_k, w_j;   /* weight strides in elements */
+    signed char dh[P2P_MAX_TAPS], dw[P2P_MAX_TAPS];
+    unsigned char wtap[P2P_MAX_TAPS];
+} p2p_conv_pass;
+
+/* out = pass(in, W) (+ bias).  in and W have dtype `dtype`, out has `out_dtype` (a bf16 layer that feeds an
+ * InstanceNorm keeps its pre-normalisation output in fp32: rounding y to bf16 before subtracting the
+ * per-plane mean would cost |mean|/std times the bf16 epsilon); bias fp32 or NULL. */
+int p2p_conv_forward(const p2p_conv_pass* pass, const void* in, const void* weight, const float* bias,
+                     void* out, int dtype, int out_dtype, void* stream);
+/* dW[wtap[t]*w_tap + k*w_k + j*w_j] += sum_{n,y,x} in[n, pad(..t..), k] * dout[n, y*oys+oyo, x*oxs+oxo, j]
+ * (fp32 accumulate into a caller-zeroed fp32 buffer; safe to call once per pass of a layer). */
+int p2p_conv_wgrad(const p2p_conv_pass* pass, const void* in, const void* dout, float* dweight, int dtype,
+                   void* stream);
+/* dbias[j] = sum over rows of dout [rows, J] (overwrites). */
+int p2p_bias_grad(const void* dout, float* dbias, long long rows, int J, int dtype, void* stream);
+/* Adjoint of reflection padding: dx[n,h,w,c] = sum of dxp over the padded positions that mirror onto (h,w).
+ * dxp is [N, H+2p, W+2p, C], dx is [N,H,W,C]. */
+int p2p_reflect_pad_fold(const void* dxp, void* dx, int N, int H, int W, int C, int p, int dtype, void* stream);
+
+/* InstanceNorm2d(affine=False, eps) [+ activation] [+ residual]:  z = act((y-mean)/sqrt(var+eps)) + res.
+ * act: 0 none, 1 ReLU, 2 LeakyReLU(slope).  norm=0 skips the normalisation (plain activation).
+ * y: [N,HW,C] `y_dtype`; res,z: `dtype`; stats: fp32 [N,C,2] = (mean, rstd), written by fwd, read by bwd. */
+int p2p_instnorm_act_fwd(const void* y, const void* res, void* z, float* stats, int N, long long HW, int C,
+                         int norm, int act, float slope, float eps, int y_dtype, int dtype, void* stream);
+/* dy from dz (and dres = dz is the caller's business): needs y and stats of the forward.
+ * work: fp32 scratch [N,C,2] (ignored when norm == 0). */
+int p2p_instnorm_act_bwd(const void* y, const float* stats, const void* dz, void* dy, float* work, int N,
+                         long long HW, int C, int norm, int act, float slope, int y_dtype, int dtype, void* stream);
+
+/* AvgPool2d(3, stride 2, padding 1, count_include_pad=False), NHWC. OH=(H-1)/2+1, OW=(W-1)/2+1. */
+int p2p_avgpool3s2_fwd(const void* x, void* y, int N, int H, int W, int C, int dtype, void* stream);
+int p2p_avgpool3s2_bwd(const void* dy, void* dx, int N, int H, int W, int C, int dtype, void* stream);
+
+/* elementwise: y = tanh(x); dx = dy * (1 - y^2) */
+int p2p_tanh_fwd(const void* x, void* y, long long n, int dtype, void* stream);
+int p2p_tanh_bwd(const void* y, const void* dy, void* dx, long long n, int dtype, void* stream);
+
+/* if loss: loss[0] += weight * mean((x - target)^2); if dx: dx = gscale * weight * 2 (x - target) / n
+ * (LSGAN, networks.py:100-110).  gscale_dev (device fp32 scalar, may be NULL) multiplies gscale: the upstream
+ * gradient never has to visit the host. */
+int p2p_loss_mse_const(const void* x, float target, float weight, float* loss, void* dx, float gscale,
+                       const float* gscale_dev, long long n, int dtype, void* stream);
+/* if loss: loss[0] += weight * mean(|a - b|); if da: da = gscale * weight * sign(a - b) / n  (feature matching) */
+int p2p_loss_l1(const void* a, const void* b, float weight, float* loss, void* da, float gscale,
+                const float* gscale_dev, long long n, int dtype, void* stream);
+
+/* torch.optim.Adam step (no weight decay, no amsgrad) over a flat fp32 buffer; also refreshes the bf16 copy
+ * used by the tensor-core kernels when w_bf16 != NULL.  step is the 1-based step count. */
+int p2p_adam_step(float* w, const float* g, float* m, float* v, void* w_bf16, long long n, float lr, float beta1,
+                  float beta2, float eps, int step, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -18,6 +18,35 @@ _SIGS = {
     "p2p_mdct4_synthesis": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int,
                                        _c.c_int64, _c.c_int, _c.c_int, _c.c_int, _c.c_int64, _c.c_float, _c.c_void_p]),
 }
+_vp, _i, _f, _ll = _c.c_void_p, _c.c_int, _c.c_float, _c.c_longlong
+MAX_TAPS = 49
+
+
+class ConvPass(ctypes.Structure):
+    """p2p_conv_pass of include/p2p_b200.h."""
+    _fields_ = [("N", _i), ("H", _i), ("W", _i), ("K", _i), ("OH", _i), ("OW", _i), ("J", _i),
+                ("gy", _i), ("gx", _i), ("sy", _i), ("sx", _i),
+                ("oys", _i), ("oyo", _i), ("oxs", _i), ("oxo", _i),
+                ("ntaps", _i), ("pad_mode", _i),
+                ("w_tap", _ll), ("w_k", _ll), ("w_j", _ll),
+                ("dh", _c.c_byte * MAX_TAPS), ("dw", _c.c_byte * MAX_TAPS), ("wtap", _c.c_ubyte * MAX_TAPS)]
+
+
+_SIGS.update({
+    "p2p_conv_forward": (_i, [_c.POINTER(ConvPass), _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "p2p_conv_wgrad": (_i, [_c.POINTER(ConvPass), _vp, _vp, _vp, _i, _vp]),
+    "p2p_bias_grad": (_i, [_vp, _vp, _ll, _i, _i, _vp]),
+    "p2p_reflect_pad_fold": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "p2p_instnorm_act_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _f, _f, _i, _i, _vp]),
+    "p2p_instnorm_act_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _f, _i, _i, _vp]),
+    "p2p_avgpool3s2_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "p2p_avgpool3s2_bwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "p2p_tanh_fwd": (_i, [_vp, _vp, _ll, _i, _vp]),
+    "p2p_tanh_bwd": (_i, [_vp, _vp, _vp, _ll, _i, _vp]),
+    "p2p_loss_mse_const": (_i, [_vp, _f, _f, _vp, _vp, _f, _vp, _ll, _i, _vp]),
+    "p2p_loss_l1": (_i, [_vp, _vp, _f, _vp, _vp, _f, _vp, _ll, _i, _vp]),
+    "p2p_adam_step": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _f, _f, _f, _f, _i, _vp]),
+})
 _lib = None
 
 

@@ -1,0 +1,401 @@
+// Bandwidth-bound layer kernels of the pix2pixHD path (NHWC): InstanceNorm(+activation, +residual),
+// AvgPool 3x3/s2, tanh, reflection-pad adjoint, bias gradient, LSGAN / L1 loss reductions, fused Adam.
+// Reference call sites: models/networks.py:18-25 (InstanceNorm2d affine=False), :166,309 (AvgPool2d
+// count_include_pad=False), :68-110 (GANLoss), pix2pixHD_model.py:390-398 (feature matching), train.py:164-184.
+#include "dtype.cuh"
+
+namespace p2p {
+namespace {
+
+constexpr int kEw = 256;   // threads of elementwise kernels
+
+__device__ __forceinline__ float act_fwd(float x, int act, float slope) {
+    if (act == 1) return x > 0.f ? x : 0.f;
+    if (act == 2) return x > 0.f ? x : slope * x;
+    return x;
+}
+__device__ __forceinline__ float act_grad(float x, int act, float slope) {
+    if (act == 1) return x > 0.f ? 1.f : 0.f;
+    if (act == 2) return x > 0.f ? 1.f : slope;
+    return 1.f;
+}
+
+// ---- InstanceNorm statistics: raw[n,c] = (sum(y - shift), sum((y - shift)^2)), shift = y[n,0,c] -------------
+// grid (ceil(C/32), N, S), block (32, 8): rows of the HW chunk are strided over threadIdx.y
+template <typename T>
+__global__ void in_stats_kernel(const T* __restrict__ y, float* __restrict__ raw, long long HW, int C, long long chunk) {
+    __shared__ float s1[8][33], s2[8][33];
+    const int c = blockIdx.x * 32 + threadIdx.x, n = blockIdx.y;
+    const long long r0 = (long long)blockIdx.z * chunk, r1 = min(HW, r0 + chunk);
+    float a = 0.f, b = 0.f;
+    if (c < C) {
+        const T* base = y + (long long)n * HW * C + c;
+        const float shift = ldf(base);
+        for (long long r = r0 + threadIdx.y; r < r1; r += 8) {
+            const float v = ldf(base + r * C) - shift;
+            a += v; b += v * v;
+        }
+    }
+    s1[threadIdx.y][threadIdx.x] = a; s2[threadIdx.y][threadIdx.x] = b;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < C) {
+#pragma unroll
+        for (int i = 1; i < 8; ++i) { a += s1[i][threadIdx.x]; b += s2[i][threadIdx.x]; }
+        atomicAdd(raw + ((long long)n * C + c) * 2, a);
+        atomicAdd(raw + ((long long)n * C + c) * 2 + 1, b);
+    }
+}
+
+template <typename T>
+__global__ void in_finalize_kernel(const T* __restrict__ y, float* __restrict__ stats, long long HW, int C, int NC, float eps) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= NC) return;
+    const int n = i / C, c = i % C;
+    const float shift = ldf(y + (long long)n * HW * C + c);
+    const float m = stats[2 * i] / (float)HW;
+    const float var = fmaxf(stats[2 * i + 1] / (float)HW - m * m, 0.f);   // biased variance (PyTorch instance_norm)
+    stats[2 * i] = m + shift;
+    stats[2 * i + 1] = rsqrtf(var + eps);
+}
+
+template <typename TY, typename T>
+__global__ void in_apply_kernel(const TY* __restrict__ y, const T* __restrict__ res, T* __restrict__ z,
+                                const float* __restrict__ stats, long long HW, int C, long long total, int norm,
+                                int act, float slope) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        float v = ldf(y + i);
+        if (norm) {
+            const long long n = i / (HW * C);
+            const float2 st = *reinterpret_cast<const float2*>(stats + (n * C + c) * 2);
+            v = (v - st.x) * st.y;
+        }
+        v = act_fwd(v, act, slope);
+        if (res) v += ldf(res + i);
+        stf(z + i, v);
+    }
+}
+
+// backward reductions: work[n,c] = (sum g, sum g*xhat), g = dz * act'(xhat)
+template <typename TY, typename T>
+__global__ void in_bwd_stats_kernel(const TY* __restrict__ y, const float* __restrict__ stats, const T* __restrict__ dz,
+                                    float* __restrict__ work, long long HW, int C, long long chunk, int act, float slope) {
+    __shared__ float s1[8][33], s2[8][33];
+    const int c = blockIdx.x * 32 + threadIdx.x, n = blockIdx.y;
+    const long long r0 = (long long)blockIdx.z * chunk, r1 = min(HW, r0 + chunk);
+    float a = 0.f, b = 0.f;
+    if (c < C) {
+        const long long off = (long long)n * HW * C + c;
+        const float mean = stats[((long long)n * C + c) * 2], rstd = stats[((long long)n * C + c) * 2 + 1];
+        for (long long r = r0 + threadIdx.y; r < r1; r += 8) {
+            const float xh = (ldf(y + off + r * C) - mean) * rstd;
+            const float g = ldf(dz + off + r * C) * act_grad(xh, act, slope);
+            a += g; b += g * xh;
+        }
+    }
+    s1[threadIdx.y][threadIdx.x] = a; s2[threadIdx.y][threadIdx.x] = b;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < C) {
+#pragma unroll
+        for (int i = 1; i < 8; ++i) { a += s1[i][threadIdx.x]; b += s2[i][threadIdx.x]; }
+        atomicAdd(work + ((long long)n * C + c) * 2, a);
+        atomicAdd(work + ((long long)n * C + c) * 2 + 1, b);
+    }
+}
+
+template <typename TY, typename T>
+__global__ void in_bwd_apply_kernel(const TY* __restrict__ y, const float* __restrict__ stats, const T* __restrict__ dz,
+                                    const float* __restrict__ work, T* __restrict__ dy, long long HW, int C,
+                                    long long total, int norm, int act, float slope) {
+    const float inv = 1.f / (float)HW;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const float v = ldf(y + i), g0 = ldf(dz + i);
+        if (!norm) { stf(dy + i, g0 * act_grad(v, act, slope)); continue; }
+        const int c = (int)(i % C);
+        const long long nc = (i / (HW * C)) * C + c;
+        const float2 st = *reinterpret_cast<const float2*>(stats + nc * 2);
+        const float2 wk = *reinterpret_cast<const float2*>(work + nc * 2);
+        const float xh = (v - st.x) * st.y;
+        const float g = g0 * act_grad(xh, act, slope);
+        stf(dy + i, st.y * (g - wk.x * inv - xh * wk.y * inv));
+    }
+}
+
+// ---- AvgPool2d(3, stride 2, pad 1, count_include_pad=False) -------------------------------------------
+template <typename T>
+__global__ void avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int H, int W, int C, int OH, int OW,
+                                   long long total) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        long long r = i / C;
+        const int ow = (int)(r % OW); r /= OW;
+        const int oh = (int)(r % OH);
+        const long long n = r / OH;
+        const int h0 = max(2 * oh - 1, 0), h1 = min(2 * oh + 1, H - 1), w0 = max(2 * ow - 1, 0), w1 = min(2 * ow + 1, W - 1);
+        float s = 0.f;
+        for (int h = h0; h <= h1; ++h)
+            for (int w = w0; w <= w1; ++w) s += ldf(x + ((n * H + h) * W + w) * C + c);
+        stf(y + i, s / (float)((h1 - h0 + 1) * (w1 - w0 + 1)));
+    }
+}
+
+template <typename T>
+__global__ void avgpool_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int H, int W, int C, int OH, int OW,
+                                   long long total) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        long long r = i / C;
+        const int w = (int)(r % W); r /= W;
+        const int h = (int)(r % H);
+        const long long n = r / H;
+        // outputs whose window [2o-1, 2o+1] contains h: o in [ceil((h-1)/2), floor((h+1)/2)]
+        float s = 0.f;
+        for (int oh = h / 2; oh <= min((h + 1) / 2, OH - 1); ++oh) {
+            const int ch = min(2 * oh + 1, H - 1) - max(2 * oh - 1, 0) + 1;
+            for (int ow = w / 2; ow <= min((w + 1) / 2, OW - 1); ++ow) {
+                const int cw = min(2 * ow + 1, W - 1) - max(2 * ow - 1, 0) + 1;
+                s += ldf(dy + ((n * OH + oh) * OW + ow) * C + c) / (float)(ch * cw);
+            }
+        }
+        stf(dx + i, s);
+    }
+}
+
+// ---- elementwise ------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void tanh_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        stf(y + i, tanhf(ldf(x + i)));
+}
+template <typename T>
+__global__ void tanh_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float t = ldf(y + i);
+        stf(dx + i, ldf(dy + i) * (1.f - t * t));
+    }
+}
+
+template <typename T>
+__global__ void reflect_fold_kernel(const T* __restrict__ dxp, T* __restrict__ dx, int H, int W, int C, int p,
+                                    long long total) {
+    const int HP = H + 2 * p, WP = W + 2 * p;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        long long r = i / C;
+        const int w = (int)(r % W); r /= W;
+        const int h = (int)(r % H);
+        const long long n = r / H;
+        int hs[3], ws[3], nh = 0, nw = 0;
+        hs[nh++] = h + p;
+        if (h >= 1 && h <= p) hs[nh++] = p - h;
+        if (h >= H - 1 - p && h <= H - 2) hs[nh++] = 2 * (H - 1) + p - h;
+        ws[nw++] = w + p;
+        if (w >= 1 && w <= p) ws[nw++] = p - w;
+        if (w >= W - 1 - p && w <= W - 2) ws[nw++] = 2 * (W - 1) + p - w;
+        float s = 0.f;
+        for (int a = 0; a < nh; ++a)
+            for (int b = 0; b < nw; ++b) s += ldf(dxp + ((n * HP + hs[a]) * WP + ws[b]) * C + c);
+        stf(dx + i, s);
+    }
+}
+
+// dbias[j] += column sums; grid (ceil(J/32), S), block (32, 8)
+template <typename T>
+__global__ void bias_grad_kernel(const T* __restrict__ dout, float* __restrict__ dbias, long long rows, int J, long long chunk) {
+    __shared__ float s1[8][33];
+    const int j = blockIdx.x * 32 + threadIdx.x;
+    const long long r0 = (long long)blockIdx.y * chunk, r1 = min(rows, r0 + chunk);
+    float a = 0.f;
+    if (j < J)
+        for (long long r = r0 + threadIdx.y; r < r1; r += 8) a += ldf(dout + r * J + j);
+    s1[threadIdx.y][threadIdx.x] = a;
+    __syncthreads();
+    if (threadIdx.y == 0 && j < J) {
+#pragma unroll
+        for (int i = 1; i < 8; ++i) a += s1[i][threadIdx.x];
+        atomicAdd(dbias + j, a);
+    }
+}
+
+// ---- losses ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void mse_const_kernel(const T* __restrict__ x, float target, float wgt, float* __restrict__ loss,
+                                 T* __restrict__ dx, float gcoef, const float* __restrict__ gdev, long long n) {
+    __shared__ float scratch[33];
+    float acc = 0.f;
+    if (gdev) gcoef *= __ldg(gdev);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float d = ldf(x + i) - target;
+        acc += d * d;
+        if (dx) stf(dx + i, gcoef * d);
+    }
+    if (loss) { acc = block_sum(acc, scratch); if (threadIdx.x == 0) atomicAdd(loss, acc * wgt / (float)n); }
+}
+
+template <typename T>
+__global__ void l1_kernel(const T* __restrict__ a, const T* __restrict__ b, float wgt, float* __restrict__ loss,
+                          T* __restrict__ da, float gcoef, const float* __restrict__ gdev, long long n) {
+    __shared__ float scratch[33];
+    float acc = 0.f;
+    if (gdev) gcoef *= __ldg(gdev);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float d = ldf(a + i) - ldf(b + i);
+        acc += fabsf(d);
+        if (da) stf(da + i, d > 0.f ? gcoef : (d < 0.f ? -gcoef : 0.f));
+    }
+    if (loss) { acc = block_sum(acc, scratch); if (threadIdx.x == 0) atomicAdd(loss, acc * wgt / (float)n); }
+}
+
+__global__ void adam_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                            __nv_bfloat16* __restrict__ wb, long long n, float step_size, float beta1, float beta2,
+                            float inv_bc2_sqrt, float eps) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float gi = g[i];
+        const float mi = beta1 * m[i] + (1.f - beta1) * gi;
+        const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+        m[i] = mi; v[i] = vi;
+        const float wi = w[i] - step_size * mi / (sqrtf(vi) * inv_bc2_sqrt + eps);
+        w[i] = wi;
+        if (wb) wb[i] = __float2bfloat16_rn(wi);
+    }
+}
+
+inline int ew_grid(long long n) {
+    long long b = (n + kEw - 1) / kEw;
+    const long long cap = 148LL * 16;
+    return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+inline int split_for(long long rows, int base_ctas) {      // chunks of the row dimension so that ~4 CTAs/SM exist
+    long long s = (148LL * 4 + base_ctas - 1) / base_ctas;
+    const long long maxs = (rows + 63) / 64;
+    if (s > maxs) s = maxs;
+    if (s < 1) s = 1;
+    if (s > 65535) s = 65535;
+    return (int)s;
+}
+
+}  // namespace
+}  // namespace p2p
+
+using namespace p2p;
+
+extern "C" int p2p_instnorm_act_fwd(const void* y, const void* res, void* z, float* stats, int N, long long HW, int C,
+                                    int norm, int act, float slope, float eps, int y_dtype, int dtype, void* stream) {
+    if (N < 0 || HW < 0 || C < 0) return fail(P2P_EINVAL, "negative size");
+    const long long total = (long long)N * HW * C;
+    if (total == 0) return P2P_OK;
+    if (!y || !z || (norm && !stats)) return fail(P2P_EINVAL, "null pointer argument");
+    if (N > 65535) return fail(P2P_ENOTSUP, "N=%d too large", N);
+    cudaStream_t st = (cudaStream_t)stream;
+    P2P_DISPATCH_DTYPE2(y_dtype, TY, dtype, T, {
+        if (norm) {
+            if (cudaMemsetAsync(stats, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
+            const int cb = (C + 31) / 32, S = split_for(HW, cb * N);
+            const long long chunk = (HW + S - 1) / S;
+            in_stats_kernel<TY><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, HW, C, chunk);
+            in_finalize_kernel<TY><<<(N * C + 255) / 256, 256, 0, st>>>((const TY*)y, stats, HW, C, N * C, eps);
+        }
+        in_apply_kernel<TY, T><<<ew_grid(total), kEw, 0, st>>>((const TY*)y, (const T*)res, (T*)z, stats, HW, C, total, norm, act, slope);
+    });
+    return check_launch("instnorm_act_fwd");
+}
+
+extern "C" int p2p_instnorm_act_bwd(const void* y, const float* stats, const void* dz, void* dy, float* work, int N,
+                                    long long HW, int C, int norm, int act, float slope, int y_dtype, int dtype, void* stream) {
+    if (N < 0 || HW < 0 || C < 0) return fail(P2P_EINVAL, "negative size");
+    const long long total = (long long)N * HW * C;
+    if (total == 0) return P2P_OK;
+    if (!y || !dz || !dy || (norm && (!stats || !work))) return fail(P2P_EINVAL, "null pointer argument");
+    if (N > 65535) return fail(P2P_ENOTSUP, "N=%d too large", N);
+    cudaStream_t st = (cudaStream_t)stream;
+    P2P_DISPATCH_DTYPE2(y_dtype, TY, dtype, T, {
+        if (norm) {
+            if (cudaMemsetAsync(work, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
+            const int cb = (C + 31) / 32, S = split_for(HW, cb * N);
+            const long long chunk = (HW + S - 1) / S;
+            in_bwd_stats_kernel<TY, T><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, (const T*)dz, work, HW, C, chunk, act, slope);
+        }
+        in_bwd_apply_kernel<TY, T><<<ew_grid(total), kEw, 0, st>>>((const TY*)y, stats, (const T*)dz, work, (T*)dy, HW, C, total, norm, act, slope);
+    });
+    return check_launch("instnorm_act_bwd");
+}
+
+extern "C" int p2p_avgpool3s2_fwd(const void* x, void* y, int N, int H, int W, int C, int dtype, void* stream) {
+    if (N < 0 || H < 1 || W < 1 || C < 0) return fail(P2P_EINVAL, "bad size");
+    const int OH = (H - 1) / 2 + 1, OW = (W - 1) / 2 + 1;
+    const long long total = (long long)N * OH * OW * C;
+    if (total == 0) return P2P_OK;
+    if (!x || !y) return fail(P2P_EINVAL, "null pointer argument");
+    P2P_DISPATCH_DTYPE(dtype, T, avgpool_fwd_kernel<T><<<ew_grid(total), kEw, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, H, W, C, OH, OW, total));
+    return check_launch("avgpool3s2_fwd");
+}
+
+extern "C" int p2p_avgpool3s2_bwd(const void* dy, void* dx, int N, int H, int W, int C, int dtype, void* stream) {
+    if (N < 0 || H < 1 || W < 1 || C < 0) return fail(P2P_EINVAL, "bad size");
+    const int OH = (H - 1) / 2 + 1, OW = (W - 1) / 2 + 1;
+    const long long total = (long long)N * H * W * C;
+    if (total == 0) return P2P_OK;
+    if (!dx || !dy) return fail(P2P_EINVAL, "null pointer argument");
+    P2P_DISPATCH_DTYPE(dtype, T, avgpool_bwd_kernel<T><<<ew_grid(total), kEw, 0, (cudaStream_t)stream>>>((const T*)dy, (T*)dx, H, W, C, OH, OW, total));
+    return check_launch("avgpool3s2_bwd");
+}
+
+extern "C" int p2p_tanh_fwd(const void* x, void* y, long long n, int dtype, void* stream) {
+    if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
+    P2P_DISPATCH_DTYPE(dtype, T, tanh_fwd_kernel<T><<<ew_grid(n), kEw, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, n));
+    return check_launch("tanh_fwd");
+}
+extern "C" int p2p_tanh_bwd(const void* y, const void* dy, void* dx, long long n, int dtype, void* stream) {
+    if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
+    P2P_DISPATCH_DTYPE(dtype, T, tanh_bwd_kernel<T><<<ew_grid(n), kEw, 0, (cudaStream_t)stream>>>((const T*)y, (const T*)dy, (T*)dx, n));
+    return check_launch("tanh_bwd");
+}
+
+extern "C" int p2p_reflect_pad_fold(const void* dxp, void* dx, int N, int H, int W, int C, int p, int dtype, void* stream) {
+    if (N < 0 || H < 1 || W < 1 || C < 0 || p < 0) return fail(P2P_EINVAL, "bad size");
+    if (p >= H || p >= W) return fail(P2P_EINVAL, "reflection pad %d must be smaller than H=%d, W=%d", p, H, W);
+    const long long total = (long long)N * H * W * C;
+    if (total == 0) return P2P_OK;
+    P2P_DISPATCH_DTYPE(dtype, T, reflect_fold_kernel<T><<<ew_grid(total), kEw, 0, (cudaStream_t)stream>>>((const T*)dxp, (T*)dx, H, W, C, p, total));
+    return check_launch("reflect_pad_fold");
+}
+
+extern "C" int p2p_bias_grad(const void* dout, float* dbias, long long rows, int J, int dtype, void* stream) {
+    if (rows < 0 || J < 0) return fail(P2P_EINVAL, "negative size");
+    if (J == 0) return P2P_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(dbias, 0, sizeof(float) * J, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
+    if (rows == 0) return P2P_OK;
+    const int jb = (J + 31) / 32, S = split_for(rows, jb);
+    const long long chunk = (rows + S - 1) / S;
+    P2P_DISPATCH_DTYPE(dtype, T, bias_grad_kernel<T><<<dim3(jb, S), dim3(32, 8), 0, st>>>((const T*)dout, dbias, rows, J, chunk));
+    return check_launch("bias_grad");
+}
+
+extern "C" int p2p_loss_mse_const(const void* x, float target, float weight, float* loss, void* dx, float gscale,
+                                  const float* gscale_dev, long long n, int dtype, void* stream) {
+    if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
+    const float gcoef = gscale * weight * 2.f / (float)n;
+    const int grid = ew_grid(n) > 592 ? 592 : ew_grid(n);
+    P2P_DISPATCH_DTYPE(dtype, T, mse_const_kernel<T><<<grid, kEw, 0, (cudaStream_t)stream>>>((const T*)x, target, weight, loss, (T*)dx, gcoef, gscale_dev, n));
+    return check_launch("loss_mse_const");
+}
+
+extern "C" int p2p_loss_l1(const void* a, const void* b, float weight, float* loss, void* da, float gscale,
+                           const float* gscale_dev, long long n, int dtype, void* stream) {
+    if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
+    const float gcoef = gscale * weight / (float)n;
+    const int grid = ew_grid(n) > 592 ? 592 : ew_grid(n);
+    P2P_DISPATCH_DTYPE(dtype, T, l1_kernel<T><<<grid, kEw, 0, (cudaStream_t)stream>>>((const T*)a, (const T*)b, weight, loss, (T*)da, gcoef, gscale_dev, n));
+    return check_launch("loss_l1");
+}
+
+extern "C" int p2p_adam_step(float* w, const float* g, float* m, float* v, void* w_bf16, long long n, float lr,
+                             float beta1, float beta2, float eps, int step, void* stream) {
+    if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
+    if (step < 1) return fail(P2P_EINVAL, "step must be >= 1");
+    const double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
+    adam_kernel<<<ew_grid(n), kEw, 0, (cudaStream_t)stream>>>(w, g, m, v, (__nv_bfloat16*)w_bf16, n, (float)(lr / bc1),
+                                                               beta1, beta2, (float)(1.0 / sqrt(bc2)), eps);
+    return check_launch("adam_step");
+}

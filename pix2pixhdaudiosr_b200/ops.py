@@ -1,0 +1,393 @@
+"""Host side of the conv-GAN kernels: implicit-GEMM pass descriptors (pure host logic, unit-tested on CPU)
+and torch.autograd.Function wrappers that call the C ABI (include/p2p_b200.h).  Internal activation layout is
+NHWC ([N,H,W,C] contiguous); dtype float32 (exact path) or bfloat16 (tensor-core path)."""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import ConvPass
+
+PAD_ZERO, PAD_REFLECT = 0, 1
+_DT = {torch.float32: 0, torch.bfloat16: 1}
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError(f"the B200 path needs CUDA tensors, got {t.device} (no CPU fallback)")
+
+
+# ---------------------------------------------------------------------------------------------------
+# pass descriptors
+# ---------------------------------------------------------------------------------------------------
+def _make_pass(N, H, W, K, OH, OW, J, gy, gx, sy, sx, oys, oyo, oxs, oxo, taps, pad_mode, w_tap, w_k, w_j):
+    """taps: list of (dh, dw, wtap)."""
+    assert 1 <= len(taps) <= _lib.MAX_TAPS, len(taps)
+    P = ConvPass()
+    P.N, P.H, P.W, P.K, P.OH, P.OW, P.J = N, H, W, K, OH, OW, J
+    P.gy, P.gx, P.sy, P.sx = gy, gx, sy, sx
+    P.oys, P.oyo, P.oxs, P.oxo = oys, oyo, oxs, oxo
+    P.ntaps, P.pad_mode = len(taps), pad_mode
+    P.w_tap, P.w_k, P.w_j = w_tap, w_k, w_j
+    for i, (dh, dw, wt) in enumerate(taps):
+        assert -128 <= dh < 128 and -128 <= dw < 128
+        P.dh[i], P.dw[i], P.wtap[i] = dh, dw, wt
+    return P
+
+
+def conv_out_size(H, k, stride, pad):
+    return (H + 2 * pad - k) // stride + 1
+
+
+def conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, stride, pad, pad_mode):
+    """y[n,oh,ow,co] = sum x[n, oh*s - pad + kh, ow*s - pad + kw, ci] W[kh,kw,co,ci]   (weight [KH][KW][Cout][Cin])"""
+    OH, OW = conv_out_size(H, KH, stride, pad), conv_out_size(W, KW, stride, pad)
+    taps = [(kh - pad, kw - pad, kh * KW + kw) for kh in range(KH) for kw in range(KW)]
+    return [_make_pass(N, H, W, Cin, OH, OW, Cout, OH, OW, stride, stride, 1, 0, 1, 0, taps, pad_mode,
+                       Cout * Cin, 1, Cin)]
+
+
+def conv_dgrad_passes(N, H, W, Cin, Cout, KH, KW, stride, pad, pad_mode):
+    """dx from dy [N,OH,OW,Cout].  Zero padding: writes dx [N,H,W,Cin].  Reflect padding: writes the gradient
+    of the PADDED input [N,H+2p,W+2p,Cin]; the caller folds it (p2p_reflect_pad_fold).
+    Returns (passes, (DH, DW)) with (DH, DW) the spatial extent written."""
+    OH, OW = conv_out_size(H, KH, stride, pad), conv_out_size(W, KW, stride, pad)
+    if pad_mode == PAD_REFLECT:
+        DH, DW, p = H + 2 * pad, W + 2 * pad, 0         # coordinates of the padded input
+    else:
+        DH, DW, p = H, W, pad
+    passes = []
+    for ph in range(stride):
+        for pw in range(stride):
+            gy, gx = (DH - ph + stride - 1) // stride, (DW - pw + stride - 1) // stride
+            if gy <= 0 or gx <= 0:
+                continue
+            taps = [((ph + p - kh) // stride, (pw + p - kw) // stride, kh * KW + kw)
+                    for kh in range(KH) for kw in range(KW)
+                    if (ph + p - kh) % stride == 0 and (pw + p - kw) % stride == 0]
+            if not taps:
+                return None, (DH, DW)       # a parity class nothing maps to: caller uses the zero-fill route
+            passes.append(_make_pass(N, OH, OW, Cout, DH, DW, Cin, gy, gx, 1, 1, stride, ph, stride, pw, taps,
+                                     PAD_ZERO, Cout * Cin, Cin, 1))
+    return passes, (DH, DW)
+
+
+def convT_out_size(H, k, stride, pad, out_pad):
+    return (H - 1) * stride - 2 * pad + k + out_pad
+
+
+def convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, stride, pad, out_pad):
+    """y[n,oh,ow,co] = sum_{ih*s - pad + kh = oh} x[n,ih,iw,ci] Wt[kh,kw,co,ci]; one pass per output parity."""
+    OH, OW = convT_out_size(H, KH, stride, pad, out_pad), convT_out_size(W, KW, stride, pad, out_pad)
+    passes = []
+    for ph in range(stride):
+        for pw in range(stride):
+            gy, gx = (OH - ph + stride - 1) // stride, (OW - pw + stride - 1) // stride
+            taps = [((ph + pad - kh) // stride, (pw + pad - kw) // stride, kh * KW + kw)
+                    for kh in range(KH) for kw in range(KW)
+                    if (ph + pad - kh) % stride == 0 and (pw + pad - kw) % stride == 0]
+            if not taps:
+                return None, (OH, OW)
+            passes.append(_make_pass(N, H, W, Cin, OH, OW, Cout, gy, gx, 1, 1, stride, ph, stride, pw, taps,
+                                     PAD_ZERO, Cout * Cin, 1, Cin))
+    return passes, (OH, OW)
+
+
+def convT_dgrad_passes(N, H, W, Cin, Cout, KH, KW, stride, pad, out_pad):
+    """dx[n,ih,iw,ci] = sum dy[n, ih*s - pad + kh, ...] Wt[kh,kw,co,ci]: a strided gather over dy."""
+    OH, OW = convT_out_size(H, KH, stride, pad, out_pad), convT_out_size(W, KW, stride, pad, out_pad)
+    taps = [(kh - pad, kw - pad, kh * KW + kw) for kh in range(KH) for kw in range(KW)]
+    return [_make_pass(N, OH, OW, Cout, H, W, Cin, H, W, stride, stride, 1, 0, 1, 0, taps, PAD_ZERO,
+                       Cout * Cin, Cin, 1)]
+
+
+# ---------------------------------------------------------------------------------------------------
+# raw launches
+# ---------------------------------------------------------------------------------------------------
+def _run_wgrad(P, x, dout, dw):
+    _lib.check(_lib.lib().p2p_conv_wgrad(ctypes.byref(P), _p(x), _p(dout), _p(dw), _DT[x.dtype], _stream()))
+
+
+def _bias_grad(dout, J):
+    db = torch.empty(J, dtype=torch.float32, device=dout.device)
+    _lib.check(_lib.lib().p2p_bias_grad(_p(dout), _p(db), dout.numel() // J, J, _DT[dout.dtype], _stream()))
+    return db
+
+
+def _weight_for(x, w32, w16):
+    """physical [KH,KW,Cout,Cin] weight in the activation dtype"""
+    if x.dtype == torch.float32:
+        return w32
+    if w16 is None:
+        raise RuntimeError("bf16 activations need the bf16 weight shadow (call sync_shadows())")
+    return w16
+
+
+# ---------------------------------------------------------------------------------------------------
+# layer implementations (plain functions on NHWC tensors; the autograd Functions below compose them)
+# ---------------------------------------------------------------------------------------------------
+ACT_NONE, ACT_RELU, ACT_LRELU = 0, 1, 2
+
+
+def _run_pass(P, x, w, bias, out):
+    _lib.check(_lib.lib().p2p_conv_forward(ctypes.byref(P), _p(x), _p(w), _p(bias), _p(out), _DT[x.dtype],
+                                           _DT[out.dtype], _stream()))
+
+
+class ConvCfg:
+    """static description of one conv / transposed-conv layer call"""
+    __slots__ = ("transposed", "stride", "pad", "pad_mode", "out_pad")
+
+    def __init__(self, transposed=False, stride=1, pad=0, pad_mode=PAD_ZERO, out_pad=0):
+        self.transposed, self.stride, self.pad, self.pad_mode, self.out_pad = transposed, stride, pad, pad_mode, out_pad
+
+
+def _phys(weight, cfg):
+    """logical weight -> physical [KH][KW][Cout][Cin] view, (Cout, Cin, KH, KW)"""
+    if cfg.transposed:
+        Cin, Cout, KH, KW = weight.shape
+        w = weight.permute(2, 3, 1, 0)
+    else:
+        Cout, Cin, KH, KW = weight.shape
+        w = weight.permute(2, 3, 0, 1)
+    assert w.is_contiguous(), "conv weights must be stored [KH][KW][Cout][Cin]"
+    return w, Cout, Cin, KH, KW
+
+
+def conv_forward(x, weight, bias, w16, cfg, out_dtype):
+    """nn.Conv2d (+ nn.ReflectionPad2d) / nn.ConvTranspose2d forward, NHWC (networks.py:145-154, 190-207, 223-246, 340-361)"""
+    N, H, W, Cx = x.shape
+    wphys, Cout, Cin, KH, KW = _phys(weight, cfg)
+    assert Cx == Cin, (Cx, Cin)
+    wq = _weight_for(x, wphys, w16)
+    if cfg.transposed:
+        passes, (OH, OW) = convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)
+        if passes is None:
+            raise NotImplementedError("transposed convolution with empty output parity classes")
+    else:
+        if cfg.pad_mode == PAD_REFLECT and (cfg.pad >= H or cfg.pad >= W):
+            raise RuntimeError("reflection padding must be smaller than the input")   # what ReflectionPad2d raises
+        passes = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
+        OH, OW = passes[0].OH, passes[0].OW
+    y = torch.empty((N, OH, OW, Cout), dtype=out_dtype, device=x.device)
+    for P in passes:
+        _run_pass(P, x, wq, bias, y)
+    return y
+
+
+def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
+    """gradients of conv_forward; dy has x's dtype.  Returns (dx, dw_logical, db)."""
+    N, H, W, _ = x.shape
+    wphys, Cout, Cin, KH, KW = _phys(weight, cfg)
+    assert dy.dtype == x.dtype and dy.is_contiguous()
+    dx = dw = db = None
+    if need_dx:
+        wq = _weight_for(x, wphys, w16)
+        if cfg.transposed:
+            dx = torch.empty_like(x)
+            _run_pass(convT_dgrad_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0], dy, wq, None, dx)
+        else:
+            passes, (DH, DW) = conv_dgrad_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
+            if passes is None:
+                raise NotImplementedError("input gradient of a convolution whose stride skips whole parity classes")
+            buf = torch.empty((N, DH, DW, Cin), dtype=x.dtype, device=x.device)
+            for P in passes:
+                _run_pass(P, dy, wq, None, buf)
+            if cfg.pad_mode == PAD_REFLECT and cfg.pad > 0:
+                dx = torch.empty_like(x)
+                _lib.check(_lib.lib().p2p_reflect_pad_fold(_p(buf), _p(dx), N, H, W, Cin, cfg.pad, _DT[x.dtype], _stream()))
+            else:
+                dx = buf
+    if need_dw:
+        dwp = torch.zeros((KH, KW, Cout, Cin), dtype=torch.float32, device=x.device)
+        if cfg.transposed:
+            for P in convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0]:
+                _run_wgrad(P, x, dy, dwp)
+            dw = dwp.permute(3, 2, 0, 1)
+        else:
+            _run_wgrad(conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)[0], x, dy, dwp)
+            dw = dwp.permute(2, 3, 0, 1)
+    if need_db:
+        db = _bias_grad(dy, Cout)
+    return dx, dw, db
+
+
+def norm_act_forward(y, res, norm, act, slope, eps, out_dtype):
+    """z = act(InstanceNorm2d(affine=False)(y)) [+ res]; returns (z, stats)"""
+    N, H, W, C = y.shape
+    z = torch.empty(y.shape, dtype=out_dtype, device=y.device)
+    stats = torch.empty((N, C, 2), dtype=torch.float32, device=y.device) if norm else None
+    if res is not None:
+        assert res.shape == y.shape and res.dtype == out_dtype and res.is_contiguous()
+    _lib.check(_lib.lib().p2p_instnorm_act_fwd(_p(y), _p(res), _p(z), _p(stats), N, H * W, C, int(norm), act, slope, eps,
+                                               _DT[y.dtype], _DT[out_dtype], _stream()))
+    return z, stats
+
+
+def norm_act_backward(y, stats, dz, norm, act, slope):
+    N, H, W, C = y.shape
+    dy = torch.empty(y.shape, dtype=dz.dtype, device=y.device)
+    work = torch.empty((N, C, 2), dtype=torch.float32, device=y.device) if norm else None
+    _lib.check(_lib.lib().p2p_instnorm_act_bwd(_p(y), _p(stats), _p(dz), _p(dy), _p(work), N, H * W, C, int(norm), act,
+                                               slope, _DT[y.dtype], _DT[dz.dtype], _stream()))
+    return dy
+
+
+# ---------------------------------------------------------------------------------------------------
+# autograd Functions (x, outputs: NHWC)
+# ---------------------------------------------------------------------------------------------------
+class ConvBlockFn(torch.autograd.Function):
+    """[ReflectionPad2d] Conv2d | ConvTranspose2d  ->  [InstanceNorm2d]  ->  [ReLU | LeakyReLU]  [+ residual]
+    as ONE differentiable op.  In bf16 mode the pre-normalisation conv output stays fp32 inside the op (see
+    include/p2p_b200.h), so only O(1)-scaled tensors are ever rounded to bf16."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, w16, res, cfg, norm, act, slope, eps):
+        _need_cuda(x, weight)
+        x = x.contiguous()
+        plain = (not norm) and act == ACT_NONE and res is None
+        y = conv_forward(x, weight, bias, w16, cfg, torch.float32 if norm else x.dtype)
+        if plain:
+            z, stats, ysave = y, None, None
+        else:
+            if res is not None:
+                res = res.contiguous()
+            z, stats = norm_act_forward(y, res, norm, act, slope, eps, x.dtype)
+            ysave = y
+        ctx.save_for_backward(x, weight, w16, ysave, stats)
+        ctx.cfg = (cfg, norm, act, slope, bias is not None, res is not None, plain)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        x, weight, w16, y, stats = ctx.saved_tensors
+        cfg, norm, act, slope, has_bias, has_res, plain = ctx.cfg
+        dz = dz.contiguous()
+        dy = dz if plain else norm_act_backward(y, stats, dz, norm, act, slope)
+        dx, dw, db = conv_backward(x, weight, w16, dy, cfg, ctx.needs_input_grad[0], ctx.needs_input_grad[1],
+                                   has_bias and ctx.needs_input_grad[2])
+        return dx, dw, db, None, (dz if has_res else None), None, None, None, None, None
+
+
+class InstNormActFn(torch.autograd.Function):
+    """stand-alone z = act(InstanceNorm2d(y)) [+ res] (norm=False: bare activation); same dtype in and out"""
+
+    @staticmethod
+    def forward(ctx, y, res, norm, act, slope, eps):
+        _need_cuda(y)
+        y = y.contiguous()
+        if res is not None:
+            res = res.contiguous()
+        z, stats = norm_act_forward(y, res, norm, act, slope, eps, y.dtype)
+        ctx.save_for_backward(y, stats)
+        ctx.cfg = (bool(norm), act, slope, res is not None)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        y, stats = ctx.saved_tensors
+        norm, act, slope, has_res = ctx.cfg
+        dz = dz.contiguous()
+        return norm_act_backward(y, stats, dz, norm, act, slope), (dz if has_res else None), None, None, None, None
+
+
+class AvgPool3s2Fn(torch.autograd.Function):
+    """nn.AvgPool2d(3, stride=2, padding=[1,1], count_include_pad=False), networks.py:166, 309."""
+
+    @staticmethod
+    def forward(ctx, x):
+        _need_cuda(x)
+        x = x.contiguous()
+        N, H, W, C = x.shape
+        y = torch.empty((N, (H - 1) // 2 + 1, (W - 1) // 2 + 1, C), dtype=x.dtype, device=x.device)
+        _lib.check(_lib.lib().p2p_avgpool3s2_fwd(_p(x), _p(y), N, H, W, C, _DT[x.dtype], _stream()))
+        ctx.shape = (N, H, W, C)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        N, H, W, C = ctx.shape
+        dy = dy.contiguous()
+        dx = torch.empty((N, H, W, C), dtype=dy.dtype, device=dy.device)
+        _lib.check(_lib.lib().p2p_avgpool3s2_bwd(_p(dy), _p(dx), N, H, W, C, _DT[dy.dtype], _stream()))
+        return dx
+
+
+class TanhFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        _need_cuda(x)
+        x = x.contiguous()
+        y = torch.empty_like(x)
+        _lib.check(_lib.lib().p2p_tanh_fwd(_p(x), _p(y), x.numel(), _DT[x.dtype], _stream()))
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        dy = dy.contiguous()
+        dx = torch.empty_like(y)
+        _lib.check(_lib.lib().p2p_tanh_bwd(_p(y), _p(dy), _p(dx), y.numel(), _DT[y.dtype], _stream()))
+        return dx
+
+
+class MseConstFn(torch.autograd.Function):
+    """weight * mean((x - target)^2) as a 0-dim fp32 tensor (nn.MSELoss against a constant label map)."""
+
+    @staticmethod
+    def forward(ctx, x, target, weight):
+        _need_cuda(x)
+        x = x.contiguous()
+        loss = torch.zeros((), dtype=torch.float32, device=x.device)
+        _lib.check(_lib.lib().p2p_loss_mse_const(_p(x), target, weight, _p(loss), None, 0.0, None, x.numel(), _DT[x.dtype], _stream()))
+        ctx.save_for_backward(x)
+        ctx.cfg = (target, weight)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (x,) = ctx.saved_tensors
+        target, weight = ctx.cfg
+        dx = torch.empty_like(x)
+        g = g.to(torch.float32).contiguous()          # upstream scalar stays on the device
+        _lib.check(_lib.lib().p2p_loss_mse_const(_p(x), target, weight, None, _p(dx), 1.0, _p(g), x.numel(), _DT[x.dtype], _stream()))
+        return dx, None, None
+
+
+class L1Fn(torch.autograd.Function):
+    """weight * mean(|a - b|), gradient to `a` only (b is the detached real feature, pix2pixHD_model.py:396-398)."""
+
+    @staticmethod
+    def forward(ctx, a, b, weight):
+        _need_cuda(a, b)
+        a, b = a.contiguous(), b.contiguous()
+        assert a.shape == b.shape and a.dtype == b.dtype
+        loss = torch.zeros((), dtype=torch.float32, device=a.device)
+        _lib.check(_lib.lib().p2p_loss_l1(_p(a), _p(b), weight, _p(loss), None, 0.0, None, a.numel(), _DT[a.dtype], _stream()))
+        ctx.save_for_backward(a, b)
+        ctx.weight = weight
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        da = torch.empty_like(a)
+        g = g.to(torch.float32).contiguous()
+        _lib.check(_lib.lib().p2p_loss_l1(_p(a), _p(b), ctx.weight, None, _p(da), 1.0, _p(g), a.numel(), _DT[a.dtype], _stream()))
+        return da, None, None
+
+
+def adam_step(w, g, m, v, w16, lr, beta1, beta2, eps, step):
+    _need_cuda(w, g, m, v)
+    assert w.is_contiguous() and g.is_contiguous() and w.dtype == torch.float32 and g.dtype == torch.float32
+    _lib.check(_lib.lib().p2p_adam_step(_p(w), _p(g), _p(m), _p(v), _p(w16), w.numel(), lr, beta1, beta2, eps, step, _stream()))
