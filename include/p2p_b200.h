@@ -100,6 +100,11 @@ typedef struct {
  * per-plane mean would cost |mean|/std times the bf16 epsilon); bias fp32 or NULL. */
 int p2p_conv_forward(const p2p_conv_pass* pass, const void* in, const void* weight, const float* bias,
                      void* out, int dtype, int out_dtype, void* stream);
+/* Testing/benchmark knob: non-zero routes every convolution pass to the exact CUDA-core kernels even where the
+ * tcgen05 tensor-core kernels (bf16, gathered channels % 16 == 0) apply.  Returns the old value. */
+int p2p_conv_force_simple(int on);
+/* Number of tcgen05 convolution kernels launched by this process so far. */
+long long p2p_conv_umma_launches(void);
 /* dW[wtap[t]*w_tap + k*w_k + j*w_j] += sum_{n,y,x} in[n, pad(..t..), k] * dout[n, y*oys+oyo, x*oxs+oxo, j]
  * (fp32 accumulate into a caller-zeroed fp32 buffer; safe to call once per pass of a layer). */
 int p2p_conv_wgrad(const p2p_conv_pass* pass, const void* in, const void* dout, float* dweight, int dtype,

@@ -34,6 +34,8 @@ class ConvPass(ctypes.Structure):
 
 _SIGS.update({
     "p2p_conv_forward": (_i, [_c.POINTER(ConvPass), _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "p2p_conv_force_simple": (_i, [_i]),
+    "p2p_conv_umma_launches": (_ll, []),
     "p2p_conv_wgrad": (_i, [_c.POINTER(ConvPass), _vp, _vp, _vp, _i, _vp]),
     "p2p_bias_grad": (_i, [_vp, _vp, _ll, _i, _i, _vp]),
     "p2p_reflect_pad_fold": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),

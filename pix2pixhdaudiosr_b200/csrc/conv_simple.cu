@@ -152,6 +152,8 @@ conv_wgrad_simple(const __grid_constant__ p2p_conv_pass P, const T* __restrict__
     }
 }
 
+}  // namespace
+
 int check_pass(const p2p_conv_pass* P) {
     if (!P) return fail(P2P_EINVAL, "null pass descriptor");
     if (P->ntaps < 1 || P->ntaps > P2P_MAX_TAPS) return fail(P2P_EINVAL, "ntaps %d out of range", P->ntaps);
@@ -162,8 +164,6 @@ int check_pass(const p2p_conv_pass* P) {
     if (P->gx > 0 && ((P->gx - 1) * P->oxs + P->oxo >= P->OW || P->oxo < 0)) return fail(P2P_EINVAL, "output cols exceed OW");
     return P2P_OK;
 }
-
-}  // namespace
 
 // entry points of the CUDA-core path; conv_dispatch.cu routes to these or to the tcgen05 kernels
 int conv_forward_simple(const p2p_conv_pass* P, const void* in, const void* weight, const float* bias, void* out,
@@ -197,14 +197,26 @@ int conv_wgrad_simple_launch(const p2p_conv_pass* P, const void* in, const void*
     return check_launch("conv_wgrad_simple");
 }
 
+int conv_forward_umma(const p2p_conv_pass* P, const void* in, const void* weight, const float* bias, void* out, int dtype,
+                      int out_dtype, cudaStream_t st);
+int conv_wgrad_umma(const p2p_conv_pass* P, const void* in, const void* dout, float* dw, int dtype, cudaStream_t st);
+
 }  // namespace p2p
 
 extern "C" int p2p_conv_forward(const p2p_conv_pass* pass, const void* in, const void* weight, const float* bias,
                                 void* out, int dtype, int out_dtype, void* stream) {
+    if (int rc = p2p::check_pass(pass)) return rc;
+    if (!in || !weight || !out) return p2p::fail(P2P_EINVAL, "null pointer argument");
+    const int rc = p2p::conv_forward_umma(pass, in, weight, bias, out, dtype, out_dtype, (cudaStream_t)stream);
+    if (rc <= 0) return rc;       // handled by the tcgen05 kernels (or failed there)
     return p2p::conv_forward_simple(pass, in, weight, bias, out, dtype, out_dtype, (cudaStream_t)stream);
 }
 
 extern "C" int p2p_conv_wgrad(const p2p_conv_pass* pass, const void* in, const void* dout, float* dweight, int dtype,
                               void* stream) {
+    if (int rc = p2p::check_pass(pass)) return rc;
+    if (!in || !dout || !dweight) return p2p::fail(P2P_EINVAL, "null pointer argument");
+    const int rc = p2p::conv_wgrad_umma(pass, in, dout, dweight, dtype, (cudaStream_t)stream);
+    if (rc <= 0) return rc;
     return p2p::conv_wgrad_simple_launch(pass, in, dout, dweight, dtype, (cudaStream_t)stream);
 }

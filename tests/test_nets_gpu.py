@@ -245,3 +245,57 @@ def test_bf16_layers_within_tolerance(layer):
     for what, a, bb in zip(("out", "dx", "dw"), res[torch.float32], res[torch.bfloat16]):
         err = float((a - bb).norm() / a.norm())
         assert err < 2e-2, (name, what, err)
+
+
+UMMA_LAYERS = [  # (name, transposed, Cin, Cout, k, stride, pad, reflect, (N, H, W), expected tcgen05 launches fwd+bwd)
+    ("res96_fullres", False, 96, 96, 3, 1, 1, True, (2, 64, 48), 3),
+    ("bottleneck_1536", False, 1536, 1536, 3, 1, 1, True, (8, 16, 4), 3),
+    ("down_s2_odd", False, 48, 96, 3, 2, 1, False, (3, 37, 29), 6),        # dgrad of a stride-2 conv = 4 parity passes
+    ("convT_up", True, 192, 96, 3, 2, 1, False, (2, 16, 12), 9),           # 4 fwd passes + 1 dgrad + 4 wgrad
+    ("d_4x4s2_pad2", False, 64, 128, 4, 2, 2, False, (2, 65, 33), 6),
+    ("d_4x4s1_odd", False, 256, 512, 4, 1, 2, False, (2, 33, 9), 3),
+    ("first7x7_out48", False, 16, 48, 7, 1, 3, True, (1, 40, 24), 3),
+    ("wide_n_tiles", False, 32, 528, 3, 1, 1, False, (1, 20, 12), 3),      # 3 column tiles of 176, ragged rows
+]
+
+
+@pytest.mark.parametrize("layer", UMMA_LAYERS, ids=[l[0] for l in UMMA_LAYERS])
+def test_tcgen05_kernels_match_cuda_core_kernels(layer):
+    """the tcgen05/TMEM implicit-GEMM kernels (conv_umma.cu) against the exact CUDA-core kernels on the SAME bf16
+    operands: both accumulate in fp32, so output / dx / dW agree to accumulation-order noise (1e-3 of the norm;
+    bf16 output rounding included) -- and the tensor-core path must really have been the one that ran."""
+    from pix2pixhdaudiosr_b200 import _lib
+    name, transposed, Cin, Cout, k, stride, pad, reflect, (N_, H, W), nlaunch = layer
+    torch.manual_seed(len(name))
+    x = torch.randn(N_, H, W, Cin, device="cuda").bfloat16()
+    shape = (Cin, Cout, k, k) if transposed else (Cout, Cin, k, k)
+    perm = (2, 3, 1, 0) if transposed else (2, 3, 0, 1)
+    inv = [perm.index(i) for i in range(4)]
+    wl = torch.randn(shape, device="cuda") * 0.05
+    b = torch.randn(Cout, device="cuda") * 0.1
+    cfg = ops.ConvCfg(transposed, stride, pad, ops.PAD_REFLECT if reflect else ops.PAD_ZERO, 1 if transposed else 0)
+    res = {}
+    for simple in (1, 0):
+        old = _lib.lib().p2p_conv_force_simple(simple)
+        try:
+            for norm in (False, True):          # bf16 output (plain) and fp32 output (feeds InstanceNorm; split-K)
+                w = torch.nn.Parameter(wl.permute(*perm).contiguous().permute(*inv))
+                w16 = w.detach().permute(*perm).contiguous().bfloat16()
+                xi = x.clone().requires_grad_(True)
+                n0 = _lib.lib().p2p_conv_umma_launches()
+                y = ops.conv_forward(xi.detach(), w.detach(), b, w16, cfg, torch.float32 if norm else torch.bfloat16)
+                g = torch.randn(y.shape, device="cuda", generator=torch.Generator("cuda").manual_seed(3)).bfloat16()
+                dx, dw, db = ops.conv_backward(xi.detach(), w.detach(), w16, g, cfg, True, True, True)
+                torch.cuda.synchronize()
+                n1 = _lib.lib().p2p_conv_umma_launches()
+                if not simple:
+                    assert n1 - n0 == nlaunch, (name, n1 - n0)
+                res[(simple, norm)] = (y.float(), dx.float(), dw.float())
+        finally:
+            _lib.lib().p2p_conv_force_simple(old)
+    for norm in (False, True):
+        for what, a, bb in zip(("out", "dx", "dw"), res[(1, norm)], res[(0, norm)]):
+            assert torch.isfinite(bb).all(), (name, what)
+            err = float((a - bb).norm() / a.norm())
+            tol = 4e-3 if (what == "dx" or (what == "out" and not norm)) else 1e-4     # bf16-rounded results vs fp32 ones
+            assert err < tol, (name, norm, what, err)
