@@ -147,6 +147,25 @@ int p2p_loss_l1(const void* a, const void* b, float weight, float* loss, void* d
 int p2p_adam_step(float* w, const float* g, float* m, float* v, void* w_bf16, long long n, float lr, float beta1,
                   float beta2, float eps, int step, void* stream);
 
+/* ---- spectrogram encode / decode around the networks (models/pix2pixHD_model.py:142-249) -----------------
+ * The image the networks see is channels-last [B, M bins (H), F frames (W), C], C = 2 with explicit +/- encoding
+ * (to_spectro :149-158: dB of alpha*pos+(1-alpha)*neg and of (1-alpha)*pos+alpha*neg), C = 1 otherwise (:160-162);
+ * dB(x) = 20 log10(max(x, min_value)) - 20.
+ * p2p_spectro_encode: spec [B,F,M] (MDCT4 output) -> logs [B,M,F,C] un-normalised, pha [B,M,F] = sign(spec), and the
+ *   batch-global min / max / sum / sum of squares accumulated in stats_work (32 bytes of device scratch).
+ * p2p_spectro_normalize: logs = (logs - min) / (max - min) in place (:193); when use_mask, rows [M-mask_rows, M) are
+ *   replaced by noise [B,mask_rows,F,C] (or zeros when noise == NULL; :196-226); norm_out[4] = max, min, mean, std. */
+int p2p_spectro_encode(const float* spec, float* logs, float* pha, void* stats_work, int B, int F, int M, int channels,
+                       float alpha, float min_value, void* stream);
+int p2p_spectro_normalize(float* logs, const void* stats_work, float* norm_out, const float* noise, int B, int F, int M,
+                          int channels, int mask_rows, int use_mask, void* stream);
+/* denormalize + explicit decode + transpose (:229-249): x is a [B,C,M,F] image with element strides (sb,sc,sh,sw) and
+ * dtype `dtype`; coef[b,f,k] = gain * decode(x[b,:,k,f]); norm = {max, min} device scalars; pha [B,M,F] or NULL
+ * multiplies the magnitude when channels == 1. */
+int p2p_spectro_decode(const void* x, long long sb, long long sc, long long sh, long long sw, const float* norm,
+                       const float* pha, float* coef, int B, int channels, int F, int M, float alpha, float min_value,
+                       float gain, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -47,6 +47,9 @@ _SIGS.update({
     "p2p_tanh_bwd": (_i, [_vp, _vp, _vp, _ll, _i, _vp]),
     "p2p_loss_mse_const": (_i, [_vp, _f, _f, _vp, _vp, _f, _vp, _ll, _i, _vp]),
     "p2p_loss_l1": (_i, [_vp, _vp, _f, _vp, _vp, _f, _vp, _ll, _i, _vp]),
+    "p2p_spectro_encode": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _vp]),
+    "p2p_spectro_normalize": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "p2p_spectro_decode": (_i, [_vp, _ll, _ll, _ll, _ll, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _f, _i, _vp]),
     "p2p_adam_step": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _f, _f, _f, _f, _i, _vp]),
 })
 _lib = None

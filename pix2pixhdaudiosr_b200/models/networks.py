@@ -73,12 +73,17 @@ class _ConvBase(nn.Module):
         self.bias = nn.Parameter(b)
         self.w16 = None                                           # bf16 shadow of the physical buffer
         self._perm = perm
+        self.weight._p2p_conv = self                              # lets optim.FusedAdam find the physical layout
 
     def physical_weight(self):
         return self.weight.permute(*self._perm)
 
     def sync_shadow(self):
-        self.w16 = self.physical_weight().detach().to(torch.bfloat16).contiguous()
+        phys = self.physical_weight().detach()
+        if self.w16 is not None and self.w16.device == phys.device and self.w16.shape == phys.shape:
+            self.w16.copy_(phys)                                  # keeps a view into FusedAdam's flat bf16 buffer valid
+        else:
+            self.w16 = phys.to(torch.bfloat16).contiguous()
 
 
 class Conv2d(_ConvBase):

@@ -1,0 +1,77 @@
+"""Fused Adam over flat buffers (reference: torch.optim.Adam(params, lr=opt.lr, betas=(opt.beta1, 0.999)) at
+models/pix2pixHD_model.py:131, 140 and optimizer_X.zero_grad()/step() at train.py:164-184).
+
+All parameters handed to the optimiser are re-homed into ONE fp32 master buffer (conv weights in their physical
+tap-major layout), with matching flat gradient / moment buffers and a flat bf16 shadow that the tcgen05 kernels
+read.  `step()` is a single `p2p_adam_step` launch that also refreshes the bf16 shadow; `zero_grad()` is one
+memset; the data-parallel gradient exchange is one all-reduce of `flat_grad` (train.py of this package)."""
+import torch
+
+from . import ops
+
+_ALIGN = 8      # elements: keeps every bf16 slice 16-byte aligned for the vector / tensor-core loads
+
+
+class FusedAdam:
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+        params = [p for p in params]
+        if not params:
+            raise ValueError("optimizer got an empty parameter list")
+        dev = params[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("FusedAdam needs CUDA parameters (no CPU fallback): move the networks to the GPU first")
+        self.param_groups = [{"params": params, "lr": lr, "betas": tuple(betas), "eps": eps}]
+        sizes = [(p.numel() + _ALIGN - 1) // _ALIGN * _ALIGN for p in params]
+        total = sum(sizes)
+        self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_grad = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_bf16 = torch.zeros(total, dtype=torch.bfloat16, device=dev)
+        self.step_count = 0
+        self._views = []
+        o = 0
+        for p, sz in zip(params, sizes):
+            n = p.numel()
+            conv = getattr(p, "_p2p_conv", None)
+            if conv is not None:
+                perm = conv._perm
+                inv = [perm.index(i) for i in range(4)]
+                phys = p.data.permute(*perm)
+                assert phys.is_contiguous(), "conv weights must be stored tap-major"
+                self.flat[o:o + n].copy_(phys.reshape(-1))
+                p.data = self.flat[o:o + n].view(phys.shape).permute(*inv)
+                gview = self.flat_grad[o:o + n].view(phys.shape).permute(*inv)
+                conv.w16 = self.flat_bf16[o:o + n].view(phys.shape)
+                conv.gphys = self.flat_grad[o:o + n].view(phys.shape)       # wgrad kernels may accumulate here directly
+            else:
+                self.flat[o:o + n].copy_(p.data.reshape(-1))
+                p.data = self.flat[o:o + n].view(p.shape)
+                gview = self.flat_grad[o:o + n].view(p.shape)
+            p.grad = gview
+            self._views.append((p, gview))
+            o += sz
+        self.flat_bf16.copy_(self.flat)
+
+    def zero_grad(self, set_to_none=False):
+        self.flat_grad.zero_()
+        for p, g in self._views:
+            if p.grad is not g:
+                p.grad = g
+
+    @torch.no_grad()
+    def step(self):
+        self.step_count += 1
+        g = self.param_groups[0]
+        ops.adam_step(self.flat, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.flat_bf16, g["lr"], g["betas"][0],
+                      g["betas"][1], g["eps"], self.step_count)
+
+    def state_dict(self):
+        return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq,
+                "param_groups": [{k: v for k, v in self.param_groups[0].items() if k != "params"}]}
+
+    def load_state_dict(self, sd):
+        self.step_count = int(sd["step"])
+        self.exp_avg.copy_(sd["exp_avg"])
+        self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+        self.param_groups[0].update(sd["param_groups"][0])

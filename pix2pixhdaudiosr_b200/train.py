@@ -1,0 +1,72 @@
+"""One optimisation step of the reference's train.py:148-184, and its data-parallel form.
+
+Reference order:  losses = model(lr, inst, hr, feat, infer)  ->  loss_D, loss_G  ->
+    optimizer_G.zero_grad(); loss_G.backward(); optimizer_G.step()
+    optimizer_D.zero_grad(); loss_D.backward(); optimizer_D.step()
+The reference's only multi-GPU mode is torch.nn.DataParallel (models/models.py:17-18), unreachable with --fp16.
+Here: one process per GPU (torchrun), each rank a full replica on its own batch shard; the ONLY exchange is the
+average of the flat gradient buffers (one NCCL all-reduce per network over NVLink / NVSwitch).  G's all-reduce is
+issued asynchronously right after loss_G.backward() and overlaps loss_D.backward(): the discriminator's backward
+touches neither G's weights nor G's gradients, so applying optimizer_G.step() after it is arithmetically the
+reference's order."""
+import torch
+import torch.distributed as dist
+
+
+def assemble_losses(model, losses):
+    """train.py:155-160"""
+    losses = [torch.mean(x) if not isinstance(x, int) else x for x in losses]
+    loss_dict = dict(zip(model.loss_names, losses))
+    loss_D = (loss_dict['D_fake'] + loss_dict['D_real']) * 0.5 + (loss_dict.get('D_fake_t', 0) + loss_dict.get('D_real_t', 0)) * 0.5
+    loss_G = (loss_dict['G_GAN'] + loss_dict.get('G_mat', 0) + loss_dict.get('G_GAN_Feat', 0) + loss_dict.get('G_VGG', 0)
+              + loss_dict.get('G_GAN_t', 0))
+    return loss_dict, loss_G, loss_D
+
+
+class GradSync:
+    """average the flat gradient buffers over the data-parallel group (no-op for a single process)"""
+
+    def __init__(self, group=None):
+        self.enabled = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+        self.group = group
+        self.world = dist.get_world_size(group) if self.enabled else 1
+
+    def start(self, optimizer):
+        if not self.enabled:
+            return None
+        return dist.all_reduce(optimizer.flat_grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+
+    def finish(self, optimizer, handle):
+        if handle is None:
+            return
+        handle.wait()                           # orders the current stream after the collective
+        optimizer.flat_grad.mul_(1.0 / self.world)
+
+
+def broadcast_parameters(model, src=0, group=None):
+    """identical replicas at start (the reference's DataParallel re-broadcasts every step)"""
+    if not (dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1):
+        return
+    for opt in (model.optimizer_G, model.optimizer_D):
+        dist.broadcast(opt.flat, src=src, group=group)
+        opt.flat_bf16.copy_(opt.flat)
+
+
+def train_step(model, lr_audio, hr_audio, inst=None, feat=None, infer=False, sync=None):
+    """returns (loss_dict, generated-or-None); loss values stay on the device (no host sync in the step)"""
+    losses, generated = model(lr_audio, inst, hr_audio, feat, infer)
+    loss_dict, loss_G, loss_D = assemble_losses(model, losses)
+    opt_G, opt_D = model.optimizer_G, model.optimizer_D
+    opt_G.zero_grad()
+    loss_G.backward()
+    h_G = sync.start(opt_G) if sync is not None else None
+    opt_D.zero_grad()
+    loss_D.backward()
+    h_D = sync.start(opt_D) if sync is not None else None
+    if sync is not None:
+        sync.finish(opt_G, h_G)
+    opt_G.step()
+    if sync is not None:
+        sync.finish(opt_D, h_D)
+    opt_D.step()
+    return {k: (v.detach() if torch.is_tensor(v) else v) for k, v in loss_dict.items()}, generated
