@@ -1,12 +1,17 @@
 #!/usr/bin/env python
 """bench.py -- the driver's measurement contract for the hot path (see DESIGN.md "Measurement").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload mdct]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload train|mdct]
 
-One JSON line on stdout (rank 0).  Workload "mdct": one step = MDCT4.forward + IMDCT4.forward over a
-batch of B synthetic 48 kHz segments (n_fft 1024, hop 512, KBD window, center; BASELINE.json config 5's
-geometry at the config-1 segment length), inputs larger than L2 so no flush is needed.
-`value` is device-resident throughput; `e2e` goes through the public modules with pinned HOST buffers.
+One JSON line on stdout (rank 0).
+Workload "train" (default; BASELINE.json configs[2]): one step = one full G3L2-ngf48 optimisation step
+(train.py:148-184) on 8 synthetic 48 kHz segments per GPU: MDCT4 -> dB/+- encoding -> LocalEnhancer ->
+3 x MultiscaleDiscriminator -> LSGAN + feature matching -> two backward passes -> two Adam steps, bf16 storage with
+fp32 accumulation; ranks are data-parallel replicas exchanging only the gradient all-reduce.  `value` = samples/s with
+the audio resident in HBM; `e2e` = the same step fed from pinned HOST audio with the losses read back every step.
+The line also carries "mdct4": the MDCT4 / IMDCT4 kernels' GB/s against the HBM peak (second half of the metric).
+Workload "mdct": one step = MDCT4.forward + IMDCT4.forward over a batch of B synthetic 48 kHz segments (n_fft 1024,
+hop 512, KBD window, center), inputs larger than L2 so no flush is needed.
 """
 import argparse
 import json
@@ -30,8 +35,9 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="mdct", choices=["mdct"])
-    ap.add_argument("--batch", type=int, default=512, help="segments per GPU per step")
+    ap.add_argument("--workload", default="train", choices=["train", "mdct"])
+    ap.add_argument("--batch", type=int, default=None, help="segments per GPU per step (train: 8, mdct: 512)")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -42,6 +48,15 @@ def peaks():
         d = json.load(open(p))
         return float(d["hbm_gbs"]), "measured"
     return 6650.0, "fallback"
+
+
+def tensor_peak():
+    """bf16 dense TFLOP/s: the SUSTAINED figure (the conv kernels are timed inside a long step)"""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "measured (sustained)"
+    return 1400.0, "fallback"
 
 
 def mdct_bytes(B, T, F, M, T_out):
@@ -281,7 +296,12 @@ def run_ours(args):
 
 def main():
     args = parse_args()
-    if args.impl == "reference":
+    if args.batch is None:
+        args.batch = 8 if args.workload == "train" else 512
+    if args.workload == "train":
+        from bench_train import run_train, run_train_reference
+        (run_train_reference if args.impl == "reference" else run_train)(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

@@ -1,0 +1,229 @@
+"""The "train" workload of bench.py: one G3L2-ngf48 optimisation step per bench step (see bench.py's docstring)."""
+import json
+import os
+import time
+
+METRIC = "G3L2 train samples/s @1/2/4/8 B200; MDCT4/IMDCT4 GB/s vs HBM peak"
+T_SEG = 127 * 512          # 65 024 samples -> 128 frames of 512 bins (S128 of SURVEY 8: [B, 2, 512, 128])
+WORKLOAD = ("G3L2 ngf48 LocalEnhancer + 2-scale D (ndf 64), GAN + feature matching, full optimisation step "
+            "(train.py:148-184), batch %d x 65024-sample 48 kHz segments per GPU -> [%d,2,512,128] MDCT4 spectrograms")
+
+
+def synth_audio(B, seed):
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    hr = 0.1 * torch.randn(B, T_SEG, generator=g)
+    lr = 0.5 * (hr + torch.roll(hr, 1, dims=1))             # a crude low-pass stands in for the 8 kHz resample
+    return lr, hr
+
+
+def _mdct_roofline(dev, steps=10, B=512, T=130816):
+    """MDCT4 / IMDCT4 kernels alone (second half of the metric): algorithmic bytes / CUDA-event time"""
+    import torch
+    from bench import HOP, N_FFT, WIN, mdct_bytes, peaks
+    from pix2pixhdaudiosr_b200.models import mdct as pm
+    from pix2pixhdaudiosr_b200.util.util import kbdwin
+    m = pm.MDCT4(N_FFT, HOP, WIN, kbdwin, True, device=dev)
+    im = pm.IMDCT4(N_FFT, HOP, WIN, kbdwin, True, device=dev)
+    x = 0.1 * torch.randn(B, T, device=dev)
+    sp, ep = m.pads(B)
+    F = (T + sp + ep - WIN) // HOP + 1
+    crop, T_out = im.out_geometry(F)
+    ba, bs = mdct_bytes(B, T, F, N_FFT // 2, T_out)
+    for _ in range(3):
+        y = pm._synthesis(pm._analysis(x, m._plan, F, sp, 1.0), m._plan, T_out, crop, 4.0 / N_FFT)
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)]
+    torch.cuda.synchronize()
+    for e in ev:
+        e[0].record()
+        spec = pm._analysis(x, m._plan, F, sp, 1.0)
+        e[1].record()
+        y = pm._synthesis(spec, m._plan, T_out, crop, 4.0 / N_FFT)
+        e[2].record()
+    torch.cuda.synchronize()
+    ms_a = sum(e[0].elapsed_time(e[1]) for e in ev) / steps
+    ms_s = sum(e[1].elapsed_time(e[2]) for e in ev) / steps
+    peak, src = peaks()
+    del x, spec, y
+    return {"workload": f"{B} segments x {T} samples, n_fft {N_FFT} hop {HOP} KBD center; inputs larger than L2",
+            "analysis": {"ms": round(ms_a, 4), "GBps": round(ba / ms_a / 1e6, 1), "frac_hbm_peak": round(ba / ms_a / 1e6 / peak, 4)},
+            "synthesis": {"ms": round(ms_s, 4), "GBps": round(bs / ms_s / 1e6, 1), "frac_hbm_peak": round(bs / ms_s / 1e6 / peak, 4)},
+            "hbm_peak_GBps": peak, "peak_source": src}
+
+
+def cpu_train_step_seconds(batch=1, steps=1):
+    """the oracle port of the reference's optimisation step (oracle/pix2pixhd_oracle.py: plain torch CPU ops on
+    reference-format state_dicts) on all host threads; returns (seconds per step, threads)"""
+    import torch
+    from oracle import pix2pixhd_oracle as O
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    cfg = {'n_fft': 1024, 'hop_length': 512, 'win_length': 1024, 'alpha': 0.6, 'min_value': 1e-7, 'explicit_encoding': True,
+           'up_ratio': 6.0, 'lambda_feat': 10.0,
+           'G': {'netG': 'local', 'n_downsample_global': 4, 'n_blocks_global': 3, 'n_local_enhancers': 1, 'n_blocks_local': 2},
+           'D': {'num_D': 2, 'n_layers_D': 3}}
+    sdG, sdD = O.random_state_dicts()
+    st = O.TrainState(sdG, sdD, cfg)
+    lr, hr = synth_audio(batch, 7)
+    t = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        st.step(lr, hr)
+        t.append(time.perf_counter() - t0)
+    return sum(t) / len(t), threads
+
+
+def run_train_reference(args):
+    """--impl reference: the reference's CPU implementation of the step (its modules are plain torch.nn on CPU; the
+    oracle port restates them -- /root/reference does not exist on the GPU box), all host threads.  One bench step =
+    one optimisation step on a bounded sample (batch 1 instead of 8) of the same workload."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    steps = max(1, min(args.steps, 6))
+    sec, threads = cpu_train_step_seconds(batch=1, steps=steps + min(args.warmup, 1))
+    val = round(1.0 / sec, 5)
+    sample = (f"batch 1 (bounded sample of the batch-{args.batch} step), {steps} timed step(s) of the requested "
+              f"{args.steps}, oracle/pix2pixhd_oracle.py on {threads} threads")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "samples/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(args.warmup, 1), "ms_per_step": round(sec * 1e3, 1), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD % (args.batch, args.batch), "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def run_train(args):
+    import torch
+    import torch.distributed as dist
+    from bench import ClockSampler, tensor_peak
+    from pix2pixhdaudiosr_b200 import _lib, ops, options
+    from pix2pixhdaudiosr_b200.models.models import create_model
+    from pix2pixhdaudiosr_b200.train import GradSync, broadcast_parameters, train_step
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, K, W = args.batch, args.steps, args.warmup
+    lib = _lib.lib()
+
+    import contextlib
+    import io
+    torch.manual_seed(1234)
+    with contextlib.redirect_stdout(io.StringIO()):
+        model = create_model(options.g3l2_opt(gpu_ids=[local], batchSize=B, precision=args.precision))
+    broadcast_parameters(model)
+    sync = GradSync()
+    lr_host, hr_host = synth_audio(B, 1000 + rank)
+    lr_host, hr_host = lr_host.pin_memory(), hr_host.pin_memory()
+    lr_d, hr_d = lr_host.to(dev), hr_host.to(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident: K full optimisation steps
+    for _ in range(W):
+        loss_dict, _ = train_step(model, lr_d, hr_d, sync=sync)
+    clocks = ClockSampler(local)
+    barrier()
+    n0 = lib.p2p_kernel_launches()
+    clocks.start()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(K):
+        loss_dict, _ = train_step(model, lr_d, hr_d, sync=sync)
+    t1.record()
+    barrier()
+    clk = clocks.stop()
+    launches = lib.p2p_kernel_launches() - n0
+    total_ms = t0.elapsed_time(t1)
+    final_losses = {k: float(v) for k, v in loss_dict.items()}
+
+    # ---- end to end: pinned host audio in, losses out to the host, every step
+    names = list(loss_dict)
+    loss_host = torch.empty(len(names), dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        l, h = lr_host.to(dev, non_blocking=True), hr_host.to(dev, non_blocking=True)
+        ld, _ = train_step(model, l, h, sync=sync)
+        loss_host.copy_(torch.stack([ld[n].float() for n in names]), non_blocking=True)
+
+    for _ in range(min(W, 2)):
+        e2e_step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        e2e_step()
+    e1.record()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+
+    # ---- one extra, un-timed step with CUDA events around every convolution launch: the roofline leg
+    ops.start_conv_timing()
+    train_step(model, lr_d, hr_d, sync=sync)
+    rec = ops.stop_conv_timing()
+
+    times = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms = times.tolist()
+    if rank == 0:
+        peak, peak_src = tensor_peak()
+        step_ms = total_ms / K
+        classes = {}
+        for kind, umma, flops, ms, _ in rec:
+            c = classes.setdefault(("tcgen05 " if umma else "cuda-core ") + kind, [0, 0.0, 0.0])
+            c[0] += 1; c[1] += flops; c[2] += ms
+        um_flops = sum(r[2] for r in rec if r[1])
+        um_ms = sum(r[3] for r in rec if r[1])
+        um_n = sum(1 for r in rec if r[1])
+        all_flops = sum(r[2] for r in rec)
+        ach = um_flops / (um_ms * 1e-3) / 1e12 if um_ms > 0 else 0.0
+        out = {
+            "metric": METRIC, "value": round(B * world * K / (total_ms * 1e-3), 2), "unit": "samples/s", "n_gpus": world,
+            "steps": K, "warmup": W, "ms_per_step": round(step_ms, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+            "config": {"workload": WORKLOAD % (B, B), "global_batch": B * world, "parallelism": f"dp{world}",
+                       "l2": "per-step working set (0.31 GB bf16 weights + 0.65 GB fp32 master + activations) exceeds the 126 MB L2; no flush",
+                       "weights": "random init N(0,0.02), seed 1234; mask_mode mode2; Adam lr 2e-4 beta1 0.5",
+                       "final_losses": final_losses},
+            "roofline": {"bound": "tensor", "kernel": "conv_umma_kernel<0|1|2> (tcgen05 implicit-GEMM fwd / dgrad / wgrad)",
+                         "achieved": round(ach, 1), "peak": peak, "unit": "TFLOP/s", "frac": round(ach / peak, 4),
+                         "peak_source": peak_src, "traffic": None, "launches_per_step": um_n,
+                         "flops_per_launch": round(um_flops / max(um_n, 1)), "ms_per_launch": round(um_ms / max(um_n, 1), 5),
+                         "ms_per_step_in_kernel": round(um_ms, 3), "share_of_step": round(um_ms / step_ms, 3),
+                         "note": "algorithmic conv FLOPs (2*MACs) of the tcgen05 launches of one step / their summed "
+                                 "CUDA-event durations, measured in an extra profiled step after the timed region"},
+            "step_tensor_utilisation": round(all_flops / (step_ms * 1e-3) / 1e12 / peak, 4),
+            "conv_flops_per_step": round(all_flops),
+            "kernels": {k: {"launches": v[0], "GFLOP": round(v[1] / 1e9, 1), "ms": round(v[2], 3),
+                            "TFLOPs": round(v[1] / (v[2] * 1e-3) / 1e12, 1) if v[2] > 0 else None}
+                        for k, v in sorted(classes.items())},
+            "e2e": {"value": round(B * world * K / (e2e_ms * 1e-3), 2), "unit": "samples/s",
+                    "h2d_bytes_per_step": 2 * B * T_SEG * 4 * world, "d2h_bytes_per_step": 4 * len(names) * world,
+                    "ms_per_step": round(e2e_ms / K, 3)},
+            "gpu_launches": int(launches), "clocks": clk,
+        }
+        del model
+        torch.cuda.empty_cache()
+        out["mdct4"] = _mdct_roofline(dev)
+        if world == 1 and not args.no_cpu_baseline:
+            sec, threads = cpu_train_step_seconds(batch=1, steps=1)
+            out["cpu_baseline"] = {"value": round(1.0 / sec, 5), "unit": "samples/s", "cores": threads, "kind": "port",
+                                   "sample": "one optimisation step at batch 1 (bounded sample of the batch-8 step), "
+                                             "oracle/pix2pixhd_oracle.py (torch CPU restatement of networks.py / "
+                                             f"pix2pixHD_model.py / train.py) on {threads} threads",
+                                   "seconds": round(sec, 2)}
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()

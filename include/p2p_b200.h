@@ -31,6 +31,8 @@ extern "C" {
 
 const char* p2p_last_error(void);
 int p2p_abi_version(void);
+/* Number of kernel launches this process has issued through the entry points below (bench.py's gpu_launches). */
+long long p2p_kernel_launches(void);
 
 /* ---- MDCT4 / IMDCT4 ------------------------------------------------------------------------
  * M = n_fft/2 bins, L = M/2 = complex FFT length.  n_fft: power of two, 16..4096.
@@ -101,7 +103,7 @@ typedef struct {
 int p2p_conv_forward(const p2p_conv_pass* pass, const void* in, const void* weight, const float* bias,
                      void* out, int dtype, int out_dtype, void* stream);
 /* Testing/benchmark knob: non-zero routes every convolution pass to the exact CUDA-core kernels even where the
- * tcgen05 tensor-core kernels (bf16, gathered channels % 16 == 0) apply.  Returns the old value. */
+ * tcgen05 tensor-core kernels (bf16, gathered channels % 16 == 0) apply; negative only queries.  Returns the old value. */
 int p2p_conv_force_simple(int on);
 /* Number of tcgen05 convolution kernels launched by this process so far. */
 long long p2p_conv_umma_launches(void);

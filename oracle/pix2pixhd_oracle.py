@@ -1,0 +1,269 @@
+"""CPU ORACLE (test infrastructure, never the product path) for the conv-GAN rows of the hot path:
+a functional restatement, on plain torch CPU ops, of
+
+    models/networks.py:129-253   LocalEnhancer / GlobalGenerator / ResnetBlock      -> generator()
+    models/networks.py:292-383   MultiscaleDiscriminator / NLayerDiscriminator      -> discriminator()
+    models/networks.py:68-110    GANLoss (LSGAN branch)                             -> gan_loss()
+    models/pix2pixHD_model.py:142-227, 229-249   to_spectro / denormalize / to_audio -> to_spectro(), to_audio()
+    models/pix2pixHD_model.py:331-435            forward (GAN + feature matching)   -> model_losses()
+    train.py:155-184             loss assembly, two backward passes, two Adam steps -> TrainState.step()
+
+working directly on reference-format state_dicts (same keys, same shapes).  Only tests/, __graft_entry__.smoke()
+and bench.py's cpu_baseline / --impl reference legs may import this file.
+
+Parity pinned: tests/test_oracle_nets.py checks it against the reference's own outputs committed under
+tests/golden/ (nets_ref.npz: network outputs and gradients; model_ref.npz: encoded images, first-step losses and
+gradients, weights after the first Adam step, 200-step loss curve, inference + reconstructed audio), all produced by
+importing /root/reference in the build container (tests/golden/make_golden_nets.py, make_golden_model.py).
+"""
+import math
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from . import mdct4_oracle as M4
+
+
+# ---- layers ------------------------------------------------------------------------------------------
+def _conv(x, sd, key, stride=1, pad=0, reflect=0):
+    if reflect:
+        x = F.pad(x, (reflect, reflect, reflect, reflect), mode='reflect')      # nn.ReflectionPad2d
+    return F.conv2d(x, sd[key + '.weight'], sd[key + '.bias'], stride=stride, padding=pad)
+
+
+def _convT(x, sd, key):
+    # nn.ConvTranspose2d(k=3, stride=2, padding=1, output_padding=1)   networks.py:151, 203
+    return F.conv_transpose2d(x, sd[key + '.weight'], sd[key + '.bias'], stride=2, padding=1, output_padding=1)
+
+
+def _in(x):
+    return F.instance_norm(x, eps=1e-5)         # InstanceNorm2d(affine=False), networks.py:22
+
+
+def _resblock(x, sd, key):
+    # networks.py:214-253
+    h = F.relu(_in(_conv(x, sd, key + '.conv_block.1', reflect=1)))
+    return x + _in(_conv(h, sd, key + '.conv_block.5', reflect=1))
+
+
+def _pool(x):
+    return F.avg_pool2d(x, 3, stride=2, padding=[1, 1], count_include_pad=False)   # networks.py:166, 309
+
+
+def _global_trunk(x, sd, prefix, n_down, n_blocks, head):
+    """GlobalGenerator.model (networks.py:183-211); head=False drops the last three modules (networks.py:138)"""
+    i = 1
+    x = F.relu(_in(_conv(x, sd, f'{prefix}.{i}', reflect=3)))
+    i = 4
+    for _ in range(n_down):
+        x = F.relu(_in(_conv(x, sd, f'{prefix}.{i}', stride=2, pad=1)))
+        i += 3
+    for _ in range(n_blocks):
+        x = _resblock(x, sd, f'{prefix}.{i}')
+        i += 1
+    for _ in range(n_down):
+        x = F.relu(_in(_convT(x, sd, f'{prefix}.{i}')))
+        i += 3
+    if head:
+        x = torch.tanh(_conv(x, sd, f'{prefix}.{i + 1}', reflect=3))
+    return x
+
+
+def generator(x, sd, netG, n_downsample_global, n_blocks_global, n_local_enhancers=1, n_blocks_local=3):
+    """define_G(...)(x) for netG in {'global', 'local'} (networks.py:27-44)"""
+    if netG == 'global':
+        return _global_trunk(x, sd, 'model', n_downsample_global, n_blocks_global, True)
+    assert netG == 'local'
+    pyramid = [x]
+    for _ in range(n_local_enhancers):
+        pyramid.append(_pool(pyramid[-1]))
+    out = _global_trunk(pyramid[-1], sd, 'model', n_downsample_global, n_blocks_global, False)
+    for n in range(1, n_local_enhancers + 1):          # networks.py:174-181
+        xi = pyramid[n_local_enhancers - n]
+        d = f'model{n}_1'
+        h = F.relu(_in(_conv(xi, sd, d + '.1', reflect=3)))
+        h = F.relu(_in(_conv(h, sd, d + '.4', stride=2, pad=1)))
+        h = h + out
+        u = f'model{n}_2'
+        for b in range(n_blocks_local):
+            h = _resblock(h, sd, f'{u}.{b}')
+        h = F.relu(_in(_convT(h, sd, f'{u}.{n_blocks_local}')))
+        if n == n_local_enhancers:
+            h = torch.tanh(_conv(h, sd, f'{u}.{n_blocks_local + 4}', reflect=3))
+        out = h
+    return out
+
+
+def discriminator(x, sd, num_D, n_layers, get_interm_feat):
+    """MultiscaleDiscriminator.forward: list (finest scale first) of feature lists (networks.py:319-331)"""
+    result = []
+    for i in range(num_D):
+        s = num_D - 1 - i
+        if get_interm_feat:
+            keys = [f'scale{s}_layer{j}.0' for j in range(n_layers + 2)]
+        else:
+            keys = [f'layer{s}.{j}' for j in [0] + [2 + 3 * k for k in range(n_layers + 1)]]
+        feats, h = [], x
+        for j, key in enumerate(keys):
+            stride = 2 if j < n_layers else 1
+            h = _conv(h, sd, key, stride=stride, pad=2)
+            if 0 < j <= n_layers:
+                h = _in(h)
+            if j <= n_layers:
+                h = F.leaky_relu(h, 0.2)
+            feats.append(h)
+        result.append(feats if get_interm_feat else [feats[-1]])
+        if i != num_D - 1:
+            x = _pool(x)
+    return result
+
+
+def gan_loss(preds, target_is_real):
+    """sum over scales of MSE(pred[-1], 1 or 0) (networks.py:100-110)"""
+    t = 1.0 if target_is_real else 0.0
+    return sum(((p[-1] - t) ** 2).mean() for p in preds)
+
+
+def feature_matching(pred_fake, pred_real, num_D, n_layers_D, lambda_feat):
+    """pix2pixHD_model.py:390-398"""
+    w = (4.0 / (n_layers_D + 1)) * (1.0 / num_D) * lambda_feat
+    loss = 0
+    for i in range(num_D):
+        for j in range(len(pred_fake[i]) - 1):
+            loss = loss + w * (pred_fake[i][j] - pred_real[i][j].detach()).abs().mean()
+    return loss
+
+
+# ---- spectrogram encode / decode -------------------------------------------------------------------------
+def _db(x, amin):
+    return 20.0 * torch.log10(torch.clamp(x, min=amin)) - 20.0     # torchaudio amplitude_to_DB(x, 20, amin, 1)
+
+
+def to_spectro(audio, cfg, mask):
+    """pix2pixHD_model.py:142-227 with the transform = MDCT4 (float64 numpy oracle, cast to float32 like MDCT2's
+    output); mask_mode None (zeros) is the deterministic variant the fixtures use"""
+    w = M4.kbdwin(cfg['win_length'])
+    spec = M4.mdct4_forward(audio.numpy(), w, cfg['n_fft'], cfg['hop_length'], True, signal_len=len(audio))
+    spectro = torch.from_numpy(spec.astype(np.float32)).unsqueeze(1).permute(0, 1, 3, 2)
+    a, amin = cfg['alpha'], cfg['min_value']
+    if cfg['explicit_encoding']:
+        neg = 0.5 * (spectro.abs() - spectro)
+        pos = spectro + neg
+        logs = torch.cat((_db(a * pos + (1 - a) * neg, amin), _db((1 - a) * pos + a * neg, amin)), dim=1)
+    else:
+        logs = _db(spectro.abs() + amin, amin)
+    pha = torch.sign(spectro)
+    hi, lo = logs.max(), logs.min()
+    norm = {'max': hi, 'min': lo, 'mean': logs.mean(), 'std': logs.var().sqrt()}
+    logs = (logs - lo) / (hi - lo)
+    if mask:
+        size = logs.size()
+        mask_size = int(size[2] * (1 - 1 / cfg['up_ratio']))
+        if mask_size > 0:
+            logs = torch.cat((logs[:, :, :-mask_size, :], torch.zeros(size[0], size[1], mask_size, size[3])), dim=2)
+    return logs, pha, norm
+
+
+def to_audio(log_spectro, norm, cfg):
+    """explicit-encoding branch of pix2pixHD_model.py:229-249 with IMDCT4"""
+    s = log_spectro.abs() * (norm['max'] - norm['min']) + norm['min']
+    amp = 10.0 * torch.pow(10.0, 0.05 * s) - cfg['min_value']          # DB_to_amplitude(., 10, 0.5) - min_value
+    spec = (amp[..., 0, :, :] - amp[..., 1, :, :]) / (2 * cfg['alpha'] - 1)
+    w = M4.kbdwin(cfg['win_length'])
+    y = M4.imdct4_forward(spec.permute(0, 2, 1).double().numpy(), w, cfg['n_fft'], cfg['hop_length'], True)
+    return math.sqrt(cfg['up_ratio'] - 1) * torch.from_numpy(y.astype(np.float32)).reshape(spec.shape[0], 1, 1, -1)
+
+
+# ---- model + optimisation step ---------------------------------------------------------------------------
+def model_losses(sdG, sdD, lr_spectro, hr_spectro, cfg):
+    """pix2pixHD_model.py:348-398 -> (G_GAN, G_GAN_Feat, D_real, D_fake, sr_result)"""
+    g = cfg['G']
+    sr = generator(lr_spectro, sdG, g['netG'], g['n_downsample_global'], g['n_blocks_global'], g['n_local_enhancers'],
+                   g['n_blocks_local'])
+    d = cfg['D']
+    run_D = lambda x: discriminator(x, sdD, d['num_D'], d['n_layers_D'], True)
+    pred_fake_pool = run_D(torch.cat((lr_spectro, sr.detach()), dim=1))
+    loss_D_fake = gan_loss(pred_fake_pool, False)
+    pred_real = run_D(torch.cat((lr_spectro, hr_spectro), dim=1))
+    loss_D_real = gan_loss(pred_real, True)
+    pred_fake = run_D(torch.cat((lr_spectro, sr), dim=1))
+    loss_G_GAN = gan_loss(pred_fake, True)
+    loss_feat = feature_matching(pred_fake, pred_real, d['num_D'], d['n_layers_D'], cfg['lambda_feat'])
+    return loss_G_GAN, loss_feat, loss_D_real, loss_D_fake, sr
+
+
+class TrainState:
+    """weights + two Adam optimisers (pix2pixHD_model.py:131, 140) stepping as train.py:155-184 does"""
+
+    def __init__(self, sdG, sdD, cfg, lr=2e-4, beta1=0.5):
+        self.cfg = cfg
+        self.G = {k: v.clone().float().requires_grad_(True) for k, v in sdG.items()}
+        self.D = {k: v.clone().float().requires_grad_(True) for k, v in sdD.items()}
+        self.opt_G = torch.optim.Adam(list(self.G.values()), lr=lr, betas=(beta1, 0.999))
+        self.opt_D = torch.optim.Adam(list(self.D.values()), lr=lr, betas=(beta1, 0.999))
+
+    def step(self, lr_audio, hr_audio, spectros=None):
+        cfg = self.cfg
+        if spectros is None:
+            with torch.no_grad():
+                hs, _, _ = to_spectro(hr_audio, cfg, False)
+                ls, _, _ = to_spectro(lr_audio, cfg, True)
+        else:
+            ls, hs = spectros
+        g_gan, g_feat, d_real, d_fake, sr = model_losses(self.G, self.D, ls, hs, cfg)
+        loss_D = (d_fake + d_real) * 0.5
+        loss_G = g_gan + g_feat
+        self.opt_G.zero_grad()
+        loss_G.backward()
+        gG = {k: v.grad.clone() for k, v in self.G.items()}
+        self.opt_G.step()
+        self.opt_D.zero_grad()
+        loss_D.backward()
+        gD = {k: v.grad.clone() for k, v in self.D.items()}
+        self.opt_D.step()
+        return [float(g_gan), float(g_feat), float(d_real), float(d_fake)], sr.detach(), gG, gD
+
+
+def random_state_dicts(ngf=48, ndf=64, input_nc=2, output_nc=2, n_down=4, n_blocks_global=3, n_blocks_local=2, num_D=2,
+                       n_layers_D=3, seed=1234):
+    """G3L2-shaped LocalEnhancer + multiscale D weights drawn N(0, 0.02) (weights_init, networks.py:10-16); biases
+    uniform as torch.nn.Conv2d does.  For timing and smoke runs only (not the reference's RNG stream)."""
+    g = torch.Generator().manual_seed(seed)
+    sdG, sdD = {}, {}
+
+    def add(sd, key, cout, cin, k, transposed=False):
+        shape = (cin, cout, k, k) if transposed else (cout, cin, k, k)
+        sd[key + '.weight'] = torch.randn(shape, generator=g) * 0.02
+        bound = 1 / math.sqrt((cout if transposed else cin) * k * k)
+        sd[key + '.bias'] = (torch.rand(cout, generator=g) * 2 - 1) * bound
+
+    c = ngf * 2
+    add(sdG, 'model.1', c, input_nc, 7)
+    i = 4
+    for _ in range(n_down):
+        add(sdG, f'model.{i}', c * 2, c, 3)
+        c *= 2
+        i += 3
+    for _ in range(n_blocks_global):
+        add(sdG, f'model.{i}.conv_block.1', c, c, 3)
+        add(sdG, f'model.{i}.conv_block.5', c, c, 3)
+        i += 1
+    for _ in range(n_down):
+        add(sdG, f'model.{i}', c // 2, c, 3, transposed=True)
+        c //= 2
+        i += 3
+    add(sdG, 'model1_1.1', ngf, input_nc, 7)
+    add(sdG, 'model1_1.4', ngf * 2, ngf, 3)
+    for b in range(n_blocks_local):
+        add(sdG, f'model1_2.{b}.conv_block.1', ngf * 2, ngf * 2, 3)
+        add(sdG, f'model1_2.{b}.conv_block.5', ngf * 2, ngf * 2, 3)
+    add(sdG, f'model1_2.{n_blocks_local}', ngf, ngf * 2, 3, transposed=True)
+    add(sdG, f'model1_2.{n_blocks_local + 4}', output_nc, ngf, 7)
+    for s in range(num_D):
+        nf, prev = ndf, input_nc + output_nc
+        for j in range(n_layers_D + 2):
+            cout = 1 if j == n_layers_D + 1 else nf
+            add(sdD, f'scale{s}_layer{j}.0', cout, prev, 4)
+            prev, nf = cout, min(nf * 2, 512)
+    return sdG, sdD

@@ -10,6 +10,7 @@ _c = ctypes
 _SIGS = {
     "p2p_last_error": (_c.c_char_p, []),
     "p2p_abi_version": (_c.c_int, []),
+    "p2p_kernel_launches": (_c.c_longlong, []),
     "p2p_mdct4_force_general": (_c.c_int, [_c.c_int]),
     "p2p_mdct4_table_words": (_c.c_int, [_c.c_int]),
     "p2p_mdct4_fill_tables": (_c.c_int, [_c.c_int, _c.c_void_p]),

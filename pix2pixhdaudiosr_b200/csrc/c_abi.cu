@@ -6,7 +6,12 @@ char* error_slot() {
     static thread_local char buf[512] = {0};
     return buf;
 }
+long long& launch_counter() {
+    static long long n = 0;
+    return n;
+}
 }  // namespace p2p
 
 extern "C" const char* p2p_last_error(void) { return p2p::error_slot(); }
-extern "C" int p2p_abi_version(void) { return 1; }
+extern "C" int p2p_abi_version(void) { return 2; }
+extern "C" long long p2p_kernel_launches(void) { return p2p::launch_counter(); }

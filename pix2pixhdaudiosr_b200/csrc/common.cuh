@@ -17,7 +17,10 @@ inline int fail(int code, const char* fmt, ...) {
     return code;
 }
 
+long long& launch_counter();   // kernels launched through the C ABI by this process (defined in c_abi.cu)
+
 inline int check_launch(const char* what) {
+    ++launch_counter();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(P2P_ECUDA, "%s: %s", what, cudaGetErrorString(e));
     return P2P_OK;

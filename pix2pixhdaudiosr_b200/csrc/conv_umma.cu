@@ -464,40 +464,39 @@ int conv_forward_umma(const p2p_conv_pass* P, const void* in, const void* weight
     a.out = out;
     a.M = M;
     a.out_bf16 = out_dtype == P2P_BF16;
-    a.BN = pick_bn(P->J);
-    a.n_tiles = (P->J + a.BN - 1) / a.BN;
     const long long mt = (M + BM - 1) / BM;
-    if (mt * a.n_tiles > 2000000000LL) return 1;
-    a.m_tiles = (int)mt;
     a.cpb = (P->K + 63) / 64;
     a.total_kb = P->ntaps * a.cpb;
-    // split the reduction when the tile count cannot fill the machine (fp32 outputs only: reduced with red.add)
-    const long long tiles = mt * a.n_tiles;
-    int nsplit = 1;
-    const bool scatter_once = true;
-    if (!a.out_bf16 && tiles < sm_count() && scatter_once) {
-        nsplit = (int)(sm_count() / tiles);
-        const int max_split = a.total_kb / 8;
-        if (nsplit > max_split) nsplit = max_split;
-        if (nsplit < 1) nsplit = 1;
+    // Tile width and reduction split: these layers are operand-load bound when few tiles exist, so model a work
+    // item's cost as k-blocks x (A rows + B rows) and minimise rounds x cost over BN (multiples of 16) and, for fp32
+    // outputs scattered densely (reduced with red.add into a zeroed buffer), over the split of the reduction.
+    const bool can_split = !a.out_bf16 && P->oys == 1 && P->oxs == 1 && P->gy == P->OH && P->gx == P->OW;
+    const int sms = sm_count();
+    double best = 1e300;
+    int best_bn = 16, best_split = 1;
+    for (int bn = 16; bn <= 256; bn += 16) {
+        const long long nt = (P->J + bn - 1) / bn;
+        if (bn > 16 && nt == (P->J + bn - 17) / (bn - 16)) continue;     // a narrower tile covers J equally
+        const int max_split = can_split ? (a.total_kb >= 8 ? a.total_kb / 4 : 1) : 1;
+        for (int sp = 1; sp <= max_split; sp = sp < 4 ? sp + 1 : sp * 2) {
+            const long long items = mt * nt * sp;
+            const long long rounds = (items + sms - 1) / sms;
+            const int kbs = (a.total_kb + sp - 1) / sp;
+            const double cost = (double)rounds * (kbs * (double)(128 + bn) + 600.0 + (sp > 1 ? 4.0 * bn : 0.0));
+            if (cost < best) { best = cost; best_bn = bn; best_split = sp; }
+        }
     }
-    a.kb_per_split = (a.total_kb + nsplit - 1) / nsplit;
+    a.BN = best_bn;
+    a.n_tiles = (P->J + a.BN - 1) / a.BN;
+    if (mt * a.n_tiles > 2000000000LL) return 1;
+    a.m_tiles = (int)mt;
+    const long long tiles = mt * a.n_tiles;
+    a.kb_per_split = (a.total_kb + best_split - 1) / best_split;
     a.nsplit = (a.total_kb + a.kb_per_split - 1) / a.kb_per_split;
     a.atomic = a.nsplit > 1;
     a.nwork = tiles * a.nsplit;
-    if (a.atomic) {
-        // every output position of this pass is zeroed, then reduced into; positions of other passes of the same
-        // layer (transposed-convolution parities) are disjoint, but the buffer is shared: zero only once per layer
-        // is the caller's job when oys/oxs > 1, so the split path is restricted to dense scatters
-        if (P->oys != 1 || P->oxs != 1 || P->gy != P->OH || P->gx != P->OW) {
-            a.nsplit = 1;
-            a.kb_per_split = a.total_kb;
-            a.atomic = 0;
-            a.nwork = tiles;
-        } else if (cudaMemsetAsync(out, 0, (size_t)M * P->J * sizeof(float), st) != cudaSuccess) {
-            return check_launch("cudaMemsetAsync(split-K output)");
-        }
-    }
+    if (a.atomic && cudaMemsetAsync(out, 0, (size_t)M * P->J * sizeof(float), st) != cudaSuccess)
+        return check_launch("cudaMemsetAsync(split-K output)");
     return mode == 0 ? launch<0>(a, st, "conv_umma_kernel<0>") : launch<1>(a, st, "conv_umma_kernel<1>");
 }
 
@@ -541,6 +540,6 @@ extern "C" long long p2p_conv_umma_launches(void) { return p2p::g_launches; }
 
 extern "C" int p2p_conv_force_simple(int on) {
     const int old = p2p::conv_umma_disabled() ? 1 : 0;
-    p2p::g_force_simple = on ? 1 : 0;
+    if (on >= 0) p2p::g_force_simple = on ? 1 : 0;      // negative: query only
     return old;
 }

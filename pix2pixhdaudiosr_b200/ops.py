@@ -113,8 +113,40 @@ def convT_dgrad_passes(N, H, W, Cin, Cout, KH, KW, stride, pad, out_pad):
 # ---------------------------------------------------------------------------------------------------
 # raw launches
 # ---------------------------------------------------------------------------------------------------
+# optional per-launch CUDA-event timing of the convolution passes (bench.py's roofline leg; off by default)
+_TIMING = None
+
+
+def start_conv_timing():
+    global _TIMING
+    _TIMING = []
+
+
+def stop_conv_timing():
+    """-> list of (kind, tensor_core?, flops, milliseconds) for every convolution pass since start_conv_timing()"""
+    global _TIMING
+    rec, _TIMING = _TIMING, None
+    torch.cuda.synchronize()
+    return [(kind, umma, flops, e0.elapsed_time(e1), shape) for kind, umma, flops, e0, e1, shape in rec]
+
+
+def _timed(kind, P, launch):
+    if _TIMING is None:
+        launch()
+        return
+    lib = _lib.lib()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n0 = lib.p2p_conv_umma_launches()
+    e0.record()
+    launch()
+    e1.record()
+    flops = 2.0 * P.N * P.gy * P.gx * P.J * P.ntaps * P.K
+    shape = dict(M=P.N * P.gy * P.gx, J=P.J, K=P.K, taps=P.ntaps, H=P.H, W=P.W, s=P.sy, os=P.oys)
+    _TIMING.append((kind, lib.p2p_conv_umma_launches() > n0, flops, e0, e1, shape))
+
+
 def _run_wgrad(P, x, dout, dw):
-    _lib.check(_lib.lib().p2p_conv_wgrad(ctypes.byref(P), _p(x), _p(dout), _p(dw), _DT[x.dtype], _stream()))
+    _timed("wgrad", P, lambda: _lib.check(_lib.lib().p2p_conv_wgrad(ctypes.byref(P), _p(x), _p(dout), _p(dw), _DT[x.dtype], _stream())))
 
 
 def _bias_grad(dout, J):
@@ -138,9 +170,9 @@ def _weight_for(x, w32, w16):
 ACT_NONE, ACT_RELU, ACT_LRELU = 0, 1, 2
 
 
-def _run_pass(P, x, w, bias, out):
-    _lib.check(_lib.lib().p2p_conv_forward(ctypes.byref(P), _p(x), _p(w), _p(bias), _p(out), _DT[x.dtype],
-                                           _DT[out.dtype], _stream()))
+def _run_pass(P, x, w, bias, out, kind="fwd"):
+    _timed(kind, P, lambda: _lib.check(_lib.lib().p2p_conv_forward(ctypes.byref(P), _p(x), _p(w), _p(bias), _p(out),
+                                                                   _DT[x.dtype], _DT[out.dtype], _stream())))
 
 
 class ConvCfg:
@@ -163,12 +195,48 @@ def _phys(weight, cfg):
     return w, Cout, Cin, KH, KW
 
 
+def _ceil16(c):
+    return (c + 15) // 16 * 16
+
+
+def _pad_last(t, c):
+    """zero-pad the last (channel) dimension to c"""
+    if t.shape[-1] == c:
+        return t
+    out = torch.zeros(t.shape[:-1] + (c,), dtype=t.dtype, device=t.device)
+    out[..., :t.shape[-1]] = t
+    return out
+
+
+def _thin(x, Cin, Cout):
+    """bf16 layers with 1-4 channels on one side (the 7x7 edge layers, D's first and logit layers) are run on the
+    tensor cores with that side zero-padded to 16 channels -- (padded Cin, padded Cout) or None"""
+    if x.dtype != torch.bfloat16 or _lib.lib().p2p_conv_force_simple(-1) == 1:
+        return None
+    if Cin % 16 == 0 and Cout % 16 == 0:
+        return None
+    return _ceil16(Cin), _ceil16(Cout)
+
+
+def _pad_weight(wq, Cout_p, Cin_p):
+    KH, KW, Cout, Cin = wq.shape
+    if (Cout, Cin) == (Cout_p, Cin_p):
+        return wq
+    out = torch.zeros((KH, KW, Cout_p, Cin_p), dtype=wq.dtype, device=wq.device)
+    out[:, :, :Cout, :Cin] = wq
+    return out
+
+
 def conv_forward(x, weight, bias, w16, cfg, out_dtype):
     """nn.Conv2d (+ nn.ReflectionPad2d) / nn.ConvTranspose2d forward, NHWC (networks.py:145-154, 190-207, 223-246, 340-361)"""
     N, H, W, Cx = x.shape
     wphys, Cout, Cin, KH, KW = _phys(weight, cfg)
     assert Cx == Cin, (Cx, Cin)
     wq = _weight_for(x, wphys, w16)
+    Jout = Cout
+    thin = _thin(x, Cin, Cout)
+    if thin is not None and thin[0] != Cin:             # the forward pass only needs the gathered side padded
+        x, wq, Cin = _pad_last(x, thin[0]), _pad_weight(wq, Cout, thin[0]), thin[0]
     if cfg.transposed:
         passes, (OH, OW) = convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)
         if passes is None:
@@ -178,7 +246,7 @@ def conv_forward(x, weight, bias, w16, cfg, out_dtype):
             raise RuntimeError("reflection padding must be smaller than the input")   # what ReflectionPad2d raises
         passes = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
         OH, OW = passes[0].OH, passes[0].OW
-    y = torch.empty((N, OH, OW, Cout), dtype=out_dtype, device=x.device)
+    y = torch.empty((N, OH, OW, Jout), dtype=out_dtype, device=x.device)
     for P in passes:
         _run_pass(P, x, wq, bias, y)
     return y
@@ -190,34 +258,44 @@ def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
     wphys, Cout, Cin, KH, KW = _phys(weight, cfg)
     assert dy.dtype == x.dtype and dy.is_contiguous()
     dx = dw = db = None
+    if need_db:
+        db = _bias_grad(dy, Cout)
+    Cin0, Cout0 = Cin, Cout
+    thin = _thin(x, Cin, Cout)
+    wq = _weight_for(x, wphys, w16) if (need_dx or thin is not None) else None
+    if thin is not None:
+        Cin, Cout = thin
+        x, dy = _pad_last(x, Cin), _pad_last(dy, Cout)
+        if need_dx:
+            wq = _pad_weight(wq, Cout, Cin)
     if need_dx:
-        wq = _weight_for(x, wphys, w16)
         if cfg.transposed:
             dx = torch.empty_like(x)
-            _run_pass(convT_dgrad_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0], dy, wq, None, dx)
+            _run_pass(convT_dgrad_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0], dy, wq, None, dx, "dgrad")
         else:
             passes, (DH, DW) = conv_dgrad_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
             if passes is None:
                 raise NotImplementedError("input gradient of a convolution whose stride skips whole parity classes")
             buf = torch.empty((N, DH, DW, Cin), dtype=x.dtype, device=x.device)
             for P in passes:
-                _run_pass(P, dy, wq, None, buf)
+                _run_pass(P, dy, wq, None, buf, "dgrad")
             if cfg.pad_mode == PAD_REFLECT and cfg.pad > 0:
                 dx = torch.empty_like(x)
                 _lib.check(_lib.lib().p2p_reflect_pad_fold(_p(buf), _p(dx), N, H, W, Cin, cfg.pad, _DT[x.dtype], _stream()))
             else:
                 dx = buf
+        if Cin != Cin0:
+            dx = dx[..., :Cin0].contiguous()
     if need_dw:
         dwp = torch.zeros((KH, KW, Cout, Cin), dtype=torch.float32, device=x.device)
         if cfg.transposed:
             for P in convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0]:
                 _run_wgrad(P, x, dy, dwp)
-            dw = dwp.permute(3, 2, 0, 1)
         else:
             _run_wgrad(conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)[0], x, dy, dwp)
-            dw = dwp.permute(2, 3, 0, 1)
-    if need_db:
-        db = _bias_grad(dy, Cout)
+        if thin is not None:
+            dwp = dwp[:, :, :Cout0, :Cin0]
+        dw = dwp.permute(3, 2, 0, 1) if cfg.transposed else dwp.permute(2, 3, 0, 1)
     return dx, dw, db
 
 
