@@ -39,6 +39,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=None, help="segments per GPU per step (train: 8, mdct: 512)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="train workload: launch the step eagerly instead of replaying a CUDA graph")
     return ap.parse_args()
 
 

@@ -113,6 +113,16 @@ int p2p_conv_wgrad(const p2p_conv_pass* pass, const void* in, const void* dout, 
                    void* stream);
 /* dbias[j] = sum over rows of dout [rows, J] (overwrites). */
 int p2p_bias_grad(const void* dout, float* dbias, long long rows, int J, int dtype, void* stream);
+/* Stride-1 convolutions as a TMA-fed shifted-window implicit GEMM (csrc/conv_window.cu): the padding is written once
+ * (p2p_pad_nhwc: xp [N, H+pt+pb, W+pl+pr, C], zero or reflection; needs C * element size % 16 == 0), then
+ *   out[n,y,x,j] (+ bias[j]) = sum_{dh<KH, dw<KW} sum_c xp[n, y+dh, x+dw, c] * W[tap, c, j],   y < Hp-KH+1, x < Wp-KW+1,
+ * bf16 operands, fp32 accumulation, out fp32 or bf16 [N, Hp-KH+1, Wp-KW+1, J].  tap = dh*KW+dw, or the flipped tap when
+ * `flip` (input gradients); W element (tap, c, j) at tap*w_tap + c*w_k + j*w_j with w_k == 1 or w_j == 1.
+ * P2P_ENOTSUP when C % 16 != 0 or the window (128 + (KH-1)*Wp + KW-1 pixel rows) exceeds 320 rows. */
+int p2p_pad_nhwc(const void* x, void* xp, int N, int H, int W, int C, int pt, int pb, int pl, int pr, int reflect,
+                 int dtype, void* stream);
+int p2p_conv_window(const void* xp, const void* weight, const float* bias, void* out, int N, int Hp, int Wp, int C, int J,
+                    int KH, int KW, int flip, long long w_tap, long long w_k, long long w_j, int out_dtype, void* stream);
 /* Adjoint of reflection padding: dx[n,h,w,c] = sum of dxp over the padded positions that mirror onto (h,w).
  * dxp is [N, H+2p, W+2p, C], dx is [N,H,W,C]. */
 int p2p_reflect_pad_fold(const void* dxp, void* dx, int N, int H, int W, int C, int p, int dtype, void* stream);
@@ -148,6 +158,12 @@ int p2p_loss_l1(const void* a, const void* b, float weight, float* loss, void* d
  * used by the tensor-core kernels when w_bf16 != NULL.  step is the 1-based step count. */
 int p2p_adam_step(float* w, const float* g, float* m, float* v, void* w_bf16, long long n, float lr, float beta1,
                   float beta2, float eps, int step, void* stream);
+
+/* The same update with the step count and the learning rate resident on the device (so that an optimisation step
+ * captured in a CUDA graph advances its own bias correction): *step_dev is incremented, then used; the gradient is
+ * multiplied by grad_scale first (1 / world size after a summing all-reduce).  scratch2: 2 floats of device scratch. */
+int p2p_adam_step_dev(float* w, const float* g, float* m, float* v, void* w_bf16, long long n, const float* lr_dev,
+                      float beta1, float beta2, float eps, float grad_scale, int* step_dev, float* scratch2, void* stream);
 
 /* ---- spectrogram encode / decode around the networks (models/pix2pixHD_model.py:142-249) -----------------
  * The image the networks see is channels-last [B, M bins (H), F frames (W), C], C = 2 with explicit +/- encoding

@@ -38,6 +38,8 @@ _SIGS.update({
     "p2p_conv_force_simple": (_i, [_i]),
     "p2p_conv_umma_launches": (_ll, []),
     "p2p_conv_wgrad": (_i, [_c.POINTER(ConvPass), _vp, _vp, _vp, _i, _vp]),
+    "p2p_pad_nhwc": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "p2p_conv_window": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _vp]),
     "p2p_bias_grad": (_i, [_vp, _vp, _ll, _i, _i, _vp]),
     "p2p_reflect_pad_fold": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_instnorm_act_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _f, _f, _i, _i, _vp]),
@@ -51,6 +53,7 @@ _SIGS.update({
     "p2p_spectro_encode": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _vp]),
     "p2p_spectro_normalize": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_spectro_decode": (_i, [_vp, _ll, _ll, _ll, _ll, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _f, _i, _vp]),
+    "p2p_adam_step_dev": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _vp, _f, _f, _f, _f, _vp, _vp, _vp]),
     "p2p_adam_step": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _f, _f, _f, _f, _i, _vp]),
 })
 _lib = None

@@ -437,6 +437,8 @@ int pick_bn(int cols) {
 
 }  // namespace
 
+void note_umma_launch() { ++g_launches; }     // the window kernel (conv_window.cu) is a tcgen05 kernel too
+
 bool conv_umma_disabled() {
     if (g_force_simple < 0) {
         const char* e = getenv("P2P_CONV_SIMPLE");

@@ -1,0 +1,420 @@
+// Stride-1 convolution as a TMA-fed implicit GEMM with *shifted-window* operand descriptors (tcgen05 / TMEM).
+//
+// The input is a materialised-padding NHWC tensor xp [N, Hp, Wp, C] (zero or reflection padding written once by
+// p2p_pad_nhwc), so a "valid" convolution  out[n,y,x,:] = sum_t W_t . xp[n, y+dh_t, x+dw_t, :]  reads, for GEMM row
+// q = (n*Hp + y)*Wp + x, the pixel row q + dh_t*Wp + dw_t: every tap is the SAME shared-memory window read through a
+// descriptor whose start address is shifted by dh_t*Wp + dw_t rows.  One TMA box load per 64-channel chunk
+// therefore feeds all KH*KW taps (9x / 16x / 49x less operand traffic than gathering im2col rows per tap), and no
+// thread touches the activations.  Rows whose (y, x) fall in the padding margin are computed and discarded
+// ((Hp*Wp)/(OH*OW) - 1 overhead: 3 % at 256x64, 6 % at 512x128 with 7x7).
+//
+// Window layout in shared memory: rows of 64 bf16 (128 bytes), 128-byte swizzle keyed on the absolute address (what
+// TMA writes and what the UMMA descriptor's base-offset field describes for starts that are not 1024-byte aligned).
+//
+// Warp roles (192 threads, 1 CTA / SM, persistent over (row tile, column tile) work items):
+//   warp 0: TMA producer -- window boxes (2 buffers) and per-tap weight tiles (4-stage ring)
+//   warp 1: TMEM allocation + tcgen05.mma issue
+//   warps 2-5: epilogue (TMEM -> registers -> bias -> global), double-buffered accumulators
+#include <cuda.h>
+#include <cstdint>
+#include "dtype.cuh"
+
+namespace p2p {
+namespace {
+
+constexpr int WBM = 128;
+constexpr int kBStages = 4;
+constexpr int kWinRowsMax = 320;                    // 40 KB per window buffer
+constexpr int WIN_BYTES = kWinRowsMax * 128;
+constexpr int WB_BYTES = 256 * 128;                 // one weight tile: up to 256 output channels x 64 channels
+constexpr int WSMEM = 2 * WIN_BYTES + kBStages * WB_BYTES + 1024 + 256;
+constexpr int kWThreads = 192;
+
+struct WindowArgs {
+    CUtensorMap tm_x;        // xp viewed [Q = N*Hp*Wp rows][C]: box [64 channels][rows_per_box]
+    CUtensorMap tm_w;        // weights: K-major [taps*J rows][C] box [64][BN]; MN-major [taps*K rows][J] box [64][64]
+    const float* bias;
+    void* out;
+    long long Q;             // GEMM rows = padded pixels
+    int N, Hp, Wp, OH, OW, C, J;
+    int ntaps;
+    int win_rows, rows_per_box, nboxes;
+    int BN, n_tiles, m_tiles, cpb;
+    int out_bf16, b_mn_major;
+    int base_off_mode;
+    short shift[P2P_MAX_TAPS];       // dh*Wp + dw
+    unsigned char wtap[P2P_MAX_TAPS];
+    long long nwork;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+        "l"(tm), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc),
+        "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// 128-byte-swizzle matrix descriptor; base_off = (start >> 7) & 7 for starts inside a 1024-byte swizzle atom
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t base_off) {
+    return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
+           ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46) | ((uint64_t)(base_off & 7) << 49) | (2ull << 61);
+}
+
+__global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_constant__ WindowArgs a) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t wbase = base + 2 * WIN_BYTES;
+    const uint32_t bars = wbase + kBStages * WB_BYTES;
+    // barriers: afull[2] aempty[2] bfull[S] bempty[S] tfull[2] tempty[2], then the TMEM base word
+    auto afull = [&](int i) { return bars + 8u * i; };
+    auto aempty = [&](int i) { return bars + 8u * (2 + i); };
+    auto bfull = [&](int s) { return bars + 8u * (4 + s); };
+    auto bempty = [&](int s) { return bars + 8u * (4 + kBStages + s); };
+    auto tfull = [&](int i) { return bars + 8u * (4 + 2 * kBStages + i); };
+    auto tempty = [&](int i) { return bars + 8u * (6 + 2 * kBStages + i); };
+    const uint32_t tmem_slot = bars + 8u * (8 + 2 * kBStages);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int BN = a.BN, C = a.C, J = a.J;
+    const uint32_t a_bytes = (uint32_t)a.nboxes * a.rows_per_box * 128u;
+    const uint32_t b_bytes = a.b_mn_major ? (uint32_t)((BN + 63) / 64) * 8192u : (uint32_t)BN * 128u;
+
+    if (warp == 1) {
+        if (lane == 0) {
+            for (int i = 0; i < 2; ++i) { mbar_init(afull(i), 1); mbar_init(aempty(i), 1); mbar_init(tfull(i), 1); mbar_init(tempty(i), 128); }
+            for (int s = 0; s < kBStages; ++s) { mbar_init(bfull(s), 1); mbar_init(bempty(s), 1); }
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+    if (warp == 0) {
+        // ================================ TMA producer ================================
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_x) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_w) : "memory");
+            int ia = 0, ib = 0;     // window loads / weight-tile loads issued so far
+            for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x) {
+                const int nt = (int)(w % a.n_tiles);
+                const long long mt = w / a.n_tiles;
+                const long long q0 = mt * WBM;
+                const int j0 = nt * BN;
+                for (int cc = 0; cc < a.cpb; ++cc, ++ia) {
+                    const int c0 = cc * 64;
+                    const int ab = ia & 1;
+                    if (ia >= 2) mbar_wait(aempty(ab), (uint32_t)(((ia >> 1) - 1) & 1));
+                    mbar_expect_tx(afull(ab), a_bytes);
+                    for (int bx = 0; bx < a.nboxes; ++bx)
+                        tma_load_2d(base + ab * WIN_BYTES + bx * a.rows_per_box * 128, &a.tm_x, c0, (int)(q0 + (long long)bx * a.rows_per_box), afull(ab));
+                    for (int t = 0; t < a.ntaps; ++t, ++ib) {
+                        const int s = ib % kBStages;
+                        if (ib >= kBStages) mbar_wait(bempty(s), (uint32_t)((ib / kBStages - 1) & 1));
+                        mbar_expect_tx(bfull(s), b_bytes);
+                        const uint32_t dst = wbase + s * WB_BYTES;
+                        if (!a.b_mn_major) {
+                            tma_load_2d(dst, &a.tm_w, c0, (int)a.wtap[t] * J + j0, bfull(s));
+                        } else {
+                            for (int jb = 0; jb * 64 < BN; ++jb)
+                                tma_load_2d(dst + jb * 8192, &a.tm_w, j0 + jb * 64, (int)a.wtap[t] * C + c0, bfull(s));
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ================================ MMA issuer ================================
+        if (lane == 0) {
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a.b_mn_major << 16) | ((uint32_t)(BN >> 3) << 17) |
+                                   ((uint32_t)(WBM >> 4) << 24);
+            int ia = 0, ib = 0, li = 0;
+            for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
+                const int acc = li & 1, v = li >> 1;
+                if (v >= 1) mbar_wait(tempty(acc), (uint32_t)((v - 1) & 1));
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * 256;
+                for (int cc = 0; cc < a.cpb; ++cc, ++ia) {
+                    const int nk16 = min(64, C - cc * 64) >> 4;
+                    const int ab = ia & 1;
+                    mbar_wait(afull(ab), (uint32_t)((ia >> 1) & 1));
+                    tc_fence_after();
+                    const uint32_t win = base + ab * WIN_BYTES;
+                    for (int t = 0; t < a.ntaps; ++t, ++ib) {
+                        const int s = ib % kBStages;
+                        mbar_wait(bfull(s), (uint32_t)((ib / kBStages) & 1));
+                        tc_fence_after();
+                        const uint32_t sa = win + (uint32_t)a.shift[t] * 128u;
+                        const uint32_t boff = a.base_off_mode ? ((sa >> 7) & 7u) : 0u;
+                        const uint32_t sb = wbase + s * WB_BYTES;
+                        for (int k16 = 0; k16 < nk16; ++k16) {
+                            const uint64_t ad = make_desc(sa + k16 * 32, 16, 1024, boff);
+                            const uint64_t bd = a.b_mn_major ? make_desc(sb + k16 * 2048, 8192, 1024, 0) : make_desc(sb + k16 * 32, 16, 1024, 0);
+                            umma_bf16(d_tmem, ad, bd, idesc, (cc > 0 || t > 0 || k16 > 0) ? 1u : 0u);
+                        }
+                        umma_commit(bempty(s));
+                    }
+                    umma_commit(aempty(ab));
+                }
+                umma_commit(tfull(acc));
+            }
+        }
+        __syncwarp();
+    } else {
+        // ================================ epilogue ================================
+        const int quarter = warp & 3, row = quarter * 32 + lane;
+        const long long plane = (long long)a.Hp * a.Wp;
+        int li = 0;
+        for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
+            const int nt = (int)(w % a.n_tiles);
+            const long long mt = w / a.n_tiles;
+            const int acc = li & 1, v = li >> 1;
+            const long long q = mt * WBM + row;
+            const int n = (int)(q / plane);
+            const int rem = (int)(q - (long long)n * plane);
+            const int y = rem / a.Wp, x = rem - y * a.Wp;
+            const bool rok = q < a.Q && y < a.OH && x < a.OW;
+            const int c_begin = nt * BN, c_count = min(BN, J - c_begin);
+            const long long obase = (((long long)n * a.OH + y) * a.OW + x) * J + c_begin;
+            mbar_wait(tfull(acc), (uint32_t)(v & 1));
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * 256;
+            for (int c = 0; c < BN; c += 16) {
+                uint32_t r[16];
+                tmem_ld16(taddr + c, r);
+                tmem_ld_wait();
+                if (!rok || c >= c_count) continue;
+                float f[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(r[i]);
+                if (a.bias) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (c + i < c_count) f[i] += __ldg(a.bias + c_begin + c + i);
+                }
+                const bool fullv = c + 16 <= c_count;
+                if (a.out_bf16) {
+                    __nv_bfloat16* o = (__nv_bfloat16*)a.out + obase + c;
+                    if (fullv && (((uintptr_t)o) & 15) == 0) {
+                        uint32_t pk[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+                            pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                        }
+                        reinterpret_cast<uint4*>(o)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                        reinterpret_cast<uint4*>(o)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            if (c + i < c_count) o[i] = __float2bfloat16_rn(f[i]);
+                    }
+                } else {
+                    float* o = (float*)a.out + obase + c;
+                    if (fullv && (((uintptr_t)o) & 15) == 0) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            reinterpret_cast<float4*>(o)[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            if (c + i < c_count) o[i] = f[i];
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(tempty(acc));
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+    }
+}
+
+// zero / reflection padding written once: xp[n, y, x, :] = x[n, map(y - pt), map(x - pl), :]
+template <typename T>
+__global__ void pad_nhwc_kernel(const T* __restrict__ x, T* __restrict__ xp, int N, int H, int W, int C8, int pt, int pl,
+                                int Hp, int Wp, int reflect) {
+    // C8 = 16-byte vectors per pixel
+    const long long total = (long long)N * Hp * Wp * C8;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C8);
+        long long p = i / C8;
+        const int xx = (int)(p % Wp);
+        p /= Wp;
+        const int yy = (int)(p % Hp);
+        const int n = (int)(p / Hp);
+        int sy = yy - pt, sx = xx - pl;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (reflect) {
+            sy = sy < 0 ? -sy : (sy >= H ? 2 * (H - 1) - sy : sy);
+            sx = sx < 0 ? -sx : (sx >= W ? 2 * (W - 1) - sx : sx);
+        }
+        if (sy >= 0 && sy < H && sx >= 0 && sx < W)
+            v = reinterpret_cast<const uint4*>(x)[(((long long)n * H + sy) * W + sx) * C8 + c];
+        reinterpret_cast<uint4*>(xp)[i] = v;
+    }
+}
+
+typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                             const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                             CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int encode_2d(CUtensorMap* tm, const void* ptr, unsigned long long inner, unsigned long long rows, unsigned box_inner,
+              unsigned box_rows) {
+    cuuint64_t dims[2] = {inner, rows};
+    cuuint64_t strides[1] = {inner * 2};            // bytes, bf16
+    cuuint32_t box[2] = {box_inner, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = cuTensorMapEncodeTiled(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(P2P_ECUDA, "cuTensorMapEncodeTiled failed (%d): inner %llu rows %llu box %u x %u", (int)r, inner, rows, box_inner, box_rows);
+    return P2P_OK;
+}
+
+int g_window_base_off_mode = 0;     // measured on B200: shifted starts need base_offset 0 (absolute-address swizzle)
+
+}  // namespace
+void note_umma_launch();
+}  // namespace p2p
+
+extern "C" int p2p_conv_window_base_off_mode(int mode) {
+    const int old = p2p::g_window_base_off_mode;
+    if (mode >= 0) p2p::g_window_base_off_mode = mode;
+    return old;
+}
+
+extern "C" int p2p_pad_nhwc(const void* x, void* xp, int N, int H, int W, int C, int pt, int pb, int pl, int pr, int reflect,
+                            int dtype, void* stream) {
+    using namespace p2p;
+    if (!x || !xp) return fail(P2P_EINVAL, "null pointer argument");
+    const int esz = dtype == P2P_BF16 ? 2 : 4;
+    if ((C * esz) % 16 != 0) return fail(P2P_ENOTSUP, "p2p_pad_nhwc needs whole 16-byte vectors per pixel (C * %d bytes)", esz);
+    if (reflect && (pt >= H || pb >= H || pl >= W || pr >= W)) return fail(P2P_EINVAL, "reflection padding must be smaller than the input");
+    if (N < 1 || H < 1 || W < 1 || pt < 0 || pb < 0 || pl < 0 || pr < 0) return fail(P2P_EINVAL, "bad padding geometry");
+    const int Hp = H + pt + pb, Wp = W + pl + pr, C8 = C * esz / 16;
+    const long long total = (long long)N * Hp * Wp * C8;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148LL * 32) blocks = 148LL * 32;
+    pad_nhwc_kernel<uint4><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)xp, N, H, W, C8, pt, pl, Hp, Wp, reflect);
+    return check_launch("pad_nhwc_kernel");
+}
+
+// out[n,y,x,j] (+bias) = sum_{dh<KH, dw<KW} sum_c xp[n, y+dh, x+dw, c] * Wt[c, j],  y < OH = Hp-KH+1, x < OW = Wp-KW+1.
+// weight tap index = flip ? (KH-1-dh)*KW + (KW-1-dw) : dh*KW + dw; element (tap, c, j) at tap*w_tap + c*w_k + j*w_j with
+// either w_k == 1 (K-major) or w_j == 1 (MN-major, the transposed read used for input gradients).
+extern "C" int p2p_conv_window(const void* xp, const void* weight, const float* bias, void* out, int N, int Hp, int Wp, int C,
+                               int J, int KH, int KW, int flip, long long w_tap, long long w_k, long long w_j, int out_dtype,
+                               void* stream) {
+    using namespace p2p;
+    if (!xp || !weight || !out) return fail(P2P_EINVAL, "null pointer argument");
+    if (KH < 1 || KW < 1 || KH * KW > P2P_MAX_TAPS || Hp < KH || Wp < KW) return fail(P2P_EINVAL, "bad window geometry");
+    if (C % 16 != 0) return fail(P2P_ENOTSUP, "window convolution needs C %% 16 == 0, got %d", C);
+    WindowArgs a;
+    a.N = N; a.Hp = Hp; a.Wp = Wp; a.OH = Hp - KH + 1; a.OW = Wp - KW + 1; a.C = C; a.J = J;
+    a.ntaps = KH * KW;
+    a.Q = (long long)N * Hp * Wp;
+    const int halo = (KH - 1) * Wp + (KW - 1);
+    a.win_rows = WBM + halo;
+    if (a.win_rows > kWinRowsMax) return fail(P2P_ENOTSUP, "window of %d rows exceeds the %d-row buffer", a.win_rows, kWinRowsMax);
+    a.nboxes = (a.win_rows + 255) / 256;
+    a.rows_per_box = (a.win_rows + a.nboxes - 1) / a.nboxes;
+    a.rows_per_box = (a.rows_per_box + 7) / 8 * 8;          // keeps every box 1024-byte aligned
+    if (a.nboxes * a.rows_per_box > kWinRowsMax) return fail(P2P_ENOTSUP, "window boxes exceed the buffer");
+    if (w_k == 1 && w_j % 8 == 0 && w_tap % 8 == 0) a.b_mn_major = 0;
+    else if (w_j == 1 && w_k % 8 == 0 && w_tap % 8 == 0 && J % 8 == 0) a.b_mn_major = 1;
+    else return fail(P2P_ENOTSUP, "weight strides not 16-byte friendly");
+    if (a.b_mn_major ? (w_tap != (long long)C * w_k) : (w_tap != (long long)J * w_j))
+        return fail(P2P_ENOTSUP, "weights must be densely packed per tap");
+    for (int dh = 0; dh < KH; ++dh)
+        for (int dw = 0; dw < KW; ++dw) {
+            const int t = dh * KW + dw;
+            a.shift[t] = (short)(dh * Wp + dw);
+            a.wtap[t] = (unsigned char)(flip ? (KH - 1 - dh) * KW + (KW - 1 - dw) : t);
+        }
+    a.bias = bias;
+    a.out = out;
+    a.out_bf16 = out_dtype == P2P_BF16;
+    a.cpb = (C + 63) / 64;
+    a.base_off_mode = g_window_base_off_mode;
+    // column tile: whole J when it fits 256 columns, else balanced multiples of 16 (MN-major: of 64)
+    {
+        const int nt = (J + 255) / 256;
+        int bn = ((J + nt - 1) / nt + 15) / 16 * 16;
+        if (a.b_mn_major) bn = (bn + 63) / 64 * 64 > 256 ? 256 : (bn + 15) / 16 * 16;
+        a.BN = bn < 16 ? 16 : bn;
+    }
+    a.n_tiles = (J + a.BN - 1) / a.BN;
+    const long long mt = (a.Q + WBM - 1) / WBM;
+    if (mt > 2000000000LL / a.n_tiles) return fail(P2P_ENOTSUP, "too many tiles");
+    a.m_tiles = (int)mt;
+    a.nwork = mt * a.n_tiles;
+    if (int rc = encode_2d(&a.tm_x, xp, (unsigned long long)C, (unsigned long long)a.Q, 64, (unsigned)a.rows_per_box)) return rc;
+    if (!a.b_mn_major) {
+        if (int rc = encode_2d(&a.tm_w, weight, (unsigned long long)C, (unsigned long long)a.ntaps * J, 64, (unsigned)a.BN)) return rc;
+    } else {
+        if (int rc = encode_2d(&a.tm_w, weight, (unsigned long long)J, (unsigned long long)a.ntaps * C, 64, 64)) return rc;
+    }
+    static bool configured = false;
+    if (!configured) {
+        if (cudaFuncSetAttribute(conv_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WSMEM) != cudaSuccess)
+            return check_launch("cudaFuncSetAttribute(conv_window_kernel)");
+        configured = true;
+    }
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long long grid = a.nwork < sms ? a.nwork : sms;
+    conv_window_kernel<<<(unsigned)grid, kWThreads, WSMEM, (cudaStream_t)stream>>>(a);
+    note_umma_launch();
+    return check_launch("conv_window_kernel");
+}

@@ -260,6 +260,28 @@ __global__ void adam_kernel(float* __restrict__ w, const float* __restrict__ g, 
     }
 }
 
+// device-resident step counter and learning rate: the whole optimisation step can live in one CUDA graph
+__global__ void adam_prepare_kernel(int* step, const float* lr, float beta1, float beta2, float* scratch) {
+    const int t = ++(*step);
+    scratch[0] = (float)((double)lr[0] / (1.0 - pow((double)beta1, (double)t)));
+    scratch[1] = (float)(1.0 / sqrt(1.0 - pow((double)beta2, (double)t)));
+}
+
+__global__ void adam_dev_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                                __nv_bfloat16* __restrict__ wb, long long n, const float* __restrict__ scratch, float beta1,
+                                float beta2, float eps, float gscale) {
+    const float step_size = scratch[0], inv_bc2_sqrt = scratch[1];
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float gi = g[i] * gscale;
+        const float mi = beta1 * m[i] + (1.f - beta1) * gi;
+        const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+        m[i] = mi; v[i] = vi;
+        const float wi = w[i] - step_size * mi / (sqrtf(vi) * inv_bc2_sqrt + eps);
+        w[i] = wi;
+        if (wb) wb[i] = __float2bfloat16_rn(wi);
+    }
+}
+
 inline int ew_grid(long long n) {
     long long b = (n + kEw - 1) / kEw;
     const long long cap = 148LL * 16;
@@ -388,6 +410,17 @@ extern "C" int p2p_loss_l1(const void* a, const void* b, float weight, float* lo
     const int grid = ew_grid(n) > 592 ? 592 : ew_grid(n);
     P2P_DISPATCH_DTYPE(dtype, T, l1_kernel<T><<<grid, kEw, 0, (cudaStream_t)stream>>>((const T*)a, (const T*)b, weight, loss, (T*)da, gcoef, gscale_dev, n));
     return check_launch("loss_l1");
+}
+
+extern "C" int p2p_adam_step_dev(float* w, const float* g, float* m, float* v, void* w_bf16, long long n,
+                                 const float* lr_dev, float beta1, float beta2, float eps, float grad_scale, int* step_dev,
+                                 float* scratch2, void* stream) {
+    if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
+    if (!w || !g || !m || !v || !lr_dev || !step_dev || !scratch2) return fail(P2P_EINVAL, "null pointer argument");
+    adam_prepare_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_dev, lr_dev, beta1, beta2, scratch2);
+    adam_dev_kernel<<<ew_grid(n), kEw, 0, (cudaStream_t)stream>>>(w, g, m, v, (__nv_bfloat16*)w_bf16, n, scratch2, beta1, beta2,
+                                                                   eps, grad_scale);
+    return check_launch("adam_step_dev");
 }
 
 extern "C" int p2p_adam_step(float* w, const float* g, float* m, float* v, void* w_bf16, long long n, float lr,

@@ -130,7 +130,7 @@ def stop_conv_timing():
     return [(kind, umma, flops, e0.elapsed_time(e1), shape) for kind, umma, flops, e0, e1, shape in rec]
 
 
-def _timed(kind, P, launch):
+def _timed(kind, P, launch, umma=None):
     if _TIMING is None:
         launch()
         return
@@ -142,7 +142,7 @@ def _timed(kind, P, launch):
     e1.record()
     flops = 2.0 * P.N * P.gy * P.gx * P.J * P.ntaps * P.K
     shape = dict(M=P.N * P.gy * P.gx, J=P.J, K=P.K, taps=P.ntaps, H=P.H, W=P.W, s=P.sy, os=P.oys)
-    _TIMING.append((kind, lib.p2p_conv_umma_launches() > n0, flops, e0, e1, shape))
+    _TIMING.append((kind + ("-window" if umma else ""), bool(umma) or lib.p2p_conv_umma_launches() > n0, flops, e0, e1, shape))
 
 
 def _run_wgrad(P, x, dout, dw):
@@ -227,6 +227,46 @@ def _pad_weight(wq, Cout_p, Cin_p):
     return out
 
 
+# ---- stride-1 layers: TMA-fed shifted-window kernel (csrc/conv_window.cu) ------------------------------------------
+USE_WINDOW = True
+_WIN_ROWS_MAX = 320
+
+
+class _Shape:
+    """what _timed needs to count FLOPs for a window launch"""
+
+    def __init__(self, N, OH, OW, J, taps, K, H, W):
+        self.N, self.gy, self.gx, self.J, self.ntaps, self.K, self.H, self.W = N, OH, OW, J, taps, K, H, W
+        self.sy = self.oys = 1
+
+
+def _window_ok(dtype, C, J, KH, KW, Hp, Wp, mn_major):
+    if not USE_WINDOW or dtype != torch.bfloat16 or _lib.lib().p2p_conv_force_simple(-1) == 1:
+        return False
+    if C % 16 != 0 or (mn_major and J % 8 != 0) or Hp < KH or Wp < KW:
+        return False
+    if 128 + (KH - 1) * Wp + (KW - 1) > _WIN_ROWS_MAX:
+        return False
+    return (Hp - KH + 1) * (Wp - KW + 1) >= 0.7 * Hp * Wp        # rows in the padding margin are computed and dropped
+
+
+def pad_nhwc(x, pt, pb, pl, pr, reflect):
+    N, H, W, C = x.shape
+    xp = torch.empty((N, H + pt + pb, W + pl + pr, C), dtype=x.dtype, device=x.device)
+    _lib.check(_lib.lib().p2p_pad_nhwc(_p(x), _p(xp), N, H, W, C, pt, pb, pl, pr, int(reflect), _DT[x.dtype], _stream()))
+    return xp
+
+
+def conv_window(xp, wq, bias, out_dtype, KH, KW, J, flip, w_tap, w_k, w_j, kind):
+    N, Hp, Wp, C = xp.shape
+    OH, OW = Hp - KH + 1, Wp - KW + 1
+    out = torch.empty((N, OH, OW, J), dtype=out_dtype, device=xp.device)
+    _timed(kind, _Shape(N, OH, OW, J, KH * KW, C, Hp, Wp),
+           lambda: _lib.check(_lib.lib().p2p_conv_window(_p(xp), _p(wq), _p(bias), _p(out), N, Hp, Wp, C, J, KH, KW, int(flip),
+                                                         w_tap, w_k, w_j, _DT[out_dtype], _stream())), umma=True)
+    return out
+
+
 def conv_forward(x, weight, bias, w16, cfg, out_dtype):
     """nn.Conv2d (+ nn.ReflectionPad2d) / nn.ConvTranspose2d forward, NHWC (networks.py:145-154, 190-207, 223-246, 340-361)"""
     N, H, W, Cx = x.shape
@@ -244,6 +284,10 @@ def conv_forward(x, weight, bias, w16, cfg, out_dtype):
     else:
         if cfg.pad_mode == PAD_REFLECT and (cfg.pad >= H or cfg.pad >= W):
             raise RuntimeError("reflection padding must be smaller than the input")   # what ReflectionPad2d raises
+        p = cfg.pad
+        if cfg.stride == 1 and _window_ok(x.dtype, Cin, Cout, KH, KW, H + 2 * p, W + 2 * p, False):
+            xp = pad_nhwc(x, p, p, p, p, cfg.pad_mode == PAD_REFLECT) if p else x
+            return conv_window(xp, wq, bias, out_dtype, KH, KW, Jout, False, Cout * Cin, 1, Cin, "fwd")
         passes = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
         OH, OW = passes[0].OH, passes[0].OW
     y = torch.empty((N, OH, OW, Jout), dtype=out_dtype, device=x.device)
@@ -273,10 +317,18 @@ def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
             dx = torch.empty_like(x)
             _run_pass(convT_dgrad_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0], dy, wq, None, dx, "dgrad")
         else:
-            passes, (DH, DW) = conv_dgrad_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
-            if passes is None:
-                raise NotImplementedError("input gradient of a convolution whose stride skips whole parity classes")
-            buf = torch.empty((N, DH, DW, Cin), dtype=x.dtype, device=x.device)
+            q = (KH - 1) if cfg.pad_mode == PAD_REFLECT else (KH - 1 - cfg.pad)      # zero margin around dy
+            OHd, OWd = dy.shape[1], dy.shape[2]
+            if (cfg.stride == 1 and KH == KW and q >= 0
+                    and _window_ok(x.dtype, Cout, Cin, KH, KW, OHd + 2 * q, OWd + 2 * q, True)):
+                dyp = pad_nhwc(dy, q, q, q, q, False) if q else dy
+                buf = conv_window(dyp, wq, None, x.dtype, KH, KW, Cin, True, Cout * Cin, Cin, 1, "dgrad")
+                passes = []
+            else:
+                passes, (DH, DW) = conv_dgrad_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
+                if passes is None:
+                    raise NotImplementedError("input gradient of a convolution whose stride skips whole parity classes")
+                buf = torch.empty((N, DH, DW, Cin), dtype=x.dtype, device=x.device)
             for P in passes:
                 _run_pass(P, dy, wq, None, buf, "dgrad")
             if cfg.pad_mode == PAD_REFLECT and cfg.pad > 0:
@@ -469,3 +521,11 @@ def adam_step(w, g, m, v, w16, lr, beta1, beta2, eps, step):
     _need_cuda(w, g, m, v)
     assert w.is_contiguous() and g.is_contiguous() and w.dtype == torch.float32 and g.dtype == torch.float32
     _lib.check(_lib.lib().p2p_adam_step(_p(w), _p(g), _p(m), _p(v), _p(w16), w.numel(), lr, beta1, beta2, eps, step, _stream()))
+
+
+def adam_step_dev(w, g, m, v, w16, lr_dev, beta1, beta2, eps, grad_scale, step_dev, scratch):
+    """Adam with the step counter / learning rate on the device (CUDA-graph friendly)"""
+    _need_cuda(w, g, m, v, lr_dev, step_dev, scratch)
+    assert w.is_contiguous() and g.is_contiguous() and w.dtype == torch.float32 and g.dtype == torch.float32
+    _lib.check(_lib.lib().p2p_adam_step_dev(_p(w), _p(g), _p(m), _p(v), _p(w16), w.numel(), _p(lr_dev), beta1, beta2, eps,
+                                            grad_scale, _p(step_dev), _p(scratch), _stream()))

@@ -29,6 +29,11 @@ class FusedAdam:
         self.exp_avg_sq = torch.zeros(total, dtype=torch.float32, device=dev)
         self.flat_bf16 = torch.zeros(total, dtype=torch.bfloat16, device=dev)
         self.step_count = 0
+        self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)      # the authoritative step counter
+        self.lr_dev = torch.full((1,), float(lr), dtype=torch.float32, device=dev)
+        self._lr_on_dev = float(lr)
+        self._scratch = torch.zeros(2, dtype=torch.float32, device=dev)
+        self.grad_scale = 1.0                                              # 1 / world size under data parallelism
         self._views = []
         o = 0
         for p, sz in zip(params, sizes):
@@ -59,19 +64,29 @@ class FusedAdam:
             if p.grad is not g:
                 p.grad = g
 
+    def sync_lr(self):
+        """push param_groups[0]['lr'] to the device (call after changing it; never inside a graph capture)"""
+        lr = float(self.param_groups[0]["lr"])
+        if lr != self._lr_on_dev:
+            self.lr_dev.fill_(lr)
+            self._lr_on_dev = lr
+
     @torch.no_grad()
     def step(self):
-        self.step_count += 1
         g = self.param_groups[0]
-        ops.adam_step(self.flat, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.flat_bf16, g["lr"], g["betas"][0],
-                      g["betas"][1], g["eps"], self.step_count)
+        if not torch.cuda.is_current_stream_capturing():
+            self.sync_lr()
+        self.step_count += 1
+        ops.adam_step_dev(self.flat, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.flat_bf16, self.lr_dev,
+                          g["betas"][0], g["betas"][1], g["eps"], self.grad_scale, self.step_dev, self._scratch)
 
     def state_dict(self):
-        return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq,
+        return {"step": int(self.step_dev.item()), "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq,
                 "param_groups": [{k: v for k, v in self.param_groups[0].items() if k != "params"}]}
 
     def load_state_dict(self, sd):
         self.step_count = int(sd["step"])
+        self.step_dev.fill_(self.step_count)
         self.exp_avg.copy_(sd["exp_avg"])
         self.exp_avg_sq.copy_(sd["exp_avg_sq"])
         self.param_groups[0].update(sd["param_groups"][0])

@@ -40,7 +40,7 @@ class GradSync:
         if handle is None:
             return
         handle.wait()                           # orders the current stream after the collective
-        optimizer.flat_grad.mul_(1.0 / self.world)
+        optimizer.grad_scale = 1.0 / self.world     # the averaging is folded into the Adam kernel's gradient read
 
 
 def broadcast_parameters(model, src=0, group=None):
@@ -70,3 +70,36 @@ def train_step(model, lr_audio, hr_audio, inst=None, feat=None, infer=False, syn
         sync.finish(opt_D, h_D)
     opt_D.step()
     return {k: (v.detach() if torch.is_tensor(v) else v) for k, v in loss_dict.items()}, generated
+
+
+class GraphedTrainStep:
+    """The whole optimisation step (MDCT4 -> encode -> G -> 3 x D -> losses -> 2 backward passes -> gradient
+    all-reduce -> 2 Adam steps) captured once into a CUDA graph and replayed: ~1500 kernel launches per step become
+    one graph launch, so the step is bounded by the device, not by Python / launch latency.  Inputs are copied into
+    static device buffers; the loss values of the last replay are in `self.losses` (device tensors)."""
+
+    def __init__(self, model, lr_audio, hr_audio, sync=None, warmup=3):
+        self.model, self.sync = model, sync
+        dev = torch.device(model.device)
+        self.lr_static = lr_audio.to(dev).clone()
+        self.hr_static = hr_audio.to(dev).clone()
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(warmup):             # allocator warm-up, cudaFuncSetAttribute calls, NCCL channel set-up
+                train_step(model, self.lr_static, self.hr_static, sync=sync)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        for opt in (model.optimizer_G, model.optimizer_D):
+            opt.sync_lr()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.losses, _ = train_step(model, self.lr_static, self.hr_static, sync=sync)
+
+    def __call__(self, lr_audio, hr_audio):
+        if lr_audio.data_ptr() != self.lr_static.data_ptr():
+            self.lr_static.copy_(lr_audio, non_blocking=True)
+        if hr_audio.data_ptr() != self.hr_static.data_ptr():
+            self.hr_static.copy_(hr_audio, non_blocking=True)
+        self.graph.replay()
+        return self.losses, None

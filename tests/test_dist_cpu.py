@@ -1,0 +1,57 @@
+"""The N>1 host logic on CPU: two `gloo` processes run the gradient exchange of pix2pixhdaudiosr_b200/train.py
+(GradSync / broadcast_parameters) on stand-in flat buffers and must end with identical, averaged gradients and
+identical parameters -- what each data-parallel replica feeds its fused Adam step with."""
+import os
+import socket
+import types
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from pix2pixhdaudiosr_b200.train import GradSync, broadcast_parameters
+    torch.manual_seed(rank)
+    mk = lambda n: types.SimpleNamespace(flat=torch.randn(n), flat_bf16=torch.zeros(n, dtype=torch.bfloat16),
+                                         flat_grad=torch.randn(n), grad_scale=1.0)
+    model = types.SimpleNamespace(optimizer_G=mk(1003), optimizer_D=mk(77))
+    local_grads = [model.optimizer_G.flat_grad.clone(), model.optimizer_D.flat_grad.clone()]
+    broadcast_parameters(model)
+    sync = GradSync()
+    assert sync.enabled and sync.world == world
+    hG = sync.start(model.optimizer_G)
+    hD = sync.start(model.optimizer_D)           # both collectives in flight, as in train_step
+    sync.finish(model.optimizer_G, hG)
+    sync.finish(model.optimizer_D, hD)
+    out[rank] = dict(wG=model.optimizer_G.flat.clone(), w16=model.optimizer_G.flat_bf16.clone(),
+                     gG=model.optimizer_G.flat_grad * model.optimizer_G.grad_scale,
+                     gD=model.optimizer_D.flat_grad * model.optimizer_D.grad_scale, local=local_grads)
+    dist.destroy_process_group()
+
+
+def test_two_rank_gradient_average_and_parameter_broadcast():
+    world = 2
+    out = mp.Manager().dict()
+    mp.spawn(_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    a, b = out[0], out[1]
+    assert torch.equal(a["wG"], b["wG"])                                   # replicas start identical (rank 0's)
+    assert torch.equal(a["w16"], a["wG"].to(torch.bfloat16))               # bf16 shadow refreshed from the master copy
+    for k, i in (("gG", 0), ("gD", 1)):
+        want = (a["local"][i] + b["local"][i]) / world
+        assert torch.allclose(a[k], want, atol=1e-6) and torch.equal(a[k], b[k])
+
+
+def test_single_process_sync_is_a_no_op():
+    from pix2pixhdaudiosr_b200.train import GradSync
+    s = GradSync()
+    assert not s.enabled and s.start(None) is None
+    s.finish(None, None)
