@@ -115,6 +115,7 @@ def convT_dgrad_passes(N, H, W, Cin, Cout, KH, KW, stride, pad, out_pad):
 # ---------------------------------------------------------------------------------------------------
 # optional per-launch CUDA-event timing of the convolution passes (bench.py's roofline leg; off by default)
 _TIMING = None
+_FLOP_RATIO = 1.0     # algorithmic / launched FLOPs of the launches being recorded (channel-padded or packed thin layers)
 
 
 def start_conv_timing():
@@ -140,7 +141,7 @@ def _timed(kind, P, launch, umma=None):
     e0.record()
     launch()
     e1.record()
-    flops = 2.0 * P.N * P.gy * P.gx * P.J * P.ntaps * P.K
+    flops = 2.0 * P.N * P.gy * P.gx * P.J * P.ntaps * P.K * _FLOP_RATIO
     shape = dict(M=P.N * P.gy * P.gx, J=P.J, K=P.K, taps=P.ntaps, H=P.H, W=P.W, s=P.sy, os=P.oys)
     _TIMING.append((kind + ("-window" if umma else ""), bool(umma) or lib.p2p_conv_umma_launches() > n0, flops, e0, e1, shape))
 
@@ -267,13 +268,141 @@ def conv_window(xp, wq, bias, out_dtype, KH, KW, J, flip, w_tap, w_k, w_j, kind)
     return out
 
 
-def conv_forward(x, weight, bias, w16, cfg, out_dtype):
+# ---- thin layers (2-4 channels on one side): fold the kernel's columns into the channel dimension ---------------------
+# A KHxKW convolution whose thin side has c channels with KW*c <= 16 becomes a KHx1 convolution on a tensor with
+# (dw, c) packed into <= 16 channels: KW x fewer taps, no zero-padded channels multiplied on the tensor cores.
+#   thin input  (G's 7x7 2->ngf layers, D's 4x4 s2 4->ndf layer):   x_pack[n, y, ox, (dw,c)] = x_pad[n, y, ox*s + dw, c]
+#   thin output (G's 7x7 ngf->2 layer, D's 4x4 ->1 logit layer):    out_pack[n, y, x', (dw,co)], summed over dw afterwards
+def _packable(x, cfg, Cin, Cout, KH, KW):
+    if x.dtype != torch.bfloat16 or cfg.transposed or _lib.lib().p2p_conv_force_simple(-1) == 1:
+        return None
+    if Cin % 16 != 0 and Cin * KW <= 16 and Cout % 16 == 0:
+        return "in"
+    if Cout % 16 != 0 and Cout * KW <= 16 and Cin % 16 == 0 and cfg.stride == 1:
+        return "out"
+    return None
+
+
+def _pad_hw(x, p, reflect):
+    """[N,H,W,C] -> [N,H+2p,W+2p,C] for any channel count (torch data movement; p2p_pad_nhwc needs 16-byte pixels)"""
+    if p == 0:
+        return x
+    N, H, W, C = x.shape
+    if (C * x.element_size()) % 16 == 0:
+        return pad_nhwc(x, p, p, p, p, reflect)
+    xc = x.permute(0, 3, 1, 2)
+    xc = torch.nn.functional.pad(xc.float(), (p, p, p, p), mode="reflect" if reflect else "constant").to(x.dtype)
+    return xc.permute(0, 2, 3, 1).contiguous()
+
+
+def _packed_in_operands(x, wq, cfg, Cin, Cout, KH, KW):
+    N, H, W, _ = x.shape
+    s, p = cfg.stride, cfg.pad
+    xp = _pad_hw(x, p, cfg.pad_mode == PAD_REFLECT)
+    Hp, Wp = xp.shape[1], xp.shape[2]
+    OH, OW = (Hp - KH) // s + 1, (Wp - KW) // s + 1
+    xpk = _pad_last(torch.cat([xp[:, :, dw: dw + (OW - 1) * s + 1: s, :] for dw in range(KW)], dim=-1), 16)
+    P = _make_pass(N, Hp, OW, 16, OH, OW, Cout, OH, OW, s, 1, 1, 0, 1, 0, [(dh, 0, dh) for dh in range(KH)], PAD_ZERO,
+                   Cout * 16, 1, 16)
+    wpk = None
+    if wq is not None:      # [KH][KW][Cout][Cin] -> [KH][Cout][(dw, c) padded to 16]
+        wpk = _pad_last(wq.permute(0, 2, 1, 3).reshape(KH, Cout, KW * Cin), 16).contiguous()
+    return xpk, wpk, P, (OH, OW)
+
+
+def _packed_out_geometry(x, cfg, Cin, Cout, KH, KW):
+    N, H, W, _ = x.shape
+    p = cfg.pad
+    Hp, Wp = H + 2 * p, W + 2 * p
+    OH, OW = Hp - KH + 1, Wp - KW + 1
+    # forward / wgrad pass: rows (y, x') over [OH, Wp], gather xp[y + dh, x'], 16 packed output channels
+    P = _make_pass(N, Hp, Wp, Cin, OH, Wp, 16, OH, Wp, 1, 1, 1, 0, 1, 0, [(dh, 0, dh) for dh in range(KH)], PAD_ZERO,
+                   16 * Cin, 1, Cin)
+    return P, (Hp, Wp, OH, OW)
+
+
+def _pack_out_weight(wq, KH, KW, Cout, Cin):
+    return _pad_rows(wq.reshape(KH, KW * Cout, Cin), 16)
+
+
+def _pad_rows(t, r):
+    if t.shape[1] == r:
+        return t.contiguous()
+    out = torch.zeros((t.shape[0], r, t.shape[2]), dtype=t.dtype, device=t.device)
+    out[:, :t.shape[1]] = t
+    return out
+
+
+def _pack_dy(dy, KW, Cout, Wp):
+    """dy [N,OH,OW,Cout] -> dy_pack[n, y, x', (dw,co)] = dy[n, y, x' - dw, co]"""
+    N, OH, OW, _ = dy.shape
+    out = torch.zeros((N, OH, Wp, 16), dtype=dy.dtype, device=dy.device)
+    for dw in range(KW):
+        out[:, :, dw: dw + OW, dw * Cout: (dw + 1) * Cout] = dy
+    return out
+
+
+def _packed_forward(kind, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype):
+    if kind == "in":
+        xpk, wpk, P, (OH, OW) = _packed_in_operands(x, wq, cfg, Cin, Cout, KH, KW)
+        y = torch.empty((x.shape[0], OH, OW, Cout), dtype=out_dtype, device=x.device)
+        _run_pass(P, xpk, wpk, bias, y)
+        return y
+    P, (Hp, Wp, OH, OW) = _packed_out_geometry(x, cfg, Cin, Cout, KH, KW)
+    xp = _pad_hw(x, cfg.pad, cfg.pad_mode == PAD_REFLECT)
+    ypk = torch.empty((x.shape[0], OH, Wp, 16), dtype=torch.float32, device=x.device)
+    _run_pass(P, xp, _pack_out_weight(wq, KH, KW, Cout, Cin), None, ypk)
+    y = ypk[:, :, 0:OW, 0:Cout]
+    for dw in range(1, KW):
+        y = y + ypk[:, :, dw: dw + OW, dw * Cout: (dw + 1) * Cout]
+    if bias is not None:
+        y = y + bias
+    return y.to(out_dtype).contiguous()
+
+
+def _packed_backward(kind, x, wq, dy, cfg, Cin, Cout, KH, KW, need_dx, need_dw):
+    """-> (dx or None, dW physical [KH][KW][Cout][Cin] fp32 or None); dx only for the thin-output kind"""
+    N, H, W, _ = x.shape
+    dx = dwp = None
+    if kind == "in":
+        if need_dw:
+            xpk, _, P, _ = _packed_in_operands(x, None, cfg, Cin, Cout, KH, KW)
+            dwk = torch.zeros((KH, Cout, 16), dtype=torch.float32, device=x.device)
+            _run_wgrad(P, xpk, dy, dwk)
+            dwp = dwk[:, :, :KW * Cin].reshape(KH, Cout, KW, Cin).permute(0, 2, 1, 3)
+        return None, dwp
+    P, (Hp, Wp, OH, OW) = _packed_out_geometry(x, cfg, Cin, Cout, KH, KW)
+    dypk = _pack_dy(dy, KW, Cout, Wp)
+    if need_dx:
+        wqk = _pack_out_weight(wq, KH, KW, Cout, Cin)
+        Pd = _make_pass(N, OH, Wp, 16, Hp, Wp, Cin, Hp, Wp, 1, 1, 1, 0, 1, 0, [(-dh, 0, dh) for dh in range(KH)], PAD_ZERO,
+                        16 * Cin, Cin, 1)
+        buf = torch.empty((N, Hp, Wp, Cin), dtype=x.dtype, device=x.device)
+        _run_pass(Pd, dypk, wqk, None, buf, "dgrad")
+        p = cfg.pad
+        if cfg.pad_mode == PAD_REFLECT and p > 0:
+            dx = torch.empty_like(x)
+            _lib.check(_lib.lib().p2p_reflect_pad_fold(_p(buf), _p(dx), N, H, W, Cin, p, _DT[x.dtype], _stream()))
+        else:
+            dx = buf[:, p: p + H, p: p + W, :].contiguous() if p else buf
+    if need_dw:
+        xp = _pad_hw(x, cfg.pad, cfg.pad_mode == PAD_REFLECT)
+        dwk = torch.zeros((KH, 16, Cin), dtype=torch.float32, device=x.device)
+        _run_wgrad(P, xp, dypk, dwk)
+        dwp = dwk[:, :KW * Cout].reshape(KH, KW, Cout, Cin)
+    return dx, dwp
+
+
+def _conv_forward(x, weight, bias, w16, cfg, out_dtype):
     """nn.Conv2d (+ nn.ReflectionPad2d) / nn.ConvTranspose2d forward, NHWC (networks.py:145-154, 190-207, 223-246, 340-361)"""
     N, H, W, Cx = x.shape
     wphys, Cout, Cin, KH, KW = _phys(weight, cfg)
     assert Cx == Cin, (Cx, Cin)
     wq = _weight_for(x, wphys, w16)
     Jout = Cout
+    pk = _packable(x, cfg, Cin, Cout, KH, KW)
+    if pk is not None:
+        return _packed_forward(pk, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype)
     thin = _thin(x, Cin, Cout)
     if thin is not None and thin[0] != Cin:             # the forward pass only needs the gathered side padded
         x, wq, Cin = _pad_last(x, thin[0]), _pad_weight(wq, Cout, thin[0]), thin[0]
@@ -296,7 +425,7 @@ def conv_forward(x, weight, bias, w16, cfg, out_dtype):
     return y
 
 
-def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
+def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
     """gradients of conv_forward; dy has x's dtype.  Returns (dx, dw_logical, db)."""
     N, H, W, _ = x.shape
     wphys, Cout, Cin, KH, KW = _phys(weight, cfg)
@@ -304,6 +433,16 @@ def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
     dx = dw = db = None
     if need_db:
         db = _bias_grad(dy, Cout)
+    pk = _packable(x, cfg, Cin, Cout, KH, KW)
+    if pk is not None and (pk == "out" or not need_dx):
+        dx, dwp = _packed_backward(pk, x, _weight_for(x, wphys, w16) if need_dx else None, dy, cfg, Cin, Cout, KH, KW,
+                                   need_dx, need_dw)
+        return dx, (dwp.permute(2, 3, 0, 1) if dwp is not None else None), db
+    pk_dw = pk == "in" and need_dw         # thin-input layer that also needs dx: dW packed, dx through the padded path
+    if pk_dw:
+        _, dwp = _packed_backward(pk, x, None, dy, cfg, Cin, Cout, KH, KW, False, True)
+        dw = dwp.permute(2, 3, 0, 1)
+        need_dw = False
     Cin0, Cout0 = Cin, Cout
     thin = _thin(x, Cin, Cout)
     wq = _weight_for(x, wphys, w16) if (need_dx or thin is not None) else None
@@ -349,6 +488,42 @@ def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
             dwp = dwp[:, :, :Cout0, :Cin0]
         dw = dwp.permute(3, 2, 0, 1) if cfg.transposed else dwp.permute(2, 3, 0, 1)
     return dx, dw, db
+
+
+def _alg_ratio(x, weight, cfg):
+    """algorithmic / launched FLOPs for the thin-layer paths (1 for every other layer)"""
+    _, Cout, Cin, KH, KW = _phys(weight, cfg)
+    if x.dtype != torch.bfloat16 or (Cin % 16 == 0 and Cout % 16 == 0):
+        return 1.0
+    pk = _packable(x, cfg, Cin, Cout, KH, KW)
+    if pk == "in":
+        return KW * Cin / 16.0
+    if pk == "out":
+        W = x.shape[2] + 2 * cfg.pad
+        return (KW * Cout / 16.0) * ((W - KW + 1) / W)
+    return (Cin * Cout) / float(_ceil16(Cin) * _ceil16(Cout))
+
+
+def conv_forward(x, weight, bias, w16, cfg, out_dtype):
+    global _FLOP_RATIO
+    if _TIMING is None:
+        return _conv_forward(x, weight, bias, w16, cfg, out_dtype)
+    _FLOP_RATIO = _alg_ratio(x, weight, cfg)
+    try:
+        return _conv_forward(x, weight, bias, w16, cfg, out_dtype)
+    finally:
+        _FLOP_RATIO = 1.0
+
+
+def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
+    global _FLOP_RATIO
+    if _TIMING is None:
+        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db)
+    _FLOP_RATIO = _alg_ratio(x, weight, cfg)
+    try:
+        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db)
+    finally:
+        _FLOP_RATIO = 1.0
 
 
 def norm_act_forward(y, res, norm, act, slope, eps, out_dtype):
