@@ -235,6 +235,14 @@ def run_train(args):
                                              "oracle/pix2pixhd_oracle.py (torch CPU restatement of networks.py / "
                                              f"pix2pixHD_model.py / train.py) on {threads} threads",
                                    "seconds": round(sec, 2)}
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # A CUDA graph that captured NCCL kernels keeps the communicator busy: destroy_process_group() was seen to hang
+        # after the result was printed.  Drop the graph, line the ranks up, and leave without the collective teardown.
+        step = None
+        torch.cuda.synchronize()
+        dist.barrier()
+        import sys
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
