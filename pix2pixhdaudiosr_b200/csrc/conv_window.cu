@@ -308,8 +308,22 @@ typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void
                              const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                              CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+// libcuda is resolved at run time through the runtime API, so the library still loads on a host without a driver
+EncodeFn encode_fn() {
+    static EncodeFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (EncodeFn)p;
+    }
+    return fn;
+}
+
 int encode_2d(CUtensorMap* tm, const void* ptr, unsigned long long inner, unsigned long long rows, unsigned box_inner,
               unsigned box_rows) {
+    EncodeFn cuTensorMapEncodeTiled = encode_fn();
+    if (!cuTensorMapEncodeTiled) return fail(P2P_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
     cuuint64_t dims[2] = {inner, rows};
     cuuint64_t strides[1] = {inner * 2};            // bytes, bf16
     cuuint32_t box[2] = {box_inner, box_rows};
