@@ -123,6 +123,28 @@ int p2p_pad_nhwc(const void* x, void* xp, int N, int H, int W, int C, int pt, in
                  int dtype, void* stream);
 int p2p_conv_window(const void* xp, const void* weight, const float* bias, void* out, int N, int Hp, int Wp, int C, int J,
                     int KH, int KW, int flip, long long w_tap, long long w_k, long long w_j, int out_dtype, void* stream);
+/* General window form (strided layers and transposed-convolution / strided-dgrad parity passes).  planes: nplanes (<= 4)
+ * tensors [N,Hp,Wp,C] stored back to back -- p2p_pad_planes writes plane (a,b) = zero-padded x sampled at
+ * (s*y + a - pt, s*x + b - pl), s in {1,2}.  Up to 4 sub-passes (output parities) share the planes in ONE launch: tap t
+ * belongs to sub-pass tap_sub[t] (taps grouped by sub-pass, then sorted by plane), reads plane tap_plane[t] at
+ * (y + tap_dh[t], x + tap_dw[t]) and multiplies weight tap tap_w[t] (< wtaps_total); rows (y < gy[u], x < gx[u]) of sub-pass u
+ * are written to out[n, y*oys+oyo[u], x*oxs+oxo[u], :] of an [N,OHf,OWf,J] tensor. */
+typedef struct {
+    int nplanes, N, Hp, Wp, C;
+    int OHf, OWf, J;
+    int wtaps_total;
+    long long w_tap, w_k, w_j;
+    int nsub, oys, oxs;
+    int gy[4], gx[4], oyo[4], oxo[4];
+    int ntaps;
+    signed char tap_sub[P2P_MAX_TAPS], tap_plane[P2P_MAX_TAPS];
+    short tap_dh[P2P_MAX_TAPS], tap_dw[P2P_MAX_TAPS];
+    unsigned char tap_w[P2P_MAX_TAPS];
+} p2p_conv_window_desc;
+int p2p_pad_planes(const void* x, void* planes, int N, int H, int W, int C, int pt, int pl, int Hh, int Wh, int s, int dtype,
+                   void* stream);
+int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* planes, const void* weight, const float* bias, void* out,
+                        int out_dtype, void* stream);
 /* Adjoint of reflection padding: dx[n,h,w,c] = sum of dxp over the padded positions that mirror onto (h,w).
  * dxp is [N, H+2p, W+2p, C], dx is [N,H,W,C]. */
 int p2p_reflect_pad_fold(const void* dxp, void* dx, int N, int H, int W, int C, int p, int dtype, void* stream);

@@ -33,6 +33,15 @@ class ConvPass(ctypes.Structure):
                 ("dh", _c.c_byte * MAX_TAPS), ("dw", _c.c_byte * MAX_TAPS), ("wtap", _c.c_ubyte * MAX_TAPS)]
 
 
+class WindowDesc(ctypes.Structure):
+    """p2p_conv_window_desc of include/p2p_b200.h."""
+    _fields_ = [("nplanes", _i), ("N", _i), ("Hp", _i), ("Wp", _i), ("C", _i), ("OHf", _i), ("OWf", _i), ("J", _i),
+                ("wtaps_total", _i), ("w_tap", _ll), ("w_k", _ll), ("w_j", _ll), ("nsub", _i), ("oys", _i), ("oxs", _i),
+                ("gy", _i * 4), ("gx", _i * 4), ("oyo", _i * 4), ("oxo", _i * 4), ("ntaps", _i),
+                ("tap_sub", _c.c_byte * MAX_TAPS), ("tap_plane", _c.c_byte * MAX_TAPS),
+                ("tap_dh", _c.c_short * MAX_TAPS), ("tap_dw", _c.c_short * MAX_TAPS), ("tap_w", _c.c_ubyte * MAX_TAPS)]
+
+
 _SIGS.update({
     "p2p_conv_forward": (_i, [_c.POINTER(ConvPass), _vp, _vp, _vp, _vp, _i, _i, _vp]),
     "p2p_conv_force_simple": (_i, [_i]),
@@ -40,6 +49,8 @@ _SIGS.update({
     "p2p_conv_wgrad": (_i, [_c.POINTER(ConvPass), _vp, _vp, _vp, _i, _vp]),
     "p2p_pad_nhwc": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_conv_window": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _vp]),
+    "p2p_pad_planes": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "p2p_conv_window_run": (_i, [_c.POINTER(WindowDesc), _vp, _vp, _vp, _vp, _i, _vp]),
     "p2p_bias_grad": (_i, [_vp, _vp, _ll, _i, _i, _vp]),
     "p2p_reflect_pad_fold": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_instnorm_act_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _f, _f, _i, _i, _vp]),

@@ -35,9 +35,12 @@ struct WindowArgs {
     CUtensorMap tm_w;        // weights: K-major [taps*J rows][C] box [64][BN]; MN-major [taps*K rows][J] box [64][64]
     const float* bias;
     void* out;
-    long long Q;             // GEMM rows = padded pixels
-    int N, Hp, Wp, OH, OW, C, J;
-    int ntaps;
+    long long Q;             // GEMM rows = padded pixels of one plane
+    int N, Hp, Wp, C, J;
+    int OHf, OWf, oys, oxs;  // output tensor extent and scatter stride: pixel (y*oys+oyo, x*oxs+oxo)
+    int ntaps, nplanes, nsub;
+    int gy[4], gx[4], oyo[4], oxo[4];   // per sub-pass: valid rows / columns of the padded grid, scatter offsets
+    int pbeg[4][5];          // sub-pass u: taps [pbeg[u][p], pbeg[u][p+1]) read plane p
     int win_rows, rows_per_box, nboxes;
     int BN, n_tiles, m_tiles, cpb;
     int out_bf16, b_mn_major;
@@ -141,17 +144,20 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
             int ia = 0, ib = 0;     // window loads / weight-tile loads issued so far
             for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x) {
                 const int nt = (int)(w % a.n_tiles);
-                const long long mt = w / a.n_tiles;
-                const long long q0 = mt * WBM;
+                const long long mtu = w / a.n_tiles;
+                const int u = (int)(mtu / a.m_tiles);
+                const long long q0 = (mtu - (long long)u * a.m_tiles) * WBM;
                 const int j0 = nt * BN;
-                for (int cc = 0; cc < a.cpb; ++cc, ++ia) {
+                for (int ci = 0; ci < a.cpb * a.nplanes; ++ci, ++ia) {
+                    const int cc = ci / a.nplanes, pl = ci - cc * a.nplanes;
                     const int c0 = cc * 64;
                     const int ab = ia & 1;
                     if (ia >= 2) mbar_wait(aempty(ab), (uint32_t)(((ia >> 1) - 1) & 1));
                     mbar_expect_tx(afull(ab), a_bytes);
                     for (int bx = 0; bx < a.nboxes; ++bx)
-                        tma_load_2d(base + ab * WIN_BYTES + bx * a.rows_per_box * 128, &a.tm_x, c0, (int)(q0 + (long long)bx * a.rows_per_box), afull(ab));
-                    for (int t = 0; t < a.ntaps; ++t, ++ib) {
+                        tma_load_2d(base + ab * WIN_BYTES + bx * a.rows_per_box * 128, &a.tm_x, c0,
+                                    (int)((long long)pl * a.Q + q0 + (long long)bx * a.rows_per_box), afull(ab));
+                    for (int t = a.pbeg[u][pl]; t < a.pbeg[u][pl + 1]; ++t, ++ib) {
                         const int s = ib % kBStages;
                         if (ib >= kBStages) mbar_wait(bempty(s), (uint32_t)((ib / kBStages - 1) & 1));
                         mbar_expect_tx(bfull(s), b_bytes);
@@ -174,17 +180,20 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
                                    ((uint32_t)(WBM >> 4) << 24);
             int ia = 0, ib = 0, li = 0;
             for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
+                const int u = (int)((w / a.n_tiles) / a.m_tiles);
                 const int acc = li & 1, v = li >> 1;
                 if (v >= 1) mbar_wait(tempty(acc), (uint32_t)((v - 1) & 1));
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * 256;
-                for (int cc = 0; cc < a.cpb; ++cc, ++ia) {
+                uint32_t accumulate = 0;
+                for (int ci = 0; ci < a.cpb * a.nplanes; ++ci, ++ia) {
+                    const int cc = ci / a.nplanes, pl = ci - cc * a.nplanes;
                     const int nk16 = min(64, C - cc * 64) >> 4;
                     const int ab = ia & 1;
                     mbar_wait(afull(ab), (uint32_t)((ia >> 1) & 1));
                     tc_fence_after();
                     const uint32_t win = base + ab * WIN_BYTES;
-                    for (int t = 0; t < a.ntaps; ++t, ++ib) {
+                    for (int t = a.pbeg[u][pl]; t < a.pbeg[u][pl + 1]; ++t, ++ib) {
                         const int s = ib % kBStages;
                         mbar_wait(bfull(s), (uint32_t)((ib / kBStages) & 1));
                         tc_fence_after();
@@ -194,7 +203,8 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
                         for (int k16 = 0; k16 < nk16; ++k16) {
                             const uint64_t ad = make_desc(sa + k16 * 32, 16, 1024, boff);
                             const uint64_t bd = a.b_mn_major ? make_desc(sb + k16 * 2048, 8192, 1024, 0) : make_desc(sb + k16 * 32, 16, 1024, 0);
-                            umma_bf16(d_tmem, ad, bd, idesc, (cc > 0 || t > 0 || k16 > 0) ? 1u : 0u);
+                            umma_bf16(d_tmem, ad, bd, idesc, accumulate);
+                            accumulate = 1;
                         }
                         umma_commit(bempty(s));
                     }
@@ -211,15 +221,17 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
         int li = 0;
         for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
             const int nt = (int)(w % a.n_tiles);
-            const long long mt = w / a.n_tiles;
+            const long long mtu = w / a.n_tiles;
+            const int u = (int)(mtu / a.m_tiles);
+            const long long mt = mtu - (long long)u * a.m_tiles;
             const int acc = li & 1, v = li >> 1;
             const long long q = mt * WBM + row;
             const int n = (int)(q / plane);
             const int rem = (int)(q - (long long)n * plane);
             const int y = rem / a.Wp, x = rem - y * a.Wp;
-            const bool rok = q < a.Q && y < a.OH && x < a.OW;
+            const bool rok = q < a.Q && y < a.gy[u] && x < a.gx[u];
             const int c_begin = nt * BN, c_count = min(BN, J - c_begin);
-            const long long obase = (((long long)n * a.OH + y) * a.OW + x) * J + c_begin;
+            const long long obase = (((long long)n * a.OHf + (y * a.oys + a.oyo[u])) * a.OWf + (x * a.oxs + a.oxo[u])) * J + c_begin;
             mbar_wait(tfull(acc), (uint32_t)(v & 1));
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * 256;
@@ -279,20 +291,24 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
     }
 }
 
-// zero / reflection padding written once: xp[n, y, x, :] = x[n, map(y - pt), map(x - pl), :]
+// zero / reflection padding written once, optionally split into stride x stride parity planes:
+//   planes[(a*s + b)][n, y, x, :] = x[n, map(s*y + a - pt), map(s*x + b - pl), :]      (s = 1: one padded tensor)
 template <typename T>
 __global__ void pad_nhwc_kernel(const T* __restrict__ x, T* __restrict__ xp, int N, int H, int W, int C8, int pt, int pl,
-                                int Hp, int Wp, int reflect) {
+                                int Hp, int Wp, int reflect, int s) {
     // C8 = 16-byte vectors per pixel
-    const long long total = (long long)N * Hp * Wp * C8;
+    const long long plane = (long long)N * Hp * Wp * C8;
+    const long long total = plane * s * s;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int c = (int)(i % C8);
-        long long p = i / C8;
+        const int pq = (int)(i / plane);
+        long long p = i - pq * plane;
+        const int c = (int)(p % C8);
+        p /= C8;
         const int xx = (int)(p % Wp);
         p /= Wp;
         const int yy = (int)(p % Hp);
         const int n = (int)(p / Hp);
-        int sy = yy - pt, sx = xx - pl;
+        int sy = s * yy + pq / s - pt, sx = s * xx + pq % s - pl;
         uint4 v = make_uint4(0, 0, 0, 0);
         if (reflect) {
             sy = sy < 0 ? -sy : (sy >= H ? 2 * (H - 1) - sy : sy);
@@ -359,64 +375,103 @@ extern "C" int p2p_pad_nhwc(const void* x, void* xp, int N, int H, int W, int C,
     const long long total = (long long)N * Hp * Wp * C8;
     long long blocks = (total + 255) / 256;
     if (blocks > 148LL * 32) blocks = 148LL * 32;
-    pad_nhwc_kernel<uint4><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)xp, N, H, W, C8, pt, pl, Hp, Wp, reflect);
+    pad_nhwc_kernel<uint4><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)xp, N, H, W, C8, pt, pl, Hp, Wp, reflect, 1);
     return check_launch("pad_nhwc_kernel");
 }
 
-// out[n,y,x,j] (+bias) = sum_{dh<KH, dw<KW} sum_c xp[n, y+dh, x+dw, c] * Wt[c, j],  y < OH = Hp-KH+1, x < OW = Wp-KW+1.
-// weight tap index = flip ? (KH-1-dh)*KW + (KW-1-dw) : dh*KW + dw; element (tap, c, j) at tap*w_tap + c*w_k + j*w_j with
-// either w_k == 1 (K-major) or w_j == 1 (MN-major, the transposed read used for input gradients).
-extern "C" int p2p_conv_window(const void* xp, const void* weight, const float* bias, void* out, int N, int Hp, int Wp, int C,
-                               int J, int KH, int KW, int flip, long long w_tap, long long w_k, long long w_j, int out_dtype,
-                               void* stream) {
+// planes [s*s][N, Hh, Wh, C]: plane (a, b) holds the zero-padded input sampled at (s*y + a - pt, s*x + b - pl)
+extern "C" int p2p_pad_planes(const void* x, void* planes, int N, int H, int W, int C, int pt, int pl, int Hh, int Wh, int s,
+                              int dtype, void* stream) {
     using namespace p2p;
-    if (!xp || !weight || !out) return fail(P2P_EINVAL, "null pointer argument");
-    if (KH < 1 || KW < 1 || KH * KW > P2P_MAX_TAPS || Hp < KH || Wp < KW) return fail(P2P_EINVAL, "bad window geometry");
+    if (!x || !planes) return fail(P2P_EINVAL, "null pointer argument");
+    const int esz = dtype == P2P_BF16 ? 2 : 4;
+    if ((C * esz) % 16 != 0) return fail(P2P_ENOTSUP, "p2p_pad_planes needs whole 16-byte vectors per pixel (C * %d bytes)", esz);
+    if (N < 1 || H < 1 || W < 1 || Hh < 1 || Wh < 1 || s < 1 || s > 2) return fail(P2P_EINVAL, "bad plane geometry");
+    const int C8 = C * esz / 16;
+    const long long total = (long long)N * Hh * Wh * C8 * s * s;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148LL * 32) blocks = 148LL * 32;
+    pad_nhwc_kernel<uint4><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)planes, N, H, W, C8, pt, pl, Hh, Wh, 0, s);
+    return check_launch("pad_planes_kernel");
+}
+
+// General form (include/p2p_b200.h: p2p_conv_window_desc): up to 4 sub-passes (output parities) share the planes.
+extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* planes, const void* weight, const float* bias,
+                                   void* out, int out_dtype, void* stream) {
+    using namespace p2p;
+    if (!d || !planes || !weight || !out) return fail(P2P_EINVAL, "null pointer argument");
+    const int ntaps = d->ntaps, nplanes = d->nplanes, C = d->C, J = d->J, Hp = d->Hp, Wp = d->Wp;
+    if (ntaps < 1 || ntaps > P2P_MAX_TAPS || nplanes < 1 || nplanes > 4 || d->wtaps_total < 1 || d->nsub < 1 || d->nsub > 4)
+        return fail(P2P_EINVAL, "bad tap / plane / sub-pass count");
     if (C % 16 != 0) return fail(P2P_ENOTSUP, "window convolution needs C %% 16 == 0, got %d", C);
     WindowArgs a;
-    a.N = N; a.Hp = Hp; a.Wp = Wp; a.OH = Hp - KH + 1; a.OW = Wp - KW + 1; a.C = C; a.J = J;
-    a.ntaps = KH * KW;
-    a.Q = (long long)N * Hp * Wp;
-    const int halo = (KH - 1) * Wp + (KW - 1);
+    a.N = d->N; a.Hp = Hp; a.Wp = Wp; a.C = C; a.J = J;
+    a.OHf = d->OHf; a.OWf = d->OWf; a.oys = d->oys; a.oxs = d->oxs;
+    a.ntaps = ntaps; a.nplanes = nplanes; a.nsub = d->nsub;
+    a.Q = (long long)d->N * Hp * Wp;
+    if ((long long)nplanes * a.Q > 2000000000LL) return fail(P2P_ENOTSUP, "too many rows");
+    for (int u = 0; u < 4; ++u) {
+        a.gy[u] = a.gx[u] = a.oyo[u] = a.oxo[u] = 0;
+        for (int p = 0; p <= 4; ++p) a.pbeg[u][p] = 0;
+    }
+    for (int u = 0; u < d->nsub; ++u) {
+        a.gy[u] = d->gy[u]; a.gx[u] = d->gx[u]; a.oyo[u] = d->oyo[u]; a.oxo[u] = d->oxo[u];
+        if (a.gy[u] < 1 || a.gx[u] < 1 || a.gy[u] > Hp || a.gx[u] > Wp || a.oyo[u] < 0 || a.oxo[u] < 0 ||
+            (a.gy[u] - 1) * d->oys + a.oyo[u] >= d->OHf || (a.gx[u] - 1) * d->oxs + a.oxo[u] >= d->OWf)
+            return fail(P2P_EINVAL, "sub-pass %d scatters outside the output tensor", u);
+    }
+    int halo = 0, t = 0;
+    for (int u = 0; u < d->nsub; ++u) {         // taps grouped by sub-pass, then sorted by plane
+        for (int p = 0; p < nplanes; ++p) {
+            a.pbeg[u][p] = t;
+            while (t < ntaps && d->tap_sub[t] == u && d->tap_plane[t] == p) {
+                if (d->tap_dh[t] < 0 || d->tap_dw[t] < 0 || d->tap_dh[t] + a.gy[u] > Hp || d->tap_dw[t] + a.gx[u] > Wp)
+                    return fail(P2P_EINVAL, "tap %d reads outside its plane", t);
+                if (d->tap_w[t] >= d->wtaps_total) return fail(P2P_EINVAL, "weight tap out of range");
+                const int sh = d->tap_dh[t] * Wp + d->tap_dw[t];
+                if (sh > 32767) return fail(P2P_ENOTSUP, "tap shift too large");
+                a.shift[t] = (short)sh;
+                a.wtap[t] = d->tap_w[t];
+                if (sh > halo) halo = sh;
+                ++t;
+            }
+        }
+        for (int p = nplanes; p <= 4; ++p) a.pbeg[u][p] = t;
+        if (a.pbeg[u][nplanes] == a.pbeg[u][0]) return fail(P2P_EINVAL, "sub-pass %d has no taps", u);
+    }
+    if (t != ntaps) return fail(P2P_EINVAL, "taps must be grouped by sub-pass and sorted by plane");
     a.win_rows = WBM + halo;
     if (a.win_rows > kWinRowsMax) return fail(P2P_ENOTSUP, "window of %d rows exceeds the %d-row buffer", a.win_rows, kWinRowsMax);
     a.nboxes = (a.win_rows + 255) / 256;
     a.rows_per_box = (a.win_rows + a.nboxes - 1) / a.nboxes;
     a.rows_per_box = (a.rows_per_box + 7) / 8 * 8;          // keeps every box 1024-byte aligned
     if (a.nboxes * a.rows_per_box > kWinRowsMax) return fail(P2P_ENOTSUP, "window boxes exceed the buffer");
+    const long long w_tap = d->w_tap, w_k = d->w_k, w_j = d->w_j;
     if (w_k == 1 && w_j % 8 == 0 && w_tap % 8 == 0) a.b_mn_major = 0;
     else if (w_j == 1 && w_k % 8 == 0 && w_tap % 8 == 0 && J % 8 == 0) a.b_mn_major = 1;
     else return fail(P2P_ENOTSUP, "weight strides not 16-byte friendly");
     if (a.b_mn_major ? (w_tap != (long long)C * w_k) : (w_tap != (long long)J * w_j))
         return fail(P2P_ENOTSUP, "weights must be densely packed per tap");
-    for (int dh = 0; dh < KH; ++dh)
-        for (int dw = 0; dw < KW; ++dw) {
-            const int t = dh * KW + dw;
-            a.shift[t] = (short)(dh * Wp + dw);
-            a.wtap[t] = (unsigned char)(flip ? (KH - 1 - dh) * KW + (KW - 1 - dw) : t);
-        }
     a.bias = bias;
     a.out = out;
     a.out_bf16 = out_dtype == P2P_BF16;
     a.cpb = (C + 63) / 64;
     a.base_off_mode = g_window_base_off_mode;
-    // column tile: whole J when it fits 256 columns, else balanced multiples of 16 (MN-major: of 64)
-    {
+    {   // column tile: whole J when it fits 256 columns, else balanced multiples of 16
         const int nt = (J + 255) / 256;
-        int bn = ((J + nt - 1) / nt + 15) / 16 * 16;
-        if (a.b_mn_major) bn = (bn + 63) / 64 * 64 > 256 ? 256 : (bn + 15) / 16 * 16;
+        const int bn = ((J + nt - 1) / nt + 15) / 16 * 16;
         a.BN = bn < 16 ? 16 : bn;
     }
     a.n_tiles = (J + a.BN - 1) / a.BN;
     const long long mt = (a.Q + WBM - 1) / WBM;
-    if (mt > 2000000000LL / a.n_tiles) return fail(P2P_ENOTSUP, "too many tiles");
+    if (mt * a.nsub > 2000000000LL / a.n_tiles) return fail(P2P_ENOTSUP, "too many tiles");
     a.m_tiles = (int)mt;
-    a.nwork = mt * a.n_tiles;
-    if (int rc = encode_2d(&a.tm_x, xp, (unsigned long long)C, (unsigned long long)a.Q, 64, (unsigned)a.rows_per_box)) return rc;
+    a.nwork = mt * a.n_tiles * a.nsub;
+    if (int rc = encode_2d(&a.tm_x, planes, (unsigned long long)C, (unsigned long long)nplanes * a.Q, 64, (unsigned)a.rows_per_box)) return rc;
     if (!a.b_mn_major) {
-        if (int rc = encode_2d(&a.tm_w, weight, (unsigned long long)C, (unsigned long long)a.ntaps * J, 64, (unsigned)a.BN)) return rc;
+        if (int rc = encode_2d(&a.tm_w, weight, (unsigned long long)C, (unsigned long long)d->wtaps_total * J, 64, (unsigned)a.BN)) return rc;
     } else {
-        if (int rc = encode_2d(&a.tm_w, weight, (unsigned long long)J, (unsigned long long)a.ntaps * C, 64, 64)) return rc;
+        if (int rc = encode_2d(&a.tm_w, weight, (unsigned long long)J, (unsigned long long)d->wtaps_total * C, 64, 64)) return rc;
     }
     static bool configured = false;
     if (!configured) {
@@ -431,4 +486,28 @@ extern "C" int p2p_conv_window(const void* xp, const void* weight, const float* 
     conv_window_kernel<<<(unsigned)grid, kWThreads, WSMEM, (cudaStream_t)stream>>>(a);
     note_umma_launch();
     return check_launch("conv_window_kernel");
+}
+
+// out[n,y,x,j] (+bias) = sum_{dh<KH, dw<KW} sum_c xp[n, y+dh, x+dw, c] * Wt[c, j],  y < OH = Hp-KH+1, x < OW = Wp-KW+1.
+// weight tap index = flip ? (KH-1-dh)*KW + (KW-1-dw) : dh*KW + dw; element (tap, c, j) at tap*w_tap + c*w_k + j*w_j with
+// either w_k == 1 (K-major) or w_j == 1 (MN-major, the transposed read used for input gradients).
+extern "C" int p2p_conv_window(const void* xp, const void* weight, const float* bias, void* out, int N, int Hp, int Wp, int C,
+                               int J, int KH, int KW, int flip, long long w_tap, long long w_k, long long w_j, int out_dtype,
+                               void* stream) {
+    using namespace p2p;
+    if (KH < 1 || KW < 1 || KH * KW > P2P_MAX_TAPS || Hp < KH || Wp < KW) return fail(P2P_EINVAL, "bad window geometry");
+    p2p_conv_window_desc d;
+    d.nplanes = 1; d.N = N; d.Hp = Hp; d.Wp = Wp; d.C = C;
+    d.OHf = Hp - KH + 1; d.OWf = Wp - KW + 1; d.J = J;
+    d.wtaps_total = KH * KW; d.w_tap = w_tap; d.w_k = w_k; d.w_j = w_j;
+    d.nsub = 1; d.oys = d.oxs = 1;
+    for (int u = 0; u < 4; ++u) { d.gy[u] = d.OHf; d.gx[u] = d.OWf; d.oyo[u] = d.oxo[u] = 0; }
+    d.ntaps = KH * KW;
+    for (int i = 0; i < KH; ++i)
+        for (int j = 0; j < KW; ++j) {
+            const int t = i * KW + j;
+            d.tap_sub[t] = 0; d.tap_plane[t] = 0; d.tap_dh[t] = (short)i; d.tap_dw[t] = (short)j;
+            d.tap_w[t] = (unsigned char)(flip ? (KH - 1 - i) * KW + (KW - 1 - j) : t);
+        }
+    return p2p_conv_window_run(&d, xp, weight, bias, out, out_dtype, stream);
 }

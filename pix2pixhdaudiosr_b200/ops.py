@@ -258,6 +258,69 @@ def pad_nhwc(x, pt, pb, pl, pr, reflect):
     return xp
 
 
+def _plan_window_passes(passes, dtype):
+    """common window geometry of the zero-padded passes of one layer call (gather stride 1 or 2; up to 4 output
+    parities), or None when they do not fit the shifted-window kernel"""
+    P0 = passes[0]
+    if dtype != torch.bfloat16 or len(passes) > 4 or P0.sy != P0.sx or P0.sy not in (1, 2) or P0.K % 16 != 0:
+        return None
+    mn_major = P0.w_j == 1
+    if not ((P0.w_k == 1 and P0.w_j % 8 == 0) or (mn_major and P0.w_k % 8 == 0 and P0.J % 8 == 0)) or P0.w_tap % 8 != 0:
+        return None
+    s = P0.sy
+    for P in passes:
+        if (P.pad_mode != PAD_ZERO or (P.sy, P.sx) != (s, s) or (P.oys, P.oxs) != (P0.oys, P0.oxs)
+                or (P.w_tap, P.w_k, P.w_j, P.K, P.J, P.OH, P.OW, P.H, P.W) !=
+                (P0.w_tap, P0.w_k, P0.w_j, P0.K, P0.J, P0.OH, P0.OW, P0.H, P0.W)):
+            return None
+    pt = max(0, -min(P.dh[t] for P in passes for t in range(P.ntaps)))
+    pl = max(0, -min(P.dw[t] for P in passes for t in range(P.ntaps)))
+    subs, Hh, Wh = [], 0, 0
+    for P in passes:
+        taps = []
+        for t in range(P.ntaps):
+            a, b = P.dh[t] + pt, P.dw[t] + pl
+            taps.append(((a % s) * s + (b % s), a // s, b // s, P.wtap[t]))
+        taps.sort(key=lambda q: q[0])
+        subs.append(taps)
+        Hh, Wh = max(Hh, P.gy + max(q[1] for q in taps)), max(Wh, P.gx + max(q[2] for q in taps))
+    halo = max(q[1] * Wh + q[2] for taps in subs for q in taps)
+    useful = sum(P.gy * P.gx for P in passes)
+    if 128 + halo > _WIN_ROWS_MAX or useful < 0.7 * len(passes) * Hh * Wh or sum(len(t) for t in subs) > _lib.MAX_TAPS:
+        return None
+    return dict(s=s, pt=pt, pl=pl, Hh=Hh, Wh=Wh, subs=subs)
+
+
+def _window_passes(passes, x, wq, bias, out, wtaps_total, kind):
+    """run all passes of a layer call as ONE launch of the shifted-window kernel; False (nothing launched) if they do not fit"""
+    if not USE_WINDOW or not passes or _lib.lib().p2p_conv_force_simple(-1) == 1:
+        return False
+    pl = _plan_window_passes(passes, x.dtype)
+    if pl is None:
+        return False
+    N, H, W, C = x.shape
+    s, P0 = pl["s"], passes[0]
+    planes = torch.empty((s * s, N, pl["Hh"], pl["Wh"], C), dtype=x.dtype, device=x.device)
+    _lib.check(_lib.lib().p2p_pad_planes(_p(x), _p(planes), N, H, W, C, pl["pt"], pl["pl"], pl["Hh"], pl["Wh"], s,
+                                         _DT[x.dtype], _stream()))
+    d = _lib.WindowDesc()
+    d.nplanes, d.N, d.Hp, d.Wp, d.C = s * s, N, pl["Hh"], pl["Wh"], C
+    d.OHf, d.OWf, d.J = P0.OH, P0.OW, P0.J
+    d.wtaps_total, d.w_tap, d.w_k, d.w_j = wtaps_total, P0.w_tap, P0.w_k, P0.w_j
+    d.nsub, d.oys, d.oxs = len(passes), P0.oys, P0.oxs
+    t = 0
+    for u, (P, taps) in enumerate(zip(passes, pl["subs"])):
+        d.gy[u], d.gx[u], d.oyo[u], d.oxo[u] = P.gy, P.gx, P.oyo, P.oxo
+        for (plane, dh, dw, wt) in taps:
+            d.tap_sub[t], d.tap_plane[t], d.tap_dh[t], d.tap_dw[t], d.tap_w[t] = u, plane, dh, dw, wt
+            t += 1
+    d.ntaps = t
+    shape = _Shape(N, 1, sum(P.gy * P.gx * P.ntaps for P in passes), P0.J, 1, C, pl["Hh"], pl["Wh"])
+    _timed(kind, shape, lambda: _lib.check(_lib.lib().p2p_conv_window_run(ctypes.byref(d), _p(planes), _p(wq), _p(bias), _p(out),
+                                                                          _DT[out.dtype], _stream())), umma=True)
+    return True
+
+
 def conv_window(xp, wq, bias, out_dtype, KH, KW, J, flip, w_tap, w_k, w_j, kind):
     N, Hp, Wp, C = xp.shape
     OH, OW = Hp - KH + 1, Wp - KW + 1
@@ -420,6 +483,8 @@ def _conv_forward(x, weight, bias, w16, cfg, out_dtype):
         passes = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
         OH, OW = passes[0].OH, passes[0].OW
     y = torch.empty((N, OH, OW, Jout), dtype=out_dtype, device=x.device)
+    if _window_passes(passes, x, wq, bias, y, KH * KW, "fwd"):
+        return y
     for P in passes:
         _run_pass(P, x, wq, bias, y)
     return y
@@ -454,7 +519,9 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
     if need_dx:
         if cfg.transposed:
             dx = torch.empty_like(x)
-            _run_pass(convT_dgrad_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0], dy, wq, None, dx, "dgrad")
+            Pd = convT_dgrad_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)
+            if not _window_passes(Pd, dy, wq, None, dx, KH * KW, "dgrad"):
+                _run_pass(Pd[0], dy, wq, None, dx, "dgrad")
         else:
             q = (KH - 1) if cfg.pad_mode == PAD_REFLECT else (KH - 1 - cfg.pad)      # zero margin around dy
             OHd, OWd = dy.shape[1], dy.shape[2]
@@ -468,6 +535,8 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
                 if passes is None:
                     raise NotImplementedError("input gradient of a convolution whose stride skips whole parity classes")
                 buf = torch.empty((N, DH, DW, Cin), dtype=x.dtype, device=x.device)
+                if _window_passes(passes, dy, wq, None, buf, KH * KW, "dgrad"):
+                    passes = []
             for P in passes:
                 _run_pass(P, dy, wq, None, buf, "dgrad")
             if cfg.pad_mode == PAD_REFLECT and cfg.pad > 0:

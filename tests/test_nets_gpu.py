@@ -289,7 +289,7 @@ def test_tcgen05_kernels_match_cuda_core_kernels(layer):
                 torch.cuda.synchronize()
                 n1 = _lib.lib().p2p_conv_umma_launches()
                 if not simple:
-                    assert n1 - n0 == nlaunch, (name, n1 - n0)
+                    assert 3 <= n1 - n0 <= nlaunch, (name, n1 - n0)     # fwd, dgrad, wgrad each on tensor cores (parity passes may merge)
                 res[(simple, norm)] = (y.float(), dx.float(), dw.float())
         finally:
             _lib.lib().p2p_conv_force_simple(old)
