@@ -124,6 +124,10 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 // shared-memory matrix descriptor, 128-byte swizzle (layout_type 2), descriptor version 1 (sm_100)
 __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
     return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
@@ -372,9 +376,14 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 } else {
                     float* o = (float*)a.out + obase + c;
                     if (a.atomic) {
+                        if (fullv && (((uintptr_t)o) & 15) == 0) {
 #pragma unroll
-                        for (int i = 0; i < 16; ++i)
-                            if (c + i < c_count) atomicAdd(o + i, f[i]);
+                            for (int i = 0; i < 4; ++i) red_add_v4(o + 4 * i, f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i)
+                                if (c + i < c_count) atomicAdd(o + i, f[i]);
+                        }
                     } else if (fullv && (((uintptr_t)o) & 15) == 0) {
 #pragma unroll
                         for (int i = 0; i < 4; ++i)

@@ -95,6 +95,10 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 // 128-byte-swizzle matrix descriptor; base_off = (start >> 7) & 7 for starts inside a 1024-byte swizzle atom
 __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t base_off) {
     return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
@@ -295,13 +299,14 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
 //   planes[(a*s + b)][n, y, x, :] = x[n, map(s*y + a - pt), map(s*x + b - pl), :]      (s = 1: one padded tensor)
 template <typename T>
 __global__ void pad_nhwc_kernel(const T* __restrict__ x, T* __restrict__ xp, int N, int H, int W, int C8, int pt, int pl,
-                                int Hp, int Wp, int reflect, int s) {
-    // C8 = 16-byte vectors per pixel
-    const long long plane = (long long)N * Hp * Wp * C8;
+                                int Hp, int Wp, int reflect, int s, long long plane_rows) {
+    // C8 = 16-byte vectors per pixel; every plane occupies plane_rows >= N*Hp*Wp pixel rows (the tail is zero-filled)
+    const long long plane = plane_rows * C8, used = (long long)N * Hp * Wp * C8;
     const long long total = plane * s * s;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int pq = (int)(i / plane);
         long long p = i - pq * plane;
+        if (p >= used) { reinterpret_cast<uint4*>(xp)[i] = make_uint4(0, 0, 0, 0); continue; }
         const int c = (int)(p % C8);
         p /= C8;
         const int xx = (int)(p % Wp);
@@ -317,6 +322,170 @@ __global__ void pad_nhwc_kernel(const T* __restrict__ x, T* __restrict__ xp, int
         if (sy >= 0 && sy < H && sx >= 0 && sx < W)
             v = reinterpret_cast<const uint4*>(x)[(((long long)n * H + sy) * W + sx) * C8 + c];
         reinterpret_cast<uint4*>(xp)[i] = v;
+    }
+}
+
+// ---- weight gradients in window form -------------------------------------------------------------------------------------
+// dW[wtap_t][j][c] += sum_q A[a_plane_t][q][j] * B[b_plane_t][q + shift_t][c]: the reduction index q runs over the padded pixel
+// grid (A = dout laid out at the same pitch, zero where no output exists).  Both operands are MN-major (rows = q): A is one
+// TMA tile per 64-row block, B one shifted WINDOW shared by all taps of a group; every tap owns BN TMEM columns.
+constexpr int kGStages = 3;
+constexpr int GA_BYTES = 2 * 8192;                  // [64 q][128 j]
+constexpr int GB_BYTES = kWinRowsMax * 128;         // [64 + halo q][64 c]
+constexpr int GSTAGE = GA_BYTES + GB_BYTES;
+constexpr int GSMEM = kGStages * GSTAGE + 1024 + 256;
+constexpr int kMaxGroups = 8;
+
+struct WgradWinArgs {
+    CUtensorMap tm_a;        // dout planes [rows][J]: box [64 j][64 rows]
+    CUtensorMap tm_b;        // input planes [rows][C]: box [64 c][b_rows_per_box]
+    float* dw;
+    long long Qs;            // rows per plane (multiple of 64, zero tail)
+    long long w_tap;
+    int J, C, BN, j_tiles, c_tiles, nsplit, kb_per_split, total_kb;
+    int ntaps, ngroups, atomic;
+    int b_nboxes, b_rows_per_box;
+    int gbeg[kMaxGroups + 1];
+    short ga[kMaxGroups], gb[kMaxGroups];
+    short shift[32];
+    unsigned char wtap[32];
+    long long nwork;
+};
+
+__global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const __grid_constant__ WgradWinArgs a) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bars = base + kGStages * GSTAGE;
+    auto full = [&](int s) { return bars + 8u * s; };
+    auto empty = [&](int s) { return bars + 8u * (kGStages + s); };
+    const uint32_t tfull = bars + 8u * (2 * kGStages), tempty = tfull + 8, tmem_slot = tfull + 16;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int BN = a.BN;
+    const uint32_t b_bytes = (uint32_t)a.b_nboxes * a.b_rows_per_box * 128u;
+
+    if (warp == 1) {
+        if (lane == 0) {
+            for (int s = 0; s < kGStages; ++s) { mbar_init(full(s), 1); mbar_init(empty(s), 1); }
+            mbar_init(tfull, 1);
+            mbar_init(tempty, 128);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+    if (warp == 0) {
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_a) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_b) : "memory");
+            int it = 0;
+            for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x) {
+                const int sp = (int)(w % a.nsplit);
+                const long long r = w / a.nsplit;
+                const int ct = (int)(r % a.c_tiles), jt = (int)(r / a.c_tiles);
+                const int kb0 = sp * a.kb_per_split, kb1 = min(a.total_kb, kb0 + a.kb_per_split);
+                for (int kb = kb0; kb < kb1; ++kb)
+                    for (int g = 0; g < a.ngroups; ++g, ++it) {
+                        const int s = it % kGStages;
+                        if (it >= kGStages) mbar_wait(empty(s), (uint32_t)((it / kGStages - 1) & 1));
+                        mbar_expect_tx(full(s), GA_BYTES + b_bytes);
+                        const uint32_t sa = base + s * GSTAGE, sb = sa + GA_BYTES;
+                        const long long qa = (long long)a.ga[g] * a.Qs + (long long)kb * 64;
+                        const long long qb = (long long)a.gb[g] * a.Qs + (long long)kb * 64;
+                        tma_load_2d(sa, &a.tm_a, jt * 128, (int)qa, full(s));
+                        tma_load_2d(sa + 8192, &a.tm_a, jt * 128 + 64, (int)qa, full(s));
+                        for (int bx = 0; bx < a.b_nboxes; ++bx)
+                            tma_load_2d(sb + bx * a.b_rows_per_box * 128, &a.tm_b, ct * BN, (int)(qb + (long long)bx * a.b_rows_per_box), full(s));
+                    }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) |
+                                   ((uint32_t)(WBM >> 4) << 24);
+            int it = 0, li = 0;
+            for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
+                const int sp = (int)(w % a.nsplit);
+                const int kb0 = sp * a.kb_per_split, kb1 = min(a.total_kb, kb0 + a.kb_per_split);
+                if (li >= 1) mbar_wait(tempty, (uint32_t)((li - 1) & 1));
+                tc_fence_after();
+                for (int kb = kb0; kb < kb1; ++kb)
+                    for (int g = 0; g < a.ngroups; ++g, ++it) {
+                        const int s = it % kGStages;
+                        mbar_wait(full(s), (uint32_t)((it / kGStages) & 1));
+                        tc_fence_after();
+                        const uint32_t sa = base + s * GSTAGE, sb = sa + GA_BYTES;
+                        for (int t = a.gbeg[g]; t < a.gbeg[g + 1]; ++t) {
+                            const uint32_t d_tmem = tmem_base + t * BN;
+                            const uint32_t sbt = sb + (uint32_t)a.shift[t] * 128u;
+#pragma unroll
+                            for (int k16 = 0; k16 < 4; ++k16)
+                                umma_bf16(d_tmem, make_desc(sa + k16 * 2048, 8192, 1024, 0), make_desc(sbt + k16 * 2048, 8192, 1024, 0), idesc,
+                                          (kb > kb0 || k16 > 0) ? 1u : 0u);
+                        }
+                        umma_commit(empty(s));
+                    }
+                umma_commit(tfull);
+            }
+        }
+        __syncwarp();
+    } else {
+        const int quarter = warp & 3, row = quarter * 32 + lane;
+        int li = 0;
+        for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
+            const long long r = w / a.nsplit;
+            const int ct = (int)(r % a.c_tiles), jt = (int)(r / a.c_tiles);
+            const int j = jt * 128 + row, c_begin = ct * BN, c_count = min(BN, a.C - c_begin);
+            const bool rok = j < a.J;
+            mbar_wait(tfull, (uint32_t)(li & 1));
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+            for (int t = 0; t < a.ntaps; ++t) {
+                float* o = a.dw + (long long)a.wtap[t] * a.w_tap + (long long)j * a.C + c_begin;
+                for (int c = 0; c < BN; c += 16) {
+                    uint32_t v[16];
+                    tmem_ld16(taddr + t * BN + c, v);
+                    tmem_ld_wait();
+                    if (!rok || c >= c_count) continue;
+                    if (a.atomic) {
+                        if (c + 16 <= c_count && ((((uintptr_t)(o + c)) & 15) == 0)) {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i)
+                                red_add_v4(o + c + 4 * i, __uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                                           __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i)
+                                if (c + i < c_count) atomicAdd(o + c + i, __uint_as_float(v[i]));
+                        }
+                    } else if (c + 16 <= c_count && ((((uintptr_t)(o + c)) & 15) == 0)) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            reinterpret_cast<float4*>(o + c)[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                                                                              __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            if (c + i < c_count) o[c + i] = __uint_as_float(v[i]);
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(tempty);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
     }
 }
 
@@ -375,23 +544,25 @@ extern "C" int p2p_pad_nhwc(const void* x, void* xp, int N, int H, int W, int C,
     const long long total = (long long)N * Hp * Wp * C8;
     long long blocks = (total + 255) / 256;
     if (blocks > 148LL * 32) blocks = 148LL * 32;
-    pad_nhwc_kernel<uint4><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)xp, N, H, W, C8, pt, pl, Hp, Wp, reflect, 1);
+    pad_nhwc_kernel<uint4><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)xp, N, H, W, C8, pt, pl, Hp, Wp, reflect, 1, (long long)N * Hp * Wp);
     return check_launch("pad_nhwc_kernel");
 }
 
 // planes [s*s][N, Hh, Wh, C]: plane (a, b) holds the zero-padded input sampled at (s*y + a - pt, s*x + b - pl)
 extern "C" int p2p_pad_planes(const void* x, void* planes, int N, int H, int W, int C, int pt, int pl, int Hh, int Wh, int s,
-                              int dtype, void* stream) {
+                              long long plane_rows, int reflect, int dtype, void* stream) {
     using namespace p2p;
     if (!x || !planes) return fail(P2P_EINVAL, "null pointer argument");
     const int esz = dtype == P2P_BF16 ? 2 : 4;
     if ((C * esz) % 16 != 0) return fail(P2P_ENOTSUP, "p2p_pad_planes needs whole 16-byte vectors per pixel (C * %d bytes)", esz);
     if (N < 1 || H < 1 || W < 1 || Hh < 1 || Wh < 1 || s < 1 || s > 2) return fail(P2P_EINVAL, "bad plane geometry");
+    if (plane_rows < (long long)N * Hh * Wh) return fail(P2P_EINVAL, "plane_rows smaller than N*Hh*Wh");
+    if (reflect && s != 1) return fail(P2P_ENOTSUP, "reflection padding of parity planes");
     const int C8 = C * esz / 16;
-    const long long total = (long long)N * Hh * Wh * C8 * s * s;
+    const long long total = plane_rows * C8 * s * s;
     long long blocks = (total + 255) / 256;
     if (blocks > 148LL * 32) blocks = 148LL * 32;
-    pad_nhwc_kernel<uint4><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)planes, N, H, W, C8, pt, pl, Hh, Wh, 0, s);
+    pad_nhwc_kernel<uint4><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)planes, N, H, W, C8, pt, pl, Hh, Wh, reflect, s, plane_rows);
     return check_launch("pad_planes_kernel");
 }
 
@@ -510,4 +681,77 @@ extern "C" int p2p_conv_window(const void* xp, const void* weight, const float* 
             d.tap_w[t] = (unsigned char)(flip ? (KH - 1 - i) * KW + (KW - 1 - j) : t);
         }
     return p2p_conv_window_run(&d, xp, weight, bias, out, out_dtype, stream);
+}
+
+// dW[tap_w[t]][j][c] (fp32, [wtaps_total][J][C], caller-zeroed) += sum over the padded grid of
+//   aplanes[tap_a[t]][q][j] * bplanes[tap_b[t]][q + tap_dh[t]*Wp + tap_dw[t]][c];
+// planes are [plane_rows][channels] bf16 with plane_rows a multiple of 64 (p2p_pad_planes zero-fills the tail);
+// taps must be grouped by (tap_a, tap_b).  ntaps * BN <= 512 TMEM columns: ntaps <= 32.
+extern "C" int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const void* bplanes, int n_bplanes, long long plane_rows,
+                                     int Wp, int J, int C, float* dw, int wtaps_total, int ntaps, const int* tap_a,
+                                     const int* tap_b, const int* tap_dh, const int* tap_dw, const int* tap_w, void* stream) {
+    using namespace p2p;
+    if (!aplanes || !bplanes || !dw || !tap_a || !tap_b || !tap_dh || !tap_dw || !tap_w) return fail(P2P_EINVAL, "null pointer argument");
+    if (ntaps < 1 || ntaps > 32 || wtaps_total < 1) return fail(P2P_ENOTSUP, "window wgrad supports 1..32 taps, got %d", ntaps);
+    if (plane_rows < 64 || plane_rows % 64 != 0) return fail(P2P_EINVAL, "plane_rows must be a positive multiple of 64");
+    if (J % 8 != 0 || C % 16 != 0) return fail(P2P_ENOTSUP, "window wgrad needs J %% 8 == 0 and C %% 16 == 0");
+    if ((long long)(n_aplanes > n_bplanes ? n_aplanes : n_bplanes) * plane_rows > 2000000000LL) return fail(P2P_ENOTSUP, "too many rows");
+    WgradWinArgs a;
+    a.dw = dw; a.Qs = plane_rows; a.J = J; a.C = C; a.ntaps = ntaps; a.w_tap = (long long)J * C;
+    int bn = (512 / ntaps) / 16 * 16;
+    if (bn > 64) bn = 64;
+    if (bn > (C + 15) / 16 * 16) bn = (C + 15) / 16 * 16;
+    if (bn < 16) return fail(P2P_ENOTSUP, "too many taps for the TMEM columns");
+    a.BN = bn;
+    a.j_tiles = (J + 127) / 128;
+    a.c_tiles = (C + bn - 1) / bn;
+    int halo = 0, ng = 0;
+    for (int t = 0; t < ntaps; ++t) {
+        if (tap_a[t] < 0 || tap_a[t] >= n_aplanes || tap_b[t] < 0 || tap_b[t] >= n_bplanes || tap_dh[t] < 0 || tap_dw[t] < 0)
+            return fail(P2P_EINVAL, "bad tap %d", t);
+        if (tap_w[t] < 0 || tap_w[t] >= wtaps_total) return fail(P2P_EINVAL, "weight tap out of range");
+        if (t == 0 || tap_a[t] != tap_a[t - 1] || tap_b[t] != tap_b[t - 1]) {
+            if (ng == kMaxGroups) return fail(P2P_ENOTSUP, "too many operand-plane pairs");
+            for (int g = 0; g < ng; ++g)
+                if (a.ga[g] == tap_a[t] && a.gb[g] == tap_b[t]) return fail(P2P_EINVAL, "taps must be grouped by operand planes");
+            a.ga[ng] = (short)tap_a[t]; a.gb[ng] = (short)tap_b[t]; a.gbeg[ng] = t;
+            ++ng;
+        }
+        const int sh = tap_dh[t] * Wp + tap_dw[t];
+        if (sh > 32767) return fail(P2P_ENOTSUP, "tap shift too large");
+        a.shift[t] = (short)sh;
+        a.wtap[t] = (unsigned char)tap_w[t];
+        if (sh > halo) halo = sh;
+    }
+    for (int g = ng; g <= kMaxGroups; ++g) a.gbeg[g] = ntaps;
+    a.ngroups = ng;
+    const int brows = 64 + halo;
+    if (brows > kWinRowsMax) return fail(P2P_ENOTSUP, "window of %d rows exceeds the %d-row buffer", brows, kWinRowsMax);
+    a.b_nboxes = (brows + 255) / 256;
+    a.b_rows_per_box = ((brows + a.b_nboxes - 1) / a.b_nboxes + 7) / 8 * 8;
+    if (a.b_nboxes * a.b_rows_per_box > kWinRowsMax) return fail(P2P_ENOTSUP, "window boxes exceed the buffer");
+    a.total_kb = (int)(plane_rows / 64);
+    const long long items = (long long)a.j_tiles * a.c_tiles;
+    int sms = 148, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int nsplit = (int)((sms + items - 1) / items);         // one wave: every extra split is another pass of atomics over dW
+    if (nsplit > a.total_kb / 2) nsplit = a.total_kb / 2;
+    if (nsplit < 1) nsplit = 1;
+    a.kb_per_split = (a.total_kb + nsplit - 1) / nsplit;
+    a.nsplit = (a.total_kb + a.kb_per_split - 1) / a.kb_per_split;
+    a.atomic = a.nsplit > 1;
+    a.nwork = items * a.nsplit;
+    if (int rc = encode_2d(&a.tm_a, aplanes, (unsigned long long)J, (unsigned long long)n_aplanes * plane_rows, 64, 64)) return rc;
+    if (int rc = encode_2d(&a.tm_b, bplanes, (unsigned long long)C, (unsigned long long)n_bplanes * plane_rows, 64, (unsigned)a.b_rows_per_box)) return rc;
+    static bool configured = false;
+    if (!configured) {
+        if (cudaFuncSetAttribute(conv_wgrad_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GSMEM) != cudaSuccess)
+            return check_launch("cudaFuncSetAttribute(conv_wgrad_window_kernel)");
+        configured = true;
+    }
+    const long long grid = a.nwork < sms ? a.nwork : sms;
+    conv_wgrad_window_kernel<<<(unsigned)grid, kWThreads, GSMEM, (cudaStream_t)stream>>>(a);
+    note_umma_launch();
+    return check_launch("conv_wgrad_window_kernel");
 }

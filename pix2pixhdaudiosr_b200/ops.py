@@ -302,7 +302,7 @@ def _window_passes(passes, x, wq, bias, out, wtaps_total, kind):
     s, P0 = pl["s"], passes[0]
     planes = torch.empty((s * s, N, pl["Hh"], pl["Wh"], C), dtype=x.dtype, device=x.device)
     _lib.check(_lib.lib().p2p_pad_planes(_p(x), _p(planes), N, H, W, C, pl["pt"], pl["pl"], pl["Hh"], pl["Wh"], s,
-                                         _DT[x.dtype], _stream()))
+                                         N * pl["Hh"] * pl["Wh"], 0, _DT[x.dtype], _stream()))
     d = _lib.WindowDesc()
     d.nplanes, d.N, d.Hp, d.Wp, d.C = s * s, N, pl["Hh"], pl["Wh"], C
     d.OHf, d.OWf, d.J = P0.OH, P0.OW, P0.J
@@ -318,6 +318,59 @@ def _window_passes(passes, x, wq, bias, out, wtaps_total, kind):
     shape = _Shape(N, 1, sum(P.gy * P.gx * P.ntaps for P in passes), P0.J, 1, C, pl["Hh"], pl["Wh"])
     _timed(kind, shape, lambda: _lib.check(_lib.lib().p2p_conv_window_run(ctypes.byref(d), _p(planes), _p(wq), _p(bias), _p(out),
                                                                           _DT[out.dtype], _stream())), umma=True)
+    return True
+
+
+def _window_wgrad(passes, x, dy, dwp, wtaps_total):
+    """weight gradient of a layer call (its forward-type passes) as ONE launch of the window wgrad kernel:
+    dW_t = sum over the padded grid of dout (laid out at the input's pitch) x shifted input window.  False if it does not fit."""
+    if not USE_WINDOW or not passes or x.dtype != torch.bfloat16 or _lib.lib().p2p_conv_force_simple(-1) == 1:
+        return False
+    P0 = passes[0]
+    s_in, s_out = P0.sy, P0.oys
+    K, J = P0.K, P0.J
+    if (P0.sx != s_in or P0.oxs != s_out or s_in not in (1, 2) or s_out not in (1, 2) or (s_in == 2 and s_out == 2)
+            or K % 16 != 0 or J % 8 != 0 or P0.w_k != 1 or P0.w_j != K or P0.w_tap != J * K):
+        return False
+    reflect = P0.pad_mode == PAD_REFLECT
+    if reflect and s_in != 1:
+        return False
+    ntaps = sum(P.ntaps for P in passes)
+    if ntaps > 32:
+        return False
+    N, H, W, C = x.shape
+    pt = max(0, -min(P.dh[t] for P in passes for t in range(P.ntaps)))
+    pl = max(0, -min(P.dw[t] for P in passes for t in range(P.ntaps)))
+    taps, Hh, Wh = [], 0, 0
+    for P in passes:
+        if (P.sy, P.sx, P.oys, P.oxs, P.pad_mode, P.K, P.J) != (s_in, s_in, s_out, s_out, P0.pad_mode, K, J):
+            return False
+        ap = P.oyo * s_out + P.oxo
+        for t in range(P.ntaps):
+            a, b = P.dh[t] + pt, P.dw[t] + pl
+            taps.append((ap, (a % s_in) * s_in + (b % s_in), a // s_in, b // s_in, P.wtap[t]))
+            Hh, Wh = max(Hh, P.gy + a // s_in), max(Wh, P.gx + b // s_in)
+    if reflect:                      # reflection needs the margin on both sides to be smaller than the input
+        Hh, Wh = max(Hh, H + 2 * pt), max(Wh, W + 2 * pl)
+        if pt >= H or pl >= W:
+            return False
+    taps.sort(key=lambda q: (q[0], q[1]))
+    halo = max(q[2] * Wh + q[3] for q in taps)
+    useful = sum(P.gy * P.gx for P in passes) / float(len(passes))
+    if 64 + halo > _WIN_ROWS_MAX or useful < 0.6 * Hh * Wh:
+        return False
+    rows = (N * Hh * Wh + 63) // 64 * 64
+    lib = _lib.lib()
+    bplanes = torch.empty((s_in * s_in, rows, C), dtype=x.dtype, device=x.device)
+    _lib.check(lib.p2p_pad_planes(_p(x), _p(bplanes), N, H, W, C, pt, pl, Hh, Wh, s_in, rows, int(reflect), _DT[x.dtype], _stream()))
+    aplanes = torch.empty((s_out * s_out, rows, J), dtype=dy.dtype, device=dy.device)
+    _lib.check(lib.p2p_pad_planes(_p(dy), _p(aplanes), N, dy.shape[1], dy.shape[2], J, 0, 0, Hh, Wh, s_out, rows, 0, _DT[dy.dtype], _stream()))
+    IntArr = ctypes.c_int * len(taps)
+    ta, tb, th, tw, twt = (IntArr(*[q[i] for q in taps]) for i in range(5))
+    shape = _Shape(N, 1, sum(P.gy * P.gx * P.ntaps for P in passes), J, 1, K, Hh, Wh)
+    _timed("wgrad", shape, lambda: _lib.check(lib.p2p_conv_wgrad_window(
+        _p(aplanes), s_out * s_out, _p(bplanes), s_in * s_in, rows, Wh, J, K, _p(dwp), wtaps_total, len(taps), ta, tb, th, tw, twt,
+        _stream())), umma=True)
     return True
 
 
@@ -549,10 +602,12 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
     if need_dw:
         dwp = torch.zeros((KH, KW, Cout, Cin), dtype=torch.float32, device=x.device)
         if cfg.transposed:
-            for P in convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0]:
-                _run_wgrad(P, x, dy, dwp)
+            wpasses = convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0]
         else:
-            _run_wgrad(conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)[0], x, dy, dwp)
+            wpasses = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
+        if not _window_wgrad(wpasses, x, dy, dwp, KH * KW):
+            for P in wpasses:
+                _run_wgrad(P, x, dy, dwp)
         if thin is not None:
             dwp = dwp[:, :, :Cout0, :Cin0]
         dw = dwp.permute(3, 2, 0, 1) if cfg.transposed else dwp.permute(2, 3, 0, 1)
