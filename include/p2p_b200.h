@@ -108,7 +108,8 @@ int p2p_conv_force_simple(int on);
 /* Number of tcgen05 convolution kernels launched by this process so far. */
 long long p2p_conv_umma_launches(void);
 /* dW[wtap[t]*w_tap + k*w_k + j*w_j] += sum_{n,y,x} in[n, pad(..t..), k] * dout[n, y*oys+oyo, x*oxs+oxo, j]
- * (fp32 accumulate into a caller-zeroed fp32 buffer; safe to call once per pass of a layer). */
+ * (fp32 accumulate with red.add into the caller's fp32 buffer -- zeroed, or a live gradient buffer being
+ * accumulated; safe to call once per pass of a layer). */
 int p2p_conv_wgrad(const p2p_conv_pass* pass, const void* in, const void* dout, float* dweight, int dtype,
                    void* stream);
 /* dbias[j] = sum over rows of dout [rows, J] (overwrites). */
@@ -144,7 +145,7 @@ typedef struct {
 int p2p_pad_planes(const void* x, void* planes, int N, int H, int W, int C, int pt, int pl, int Hh, int Wh, int s,
                    long long plane_rows /* >= N*Hh*Wh; the tail of every plane is zero-filled */, int reflect /* s == 1 only */,
                    int dtype, void* stream);
-/* Weight gradients in window form:  dW[tap_w[t]][j][c] (fp32 [wtaps_total][J][C], caller-zeroed) +=
+/* Weight gradients in window form:  dW[tap_w[t]][j][c] (fp32 [wtaps_total][J][C], accumulated with red.add) +=
  *   sum_q aplanes[tap_a[t]][q][j] * bplanes[tap_b[t]][q + tap_dh[t]*Wp + tap_dw[t]][c]
  * over the padded pixel grid: aplanes = the output gradient laid out at the pitch of the padded input (zero where no output
  * exists), bplanes = the padded input (or its parity planes).  plane_rows % 64 == 0; taps grouped by (tap_a, tap_b); <= 32 taps. */

@@ -31,7 +31,7 @@ constexpr int kThreads = 288;
 constexpr int A_BYTES = 128 * 128;       // 16 KB: [128 rows][64 bf16] or 2 x [64 rows][64 bf16]
 constexpr int B_BYTES = 256 * 128;       // 32 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int SMEM_BYTES = kStages * STAGE_BYTES + 1024 /* alignment slack */ + 256 /* barriers */;
+constexpr int SMEM_BYTES = kStages * STAGE_BYTES + 1024 /* alignment slack */ + 256 /* barriers */ + 2048 /* staged bias */;
 constexpr int BLOCK64 = 64 * 128;        // bytes of one [64 rows][64 bf16] block
 
 struct UmmaArgs {
@@ -287,6 +287,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         // ================================ MMA issuer (one thread) ================================
         if (lane == 0) {
             const uint32_t idesc = make_idesc(BN, MODE == 2, MODE != 0);
+            // loop-invariant descriptor halves; the k16 advance is an add on the start-address field
+            const uint64_t a_hi = MODE == 2 ? make_desc(0, BLOCK64, 1024) : make_desc(0, 16, 1024);
+            const uint64_t b_hi = MODE == 0 ? make_desc(0, 16, 1024) : make_desc(0, BLOCK64, 1024);
+            const uint32_t a_k16 = MODE == 2 ? (2048u >> 4) : (32u >> 4), b_k16 = MODE == 0 ? (32u >> 4) : (2048u >> 4);
             int it = 0, li = 0;
             for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
                 const Work wk = decode_work<MODE>(a, w);
@@ -295,21 +299,22 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 if (v >= 1) mbar_wait(tempty(acc), (uint32_t)((v - 1) & 1));
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * 256;
+                int cc = MODE != 2 ? kb0 % a.cpb : 0;        // channel chunk inside the tap (the last one may be short)
                 for (int kb = kb0; kb < kb1; ++kb, ++it) {
                     int nk16 = 4;
                     if (MODE != 2) {
-                        const int t = kb / a.cpb, c0 = (kb - t * a.cpb) * 64;
-                        nk16 = min(64, K - c0) >> 4;
+                        nk16 = min(64, K - cc * 64) >> 4;
+                        if (++cc == a.cpb) cc = 0;
                     }
                     const int s = it % kStages;
+                    const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_BYTES;
+                    const uint64_t ad = a_hi | (uint64_t)(sa >> 4), bd = b_hi | (uint64_t)(sb >> 4);
                     mbar_wait(full(s), (uint32_t)((it / kStages) & 1));
                     tc_fence_after();
-                    const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_BYTES;
-                    for (int k16 = 0; k16 < nk16; ++k16) {
-                        const uint64_t ad = MODE == 2 ? make_desc(sa + k16 * 2048, BLOCK64, 1024) : make_desc(sa + k16 * 32, 16, 1024);
-                        const uint64_t bd = MODE == 0 ? make_desc(sb + k16 * 32, 16, 1024) : make_desc(sb + k16 * 2048, BLOCK64, 1024);
-                        umma_bf16(d_tmem, ad, bd, idesc, (kb > kb0 || k16 > 0) ? 1u : 0u);
-                    }
+                    umma_bf16(d_tmem, ad, bd, idesc, kb > kb0 ? 1u : 0u);
+                    if (nk16 > 1) umma_bf16(d_tmem, ad + a_k16, bd + b_k16, idesc, 1u);
+                    if (nk16 > 2) umma_bf16(d_tmem, ad + 2 * a_k16, bd + 2 * b_k16, idesc, 1u);
+                    if (nk16 > 3) umma_bf16(d_tmem, ad + 3 * a_k16, bd + 3 * b_k16, idesc, 1u);
                     umma_commit(empty(s));
                 }
                 umma_commit(tfull(acc));
@@ -340,21 +345,32 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                 obase = (long long)P.wtap[wk.tap] * P.w_tap + (long long)j * P.w_j + c_begin;
             }
             const bool add_bias = MODE != 2 && a.bias != nullptr && wk.sp == 0;
+            float* bs_ = reinterpret_cast<float*>(smem_raw + (bars + 256 - smem_u32(smem_raw))) + acc * 256;
+            if (MODE != 2) {
+                for (int c = row; c < BN; c += 128) bs_[c] = (add_bias && c < c_count) ? __ldg(a.bias + c_begin + c) : 0.f;
+                asm volatile("bar.sync 1, 128;" ::: "memory");      // double-buffered by accumulator slot
+            }
             mbar_wait(tfull(acc), (uint32_t)(v & 1));
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + acc * 256;
-            for (int c = 0; c < BN; c += 16) {
-                uint32_t r[16];
-                tmem_ld16(taddr + c, r);
-                tmem_ld_wait();
+            for (int c2 = 0; c2 < BN; c2 += 32) {
+              uint32_t r2[2][16];
+              tmem_ld16(taddr + c2, r2[0]);
+              if (c2 + 16 < BN) tmem_ld16(taddr + c2 + 16, r2[1]);
+              tmem_ld_wait();
+#pragma unroll
+              for (int hh = 0; hh < 2; ++hh) {
+                const int c = c2 + hh * 16;
                 if (!rok || c >= c_count) continue;
                 float f[16];
 #pragma unroll
-                for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(r[i]);
-                if (add_bias) {
+                for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(r2[hh][i]);
+                if (MODE != 2) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (c + i < c_count) f[i] += __ldg(a.bias + c_begin + c + i);
+                    for (int i = 0; i < 4; ++i) {
+                        const float4 bv = *reinterpret_cast<const float4*>(bs_ + c + 4 * i);
+                        f[4 * i] += bv.x; f[4 * i + 1] += bv.y; f[4 * i + 2] += bv.z; f[4 * i + 3] += bv.w;
+                    }
                 }
                 const bool fullv = c + 16 <= c_count;
                 if (a.out_bf16) {
@@ -394,6 +410,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                             if (c + i < c_count) o[i] = f[i];
                     }
                 }
+              }
             }
             tc_fence_before();
             mbar_arrive(tempty(acc));
@@ -540,7 +557,7 @@ int conv_wgrad_umma(const p2p_conv_pass* P, const void* in, const void* dout, fl
     }
     a.kb_per_split = (a.total_kb + nsplit - 1) / nsplit;
     a.nsplit = (a.total_kb + a.kb_per_split - 1) / a.kb_per_split;
-    a.atomic = a.nsplit > 1;      // dW is caller-zeroed and the taps of different passes of a layer are disjoint
+    a.atomic = 1;                 // dW += : the caller may hand in a live gradient buffer (FusedAdam's flat grads)
     a.nwork = tiles * a.nsplit;
     return launch<2>(a, st, "conv_umma_kernel<2>");
 }

@@ -23,11 +23,12 @@ namespace p2p {
 namespace {
 
 constexpr int WBM = 128;
-constexpr int kBStages = 4;
+constexpr int kBStagesMax = 16;
 constexpr int kWinRowsMax = 320;                    // 40 KB per window buffer
 constexpr int WIN_BYTES = kWinRowsMax * 128;
 constexpr int WB_BYTES = 256 * 128;                 // one weight tile: up to 256 output channels x 64 channels
-constexpr int WSMEM = 2 * WIN_BYTES + kBStages * WB_BYTES + 1024 + 256;
+constexpr int WRING_BYTES = 4 * WB_BYTES;             // 128 KB of weight tiles in flight, cut into b_stage_bytes stages
+constexpr int WSMEM = 2 * WIN_BYTES + WRING_BYTES + 1024 + 512 + 2048;     // + barriers + 2 x 256 staged bias values
 constexpr int kWThreads = 192;
 
 struct WindowArgs {
@@ -45,6 +46,7 @@ struct WindowArgs {
     int BN, n_tiles, m_tiles, cpb;
     int out_bf16, b_mn_major;
     int base_off_mode;
+    int b_stages, b_stage_bytes;   // weight-tile ring: as many stages as fit 128 KB (TMA latency needs bytes in flight)
     short shift[P2P_MAX_TAPS];       // dh*Wp + dw
     unsigned char wtap[P2P_MAX_TAPS];
     long long nwork;
@@ -109,15 +111,18 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t wbase = base + 2 * WIN_BYTES;
-    const uint32_t bars = wbase + kBStages * WB_BYTES;
-    // barriers: afull[2] aempty[2] bfull[S] bempty[S] tfull[2] tempty[2], then the TMEM base word
+    const uint32_t bars = wbase + WRING_BYTES;
+    const int kBStages = a.b_stages;
+    // barriers: afull[2] aempty[2] bfull[16] bempty[16] tfull[2] tempty[2], then the TMEM base word
     auto afull = [&](int i) { return bars + 8u * i; };
     auto aempty = [&](int i) { return bars + 8u * (2 + i); };
     auto bfull = [&](int s) { return bars + 8u * (4 + s); };
-    auto bempty = [&](int s) { return bars + 8u * (4 + kBStages + s); };
-    auto tfull = [&](int i) { return bars + 8u * (4 + 2 * kBStages + i); };
-    auto tempty = [&](int i) { return bars + 8u * (6 + 2 * kBStages + i); };
-    const uint32_t tmem_slot = bars + 8u * (8 + 2 * kBStages);
+    auto bempty = [&](int s) { return bars + 8u * (4 + kBStagesMax + s); };
+    auto tfull = [&](int i) { return bars + 8u * (4 + 2 * kBStagesMax + i); };
+    auto tempty = [&](int i) { return bars + 8u * (6 + 2 * kBStagesMax + i); };
+    const uint32_t tmem_slot = bars + 8u * (8 + 2 * kBStagesMax);
+    const uint32_t WB_STRIDE = (uint32_t)a.b_stage_bytes;
+    const uint32_t bias_u32 = bars + 512;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int BN = a.BN, C = a.C, J = a.J;
@@ -145,7 +150,8 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
         if (lane == 0) {
             asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_x) : "memory");
             asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_w) : "memory");
-            int ia = 0, ib = 0;     // window loads / weight-tile loads issued so far
+            int ia = 0;                     // window loads issued so far
+            uint32_t bs = 0, bph = 1;       // weight ring: stage, parity of the "empty" wait (first lap passes at once)
             for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x) {
                 const int nt = (int)(w % a.n_tiles);
                 const long long mtu = w / a.n_tiles;
@@ -161,11 +167,12 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
                     for (int bx = 0; bx < a.nboxes; ++bx)
                         tma_load_2d(base + ab * WIN_BYTES + bx * a.rows_per_box * 128, &a.tm_x, c0,
                                     (int)((long long)pl * a.Q + q0 + (long long)bx * a.rows_per_box), afull(ab));
-                    for (int t = a.pbeg[u][pl]; t < a.pbeg[u][pl + 1]; ++t, ++ib) {
-                        const int s = ib % kBStages;
-                        if (ib >= kBStages) mbar_wait(bempty(s), (uint32_t)((ib / kBStages - 1) & 1));
+                    for (int t = a.pbeg[u][pl]; t < a.pbeg[u][pl + 1]; ++t) {
+                        const uint32_t s = bs;
+                        mbar_wait(bempty(s), bph);
+                        if (++bs == (uint32_t)kBStages) { bs = 0; bph ^= 1u; }
                         mbar_expect_tx(bfull(s), b_bytes);
-                        const uint32_t dst = wbase + s * WB_BYTES;
+                        const uint32_t dst = wbase + s * WB_STRIDE;
                         if (!a.b_mn_major) {
                             tma_load_2d(dst, &a.tm_w, c0, (int)a.wtap[t] * J + j0, bfull(s));
                         } else {
@@ -182,7 +189,13 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
         if (lane == 0) {
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a.b_mn_major << 16) | ((uint32_t)(BN >> 3) << 17) |
                                    ((uint32_t)(WBM >> 4) << 24);
-            int ia = 0, ib = 0, li = 0;
+            // descriptors: everything but the 14-bit start address is loop invariant; per-k16 advance is an add on the
+            // low word (+32 B along K for K-major tiles, +2048 B for MN-major weight tiles)
+            const uint64_t a_hi = make_desc(0, 16, 1024, 0);
+            const uint64_t b_hi = a.b_mn_major ? make_desc(0, 8192, 1024, 0) : make_desc(0, 16, 1024, 0);
+            const uint32_t b_k16 = a.b_mn_major ? (2048u >> 4) : (32u >> 4);
+            int ia = 0, li = 0;
+            uint32_t bs = 0, bph = 0;       // weight ring: stage, parity of the "full" wait
             for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
                 const int u = (int)((w / a.n_tiles) / a.m_tiles);
                 const int acc = li & 1, v = li >> 1;
@@ -197,19 +210,19 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
                     mbar_wait(afull(ab), (uint32_t)((ia >> 1) & 1));
                     tc_fence_after();
                     const uint32_t win = base + ab * WIN_BYTES;
-                    for (int t = a.pbeg[u][pl]; t < a.pbeg[u][pl + 1]; ++t, ++ib) {
-                        const int s = ib % kBStages;
-                        mbar_wait(bfull(s), (uint32_t)((ib / kBStages) & 1));
+                    const int t_end = a.pbeg[u][pl + 1];
+                    for (int t = a.pbeg[u][pl]; t < t_end; ++t) {
+                        const uint32_t s = bs;
+                        const uint64_t ad = a_hi | (uint64_t)((win + (uint32_t)a.shift[t] * 128u) >> 4);
+                        const uint64_t bd = b_hi | (uint64_t)((wbase + s * WB_STRIDE) >> 4);
+                        mbar_wait(bfull(s), bph);
+                        if (++bs == (uint32_t)kBStages) { bs = 0; bph ^= 1u; }
                         tc_fence_after();
-                        const uint32_t sa = win + (uint32_t)a.shift[t] * 128u;
-                        const uint32_t boff = a.base_off_mode ? ((sa >> 7) & 7u) : 0u;
-                        const uint32_t sb = wbase + s * WB_BYTES;
-                        for (int k16 = 0; k16 < nk16; ++k16) {
-                            const uint64_t ad = make_desc(sa + k16 * 32, 16, 1024, boff);
-                            const uint64_t bd = a.b_mn_major ? make_desc(sb + k16 * 2048, 8192, 1024, 0) : make_desc(sb + k16 * 32, 16, 1024, 0);
-                            umma_bf16(d_tmem, ad, bd, idesc, accumulate);
-                            accumulate = 1;
-                        }
+                        umma_bf16(d_tmem, ad, bd, idesc, accumulate);
+                        if (nk16 > 1) umma_bf16(d_tmem, ad + 2, bd + b_k16, idesc, 1);
+                        if (nk16 > 2) umma_bf16(d_tmem, ad + 4, bd + 2 * b_k16, idesc, 1);
+                        if (nk16 > 3) umma_bf16(d_tmem, ad + 6, bd + 3 * b_k16, idesc, 1);
+                        accumulate = 1;
                         umma_commit(bempty(s));
                     }
                     umma_commit(aempty(ab));
@@ -221,7 +234,9 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
     } else {
         // ================================ epilogue ================================
         const int quarter = warp & 3, row = quarter * 32 + lane;
+        const int et = (warp - 2) * 32 + lane;            // 0..127 over the epilogue warps
         const long long plane = (long long)a.Hp * a.Wp;
+        float* bias_s = reinterpret_cast<float*>(smem_raw + (bias_u32 - smem_u32(smem_raw)));
         int li = 0;
         for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
             const int nt = (int)(w % a.n_tiles);
@@ -229,56 +244,65 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
             const int u = (int)(mtu / a.m_tiles);
             const long long mt = mtu - (long long)u * a.m_tiles;
             const int acc = li & 1, v = li >> 1;
+            const int c_begin = nt * BN, c_count = min(BN, J - c_begin);
+            float* bs_ = bias_s + acc * 256;
+            for (int c = et; c < BN; c += 128) bs_[c] = (a.bias && c < c_count) ? __ldg(a.bias + c_begin + c) : 0.f;
             const long long q = mt * WBM + row;
             const int n = (int)(q / plane);
             const int rem = (int)(q - (long long)n * plane);
             const int y = rem / a.Wp, x = rem - y * a.Wp;
             const bool rok = q < a.Q && y < a.gy[u] && x < a.gx[u];
-            const int c_begin = nt * BN, c_count = min(BN, J - c_begin);
             const long long obase = (((long long)n * a.OHf + (y * a.oys + a.oyo[u])) * a.OWf + (x * a.oxs + a.oxo[u])) * J + c_begin;
+            asm volatile("bar.sync 1, 128;" ::: "memory");      // bias staged (double-buffered by accumulator slot)
             mbar_wait(tfull(acc), (uint32_t)(v & 1));
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * 256;
-            for (int c = 0; c < BN; c += 16) {
-                uint32_t r[16];
-                tmem_ld16(taddr + c, r);
+            for (int c2 = 0; c2 < BN; c2 += 32) {
+                uint32_t r2[2][16];
+                tmem_ld16(taddr + c2, r2[0]);
+                if (c2 + 16 < BN) tmem_ld16(taddr + c2 + 16, r2[1]);
                 tmem_ld_wait();
-                if (!rok || c >= c_count) continue;
-                float f[16];
 #pragma unroll
-                for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(r[i]);
-                if (a.bias) {
+                for (int hh = 0; hh < 2; ++hh) {
+                    const int c = c2 + hh * 16;
+                    if (!rok || c >= c_count) continue;
+                    float f[16];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (c + i < c_count) f[i] += __ldg(a.bias + c_begin + c + i);
-                }
-                const bool fullv = c + 16 <= c_count;
-                if (a.out_bf16) {
-                    __nv_bfloat16* o = (__nv_bfloat16*)a.out + obase + c;
-                    if (fullv && (((uintptr_t)o) & 15) == 0) {
-                        uint32_t pk[8];
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
-                            pk[i] = *reinterpret_cast<uint32_t*>(&h);
-                        }
-                        reinterpret_cast<uint4*>(o)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                        reinterpret_cast<uint4*>(o)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i)
-                            if (c + i < c_count) o[i] = __float2bfloat16_rn(f[i]);
+                    for (int i = 0; i < 4; ++i) {
+                        const float4 bv = *reinterpret_cast<const float4*>(bs_ + c + 4 * i);
+                        f[4 * i] = __uint_as_float(r2[hh][4 * i]) + bv.x;
+                        f[4 * i + 1] = __uint_as_float(r2[hh][4 * i + 1]) + bv.y;
+                        f[4 * i + 2] = __uint_as_float(r2[hh][4 * i + 2]) + bv.z;
+                        f[4 * i + 3] = __uint_as_float(r2[hh][4 * i + 3]) + bv.w;
                     }
-                } else {
-                    float* o = (float*)a.out + obase + c;
-                    if (fullv && (((uintptr_t)o) & 15) == 0) {
+                    const bool fullv = c + 16 <= c_count;
+                    if (a.out_bf16) {
+                        __nv_bfloat16* o = (__nv_bfloat16*)a.out + obase + c;
+                        if (fullv && (((uintptr_t)o) & 15) == 0) {
+                            uint32_t pk[8];
 #pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            reinterpret_cast<float4*>(o)[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                            for (int i = 0; i < 8; ++i) {
+                                __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+                                pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                            }
+                            reinterpret_cast<uint4*>(o)[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                            reinterpret_cast<uint4*>(o)[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i)
+                                if (c + i < c_count) o[i] = __float2bfloat16_rn(f[i]);
+                        }
                     } else {
+                        float* o = (float*)a.out + obase + c;
+                        if (fullv && (((uintptr_t)o) & 15) == 0) {
 #pragma unroll
-                        for (int i = 0; i < 16; ++i)
-                            if (c + i < c_count) o[i] = f[i];
+                            for (int i = 0; i < 4; ++i)
+                                reinterpret_cast<float4*>(o)[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i)
+                                if (c + i < c_count) o[i] = f[i];
+                        }
                     }
                 }
             }
@@ -329,11 +353,10 @@ __global__ void pad_nhwc_kernel(const T* __restrict__ x, T* __restrict__ xp, int
 // dW[wtap_t][j][c] += sum_q A[a_plane_t][q][j] * B[b_plane_t][q + shift_t][c]: the reduction index q runs over the padded pixel
 // grid (A = dout laid out at the same pitch, zero where no output exists).  Both operands are MN-major (rows = q): A is one
 // TMA tile per 64-row block, B one shifted WINDOW shared by all taps of a group; every tap owns BN TMEM columns.
-constexpr int kGStages = 3;
+constexpr int kGStagesMax = 8;
 constexpr int GA_BYTES = 2 * 8192;                  // [64 q][128 j]
-constexpr int GB_BYTES = kWinRowsMax * 128;         // [64 + halo q][64 c]
-constexpr int GSTAGE = GA_BYTES + GB_BYTES;
-constexpr int GSMEM = kGStages * GSTAGE + 1024 + 256;
+constexpr int GRING_BYTES = 3 * (GA_BYTES + kWinRowsMax * 128);     // 168 KB cut into stages of A tile + B window
+constexpr int GSMEM = GRING_BYTES + 1024 + 256;
 constexpr int kMaxGroups = 8;
 
 struct WgradWinArgs {
@@ -345,6 +368,7 @@ struct WgradWinArgs {
     int J, C, BN, j_tiles, c_tiles, nsplit, kb_per_split, total_kb;
     int ntaps, ngroups, atomic;
     int b_nboxes, b_rows_per_box;
+    int stages, stage_bytes;
     int gbeg[kMaxGroups + 1];
     short ga[kMaxGroups], gb[kMaxGroups];
     short shift[32];
@@ -355,10 +379,12 @@ struct WgradWinArgs {
 __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const __grid_constant__ WgradWinArgs a) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t bars = base + kGStages * GSTAGE;
+    const uint32_t bars = base + GRING_BYTES;
+    const int kGStages = a.stages;
+    const uint32_t GSTAGE = (uint32_t)a.stage_bytes;
     auto full = [&](int s) { return bars + 8u * s; };
-    auto empty = [&](int s) { return bars + 8u * (kGStages + s); };
-    const uint32_t tfull = bars + 8u * (2 * kGStages), tempty = tfull + 8, tmem_slot = tfull + 16;
+    auto empty = [&](int s) { return bars + 8u * (kGStagesMax + s); };
+    const uint32_t tfull = bars + 8u * (2 * kGStagesMax), tempty = tfull + 8, tmem_slot = tfull + 16;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int BN = a.BN;
     const uint32_t b_bytes = (uint32_t)a.b_nboxes * a.b_rows_per_box * 128u;
@@ -384,16 +410,17 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
         if (lane == 0) {
             asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_a) : "memory");
             asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_b) : "memory");
-            int it = 0;
+            uint32_t rs = 0, rph = 1;       // ring stage, parity of the "empty" wait (first lap passes at once)
             for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x) {
                 const int sp = (int)(w % a.nsplit);
                 const long long r = w / a.nsplit;
                 const int ct = (int)(r % a.c_tiles), jt = (int)(r / a.c_tiles);
                 const int kb0 = sp * a.kb_per_split, kb1 = min(a.total_kb, kb0 + a.kb_per_split);
                 for (int kb = kb0; kb < kb1; ++kb)
-                    for (int g = 0; g < a.ngroups; ++g, ++it) {
-                        const int s = it % kGStages;
-                        if (it >= kGStages) mbar_wait(empty(s), (uint32_t)((it / kGStages - 1) & 1));
+                    for (int g = 0; g < a.ngroups; ++g) {
+                        const uint32_t s = rs;
+                        mbar_wait(empty(s), rph);
+                        if (++rs == (uint32_t)kGStages) { rs = 0; rph ^= 1u; }
                         mbar_expect_tx(full(s), GA_BYTES + b_bytes);
                         const uint32_t sa = base + s * GSTAGE, sb = sa + GA_BYTES;
                         const long long qa = (long long)a.ga[g] * a.Qs + (long long)kb * 64;
@@ -410,25 +437,31 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
         if (lane == 0) {
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) |
                                    ((uint32_t)(WBM >> 4) << 24);
-            int it = 0, li = 0;
+            const uint64_t d_hi = make_desc(0, 8192, 1024, 0);      // both operands MN-major; +2048 B per k16
+            int li = 0;
+            uint32_t rs = 0, rph = 0;
             for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
                 const int sp = (int)(w % a.nsplit);
                 const int kb0 = sp * a.kb_per_split, kb1 = min(a.total_kb, kb0 + a.kb_per_split);
                 if (li >= 1) mbar_wait(tempty, (uint32_t)((li - 1) & 1));
                 tc_fence_after();
                 for (int kb = kb0; kb < kb1; ++kb)
-                    for (int g = 0; g < a.ngroups; ++g, ++it) {
-                        const int s = it % kGStages;
-                        mbar_wait(full(s), (uint32_t)((it / kGStages) & 1));
-                        tc_fence_after();
+                    for (int g = 0; g < a.ngroups; ++g) {
+                        const uint32_t s = rs;
                         const uint32_t sa = base + s * GSTAGE, sb = sa + GA_BYTES;
-                        for (int t = a.gbeg[g]; t < a.gbeg[g + 1]; ++t) {
+                        const uint64_t ad = d_hi | (uint64_t)(sa >> 4);
+                        const uint32_t first = kb > kb0 ? 1u : 0u;
+                        mbar_wait(full(s), rph);
+                        if (++rs == (uint32_t)kGStages) { rs = 0; rph ^= 1u; }
+                        tc_fence_after();
+                        const int t_end = a.gbeg[g + 1];
+                        for (int t = a.gbeg[g]; t < t_end; ++t) {
                             const uint32_t d_tmem = tmem_base + t * BN;
-                            const uint32_t sbt = sb + (uint32_t)a.shift[t] * 128u;
-#pragma unroll
-                            for (int k16 = 0; k16 < 4; ++k16)
-                                umma_bf16(d_tmem, make_desc(sa + k16 * 2048, 8192, 1024, 0), make_desc(sbt + k16 * 2048, 8192, 1024, 0), idesc,
-                                          (kb > kb0 || k16 > 0) ? 1u : 0u);
+                            const uint64_t bd = d_hi | (uint64_t)((sb + (uint32_t)a.shift[t] * 128u) >> 4);
+                            umma_bf16(d_tmem, ad, bd, idesc, first);
+                            umma_bf16(d_tmem, ad + 128, bd + 128, idesc, 1);
+                            umma_bf16(d_tmem, ad + 256, bd + 256, idesc, 1);
+                            umma_bf16(d_tmem, ad + 384, bd + 384, idesc, 1);
                         }
                         umma_commit(empty(s));
                     }
@@ -449,12 +482,16 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
             for (int t = 0; t < a.ntaps; ++t) {
                 float* o = a.dw + (long long)a.wtap[t] * a.w_tap + (long long)j * a.C + c_begin;
-                for (int c = 0; c < BN; c += 16) {
-                    uint32_t v[16];
-                    tmem_ld16(taddr + t * BN + c, v);
+                for (int c2 = 0; c2 < BN; c2 += 32) {
+                    uint32_t v2[2][16];
+                    tmem_ld16(taddr + t * BN + c2, v2[0]);
+                    if (c2 + 16 < BN) tmem_ld16(taddr + t * BN + c2 + 16, v2[1]);
                     tmem_ld_wait();
-                    if (!rok || c >= c_count) continue;
-                    if (a.atomic) {
+#pragma unroll
+                    for (int hh = 0; hh < 2; ++hh) {
+                        const int c = c2 + hh * 16;
+                        const uint32_t(&v)[16] = v2[hh];
+                        if (!rok || c >= c_count) continue;
                         if (c + 16 <= c_count && ((((uintptr_t)(o + c)) & 15) == 0)) {
 #pragma unroll
                             for (int i = 0; i < 4; ++i)
@@ -465,15 +502,6 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
                             for (int i = 0; i < 16; ++i)
                                 if (c + i < c_count) atomicAdd(o + c + i, __uint_as_float(v[i]));
                         }
-                    } else if (c + 16 <= c_count && ((((uintptr_t)(o + c)) & 15) == 0)) {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            reinterpret_cast<float4*>(o + c)[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
-                                                                              __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i)
-                            if (c + i < c_count) o[c + i] = __uint_as_float(v[i]);
                     }
                 }
             }
@@ -634,6 +662,9 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
         a.BN = bn < 16 ? 16 : bn;
     }
     a.n_tiles = (J + a.BN - 1) / a.BN;
+    a.b_stage_bytes = a.b_mn_major ? ((a.BN + 63) / 64) * 8192 : ((a.BN * 128 + 1023) / 1024) * 1024;
+    a.b_stages = WRING_BYTES / a.b_stage_bytes;
+    if (a.b_stages > kBStagesMax) a.b_stages = kBStagesMax;
     const long long mt = (a.Q + WBM - 1) / WBM;
     if (mt * a.nsub > 2000000000LL / a.n_tiles) return fail(P2P_ENOTSUP, "too many tiles");
     a.m_tiles = (int)mt;
@@ -730,6 +761,9 @@ extern "C" int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const v
     a.b_nboxes = (brows + 255) / 256;
     a.b_rows_per_box = ((brows + a.b_nboxes - 1) / a.b_nboxes + 7) / 8 * 8;
     if (a.b_nboxes * a.b_rows_per_box > kWinRowsMax) return fail(P2P_ENOTSUP, "window boxes exceed the buffer");
+    a.stage_bytes = GA_BYTES + a.b_nboxes * a.b_rows_per_box * 128;
+    a.stages = GRING_BYTES / a.stage_bytes;
+    if (a.stages > kGStagesMax) a.stages = kGStagesMax;
     a.total_kb = (int)(plane_rows / 64);
     const long long items = (long long)a.j_tiles * a.c_tiles;
     int sms = 148, dev = 0;
@@ -740,7 +774,7 @@ extern "C" int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const v
     if (nsplit < 1) nsplit = 1;
     a.kb_per_split = (a.total_kb + nsplit - 1) / nsplit;
     a.nsplit = (a.total_kb + a.kb_per_split - 1) / a.kb_per_split;
-    a.atomic = a.nsplit > 1;
+    a.atomic = 1;                 // dW += : the caller may hand in a live gradient buffer
     a.nwork = items * a.nsplit;
     if (int rc = encode_2d(&a.tm_a, aplanes, (unsigned long long)J, (unsigned long long)n_aplanes * plane_rows, 64, 64)) return rc;
     if (int rc = encode_2d(&a.tm_b, bplanes, (unsigned long long)C, (unsigned long long)n_bplanes * plane_rows, 64, (unsigned)a.b_rows_per_box)) return rc;

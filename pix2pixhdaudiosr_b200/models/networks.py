@@ -72,6 +72,7 @@ class _ConvBase(nn.Module):
         self.weight = nn.Parameter(phys.permute(*inv))            # logical view of the physical buffer
         self.bias = nn.Parameter(b)
         self.w16 = None                                           # bf16 shadow of the physical buffer
+        self.gphys = None                                         # FusedAdam: this weight's slice of the flat grads
         self._perm = perm
         self.weight._p2p_conv = self                              # lets optim.FusedAdam find the physical layout
 
@@ -142,7 +143,7 @@ def _conv_block(conv, x, cfg, needs_wgrad, norm, act_mod, res):
         conv.sync_shadow()
     act, slope = _act_code(act_mod)
     return ops.ConvBlockFn.apply(x, w, b, conv.w16, res, cfg, norm is not None, act, slope,
-                                 norm.eps if norm is not None else 0.0)
+                                 norm.eps if norm is not None else 0.0, conv.gphys if needs_wgrad else None)
 
 
 def weights_init(m):

@@ -543,8 +543,10 @@ def _conv_forward(x, weight, bias, w16, cfg, out_dtype):
     return y
 
 
-def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
-    """gradients of conv_forward; dy has x's dtype.  Returns (dx, dw_logical, db)."""
+def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None):
+    """gradients of conv_forward; dy has x's dtype.  Returns (dx, dw_logical, db).  With `gphys` (FusedAdam's view of
+    this weight's slice of the flat gradient buffer, physical layout) the wgrad kernels accumulate straight into it
+    and dw comes back None -- no zero-fill, no AccumulateGrad add."""
     N, H, W, _ = x.shape
     wphys, Cout, Cin, KH, KW = _phys(weight, cfg)
     assert dy.dtype == x.dtype and dy.is_contiguous()
@@ -600,7 +602,8 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
         if Cin != Cin0:
             dx = dx[..., :Cin0].contiguous()
     if need_dw:
-        dwp = torch.zeros((KH, KW, Cout, Cin), dtype=torch.float32, device=x.device)
+        direct = gphys is not None and thin is None and tuple(gphys.shape) == (KH, KW, Cout, Cin)
+        dwp = gphys if direct else torch.zeros((KH, KW, Cout, Cin), dtype=torch.float32, device=x.device)
         if cfg.transposed:
             wpasses = convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0]
         else:
@@ -608,6 +611,8 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
         if not _window_wgrad(wpasses, x, dy, dwp, KH * KW):
             for P in wpasses:
                 _run_wgrad(P, x, dy, dwp)
+        if direct:
+            return dx, None, db
         if thin is not None:
             dwp = dwp[:, :, :Cout0, :Cin0]
         dw = dwp.permute(3, 2, 0, 1) if cfg.transposed else dwp.permute(2, 3, 0, 1)
@@ -639,13 +644,13 @@ def conv_forward(x, weight, bias, w16, cfg, out_dtype):
         _FLOP_RATIO = 1.0
 
 
-def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db):
+def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None):
     global _FLOP_RATIO
     if _TIMING is None:
-        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db)
+        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys)
     _FLOP_RATIO = _alg_ratio(x, weight, cfg)
     try:
-        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db)
+        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys)
     finally:
         _FLOP_RATIO = 1.0
 
@@ -680,7 +685,7 @@ class ConvBlockFn(torch.autograd.Function):
     include/p2p_b200.h), so only O(1)-scaled tensors are ever rounded to bf16."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, w16, res, cfg, norm, act, slope, eps):
+    def forward(ctx, x, weight, bias, w16, res, cfg, norm, act, slope, eps, gphys=None):
         _need_cuda(x, weight)
         x = x.contiguous()
         plain = (not norm) and act == ACT_NONE and res is None
@@ -694,6 +699,7 @@ class ConvBlockFn(torch.autograd.Function):
             ysave = y
         ctx.save_for_backward(x, weight, w16, ysave, stats)
         ctx.cfg = (cfg, norm, act, slope, bias is not None, res is not None, plain)
+        ctx.gphys = gphys
         return z
 
     @staticmethod
@@ -703,8 +709,8 @@ class ConvBlockFn(torch.autograd.Function):
         dz = dz.contiguous()
         dy = dz if plain else norm_act_backward(y, stats, dz, norm, act, slope)
         dx, dw, db = conv_backward(x, weight, w16, dy, cfg, ctx.needs_input_grad[0], ctx.needs_input_grad[1],
-                                   has_bias and ctx.needs_input_grad[2])
-        return dx, dw, db, None, (dz if has_res else None), None, None, None, None, None
+                                   has_bias and ctx.needs_input_grad[2], ctx.gphys)
+        return dx, dw, db, None, (dz if has_res else None), None, None, None, None, None, None
 
 
 class InstNormActFn(torch.autograd.Function):
