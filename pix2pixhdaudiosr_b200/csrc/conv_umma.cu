@@ -102,6 +102,11 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ bool elect_one() {     // one lane of a converged warp
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -284,8 +289,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
         fence_proxy_async();
         for (int d = it > kLook ? it - kLook : 0; d < it; ++d) mbar_arrive(full(d % kStages));
     } else if (warp == 8) {
-        // ================================ MMA issuer (one thread) ================================
-        if (lane == 0) {
+        // ================================ MMA issuer (warp-uniform schedule, one elected lane issues) ==========
+        {
             const uint32_t idesc = make_idesc(BN, MODE == 2, MODE != 0);
             // loop-invariant descriptor halves; the k16 advance is an add on the start-address field
             const uint64_t a_hi = MODE == 2 ? make_desc(0, BLOCK64, 1024) : make_desc(0, 16, 1024);
@@ -311,13 +316,17 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     const uint64_t ad = a_hi | (uint64_t)(sa >> 4), bd = b_hi | (uint64_t)(sb >> 4);
                     mbar_wait(full(s), (uint32_t)((it / kStages) & 1));
                     tc_fence_after();
-                    umma_bf16(d_tmem, ad, bd, idesc, kb > kb0 ? 1u : 0u);
-                    if (nk16 > 1) umma_bf16(d_tmem, ad + a_k16, bd + b_k16, idesc, 1u);
-                    if (nk16 > 2) umma_bf16(d_tmem, ad + 2 * a_k16, bd + 2 * b_k16, idesc, 1u);
-                    if (nk16 > 3) umma_bf16(d_tmem, ad + 3 * a_k16, bd + 3 * b_k16, idesc, 1u);
-                    umma_commit(empty(s));
+                    if (elect_one()) {
+                        umma_bf16(d_tmem, ad, bd, idesc, kb > kb0 ? 1u : 0u);
+                        if (nk16 > 1) umma_bf16(d_tmem, ad + a_k16, bd + b_k16, idesc, 1u);
+                        if (nk16 > 2) umma_bf16(d_tmem, ad + 2 * a_k16, bd + 2 * b_k16, idesc, 1u);
+                        if (nk16 > 3) umma_bf16(d_tmem, ad + 3 * a_k16, bd + 3 * b_k16, idesc, 1u);
+                        umma_commit(empty(s));
+                    }
+                    __syncwarp();
                 }
-                umma_commit(tfull(acc));
+                if (elect_one()) umma_commit(tfull(acc));
+                __syncwarp();
             }
         }
         __syncwarp();

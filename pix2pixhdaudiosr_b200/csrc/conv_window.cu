@@ -76,6 +76,11 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm,
         "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
         "l"(tm), "r"(c0), "r"(c1), "r"(bar) : "memory");
 }
+__device__ __forceinline__ bool elect_one() {     // one lane of a converged warp
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
@@ -186,7 +191,7 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
         __syncwarp();
     } else if (warp == 1) {
         // ================================ MMA issuer ================================
-        if (lane == 0) {
+        {   // the whole warp walks the schedule (keeps every value warp-uniform); one elected lane issues
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a.b_mn_major << 16) | ((uint32_t)(BN >> 3) << 17) |
                                    ((uint32_t)(WBM >> 4) << 24);
             // descriptors: everything but the 14-bit start address is loop invariant; per-k16 advance is an add on the
@@ -218,16 +223,21 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
                         mbar_wait(bfull(s), bph);
                         if (++bs == (uint32_t)kBStages) { bs = 0; bph ^= 1u; }
                         tc_fence_after();
-                        umma_bf16(d_tmem, ad, bd, idesc, accumulate);
-                        if (nk16 > 1) umma_bf16(d_tmem, ad + 2, bd + b_k16, idesc, 1);
-                        if (nk16 > 2) umma_bf16(d_tmem, ad + 4, bd + 2 * b_k16, idesc, 1);
-                        if (nk16 > 3) umma_bf16(d_tmem, ad + 6, bd + 3 * b_k16, idesc, 1);
+                        if (elect_one()) {
+                            umma_bf16(d_tmem, ad, bd, idesc, accumulate);
+                            if (nk16 > 1) umma_bf16(d_tmem, ad + 2, bd + b_k16, idesc, 1);
+                            if (nk16 > 2) umma_bf16(d_tmem, ad + 4, bd + 2 * b_k16, idesc, 1);
+                            if (nk16 > 3) umma_bf16(d_tmem, ad + 6, bd + 3 * b_k16, idesc, 1);
+                            umma_commit(bempty(s));
+                        }
+                        __syncwarp();
                         accumulate = 1;
-                        umma_commit(bempty(s));
                     }
-                    umma_commit(aempty(ab));
+                    if (elect_one()) umma_commit(aempty(ab));
+                    __syncwarp();
                 }
-                umma_commit(tfull(acc));
+                if (elect_one()) umma_commit(tfull(acc));
+                __syncwarp();
             }
         }
         __syncwarp();
@@ -434,7 +444,7 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
         }
         __syncwarp();
     } else if (warp == 1) {
-        if (lane == 0) {
+        {   // whole warp walks the schedule, one elected lane issues
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) |
                                    ((uint32_t)(WBM >> 4) << 24);
             const uint64_t d_hi = make_desc(0, 8192, 1024, 0);      // both operands MN-major; +2048 B per k16
@@ -455,17 +465,21 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
                         if (++rs == (uint32_t)kGStages) { rs = 0; rph ^= 1u; }
                         tc_fence_after();
                         const int t_end = a.gbeg[g + 1];
-                        for (int t = a.gbeg[g]; t < t_end; ++t) {
-                            const uint32_t d_tmem = tmem_base + t * BN;
-                            const uint64_t bd = d_hi | (uint64_t)((sb + (uint32_t)a.shift[t] * 128u) >> 4);
-                            umma_bf16(d_tmem, ad, bd, idesc, first);
-                            umma_bf16(d_tmem, ad + 128, bd + 128, idesc, 1);
-                            umma_bf16(d_tmem, ad + 256, bd + 256, idesc, 1);
-                            umma_bf16(d_tmem, ad + 384, bd + 384, idesc, 1);
+                        if (elect_one()) {
+                            for (int t = a.gbeg[g]; t < t_end; ++t) {
+                                const uint32_t d_tmem = tmem_base + t * BN;
+                                const uint64_t bd = d_hi | (uint64_t)((sb + (uint32_t)a.shift[t] * 128u) >> 4);
+                                umma_bf16(d_tmem, ad, bd, idesc, first);
+                                umma_bf16(d_tmem, ad + 128, bd + 128, idesc, 1);
+                                umma_bf16(d_tmem, ad + 256, bd + 256, idesc, 1);
+                                umma_bf16(d_tmem, ad + 384, bd + 384, idesc, 1);
+                            }
+                            umma_commit(empty(s));
                         }
-                        umma_commit(empty(s));
+                        __syncwarp();
                     }
-                umma_commit(tfull);
+                if (elect_one()) umma_commit(tfull);
+                __syncwarp();
             }
         }
         __syncwarp();

@@ -30,7 +30,7 @@ def main():
     torch.manual_seed(0)
     print("%-24s %-6s %9s %9s %8s" % ("layer", "pass", "GFLOP", "ms", "TFLOP/s"))
     for name, tr, Cin, Cout, k, stride, pad, reflect, (N, H, W), norm in LAYERS:
-        if args.only and args.only != name:
+        if args.only and name not in args.only.split(","):
             continue
         x = torch.randn(N, H, W, Cin, device="cuda").bfloat16()
         shape = (Cin, Cout, k, k) if tr else (Cout, Cin, k, k)
