@@ -158,6 +158,17 @@ int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* planes, const
  * dxp is [N, H+2p, W+2p, C], dx is [N,H,W,C]. */
 int p2p_reflect_pad_fold(const void* dxp, void* dx, int N, int H, int W, int C, int p, int dtype, void* stream);
 
+/* Operand packing for the thin layers (networks.py:145-154 G's 7x7 2->ngf / ngf->2 convolutions, :340-361 D's 4->ndf and
+ * ->1 logit convolutions): KW*C <= 16 kernel-column x channel pairs become the 16 tensor-core channels of a KHx1 convolution.
+ *   pack_in:  xpk[n, y, ox, dw*C + c]      = pad(x)[n, y, ox*stride + dw, c]          xpk: [N][H+2pad][OW][16]
+ *   fold_out: y[n, oh, ow, co]             = bias[co] + sum_dw ypk[n, oh, ow + dw, dw*Cout + co]   ypk: fp32 [N][OH][Wp][16]
+ *   pack_dy:  dypk[n, y, x', dw*Cout + co] = dy[n, y, x' - dw, co] (0 outside)        dypk: [N][OH][Wp][16] */
+int p2p_pack_in(const void* x, void* xpk, int N, int H, int W, int C, int KW, int stride, int pad, int reflect, int OW,
+                int dtype, void* stream);
+int p2p_fold_out(const float* ypk, const float* bias, void* y, int N, int OH, int Wp, int OW, int KW, int Cout, int out_dtype,
+                 void* stream);
+int p2p_pack_dy(const void* dy, void* dypk, int N, int OH, int OW, int Cout, int KW, int Wp, int dtype, void* stream);
+
 /* InstanceNorm2d(affine=False, eps) [+ activation] [+ residual]:  z = act((y-mean)/sqrt(var+eps)) + res.
  * act: 0 none, 1 ReLU, 2 LeakyReLU(slope).  norm=0 skips the normalisation (plain activation).
  * y: [N,HW,C] `y_dtype`; res,z: `dtype`; stats: fp32 [N,C,2] = (mean, rstd), written by fwd, read by bwd. */

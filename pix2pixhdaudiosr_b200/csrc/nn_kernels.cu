@@ -121,6 +121,173 @@ __global__ void in_bwd_apply_kernel(const TY* __restrict__ y, const float* __res
     }
 }
 
+
+// ---- four-channel (vector) forms of the InstanceNorm kernels: C % 4 == 0, aligned pointers, < 2^31 vectors ----------
+// grid (ceil(C4/32), N, S), block (32, 8)
+template <typename T>
+__global__ void __launch_bounds__(256) in_stats_v4_kernel(const T* __restrict__ y, float* __restrict__ raw, int HW, int C, int chunk) {
+    __shared__ float sm[8][32][9];
+    const int cg = blockIdx.x * 32 + threadIdx.x, n = blockIdx.y, C4 = C >> 2;
+    const int r0 = blockIdx.z * chunk, r1 = min(HW, r0 + chunk);
+    float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f};
+    if (cg < C4) {
+        const T* base = y + (long long)n * HW * C + cg * 4;
+        float shift[4];
+        ld4(base, shift);
+        int r = r0 + threadIdx.y;
+        for (; r + 8 < r1; r += 16) {
+            float v[4], u[4];
+            ld4(base + (long long)r * C, v);
+            ld4(base + (long long)(r + 8) * C, u);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float d = v[i] - shift[i], e = u[i] - shift[i];
+                a[i] += d + e; b[i] += d * d + e * e;
+            }
+        }
+        for (; r < r1; r += 8) {
+            float v[4];
+            ld4(base + (long long)r * C, v);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { const float d = v[i] - shift[i]; a[i] += d; b[i] += d * d; }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { sm[threadIdx.y][threadIdx.x][i] = a[i]; sm[threadIdx.y][threadIdx.x][4 + i] = b[i]; }
+    __syncthreads();
+    // 256 threads: one (column group, component) pair each
+    const int t = threadIdx.y * 32 + threadIdx.x, g = t >> 3, k = t & 7, cgo = blockIdx.x * 32 + g;
+    if (cgo < C4) {
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s += sm[i][g][k];
+        atomicAdd(raw + ((long long)n * C + cgo * 4 + (k & 3)) * 2 + (k >> 2), s);
+    }
+}
+
+template <typename TY, typename T>
+__global__ void __launch_bounds__(256) in_apply_v4_kernel(const TY* __restrict__ y, const T* __restrict__ res, T* __restrict__ z,
+                                                          const float* __restrict__ stats, unsigned HWC4, unsigned C4,
+                                                          unsigned total4, int norm, int act, float slope) {
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
+        float v[4];
+        ld4(y + 4ll * i, v);
+        if (norm) {
+            const unsigned n = i / HWC4, c4 = i % C4;
+            const float4* sp = reinterpret_cast<const float4*>(stats + ((long long)n * C4 + c4) * 8);
+            const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
+            v[0] = (v[0] - s0.x) * s0.y; v[1] = (v[1] - s0.z) * s0.w;
+            v[2] = (v[2] - s1.x) * s1.y; v[3] = (v[3] - s1.z) * s1.w;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = act_fwd(v[k], act, slope);
+        if (res) {
+            float r[4];
+            ld4(res + 4ll * i, r);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) v[k] += r[k];
+        }
+        st4(z + 4ll * i, v);
+    }
+}
+
+template <typename TY, typename T>
+__global__ void __launch_bounds__(256) in_bwd_stats_v4_kernel(const TY* __restrict__ y, const float* __restrict__ stats,
+                                                              const T* __restrict__ dz, float* __restrict__ work, int HW, int C,
+                                                              int chunk, int act, float slope) {
+    __shared__ float sm[8][32][9];
+    const int cg = blockIdx.x * 32 + threadIdx.x, n = blockIdx.y, C4 = C >> 2;
+    const int r0 = blockIdx.z * chunk, r1 = min(HW, r0 + chunk);
+    float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f};
+    if (cg < C4) {
+        const long long off = (long long)n * HW * C + cg * 4;
+        const float4* sp = reinterpret_cast<const float4*>(stats + ((long long)n * C + cg * 4) * 2);
+        const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
+        const float mean[4] = {s0.x, s0.z, s1.x, s1.z}, rstd[4] = {s0.y, s0.w, s1.y, s1.w};
+        for (int r = r0 + threadIdx.y; r < r1; r += 8) {
+            float v[4], g[4];
+            ld4(y + off + (long long)r * C, v);
+            ld4(dz + off + (long long)r * C, g);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float xh = (v[i] - mean[i]) * rstd[i];
+                const float gg = g[i] * act_grad(xh, act, slope);
+                a[i] += gg; b[i] += gg * xh;
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { sm[threadIdx.y][threadIdx.x][i] = a[i]; sm[threadIdx.y][threadIdx.x][4 + i] = b[i]; }
+    __syncthreads();
+    const int t = threadIdx.y * 32 + threadIdx.x, g = t >> 3, k = t & 7, cgo = blockIdx.x * 32 + g;
+    if (cgo < C4) {
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s += sm[i][g][k];
+        atomicAdd(work + ((long long)n * C + cgo * 4 + (k & 3)) * 2 + (k >> 2), s);
+    }
+}
+
+template <typename TY, typename T>
+__global__ void __launch_bounds__(256) in_bwd_apply_v4_kernel(const TY* __restrict__ y, const float* __restrict__ stats,
+                                                              const T* __restrict__ dz, const float* __restrict__ work,
+                                                              T* __restrict__ dy, unsigned HWC4, unsigned C4, unsigned total4,
+                                                              float inv, int norm, int act, float slope) {
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
+        float v[4], g[4], o[4];
+        ld4(y + 4ll * i, v);
+        ld4(dz + 4ll * i, g);
+        if (!norm) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) o[k] = g[k] * act_grad(v[k], act, slope);
+        } else {
+            const unsigned n = i / HWC4, c4 = i % C4;
+            const long long so = ((long long)n * C4 + c4) * 8;
+            const float4 s0 = __ldg(reinterpret_cast<const float4*>(stats + so)), s1 = __ldg(reinterpret_cast<const float4*>(stats + so) + 1);
+            const float4 w0 = __ldg(reinterpret_cast<const float4*>(work + so)), w1 = __ldg(reinterpret_cast<const float4*>(work + so) + 1);
+            const float mean[4] = {s0.x, s0.z, s1.x, s1.z}, rstd[4] = {s0.y, s0.w, s1.y, s1.w};
+            const float wa[4] = {w0.x, w0.z, w1.x, w1.z}, wb[4] = {w0.y, w0.w, w1.y, w1.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float xh = (v[k] - mean[k]) * rstd[k];
+                const float gg = g[k] * act_grad(xh, act, slope);
+                o[k] = rstd[k] * (gg - wa[k] * inv - xh * wb[k] * inv);
+            }
+        }
+        st4(dy + 4ll * i, o);
+    }
+}
+
+// adjoint of ReflectionPad2d, four channels per thread
+template <typename T>
+__global__ void __launch_bounds__(256) reflect_fold_v4_kernel(const T* __restrict__ dxp, T* __restrict__ dx, int H, int W, int C4,
+                                                              int p, unsigned total4) {
+    const int HP = H + 2 * p, WP = W + 2 * p;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
+        const unsigned c4 = i % C4;
+        unsigned r = i / C4;
+        const int w = (int)(r % W); r /= W;
+        const int h = (int)(r % H);
+        const long long n = r / H;
+        int hs[3], ws[3], nh = 0, nw = 0;
+        hs[nh++] = h + p;
+        if (h >= 1 && h <= p) hs[nh++] = p - h;
+        if (h >= H - 1 - p && h <= H - 2) hs[nh++] = 2 * (H - 1) + p - h;
+        ws[nw++] = w + p;
+        if (w >= 1 && w <= p) ws[nw++] = p - w;
+        if (w >= W - 1 - p && w <= W - 2) ws[nw++] = 2 * (W - 1) + p - w;
+        float s[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int a = 0; a < nh; ++a)
+            for (int b = 0; b < nw; ++b) {
+                float v[4];
+                ld4(dxp + (((n * HP + hs[a]) * WP + ws[b]) * C4 + c4) * 4, v);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) s[k] += v[k];
+            }
+        st4(dx + 4ll * i, s);
+    }
+}
+
 // ---- AvgPool2d(3, stride 2, pad 1, count_include_pad=False) -------------------------------------------
 template <typename T>
 __global__ void avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int H, int W, int C, int OH, int OW,
@@ -282,6 +449,35 @@ __global__ void adam_dev_kernel(float* __restrict__ w, const float* __restrict__
     }
 }
 
+__global__ void __launch_bounds__(256) adam_dev_v4_kernel(float4* __restrict__ w, const float4* __restrict__ g, float4* __restrict__ m,
+                                                          float4* __restrict__ v, uint2* __restrict__ wb, long long n4,
+                                                          const float* __restrict__ scratch, float beta1, float beta2, float eps,
+                                                          float gscale) {
+    const float step_size = scratch[0], inv_bc2_sqrt = scratch[1];
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+        const float4 gq = g[i], mq = m[i], vq = v[i], wq = w[i];
+        const float gi[4] = {gq.x * gscale, gq.y * gscale, gq.z * gscale, gq.w * gscale};
+        const float mo[4] = {mq.x, mq.y, mq.z, mq.w}, vo[4] = {vq.x, vq.y, vq.z, vq.w}, wo[4] = {wq.x, wq.y, wq.z, wq.w};
+        float mi[4], vi[4], wi[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            mi[k] = beta1 * mo[k] + (1.f - beta1) * gi[k];
+            vi[k] = beta2 * vo[k] + (1.f - beta2) * gi[k] * gi[k];
+            wi[k] = wo[k] - step_size * mi[k] / (sqrtf(vi[k]) * inv_bc2_sqrt + eps);
+        }
+        m[i] = make_float4(mi[0], mi[1], mi[2], mi[3]);
+        v[i] = make_float4(vi[0], vi[1], vi[2], vi[3]);
+        w[i] = make_float4(wi[0], wi[1], wi[2], wi[3]);
+        if (wb) {
+            const __nv_bfloat162 a = __floats2bfloat162_rn(wi[0], wi[1]), b = __floats2bfloat162_rn(wi[2], wi[3]);
+            uint2 t;
+            t.x = *reinterpret_cast<const uint32_t*>(&a);
+            t.y = *reinterpret_cast<const uint32_t*>(&b);
+            wb[i] = t;
+        }
+    }
+}
+
 inline int ew_grid(long long n) {
     long long b = (n + kEw - 1) / kEw;
     const long long cap = 148LL * 16;
@@ -309,15 +505,27 @@ extern "C" int p2p_instnorm_act_fwd(const void* y, const void* res, void* z, flo
     if (!y || !z || (norm && !stats)) return fail(P2P_EINVAL, "null pointer argument");
     if (N > 65535) return fail(P2P_ENOTSUP, "N=%d too large", N);
     cudaStream_t st = (cudaStream_t)stream;
+    const bool v4 = C % 4 == 0 && total / 4 < 2000000000LL && HW < 2000000000LL;
     P2P_DISPATCH_DTYPE2(y_dtype, TY, dtype, T, {
+        const bool vec = v4 && vec4_ok(y, sizeof(TY)) && vec4_ok(res, sizeof(T)) && vec4_ok(z, sizeof(T)) && vec4_ok(stats, 4);
         if (norm) {
             if (cudaMemsetAsync(stats, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
-            const int cb = (C + 31) / 32, S = split_for(HW, cb * N);
-            const long long chunk = (HW + S - 1) / S;
-            in_stats_kernel<TY><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, HW, C, chunk);
+            if (vec) {
+                const int cb = (C / 4 + 31) / 32, S = split_for(HW, cb * N);
+                const int chunk = (int)((HW + S - 1) / S);
+                in_stats_v4_kernel<TY><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, (int)HW, C, chunk);
+            } else {
+                const int cb = (C + 31) / 32, S = split_for(HW, cb * N);
+                const long long chunk = (HW + S - 1) / S;
+                in_stats_kernel<TY><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, HW, C, chunk);
+            }
             in_finalize_kernel<TY><<<(N * C + 255) / 256, 256, 0, st>>>((const TY*)y, stats, HW, C, N * C, eps);
         }
-        in_apply_kernel<TY, T><<<ew_grid(total), kEw, 0, st>>>((const TY*)y, (const T*)res, (T*)z, stats, HW, C, total, norm, act, slope);
+        if (vec)
+            in_apply_v4_kernel<TY, T><<<ew_grid(total / 4), kEw, 0, st>>>((const TY*)y, (const T*)res, (T*)z, stats, (unsigned)(HW * (C / 4)),
+                                                                          (unsigned)(C / 4), (unsigned)(total / 4), norm, act, slope);
+        else
+            in_apply_kernel<TY, T><<<ew_grid(total), kEw, 0, st>>>((const TY*)y, (const T*)res, (T*)z, stats, HW, C, total, norm, act, slope);
     });
     return check_launch("instnorm_act_fwd");
 }
@@ -330,14 +538,26 @@ extern "C" int p2p_instnorm_act_bwd(const void* y, const float* stats, const voi
     if (!y || !dz || !dy || (norm && (!stats || !work))) return fail(P2P_EINVAL, "null pointer argument");
     if (N > 65535) return fail(P2P_ENOTSUP, "N=%d too large", N);
     cudaStream_t st = (cudaStream_t)stream;
+    const bool v4 = C % 4 == 0 && total / 4 < 2000000000LL && HW < 2000000000LL;
     P2P_DISPATCH_DTYPE2(y_dtype, TY, dtype, T, {
+        const bool vec = v4 && vec4_ok(y, sizeof(TY)) && vec4_ok(dz, sizeof(T)) && vec4_ok(dy, sizeof(T)) && vec4_ok(stats, 4) && vec4_ok(work, 4);
         if (norm) {
             if (cudaMemsetAsync(work, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
-            const int cb = (C + 31) / 32, S = split_for(HW, cb * N);
-            const long long chunk = (HW + S - 1) / S;
-            in_bwd_stats_kernel<TY, T><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, (const T*)dz, work, HW, C, chunk, act, slope);
+            if (vec) {
+                const int cb = (C / 4 + 31) / 32, S = split_for(HW, cb * N);
+                const int chunk = (int)((HW + S - 1) / S);
+                in_bwd_stats_v4_kernel<TY, T><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, (const T*)dz, work, (int)HW, C, chunk, act, slope);
+            } else {
+                const int cb = (C + 31) / 32, S = split_for(HW, cb * N);
+                const long long chunk = (HW + S - 1) / S;
+                in_bwd_stats_kernel<TY, T><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, (const T*)dz, work, HW, C, chunk, act, slope);
+            }
         }
-        in_bwd_apply_kernel<TY, T><<<ew_grid(total), kEw, 0, st>>>((const TY*)y, stats, (const T*)dz, work, (T*)dy, HW, C, total, norm, act, slope);
+        if (vec)
+            in_bwd_apply_v4_kernel<TY, T><<<ew_grid(total / 4), kEw, 0, st>>>((const TY*)y, stats, (const T*)dz, work, (T*)dy, (unsigned)(HW * (C / 4)),
+                                                                              (unsigned)(C / 4), (unsigned)(total / 4), 1.f / (float)HW, norm, act, slope);
+        else
+            in_bwd_apply_kernel<TY, T><<<ew_grid(total), kEw, 0, st>>>((const TY*)y, stats, (const T*)dz, work, (T*)dy, HW, C, total, norm, act, slope);
     });
     return check_launch("instnorm_act_bwd");
 }
@@ -378,7 +598,13 @@ extern "C" int p2p_reflect_pad_fold(const void* dxp, void* dx, int N, int H, int
     if (p >= H || p >= W) return fail(P2P_EINVAL, "reflection pad %d must be smaller than H=%d, W=%d", p, H, W);
     const long long total = (long long)N * H * W * C;
     if (total == 0) return P2P_OK;
-    P2P_DISPATCH_DTYPE(dtype, T, reflect_fold_kernel<T><<<ew_grid(total), kEw, 0, (cudaStream_t)stream>>>((const T*)dxp, (T*)dx, H, W, C, p, total));
+    const bool v4 = C % 4 == 0 && total / 4 < 2000000000LL;
+    P2P_DISPATCH_DTYPE(dtype, T, {
+        if (v4 && vec4_ok(dxp, sizeof(T)) && vec4_ok(dx, sizeof(T)))
+            reflect_fold_v4_kernel<T><<<ew_grid(total / 4), kEw, 0, (cudaStream_t)stream>>>((const T*)dxp, (T*)dx, H, W, C / 4, p, (unsigned)(total / 4));
+        else
+            reflect_fold_kernel<T><<<ew_grid(total), kEw, 0, (cudaStream_t)stream>>>((const T*)dxp, (T*)dx, H, W, C, p, total);
+    });
     return check_launch("reflect_pad_fold");
 }
 
@@ -418,8 +644,12 @@ extern "C" int p2p_adam_step_dev(float* w, const float* g, float* m, float* v, v
     if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
     if (!w || !g || !m || !v || !lr_dev || !step_dev || !scratch2) return fail(P2P_EINVAL, "null pointer argument");
     adam_prepare_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_dev, lr_dev, beta1, beta2, scratch2);
-    adam_dev_kernel<<<ew_grid(n), kEw, 0, (cudaStream_t)stream>>>(w, g, m, v, (__nv_bfloat16*)w_bf16, n, scratch2, beta1, beta2,
-                                                                   eps, grad_scale);
+    if (n % 4 == 0 && vec4_ok(w, 4) && vec4_ok(g, 4) && vec4_ok(m, 4) && vec4_ok(v, 4) && vec4_ok(w_bf16, 2))
+        adam_dev_v4_kernel<<<ew_grid(n / 4), kEw, 0, (cudaStream_t)stream>>>((float4*)w, (const float4*)g, (float4*)m, (float4*)v,
+                                                                            (uint2*)w_bf16, n / 4, scratch2, beta1, beta2, eps, grad_scale);
+    else
+        adam_dev_kernel<<<ew_grid(n), kEw, 0, (cudaStream_t)stream>>>(w, g, m, v, (__nv_bfloat16*)w_bf16, n, scratch2, beta1, beta2,
+                                                                       eps, grad_scale);
     return check_launch("adam_step_dev");
 }
 

@@ -1,0 +1,128 @@
+// Operand packing for the thin layers (2-4 channels on one side: G's 7x7 edge layers, D's first and logit layers):
+// the kernel's columns are folded into the channel dimension so that (dw, c) fills <= 16 tensor-core channels and a
+// KHxKW convolution becomes a KHx1 convolution (see ops.py "thin layers").  One thread per packed pixel (32 bytes).
+#include "dtype.cuh"
+
+namespace p2p {
+namespace {
+
+__device__ __forceinline__ int reflect_idx(int i, int n) {
+    if (i < 0) i = -i;
+    if (i >= n) i = 2 * (n - 1) - i;
+    return i;
+}
+
+// xpk[n, y, ox, dw*C + c] = xpad[n, y, ox*s + dw, c]  (xpad = x padded by p, zeros or reflection); channels >= KW*C are zero
+template <typename T>
+__global__ void __launch_bounds__(256) pack_in_kernel(const T* __restrict__ x, T* __restrict__ xpk, int N, int H, int W, int C,
+                                                      int KW, int s, int p, int reflect, int OW, unsigned total) {
+    const int Hp = H + 2 * p;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int ox = (int)(i % OW);
+        unsigned r = i / OW;
+        const int y = (int)(r % Hp);
+        const int n = (int)(r / Hp);
+        int sy = y - p;
+        bool rowok = true;
+        if (reflect) sy = reflect_idx(sy, H); else rowok = sy >= 0 && sy < H;
+        T v[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) v[k] = T(0.f);
+        const T* row = x + ((long long)n * H + sy) * W * C;
+        for (int dw = 0; dw < KW; ++dw) {
+            int sx = ox * s + dw - p;
+            bool ok = rowok;
+            if (reflect) sx = reflect_idx(sx, W); else ok = ok && sx >= 0 && sx < W;
+            if (ok)
+                for (int c = 0; c < C; ++c) v[dw * C + c] = row[(long long)sx * C + c];
+        }
+        T* o = xpk + (long long)i * 16;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) o[k] = v[k];
+    }
+}
+
+// y[n, oh, ow, co] = bias[co] + sum_dw ypk[n, oh, ow + dw, dw*Cout + co]
+template <typename T>
+__global__ void __launch_bounds__(256) fold_out_kernel(const float* __restrict__ ypk, const float* __restrict__ bias, T* __restrict__ y,
+                                                       int OH, int Wp, int OW, int KW, int Cout, unsigned total) {
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int co = (int)(i % Cout);
+        unsigned r = i / Cout;
+        const int ow = (int)(r % OW);
+        r /= OW;       // = n * OH + oh
+        const float* src = ypk + ((long long)r * Wp + ow) * 16 + co;
+        float s = bias ? bias[co] : 0.f;
+        for (int dw = 0; dw < KW; ++dw) s += src[dw * (16 + Cout)];
+        stf(y + i, s);
+    }
+}
+
+// dypk[n, y, x', dw*Cout + co] = dy[n, y, x' - dw, co] (zero outside), 16 channels per pixel
+template <typename T>
+__global__ void __launch_bounds__(256) pack_dy_kernel(const T* __restrict__ dy, T* __restrict__ dypk, int OW, int Cout, int KW, int Wp,
+                                                      unsigned total) {
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int xp = (int)(i % Wp);
+        const unsigned r = i / Wp;     // = n * OH + y
+        T v[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) v[k] = T(0.f);
+        const T* row = dy + (long long)r * OW * Cout;
+        for (int dw = 0; dw < KW; ++dw) {
+            const int sx = xp - dw;
+            if (sx >= 0 && sx < OW)
+                for (int c = 0; c < Cout; ++c) v[dw * Cout + c] = row[sx * Cout + c];
+        }
+        T* o = dypk + (long long)i * 16;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) o[k] = v[k];
+    }
+}
+
+inline int grid_for(long long n) {
+    long long b = (n + 255) / 256;
+    return (int)(b < 1 ? 1 : (b > 148 * 16 ? 148 * 16 : b));
+}
+
+}  // namespace
+}  // namespace p2p
+
+using namespace p2p;
+
+extern "C" int p2p_pack_in(const void* x, void* xpk, int N, int H, int W, int C, int KW, int stride, int pad, int reflect,
+                           int OW, int dtype, void* stream) {
+    if (!x || !xpk) return fail(P2P_EINVAL, "null pointer argument");
+    if (N < 1 || H < 1 || W < 1 || C < 1 || KW < 1 || KW * C > 16 || stride < 1 || pad < 0 || OW < 1)
+        return fail(P2P_EINVAL, "bad packing geometry (KW*C must be <= 16)");
+    if (reflect && (pad >= H || pad >= W)) return fail(P2P_EINVAL, "reflection padding must be smaller than the input");
+    if ((OW - 1) * stride + KW > W + 2 * pad) return fail(P2P_EINVAL, "OW reaches past the padded row");
+    const long long total = (long long)N * (H + 2 * pad) * OW;
+    if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
+    P2P_DISPATCH_DTYPE(dtype, T, pack_in_kernel<T><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+        (const T*)x, (T*)xpk, N, H, W, C, KW, stride, pad, reflect, OW, (unsigned)total));
+    return check_launch("pack_in");
+}
+
+extern "C" int p2p_fold_out(const float* ypk, const float* bias, void* y, int N, int OH, int Wp, int OW, int KW, int Cout,
+                            int out_dtype, void* stream) {
+    if (!ypk || !y) return fail(P2P_EINVAL, "null pointer argument");
+    if (N < 1 || OH < 1 || OW < 1 || KW < 1 || Cout < 1 || KW * Cout > 16 || OW + KW - 1 > Wp)
+        return fail(P2P_EINVAL, "bad folding geometry (KW*Cout must be <= 16)");
+    const long long total = (long long)N * OH * OW * Cout;
+    if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
+    P2P_DISPATCH_DTYPE(out_dtype, T, fold_out_kernel<T><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+        ypk, bias, (T*)y, OH, Wp, OW, KW, Cout, (unsigned)total));
+    return check_launch("fold_out");
+}
+
+extern "C" int p2p_pack_dy(const void* dy, void* dypk, int N, int OH, int OW, int Cout, int KW, int Wp, int dtype, void* stream) {
+    if (!dy || !dypk) return fail(P2P_EINVAL, "null pointer argument");
+    if (N < 1 || OH < 1 || OW < 1 || KW < 1 || Cout < 1 || KW * Cout > 16 || Wp < OW)
+        return fail(P2P_EINVAL, "bad packing geometry (KW*Cout must be <= 16)");
+    const long long total = (long long)N * OH * Wp;
+    if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
+    P2P_DISPATCH_DTYPE(dtype, T, pack_dy_kernel<T><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+        (const T*)dy, (T*)dypk, OW, Cout, KW, Wp, (unsigned)total));
+    return check_launch("pack_dy");
+}

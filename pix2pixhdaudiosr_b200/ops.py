@@ -321,7 +321,7 @@ def _window_passes(passes, x, wq, bias, out, wtaps_total, kind):
     return True
 
 
-def _window_wgrad(passes, x, dy, dwp, wtaps_total):
+def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None):
     """weight gradient of a layer call (its forward-type passes) as ONE launch of the window wgrad kernel:
     dW_t = sum over the padded grid of dout (laid out at the input's pitch) x shifted input window.  False if it does not fit."""
     if not USE_WINDOW or not passes or x.dtype != torch.bfloat16 or _lib.lib().p2p_conv_force_simple(-1) == 1:
@@ -361,8 +361,11 @@ def _window_wgrad(passes, x, dy, dwp, wtaps_total):
         return False
     rows = (N * Hh * Wh + 63) // 64 * 64
     lib = _lib.lib()
-    bplanes = torch.empty((s_in * s_in, rows, C), dtype=x.dtype, device=x.device)
-    _lib.check(lib.p2p_pad_planes(_p(x), _p(bplanes), N, H, W, C, pt, pl, Hh, Wh, s_in, rows, int(reflect), _DT[x.dtype], _stream()))
+    if xpad is not None and xpad[0] == (pt, pl, Hh, Wh, rows, reflect, s_in, C):
+        bplanes = xpad[1]                   # the forward pass's padded copy
+    else:
+        bplanes = torch.empty((s_in * s_in, rows, C), dtype=x.dtype, device=x.device)
+        _lib.check(lib.p2p_pad_planes(_p(x), _p(bplanes), N, H, W, C, pt, pl, Hh, Wh, s_in, rows, int(reflect), _DT[x.dtype], _stream()))
     aplanes = torch.empty((s_out * s_out, rows, J), dtype=dy.dtype, device=dy.device)
     _lib.check(lib.p2p_pad_planes(_p(dy), _p(aplanes), N, dy.shape[1], dy.shape[2], J, 0, 0, Hh, Wh, s_out, rows, 0, _DT[dy.dtype], _stream()))
     IntArr = ctypes.c_int * len(taps)
@@ -374,8 +377,8 @@ def _window_wgrad(passes, x, dy, dwp, wtaps_total):
     return True
 
 
-def conv_window(xp, wq, bias, out_dtype, KH, KW, J, flip, w_tap, w_k, w_j, kind):
-    N, Hp, Wp, C = xp.shape
+def conv_window(xp, wq, bias, out_dtype, KH, KW, J, flip, w_tap, w_k, w_j, kind, shape=None):
+    N, Hp, Wp, C = shape if shape is not None else xp.shape
     OH, OW = Hp - KH + 1, Wp - KW + 1
     out = torch.empty((N, OH, OW, J), dtype=out_dtype, device=xp.device)
     _timed(kind, _Shape(N, OH, OW, J, KH * KW, C, Hp, Wp),
@@ -411,13 +414,15 @@ def _pad_hw(x, p, reflect):
     return xc.permute(0, 2, 3, 1).contiguous()
 
 
-def _packed_in_operands(x, wq, cfg, Cin, Cout, KH, KW):
+def _packed_in_operands(x, wq, cfg, Cin, Cout, KH, KW, xpk=None):
     N, H, W, _ = x.shape
     s, p = cfg.stride, cfg.pad
-    xp = _pad_hw(x, p, cfg.pad_mode == PAD_REFLECT)
-    Hp, Wp = xp.shape[1], xp.shape[2]
+    Hp, Wp = H + 2 * p, W + 2 * p
     OH, OW = (Hp - KH) // s + 1, (Wp - KW) // s + 1
-    xpk = _pad_last(torch.cat([xp[:, :, dw: dw + (OW - 1) * s + 1: s, :] for dw in range(KW)], dim=-1), 16)
+    if xpk is None:
+        xpk = torch.empty((N, Hp, OW, 16), dtype=x.dtype, device=x.device)
+        _lib.check(_lib.lib().p2p_pack_in(_p(x), _p(xpk), N, H, W, Cin, KW, s, p, int(cfg.pad_mode == PAD_REFLECT), OW,
+                                          _DT[x.dtype], _stream()))
     P = _make_pass(N, Hp, OW, 16, OH, OW, Cout, OH, OW, s, 1, 1, 0, 1, 0, [(dh, 0, dh) for dh in range(KH)], PAD_ZERO,
                    Cout * 16, 1, 16)
     wpk = None
@@ -452,37 +457,39 @@ def _pad_rows(t, r):
 def _pack_dy(dy, KW, Cout, Wp):
     """dy [N,OH,OW,Cout] -> dy_pack[n, y, x', (dw,co)] = dy[n, y, x' - dw, co]"""
     N, OH, OW, _ = dy.shape
-    out = torch.zeros((N, OH, Wp, 16), dtype=dy.dtype, device=dy.device)
-    for dw in range(KW):
-        out[:, :, dw: dw + OW, dw * Cout: (dw + 1) * Cout] = dy
+    out = torch.empty((N, OH, Wp, 16), dtype=dy.dtype, device=dy.device)
+    _lib.check(_lib.lib().p2p_pack_dy(_p(dy), _p(out), N, OH, OW, Cout, KW, Wp, _DT[dy.dtype], _stream()))
     return out
 
 
-def _packed_forward(kind, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype):
+def _packed_forward(kind, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux=None):
     if kind == "in":
         xpk, wpk, P, (OH, OW) = _packed_in_operands(x, wq, cfg, Cin, Cout, KH, KW)
+        if aux is not None:
+            aux.append(("packed_in", xpk))
         y = torch.empty((x.shape[0], OH, OW, Cout), dtype=out_dtype, device=x.device)
         _run_pass(P, xpk, wpk, bias, y)
         return y
+    N = x.shape[0]
     P, (Hp, Wp, OH, OW) = _packed_out_geometry(x, cfg, Cin, Cout, KH, KW)
     xp = _pad_hw(x, cfg.pad, cfg.pad_mode == PAD_REFLECT)
-    ypk = torch.empty((x.shape[0], OH, Wp, 16), dtype=torch.float32, device=x.device)
+    if aux is not None:
+        aux.append(("packed_out", xp))
+    ypk = torch.empty((N, OH, Wp, 16), dtype=torch.float32, device=x.device)
     _run_pass(P, xp, _pack_out_weight(wq, KH, KW, Cout, Cin), None, ypk)
-    y = ypk[:, :, 0:OW, 0:Cout]
-    for dw in range(1, KW):
-        y = y + ypk[:, :, dw: dw + OW, dw * Cout: (dw + 1) * Cout]
-    if bias is not None:
-        y = y + bias
-    return y.to(out_dtype).contiguous()
+    y = torch.empty((N, OH, OW, Cout), dtype=out_dtype, device=x.device)
+    _lib.check(_lib.lib().p2p_fold_out(_p(ypk), _p(bias), _p(y), N, OH, Wp, OW, KW, Cout, _DT[out_dtype], _stream()))
+    return y
 
 
-def _packed_backward(kind, x, wq, dy, cfg, Cin, Cout, KH, KW, need_dx, need_dw):
+def _packed_backward(kind, x, wq, dy, cfg, Cin, Cout, KH, KW, need_dx, need_dw, xpad=None):
     """-> (dx or None, dW physical [KH][KW][Cout][Cin] fp32 or None); dx only for the thin-output kind"""
     N, H, W, _ = x.shape
     dx = dwp = None
     if kind == "in":
         if need_dw:
-            xpk, _, P, _ = _packed_in_operands(x, None, cfg, Cin, Cout, KH, KW)
+            xpk, _, P, _ = _packed_in_operands(x, None, cfg, Cin, Cout, KH, KW,
+                                               xpad[1] if xpad is not None and xpad[0] == "packed_in" else None)
             dwk = torch.zeros((KH, Cout, 16), dtype=torch.float32, device=x.device)
             _run_wgrad(P, xpk, dy, dwk)
             dwp = dwk[:, :, :KW * Cin].reshape(KH, Cout, KW, Cin).permute(0, 2, 1, 3)
@@ -502,14 +509,14 @@ def _packed_backward(kind, x, wq, dy, cfg, Cin, Cout, KH, KW, need_dx, need_dw):
         else:
             dx = buf[:, p: p + H, p: p + W, :].contiguous() if p else buf
     if need_dw:
-        xp = _pad_hw(x, cfg.pad, cfg.pad_mode == PAD_REFLECT)
+        xp = xpad[1] if xpad is not None and xpad[0] == "packed_out" else _pad_hw(x, cfg.pad, cfg.pad_mode == PAD_REFLECT)
         dwk = torch.zeros((KH, 16, Cin), dtype=torch.float32, device=x.device)
         _run_wgrad(P, xp, dypk, dwk)
         dwp = dwk[:, :KW * Cout].reshape(KH, KW, Cout, Cin)
     return dx, dwp
 
 
-def _conv_forward(x, weight, bias, w16, cfg, out_dtype):
+def _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux=None):
     """nn.Conv2d (+ nn.ReflectionPad2d) / nn.ConvTranspose2d forward, NHWC (networks.py:145-154, 190-207, 223-246, 340-361)"""
     N, H, W, Cx = x.shape
     wphys, Cout, Cin, KH, KW = _phys(weight, cfg)
@@ -518,7 +525,7 @@ def _conv_forward(x, weight, bias, w16, cfg, out_dtype):
     Jout = Cout
     pk = _packable(x, cfg, Cin, Cout, KH, KW)
     if pk is not None:
-        return _packed_forward(pk, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype)
+        return _packed_forward(pk, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux)
     thin = _thin(x, Cin, Cout)
     if thin is not None and thin[0] != Cin:             # the forward pass only needs the gathered side padded
         x, wq, Cin = _pad_last(x, thin[0]), _pad_weight(wq, Cout, thin[0]), thin[0]
@@ -531,8 +538,18 @@ def _conv_forward(x, weight, bias, w16, cfg, out_dtype):
             raise RuntimeError("reflection padding must be smaller than the input")   # what ReflectionPad2d raises
         p = cfg.pad
         if cfg.stride == 1 and _window_ok(x.dtype, Cin, Cout, KH, KW, H + 2 * p, W + 2 * p, False):
-            xp = pad_nhwc(x, p, p, p, p, cfg.pad_mode == PAD_REFLECT) if p else x
-            return conv_window(xp, wq, bias, out_dtype, KH, KW, Jout, False, Cout * Cin, 1, Cin, "fwd")
+            if p:       # padded once, in the layout the wgrad window kernel wants too (rows rounded to 64, zero tail)
+                reflect = cfg.pad_mode == PAD_REFLECT
+                Hp, Wp = H + 2 * p, W + 2 * p
+                rows = (N * Hp * Wp + 63) // 64 * 64
+                xp = torch.empty((rows, Cin), dtype=x.dtype, device=x.device)
+                _lib.check(_lib.lib().p2p_pad_planes(_p(x), _p(xp), N, H, W, Cin, p, p, Hp, Wp, 1, rows, int(reflect),
+                                                     _DT[x.dtype], _stream()))
+                if aux is not None:
+                    aux.append(((p, p, Hp, Wp, rows, reflect, 1, Cin), xp))
+            else:
+                xp, Hp, Wp = x, H, W
+            return conv_window(xp, wq, bias, out_dtype, KH, KW, Jout, False, Cout * Cin, 1, Cin, "fwd", (N, Hp, Wp, Cin))
         passes = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
         OH, OW = passes[0].OH, passes[0].OW
     y = torch.empty((N, OH, OW, Jout), dtype=out_dtype, device=x.device)
@@ -543,7 +560,7 @@ def _conv_forward(x, weight, bias, w16, cfg, out_dtype):
     return y
 
 
-def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None):
+def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None, xpad=None):
     """gradients of conv_forward; dy has x's dtype.  Returns (dx, dw_logical, db).  With `gphys` (FusedAdam's view of
     this weight's slice of the flat gradient buffer, physical layout) the wgrad kernels accumulate straight into it
     and dw comes back None -- no zero-fill, no AccumulateGrad add."""
@@ -556,11 +573,11 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
     pk = _packable(x, cfg, Cin, Cout, KH, KW)
     if pk is not None and (pk == "out" or not need_dx):
         dx, dwp = _packed_backward(pk, x, _weight_for(x, wphys, w16) if need_dx else None, dy, cfg, Cin, Cout, KH, KW,
-                                   need_dx, need_dw)
+                                   need_dx, need_dw, xpad)
         return dx, (dwp.permute(2, 3, 0, 1) if dwp is not None else None), db
     pk_dw = pk == "in" and need_dw         # thin-input layer that also needs dx: dW packed, dx through the padded path
     if pk_dw:
-        _, dwp = _packed_backward(pk, x, None, dy, cfg, Cin, Cout, KH, KW, False, True)
+        _, dwp = _packed_backward(pk, x, None, dy, cfg, Cin, Cout, KH, KW, False, True, xpad)
         dw = dwp.permute(2, 3, 0, 1)
         need_dw = False
     Cin0, Cout0 = Cin, Cout
@@ -608,7 +625,7 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
             wpasses = convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0]
         else:
             wpasses = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
-        if not _window_wgrad(wpasses, x, dy, dwp, KH * KW):
+        if not _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None):
             for P in wpasses:
                 _run_wgrad(P, x, dy, dwp)
         if direct:
@@ -633,24 +650,25 @@ def _alg_ratio(x, weight, cfg):
     return (Cin * Cout) / float(_ceil16(Cin) * _ceil16(Cout))
 
 
-def conv_forward(x, weight, bias, w16, cfg, out_dtype):
+def conv_forward(x, weight, bias, w16, cfg, out_dtype, aux=None):
+    """aux: optional list; the stride-1 window path appends (key, padded planes) for conv_backward(xpad=...) to reuse"""
     global _FLOP_RATIO
     if _TIMING is None:
-        return _conv_forward(x, weight, bias, w16, cfg, out_dtype)
+        return _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux)
     _FLOP_RATIO = _alg_ratio(x, weight, cfg)
     try:
-        return _conv_forward(x, weight, bias, w16, cfg, out_dtype)
+        return _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux)
     finally:
         _FLOP_RATIO = 1.0
 
 
-def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None):
+def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None, xpad=None):
     global _FLOP_RATIO
     if _TIMING is None:
-        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys)
+        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys, xpad)
     _FLOP_RATIO = _alg_ratio(x, weight, cfg)
     try:
-        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys)
+        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys, xpad)
     finally:
         _FLOP_RATIO = 1.0
 
@@ -689,7 +707,9 @@ class ConvBlockFn(torch.autograd.Function):
         _need_cuda(x, weight)
         x = x.contiguous()
         plain = (not norm) and act == ACT_NONE and res is None
-        y = conv_forward(x, weight, bias, w16, cfg, torch.float32 if norm else x.dtype)
+        aux = [] if ctx.needs_input_grad[1] else None
+        y = conv_forward(x, weight, bias, w16, cfg, torch.float32 if norm else x.dtype, aux)
+        ctx.xpad = aux[0] if aux else None
         if plain:
             z, stats, ysave = y, None, None
         else:
@@ -709,7 +729,7 @@ class ConvBlockFn(torch.autograd.Function):
         dz = dz.contiguous()
         dy = dz if plain else norm_act_backward(y, stats, dz, norm, act, slope)
         dx, dw, db = conv_backward(x, weight, w16, dy, cfg, ctx.needs_input_grad[0], ctx.needs_input_grad[1],
-                                   has_bias and ctx.needs_input_grad[2], ctx.gphys)
+                                   has_bias and ctx.needs_input_grad[2], ctx.gphys, ctx.xpad)
         return dx, dw, db, None, (dz if has_res else None), None, None, None, None, None, None
 
 
