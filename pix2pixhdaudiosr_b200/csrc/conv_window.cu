@@ -46,7 +46,8 @@ struct WindowArgs {
     int BN, n_tiles, m_tiles, cpb;
     int out_bf16, b_mn_major;
     int base_off_mode;
-    int b_stages, b_stage_bytes;   // weight-tile ring: as many stages as fit 128 KB (TMA latency needs bytes in flight)
+    int b_stages, b_stage_bytes;
+    int nsplit, ci_per_split;      // split of the (channel chunk, plane) loop across CTAs; > 1 => fp32 red.add epilogue   // weight-tile ring: as many stages as fit 128 KB (TMA latency needs bytes in flight)
     short shift[P2P_MAX_TAPS];       // dh*Wp + dw
     unsigned char wtap[P2P_MAX_TAPS];
     long long nwork;
@@ -159,11 +160,14 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
             uint32_t bs = 0, bph = 1;       // weight ring: stage, parity of the "empty" wait (first lap passes at once)
             for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x) {
                 const int nt = (int)(w % a.n_tiles);
-                const long long mtu = w / a.n_tiles;
+                const long long wr = w / a.n_tiles;
+                const int sp = (int)(wr % a.nsplit);
+                const long long mtu = wr / a.nsplit;
                 const int u = (int)(mtu / a.m_tiles);
                 const long long q0 = (mtu - (long long)u * a.m_tiles) * WBM;
                 const int j0 = nt * BN;
-                for (int ci = 0; ci < a.cpb * a.nplanes; ++ci, ++ia) {
+                const int ci1 = min(a.cpb * a.nplanes, (sp + 1) * a.ci_per_split);
+                for (int ci = sp * a.ci_per_split; ci < ci1; ++ci, ++ia) {
                     const int cc = ci / a.nplanes, pl = ci - cc * a.nplanes;
                     const int c0 = cc * 64;
                     const int ab = ia & 1;
@@ -202,13 +206,16 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
             int ia = 0, li = 0;
             uint32_t bs = 0, bph = 0;       // weight ring: stage, parity of the "full" wait
             for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
-                const int u = (int)((w / a.n_tiles) / a.m_tiles);
+                const long long wr = w / a.n_tiles;
+                const int sp = (int)(wr % a.nsplit);
+                const int u = (int)((wr / a.nsplit) / a.m_tiles);
                 const int acc = li & 1, v = li >> 1;
                 if (v >= 1) mbar_wait(tempty(acc), (uint32_t)((v - 1) & 1));
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * 256;
                 uint32_t accumulate = 0;
-                for (int ci = 0; ci < a.cpb * a.nplanes; ++ci, ++ia) {
+                const int ci1 = min(a.cpb * a.nplanes, (sp + 1) * a.ci_per_split);
+                for (int ci = sp * a.ci_per_split; ci < ci1; ++ci, ++ia) {
                     const int cc = ci / a.nplanes, pl = ci - cc * a.nplanes;
                     const int nk16 = min(64, C - cc * 64) >> 4;
                     const int ab = ia & 1;
@@ -250,13 +257,15 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
         int li = 0;
         for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
             const int nt = (int)(w % a.n_tiles);
-            const long long mtu = w / a.n_tiles;
+            const long long wr = w / a.n_tiles;
+            const int sp = (int)(wr % a.nsplit);
+            const long long mtu = wr / a.nsplit;
             const int u = (int)(mtu / a.m_tiles);
             const long long mt = mtu - (long long)u * a.m_tiles;
             const int acc = li & 1, v = li >> 1;
             const int c_begin = nt * BN, c_count = min(BN, J - c_begin);
             float* bs_ = bias_s + acc * 256;
-            for (int c = et; c < BN; c += 128) bs_[c] = (a.bias && c < c_count) ? __ldg(a.bias + c_begin + c) : 0.f;
+            for (int c = et; c < BN; c += 128) bs_[c] = (a.bias && sp == 0 && c < c_count) ? __ldg(a.bias + c_begin + c) : 0.f;
             const long long q = mt * WBM + row;
             const int n = (int)(q / plane);
             const int rem = (int)(q - (long long)n * plane);
@@ -301,6 +310,16 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
 #pragma unroll
                             for (int i = 0; i < 16; ++i)
                                 if (c + i < c_count) o[i] = __float2bfloat16_rn(f[i]);
+                        }
+                    } else if (a.nsplit > 1) {
+                        float* o = (float*)a.out + obase + c;
+                        if (fullv && (((uintptr_t)o) & 15) == 0) {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) red_add_v4(o + 4 * i, f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i)
+                                if (c + i < c_count) atomicAdd(o + i, f[i]);
                         }
                     } else {
                         float* o = (float*)a.out + obase + c;
@@ -683,6 +702,24 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
     if (mt * a.nsub > 2000000000LL / a.n_tiles) return fail(P2P_ENOTSUP, "too many tiles");
     a.m_tiles = (int)mt;
     a.nwork = mt * a.n_tiles * a.nsub;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    a.nsplit = 1;
+    a.ci_per_split = a.cpb * nplanes;
+    if (!a.out_bf16 && a.nwork * 2 <= sms && a.cpb * nplanes >= 4) {
+        // few tiles (the 16x4-pixel bottleneck layers): split the channel loop so that one wave fills the chip; the
+        // partial tiles meet in the fp32 output through red.add
+        int ns = (int)(sms / a.nwork);
+        if (ns > a.cpb * nplanes / 2) ns = a.cpb * nplanes / 2;
+        a.ci_per_split = (a.cpb * nplanes + ns - 1) / ns;
+        a.nsplit = (a.cpb * nplanes + a.ci_per_split - 1) / a.ci_per_split;
+        if (a.nsplit > 1) {
+            const size_t bytes = (size_t)d->N * d->OHf * d->OWf * J * sizeof(float);
+            if (cudaMemsetAsync(out, 0, bytes, (cudaStream_t)stream) != cudaSuccess) return check_launch("cudaMemsetAsync(split output)");
+            a.nwork *= a.nsplit;
+        }
+    }
     if (int rc = encode_2d(&a.tm_x, planes, (unsigned long long)C, (unsigned long long)nplanes * a.Q, 64, (unsigned)a.rows_per_box)) return rc;
     if (!a.b_mn_major) {
         if (int rc = encode_2d(&a.tm_w, weight, (unsigned long long)C, (unsigned long long)d->wtaps_total * J, 64, (unsigned)a.BN)) return rc;
@@ -695,9 +732,6 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
             return check_launch("cudaFuncSetAttribute(conv_window_kernel)");
         configured = true;
     }
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const long long grid = a.nwork < sms ? a.nwork : sms;
     conv_window_kernel<<<(unsigned)grid, kWThreads, WSMEM, (cudaStream_t)stream>>>(a);
     note_umma_launch();

@@ -248,7 +248,7 @@ def _window_ok(dtype, C, J, KH, KW, Hp, Wp, mn_major):
         return False
     if 128 + (KH - 1) * Wp + (KW - 1) > _WIN_ROWS_MAX:
         return False
-    return (Hp - KH + 1) * (Wp - KW + 1) >= 0.7 * Hp * Wp        # rows in the padding margin are computed and dropped
+    return (Hp - KH + 1) * (Wp - KW + 1) >= 0.5 * Hp * Wp        # rows in the padding margin are computed and dropped
 
 
 def pad_nhwc(x, pt, pb, pl, pr, reflect):
@@ -286,7 +286,7 @@ def _plan_window_passes(passes, dtype):
         Hh, Wh = max(Hh, P.gy + max(q[1] for q in taps)), max(Wh, P.gx + max(q[2] for q in taps))
     halo = max(q[1] * Wh + q[2] for taps in subs for q in taps)
     useful = sum(P.gy * P.gx for P in passes)
-    if 128 + halo > _WIN_ROWS_MAX or useful < 0.7 * len(passes) * Hh * Wh or sum(len(t) for t in subs) > _lib.MAX_TAPS:
+    if 128 + halo > _WIN_ROWS_MAX or useful < 0.5 * len(passes) * Hh * Wh or sum(len(t) for t in subs) > _lib.MAX_TAPS:
         return None
     return dict(s=s, pt=pt, pl=pl, Hh=Hh, Wh=Wh, subs=subs)
 
@@ -316,8 +316,13 @@ def _window_passes(passes, x, wq, bias, out, wtaps_total, kind):
             t += 1
     d.ntaps = t
     shape = _Shape(N, 1, sum(P.gy * P.gx * P.ntaps for P in passes), P0.J, 1, C, pl["Hh"], pl["Wh"])
-    _timed(kind, shape, lambda: _lib.check(_lib.lib().p2p_conv_window_run(ctypes.byref(d), _p(planes), _p(wq), _p(bias), _p(out),
-                                                                          _DT[out.dtype], _stream())), umma=True)
+    run = out
+    if out.dtype != torch.float32 and _few_tiles(N * pl["Hh"] * pl["Wh"], P0.J, len(passes), (C + 63) // 64 * s * s):
+        run = torch.empty(out.shape, dtype=torch.float32, device=out.device)
+    _timed(kind, shape, lambda: _lib.check(_lib.lib().p2p_conv_window_run(ctypes.byref(d), _p(planes), _p(wq), _p(bias), _p(run),
+                                                                          _DT[run.dtype], _stream())), umma=True)
+    if run is not out:
+        out.copy_(run)
     return True
 
 
@@ -357,7 +362,7 @@ def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None):
     taps.sort(key=lambda q: (q[0], q[1]))
     halo = max(q[2] * Wh + q[3] for q in taps)
     useful = sum(P.gy * P.gx for P in passes) / float(len(passes))
-    if 64 + halo > _WIN_ROWS_MAX or useful < 0.6 * Hh * Wh:
+    if 64 + halo > _WIN_ROWS_MAX or useful < 0.5 * Hh * Wh:
         return False
     rows = (N * Hh * Wh + 63) // 64 * 64
     lib = _lib.lib()
@@ -377,14 +382,20 @@ def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None):
     return True
 
 
+def _few_tiles(rows, J, nsub, chunks):
+    """the window kernel splits its channel loop across CTAs (fp32 red.add output) when the tiles cannot fill the chip"""
+    return ((rows + 127) // 128) * ((J + 255) // 256) * nsub * 2 <= 148 and chunks >= 4
+
+
 def conv_window(xp, wq, bias, out_dtype, KH, KW, J, flip, w_tap, w_k, w_j, kind, shape=None):
     N, Hp, Wp, C = shape if shape is not None else xp.shape
     OH, OW = Hp - KH + 1, Wp - KW + 1
-    out = torch.empty((N, OH, OW, J), dtype=out_dtype, device=xp.device)
+    run_dtype = torch.float32 if _few_tiles(N * Hp * Wp, J, 1, (C + 63) // 64) else out_dtype
+    out = torch.empty((N, OH, OW, J), dtype=run_dtype, device=xp.device)
     _timed(kind, _Shape(N, OH, OW, J, KH * KW, C, Hp, Wp),
            lambda: _lib.check(_lib.lib().p2p_conv_window(_p(xp), _p(wq), _p(bias), _p(out), N, Hp, Wp, C, J, KH, KW, int(flip),
-                                                         w_tap, w_k, w_j, _DT[out_dtype], _stream())), umma=True)
-    return out
+                                                         w_tap, w_k, w_j, _DT[run_dtype], _stream())), umma=True)
+    return out if run_dtype == out_dtype else out.to(out_dtype)
 
 
 # ---- thin layers (2-4 channels on one side): fold the kernel's columns into the channel dimension ---------------------
