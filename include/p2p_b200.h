@@ -168,6 +168,18 @@ int p2p_pack_in(const void* x, void* xpk, int N, int H, int W, int C, int KW, in
 int p2p_fold_out(const float* ypk, const float* bias, void* y, int N, int OH, int Wp, int OW, int KW, int Cout, int out_dtype,
                  void* stream);
 int p2p_pack_dy(const void* dy, void* dypk, int N, int OH, int OW, int Cout, int KW, int Wp, int dtype, void* stream);
+/* Full-patch forms (bf16 only; KH*KW*C <= Kc <= 128, Kc % 8 == 0): the thin side's whole patch becomes one channel vector,
+ * so the layer is a 1x1 convolution for the window kernels.  Buffers have rows_alloc rows (a multiple of 64 for the
+ * window wgrad kernel); rows beyond the tensor and channels beyond the patch are written as zero.
+ *   im2col:       xcol[(n,oy,ox), (kh,kw,c)]    = pad(x)[n, oy*stride + kh, ox*stride + kw, c]
+ *   col2im:       dx[n,y,x,c]                   = sum_{kh,kw} dxcol[(n,oy,ox), (kh,kw,c)] with oy*stride + kh - pad = y (zero padding)
+ *   pack_dy_full: out[(n,yp,xp), (kh,kw,co)]    = dy[n, yp - kh, xp - kw, co] on the padded grid Hp = OH+KH-1, Wp = OW+KW-1 */
+int p2p_im2col(const void* x, void* xcol, int N, int H, int W, int C, int KH, int KW, int stride, int pad, int reflect, int OH,
+               int OW, int Kc, long long rows_alloc, void* stream);
+int p2p_col2im(const void* dxcol, void* dx, int N, int H, int W, int C, int KH, int KW, int stride, int pad, int OH, int OW,
+               int Kc, void* stream);
+int p2p_pack_dy_full(const void* dy, void* out, int N, int OH, int OW, int Cout, int KH, int KW, int Kc, long long rows_alloc,
+                     void* stream);
 
 /* InstanceNorm2d(affine=False, eps) [+ activation] [+ residual]:  z = act((y-mean)/sqrt(var+eps)) + res.
  * act: 0 none, 1 ReLU, 2 LeakyReLU(slope).  norm=0 skips the normalisation (plain activation).

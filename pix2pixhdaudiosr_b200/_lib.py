@@ -57,6 +57,9 @@ _SIGS.update({
     "p2p_pack_in": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_fold_out": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_pack_dy": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "p2p_im2col": (_i, [_vp, _vp] + [_i] * 12 + [_ll, _vp]),
+    "p2p_col2im": (_i, [_vp, _vp] + [_i] * 11 + [_vp]),
+    "p2p_pack_dy_full": (_i, [_vp, _vp] + [_i] * 7 + [_ll, _vp]),
     "p2p_instnorm_act_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _f, _f, _i, _i, _vp]),
     "p2p_instnorm_act_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _f, _i, _i, _vp]),
     "p2p_avgpool3s2_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),

@@ -80,6 +80,93 @@ __global__ void __launch_bounds__(256) pack_dy_kernel(const T* __restrict__ dy, 
     }
 }
 
+
+// ---- full im2col forms: the whole KHxKWxC patch (<= 128 values) becomes the channel vector of a 1x1 convolution -------
+// xcol[q, (kh,kw,c)] = pad(x)[n, oy*s + kh, ox*s + kw, c], q = (n, oy, ox) < rows; rows .. rows_alloc and k >= KH*KW*C are zero.
+// One thread per 8 consecutive k (16 bytes).
+__global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ xcol, int N, int H,
+                                                     int W, int C, int KH, int KW, int s, int p, int reflect, int OH, int OW, int Kc,
+                                                     long long rows, unsigned total) {
+    const int G = Kc >> 3, KWC = KW * C, KK = KH * KWC;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int g = (int)(i % G);
+        const unsigned q = i / G;
+        __align__(16) __nv_bfloat16 v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = __nv_bfloat16(0.f);
+        if (q < rows) {
+            const int ox = (int)(q % OW);
+            const unsigned r = q / OW;
+            const int oy = (int)(r % OH), n = (int)(r / OH);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int k = g * 8 + e;
+                if (k < KK) {
+                    const int kh = k / KWC, rem = k - kh * KWC, kw = rem / C, c = rem - kw * C;
+                    int iy = oy * s + kh - p, ix = ox * s + kw - p;
+                    bool ok = true;
+                    if (reflect) { iy = reflect_idx(iy, H); ix = reflect_idx(ix, W); }
+                    else ok = iy >= 0 && iy < H && ix >= 0 && ix < W;
+                    if (ok) v[e] = x[(((long long)n * H + iy) * W + ix) * C + c];
+                }
+            }
+        }
+        *reinterpret_cast<uint4*>(xcol + (long long)i * 8) = *reinterpret_cast<const uint4*>(v);
+    }
+}
+
+// adjoint of im2col with zero padding: dx[n, y, x, c] = sum over (kh, kw) with (y + p - kh, x + p - kw) = s * (oy, ox)
+__global__ void __launch_bounds__(256) col2im_kernel(const __nv_bfloat16* __restrict__ dxcol, __nv_bfloat16* __restrict__ dx, int H, int W,
+                                                     int C, int KH, int KW, int s, int p, int OH, int OW, int Kc, unsigned total) {
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int c = (int)(i % C);
+        unsigned r = i / C;
+        const int x = (int)(r % W); r /= W;
+        const int y = (int)(r % H);
+        const long long n = r / H;
+        float acc = 0.f;
+        for (int kh = 0; kh < KH; ++kh) {
+            const int ty = y + p - kh;
+            if (ty < 0 || ty % s != 0 || ty / s >= OH) continue;
+            for (int kw = 0; kw < KW; ++kw) {
+                const int tx = x + p - kw;
+                if (tx < 0 || tx % s != 0 || tx / s >= OW) continue;
+                acc += __bfloat162float(dxcol[((n * OH + ty / s) * OW + tx / s) * Kc + (kh * KW + kw) * C + c]);
+            }
+        }
+        dx[i] = __float2bfloat16_rn(acc);
+    }
+}
+
+// dyfull[q, (kh,kw,co)] = dy[n, yp - kh, xp - kw, co] on the padded grid q = (n, yp, xp) (zero outside / beyond rows / k >= KH*KW*Cout)
+__global__ void __launch_bounds__(256) pack_dy_full_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ out, int OH,
+                                                           int OW, int Cout, int KH, int KW, int Hp, int Wp, int Kc, long long rows,
+                                                           unsigned total) {
+    const int G = Kc >> 3, KWC = KW * Cout, KK = KH * KWC;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int g = (int)(i % G);
+        const unsigned q = i / G;
+        __align__(16) __nv_bfloat16 v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = __nv_bfloat16(0.f);
+        if (q < rows) {
+            const int xp = (int)(q % Wp);
+            const unsigned r = q / Wp;
+            const int yp = (int)(r % Hp), n = (int)(r / Hp);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int k = g * 8 + e;
+                if (k < KK) {
+                    const int kh = k / KWC, rem = k - kh * KWC, kw = rem / Cout, co = rem - kw * Cout;
+                    const int sy = yp - kh, sx = xp - kw;
+                    if (sy >= 0 && sy < OH && sx >= 0 && sx < OW) v[e] = dy[(((long long)n * OH + sy) * OW + sx) * Cout + co];
+                }
+            }
+        }
+        *reinterpret_cast<uint4*>(out + (long long)i * 8) = *reinterpret_cast<const uint4*>(v);
+    }
+}
+
 inline int grid_for(long long n) {
     long long b = (n + 255) / 256;
     return (int)(b < 1 ? 1 : (b > 148 * 16 ? 148 * 16 : b));
@@ -125,4 +212,48 @@ extern "C" int p2p_pack_dy(const void* dy, void* dypk, int N, int OH, int OW, in
     P2P_DISPATCH_DTYPE(dtype, T, pack_dy_kernel<T><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
         (const T*)dy, (T*)dypk, OW, Cout, KW, Wp, (unsigned)total));
     return check_launch("pack_dy");
+}
+
+extern "C" int p2p_im2col(const void* x, void* xcol, int N, int H, int W, int C, int KH, int KW, int stride, int pad, int reflect,
+                          int OH, int OW, int Kc, long long rows_alloc, void* stream) {
+    if (!x || !xcol) return fail(P2P_EINVAL, "null pointer argument");
+    if (N < 1 || H < 1 || W < 1 || C < 1 || KH < 1 || KW < 1 || stride < 1 || pad < 0 || OH < 1 || OW < 1 || Kc % 8 != 0 ||
+        KH * KW * C > Kc)
+        return fail(P2P_EINVAL, "bad im2col geometry (KH*KW*C must fit Kc, Kc %% 8 == 0)");
+    if ((OH - 1) * stride + KH > H + 2 * pad || (OW - 1) * stride + KW > W + 2 * pad) return fail(P2P_EINVAL, "output reaches past the padded input");
+    if (reflect && (pad >= H || pad >= W)) return fail(P2P_EINVAL, "reflection padding must be smaller than the input");
+    const long long rows = (long long)N * OH * OW;
+    if (rows_alloc < rows) return fail(P2P_EINVAL, "rows_alloc smaller than N*OH*OW");
+    const long long total = rows_alloc * (Kc / 8);
+    if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
+    im2col_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)xcol, N, H, W, C, KH, KW,
+                                                                     stride, pad, reflect, OH, OW, Kc, rows, (unsigned)total);
+    return check_launch("im2col");
+}
+
+extern "C" int p2p_col2im(const void* dxcol, void* dx, int N, int H, int W, int C, int KH, int KW, int stride, int pad, int OH,
+                          int OW, int Kc, void* stream) {
+    if (!dxcol || !dx) return fail(P2P_EINVAL, "null pointer argument");
+    if (N < 1 || H < 1 || W < 1 || C < 1 || KH < 1 || KW < 1 || stride < 1 || pad < 0 || OH < 1 || OW < 1 || KH * KW * C > Kc)
+        return fail(P2P_EINVAL, "bad col2im geometry");
+    const long long total = (long long)N * H * W * C;
+    if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
+    col2im_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dxcol, (__nv_bfloat16*)dx, H, W, C, KH, KW,
+                                                                     stride, pad, OH, OW, Kc, (unsigned)total);
+    return check_launch("col2im");
+}
+
+extern "C" int p2p_pack_dy_full(const void* dy, void* out, int N, int OH, int OW, int Cout, int KH, int KW, int Kc,
+                                long long rows_alloc, void* stream) {
+    if (!dy || !out) return fail(P2P_EINVAL, "null pointer argument");
+    if (N < 1 || OH < 1 || OW < 1 || Cout < 1 || KH < 1 || KW < 1 || Kc % 8 != 0 || KH * KW * Cout > Kc)
+        return fail(P2P_EINVAL, "bad packing geometry (KH*KW*Cout must fit Kc, Kc %% 8 == 0)");
+    const int Hp = OH + KH - 1, Wp = OW + KW - 1;
+    const long long rows = (long long)N * Hp * Wp;
+    if (rows_alloc < rows) return fail(P2P_EINVAL, "rows_alloc smaller than the padded grid");
+    const long long total = rows_alloc * (Kc / 8);
+    if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
+    pack_dy_full_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dy, (__nv_bfloat16*)out, OH, OW, Cout,
+                                                                           KH, KW, Hp, Wp, Kc, rows, (unsigned)total);
+    return check_launch("pack_dy_full");
 }

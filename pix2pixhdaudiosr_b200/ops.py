@@ -483,7 +483,8 @@ def _packed_forward(kind, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux=No
         return y
     N = x.shape[0]
     P, (Hp, Wp, OH, OW) = _packed_out_geometry(x, cfg, Cin, Cout, KH, KW)
-    xp = _pad_hw(x, cfg.pad, cfg.pad_mode == PAD_REFLECT)
+    xp = _pad_rows64(x, cfg.pad, cfg.pad_mode == PAD_REFLECT) if (Cin * x.element_size()) % 16 == 0 else \
+        _pad_hw(x, cfg.pad, cfg.pad_mode == PAD_REFLECT)
     if aux is not None:
         aux.append(("packed_out", xp))
     ypk = torch.empty((N, OH, Wp, 16), dtype=torch.float32, device=x.device)
@@ -527,6 +528,139 @@ def _packed_backward(kind, x, wq, dy, cfg, Cin, Cout, KH, KW, need_dx, need_dw, 
     return dx, dwp
 
 
+# ---- thin layers whose whole patch fits 128 channels: 1x1 convolutions on packed operands (csrc/pack.cu) ------------------
+def _colable(x, cfg, Cin, Cout, KH, KW):
+    """'in': im2col of the thin input makes the layer a 1x1 convolution (forward, dW, dx);
+    'out': the output gradient packed over the patch makes dW and dx 1x1 convolutions (the forward stays column-packed)"""
+    if x.dtype != torch.bfloat16 or cfg.transposed or not USE_WINDOW or _lib.lib().p2p_conv_force_simple(-1) == 1:
+        return None
+    if Cin % 16 != 0 and Cin * KH * KW <= 128 and Cout % 16 == 0:
+        return "in"
+    if Cout % 16 != 0 and Cout * KH * KW <= 128 and Cout * KW <= 16 and Cin % 16 == 0 and cfg.stride == 1:
+        return "out"
+    return None
+
+
+def _rows64(n):
+    return (n + 63) // 64 * 64
+
+
+def _with_ratio(r, fn):
+    global _FLOP_RATIO
+    old, _FLOP_RATIO = _FLOP_RATIO, r
+    try:
+        return fn()
+    finally:
+        _FLOP_RATIO = old
+
+
+def _wgrad_1x1(a2d, b2d, rows, J, C, dw, Wp):
+    """dw[J][C] (fp32) += a2d[rows][J]^T b2d[rows][C]; rows % 64 == 0, tails zero"""
+    one = (ctypes.c_int * 1)(0)
+    shape = _Shape(1, 1, rows, J, 1, C, 1, rows)
+    _timed("wgrad", shape, lambda: _lib.check(_lib.lib().p2p_conv_wgrad_window(
+        _p(a2d), 1, _p(b2d), 1, rows, Wp, J, C, _p(dw), 1, 1, one, one, one, one, one, _stream())), umma=True)
+
+
+def _col_in_geometry(x, cfg, Cin, KH, KW):
+    N, H, W, _ = x.shape
+    s, p = cfg.stride, cfg.pad
+    OH, OW = (H + 2 * p - KH) // s + 1, (W + 2 * p - KW) // s + 1
+    return N, H, W, s, p, OH, OW, _ceil16(KH * KW * Cin)
+
+
+def _col_weight(wq, Kc):
+    """[KH][KW][Cout][Cin] -> [Cout][(kh,kw,c) zero-padded to Kc]"""
+    KH, KW, Cout, Cin = wq.shape
+    return _pad_last(wq.permute(2, 0, 1, 3).reshape(Cout, KH * KW * Cin), Kc).contiguous()
+
+
+def _im2col(x, cfg, Cin, KH, KW):
+    N, H, W, s, p, OH, OW, Kc = _col_in_geometry(x, cfg, Cin, KH, KW)
+    rows = _rows64(N * OH * OW)
+    xcol = torch.empty((rows, Kc), dtype=x.dtype, device=x.device)
+    _lib.check(_lib.lib().p2p_im2col(_p(x), _p(xcol), N, H, W, Cin, KH, KW, s, p, int(cfg.pad_mode == PAD_REFLECT), OH, OW, Kc,
+                                     rows, _stream()))
+    return xcol
+
+
+def _col_in_forward(x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux):
+    N, H, W, s, p, OH, OW, Kc = _col_in_geometry(x, cfg, Cin, KH, KW)
+    xcol = _im2col(x, cfg, Cin, KH, KW)
+    if aux is not None:
+        aux.append(("col_in", xcol))
+    return _with_ratio(KH * KW * Cin / float(Kc),
+                       lambda: conv_window(xcol, _col_weight(wq, Kc), bias, out_dtype, 1, 1, Cout, False, Cout * Kc, 1, Kc, "fwd",
+                                           (N, OH, OW, Kc)))
+
+
+def _col_in_backward(x, wq, dy, cfg, Cin, Cout, KH, KW, need_dx, need_dw, xpad):
+    """-> (dx or None, dW physical [KH][KW][Cout][Cin] fp32 or None); dx only with zero padding"""
+    N, H, W, s, p, OH, OW, Kc = _col_in_geometry(x, cfg, Cin, KH, KW)
+    ratio = KH * KW * Cin / float(Kc)
+    dx = dwp = None
+    if need_dw:
+        xcol = xpad[1] if xpad is not None and xpad[0] == "col_in" else _im2col(x, cfg, Cin, KH, KW)
+        rows = xcol.shape[0]
+        if rows == N * OH * OW:
+            dy2 = dy
+        else:
+            dy2 = torch.empty((rows, Cout), dtype=dy.dtype, device=dy.device)
+            _lib.check(_lib.lib().p2p_pad_planes(_p(dy), _p(dy2), N, OH, OW, Cout, 0, 0, OH, OW, 1, rows, 0, _DT[dy.dtype], _stream()))
+        dwcol = torch.zeros((Cout, Kc), dtype=torch.float32, device=x.device)
+        _with_ratio(ratio, lambda: _wgrad_1x1(dy2, xcol, rows, Cout, Kc, dwcol, OW))
+        dwp = dwcol[:, :KH * KW * Cin].reshape(Cout, KH, KW, Cin).permute(1, 2, 0, 3)
+    if need_dx:
+        dxcol = _with_ratio(ratio, lambda: conv_window(dy, _col_weight(wq, Kc), None, x.dtype, 1, 1, Kc, False, Cout * Kc, Kc, 1,
+                                                       "dgrad", (N, OH, OW, Cout)))
+        dx = torch.empty_like(x)
+        _lib.check(_lib.lib().p2p_col2im(_p(dxcol), _p(dx), N, H, W, Cin, KH, KW, s, p, OH, OW, Kc, _stream()))
+    return dx, dwp
+
+
+def _col_out_backward(x, wq, dy, cfg, Cin, Cout, KH, KW, need_dx, need_dw, xpad):
+    """thin-output layer (stride 1): dyfull[(n,yp,xp), (kh,kw,co)] = dy[n, yp-kh, xp-kw, co] turns dW and dx into 1x1 products"""
+    N, H, W, _ = x.shape
+    p = cfg.pad
+    Hp, Wp = H + 2 * p, W + 2 * p
+    OH, OW = Hp - KH + 1, Wp - KW + 1
+    Kc = _ceil16(KH * KW * Cout)
+    rows = _rows64(N * Hp * Wp)
+    ratio = (KH * KW * Cout / float(Kc)) * (OH * OW / float(Hp * Wp))
+    dyfull = torch.empty((rows, Kc), dtype=dy.dtype, device=dy.device)
+    _lib.check(_lib.lib().p2p_pack_dy_full(_p(dy), _p(dyfull), N, OH, OW, Cout, KH, KW, Kc, rows, _stream()))
+    dx = dwp = None
+    if need_dx:
+        wfull = _pad_rows(wq.reshape(1, KH * KW * Cout, Cin), Kc)[0]        # [Kc][Cin]
+        buf = _with_ratio(ratio, lambda: conv_window(dyfull, wfull, None, x.dtype, 1, 1, Cin, False, Kc * Cin, Cin, 1, "dgrad",
+                                                     (N, Hp, Wp, Kc)))
+        if cfg.pad_mode == PAD_REFLECT and p > 0:
+            dx = torch.empty_like(x)
+            _lib.check(_lib.lib().p2p_reflect_pad_fold(_p(buf), _p(dx), N, H, W, Cin, p, _DT[x.dtype], _stream()))
+        else:
+            dx = buf[:, p: p + H, p: p + W, :].contiguous() if p else buf
+    if need_dw:
+        if xpad is not None and xpad[0] == "packed_out" and xpad[1].shape[0] == rows:
+            xp = xpad[1]
+        else:
+            xp = _pad_rows64(x, p, cfg.pad_mode == PAD_REFLECT)
+        dwfull = torch.zeros((Kc, Cin), dtype=torch.float32, device=x.device)
+        _with_ratio(ratio, lambda: _wgrad_1x1(dyfull, xp, rows, Kc, Cin, dwfull, Wp))
+        dwp = dwfull[:KH * KW * Cout].reshape(KH, KW, Cout, Cin)
+    return dx, dwp
+
+
+def _pad_rows64(x, p, reflect):
+    """x padded by p on every side as [rows64(N*Hp*Wp)][C] with a zero tail (C * itemsize % 16 == 0)"""
+    N, H, W, C = x.shape
+    Hp, Wp = H + 2 * p, W + 2 * p
+    rows = _rows64(N * Hp * Wp)
+    xp = torch.empty((rows, C), dtype=x.dtype, device=x.device)
+    _lib.check(_lib.lib().p2p_pad_planes(_p(x), _p(xp), N, H, W, C, p, p, Hp, Wp, 1, rows, int(reflect), _DT[x.dtype], _stream()))
+    return xp
+
+
+
 def _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux=None):
     """nn.Conv2d (+ nn.ReflectionPad2d) / nn.ConvTranspose2d forward, NHWC (networks.py:145-154, 190-207, 223-246, 340-361)"""
     N, H, W, Cx = x.shape
@@ -534,6 +668,8 @@ def _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux=None):
     assert Cx == Cin, (Cx, Cin)
     wq = _weight_for(x, wphys, w16)
     Jout = Cout
+    if _colable(x, cfg, Cin, Cout, KH, KW) == "in":
+        return _col_in_forward(x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux)
     pk = _packable(x, cfg, Cin, Cout, KH, KW)
     if pk is not None:
         return _packed_forward(pk, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux)
@@ -581,6 +717,15 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
     dx = dw = db = None
     if need_db:
         db = _bias_grad(dy, Cout)
+    col = _colable(x, cfg, Cin, Cout, KH, KW)
+    if col == "in" and (not need_dx or cfg.pad_mode == PAD_ZERO or cfg.pad == 0):
+        dx, dwp = _col_in_backward(x, _weight_for(x, wphys, w16) if need_dx else None, dy, cfg, Cin, Cout, KH, KW, need_dx,
+                                   need_dw, xpad)
+        return dx, (dwp.permute(2, 3, 0, 1) if dwp is not None else None), db
+    if col == "out":
+        dx, dwp = _col_out_backward(x, _weight_for(x, wphys, w16) if need_dx else None, dy, cfg, Cin, Cout, KH, KW, need_dx,
+                                    need_dw, xpad)
+        return dx, (dwp.permute(2, 3, 0, 1) if dwp is not None else None), db
     pk = _packable(x, cfg, Cin, Cout, KH, KW)
     if pk is not None and (pk == "out" or not need_dx):
         dx, dwp = _packed_backward(pk, x, _weight_for(x, wphys, w16) if need_dx else None, dy, cfg, Cin, Cout, KH, KW,
@@ -652,6 +797,8 @@ def _alg_ratio(x, weight, cfg):
     _, Cout, Cin, KH, KW = _phys(weight, cfg)
     if x.dtype != torch.bfloat16 or (Cin % 16 == 0 and Cout % 16 == 0):
         return 1.0
+    if _colable(x, cfg, Cin, Cout, KH, KW) == "in":
+        return 1.0          # set per launch by the im2col path
     pk = _packable(x, cfg, Cin, Cout, KH, KW)
     if pk == "in":
         return KW * Cin / 16.0
