@@ -403,15 +403,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
                     if (a.atomic) {
                         if (fullv && (((uintptr_t)o) & 15) == 0) {
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                if (MODE == 2 && a.nsplit == 1) {   // sole writer of the tile: plain read-add-write
-                                    float4 t = reinterpret_cast<const float4*>(o)[i];
-                                    t.x += f[4 * i]; t.y += f[4 * i + 1]; t.z += f[4 * i + 2]; t.w += f[4 * i + 3];
-                                    reinterpret_cast<float4*>(o)[i] = t;
-                                } else {
-                                    red_add_v4(o + 4 * i, f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
-                                }
-                            }
+                            for (int i = 0; i < 4; ++i) red_add_v4(o + 4 * i, f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
                         } else {
 #pragma unroll
                             for (int i = 0; i < 16; ++i)

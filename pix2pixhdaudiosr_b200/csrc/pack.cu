@@ -88,6 +88,12 @@ __global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __rest
                                                      int W, int C, int KH, int KW, int s, int p, int reflect, int OH, int OW, int Kc,
                                                      long long rows, unsigned total) {
     const int G = Kc >> 3, KWC = KW * C, KK = KH * KWC;
+    __shared__ int tab[128];            // k -> kh << 16 | kw << 8 | c
+    for (int k = threadIdx.x; k < 128; k += blockDim.x) {
+        const int kh = k / KWC, rem = k - kh * KWC, kw = rem / C;
+        tab[k] = (kh << 16) | (kw << 8) | (rem - kw * C);
+    }
+    __syncthreads();
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int g = (int)(i % G);
         const unsigned q = i / G;
@@ -102,7 +108,7 @@ __global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __rest
             for (int e = 0; e < 8; ++e) {
                 const int k = g * 8 + e;
                 if (k < KK) {
-                    const int kh = k / KWC, rem = k - kh * KWC, kw = rem / C, c = rem - kw * C;
+                    const int t = tab[k], kh = t >> 16, kw = (t >> 8) & 255, c = t & 255;
                     int iy = oy * s + kh - p, ix = ox * s + kw - p;
                     bool ok = true;
                     if (reflect) { iy = reflect_idx(iy, H); ix = reflect_idx(ix, W); }
@@ -143,6 +149,12 @@ __global__ void __launch_bounds__(256) pack_dy_full_kernel(const __nv_bfloat16* 
                                                            int OW, int Cout, int KH, int KW, int Hp, int Wp, int Kc, long long rows,
                                                            unsigned total) {
     const int G = Kc >> 3, KWC = KW * Cout, KK = KH * KWC;
+    __shared__ int tab[128];            // k -> kh << 16 | kw << 8 | co
+    for (int k = threadIdx.x; k < 128; k += blockDim.x) {
+        const int kh = k / KWC, rem = k - kh * KWC, kw = rem / Cout;
+        tab[k] = (kh << 16) | (kw << 8) | (rem - kw * Cout);
+    }
+    __syncthreads();
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int g = (int)(i % G);
         const unsigned q = i / G;
@@ -157,7 +169,7 @@ __global__ void __launch_bounds__(256) pack_dy_full_kernel(const __nv_bfloat16* 
             for (int e = 0; e < 8; ++e) {
                 const int k = g * 8 + e;
                 if (k < KK) {
-                    const int kh = k / KWC, rem = k - kh * KWC, kw = rem / Cout, co = rem - kw * Cout;
+                    const int t = tab[k], kh = t >> 16, kw = (t >> 8) & 255, co = t & 255;
                     const int sy = yp - kh, sx = xp - kw;
                     if (sy >= 0 && sy < OH && sx >= 0 && sx < OW) v[e] = dy[(((long long)n * OH + sy) * OW + sx) * Cout + co];
                 }
@@ -218,8 +230,8 @@ extern "C" int p2p_im2col(const void* x, void* xcol, int N, int H, int W, int C,
                           int OH, int OW, int Kc, long long rows_alloc, void* stream) {
     if (!x || !xcol) return fail(P2P_EINVAL, "null pointer argument");
     if (N < 1 || H < 1 || W < 1 || C < 1 || KH < 1 || KW < 1 || stride < 1 || pad < 0 || OH < 1 || OW < 1 || Kc % 8 != 0 ||
-        KH * KW * C > Kc)
-        return fail(P2P_EINVAL, "bad im2col geometry (KH*KW*C must fit Kc, Kc %% 8 == 0)");
+        KH * KW * C > Kc || Kc > 128)
+        return fail(P2P_EINVAL, "bad im2col geometry (KH*KW*C must fit Kc <= 128, Kc %% 8 == 0)");
     if ((OH - 1) * stride + KH > H + 2 * pad || (OW - 1) * stride + KW > W + 2 * pad) return fail(P2P_EINVAL, "output reaches past the padded input");
     if (reflect && (pad >= H || pad >= W)) return fail(P2P_EINVAL, "reflection padding must be smaller than the input");
     const long long rows = (long long)N * OH * OW;
@@ -246,8 +258,8 @@ extern "C" int p2p_col2im(const void* dxcol, void* dx, int N, int H, int W, int 
 extern "C" int p2p_pack_dy_full(const void* dy, void* out, int N, int OH, int OW, int Cout, int KH, int KW, int Kc,
                                 long long rows_alloc, void* stream) {
     if (!dy || !out) return fail(P2P_EINVAL, "null pointer argument");
-    if (N < 1 || OH < 1 || OW < 1 || Cout < 1 || KH < 1 || KW < 1 || Kc % 8 != 0 || KH * KW * Cout > Kc)
-        return fail(P2P_EINVAL, "bad packing geometry (KH*KW*Cout must fit Kc, Kc %% 8 == 0)");
+    if (N < 1 || OH < 1 || OW < 1 || Cout < 1 || KH < 1 || KW < 1 || Kc % 8 != 0 || KH * KW * Cout > Kc || Kc > 128)
+        return fail(P2P_EINVAL, "bad packing geometry (KH*KW*Cout must fit Kc <= 128, Kc %% 8 == 0)");
     const int Hp = OH + KH - 1, Wp = OW + KW - 1;
     const long long rows = (long long)N * Hp * Wp;
     if (rows_alloc < rows) return fail(P2P_EINVAL, "rows_alloc smaller than the padded grid");
