@@ -148,10 +148,12 @@ int p2p_pad_planes(const void* x, void* planes, int N, int H, int W, int C, int 
 /* Weight gradients in window form:  dW[tap_w[t]][j][c] (fp32 [wtaps_total][J][C], accumulated with red.add) +=
  *   sum_q aplanes[tap_a[t]][q][j] * bplanes[tap_b[t]][q + tap_dh[t]*Wp + tap_dw[t]][c]
  * over the padded pixel grid: aplanes = the output gradient laid out at the pitch of the padded input (zero where no output
- * exists), bplanes = the padded input (or its parity planes).  plane_rows % 64 == 0; taps grouped by (tap_a, tap_b); <= 32 taps. */
+ * exists), bplanes = the padded input (or its parity planes).  plane_rows % 64 == 0; taps grouped by (tap_a, tap_b); <= 32 taps.
+ * dw_is_zero != 0 promises that dW holds zeros (first gradient after zero_grad): tiles with a single writer are then stored
+ * instead of red.add-ed. */
 int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const void* bplanes, int n_bplanes, long long plane_rows, int Wp,
                           int J, int C, float* dw, int wtaps_total, int ntaps, const int* tap_a, const int* tap_b,
-                          const int* tap_dh, const int* tap_dw, const int* tap_w, void* stream);
+                          const int* tap_dh, const int* tap_dw, const int* tap_w, int dw_is_zero, void* stream);
 int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* planes, const void* weight, const float* bias, void* out,
                         int out_dtype, void* stream);
 /* Adjoint of reflection padding: dx[n,h,w,c] = sum of dxp over the padded positions that mirror onto (h,w).

@@ -50,7 +50,7 @@ _SIGS.update({
     "p2p_pad_nhwc": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_conv_window": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _vp]),
     "p2p_pad_planes": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _ll, _i, _i, _vp]),
-    "p2p_conv_wgrad_window": (_i, [_vp, _i, _vp, _i, _ll, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "p2p_conv_wgrad_window": (_i, [_vp, _i, _vp, _i, _ll, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "p2p_conv_window_run": (_i, [_c.POINTER(WindowDesc), _vp, _vp, _vp, _vp, _i, _vp]),
     "p2p_bias_grad": (_i, [_vp, _vp, _ll, _i, _i, _vp]),
     "p2p_reflect_pad_fold": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),

@@ -24,11 +24,13 @@ namespace {
 
 constexpr int WBM = 128;
 constexpr int kBStagesMax = 16;
-constexpr int kWinRowsMax = 320;                    // 40 KB per window buffer
+constexpr int kWinRowsMax = 312;                    // 39 KB per window buffer
 constexpr int WIN_BYTES = kWinRowsMax * 128;
 constexpr int WB_BYTES = 256 * 128;                 // one weight tile: up to 256 output channels x 64 channels
 constexpr int WRING_BYTES = 4 * WB_BYTES;             // 128 KB of weight tiles in flight, cut into b_stage_bytes stages
-constexpr int WSMEM = 2 * WIN_BYTES + WRING_BYTES + 1024 + 512 + 2048;     // + barriers + 2 x 256 staged bias values
+constexpr int EPI_STAGE_BYTES = 4 * 4096;           // one 32-row x 128-byte transposition tile per epilogue warp
+constexpr int WSMEM = 2 * WIN_BYTES + WRING_BYTES + 1024 + 512 + 2048 + EPI_STAGE_BYTES;     // + barriers + 2 x 256 staged bias values
+static_assert(WSMEM <= 232448, "window kernel shared memory");
 constexpr int kWThreads = 192;
 
 struct WindowArgs {
@@ -47,6 +49,7 @@ struct WindowArgs {
     int out_bf16, b_mn_major;
     int base_off_mode;
     int b_stages, b_stage_bytes;
+    int fast_epi;                  // output rows 16-byte aligned: staged, coalesced epilogue stores
     int nsplit, ci_per_split;      // split of the (channel chunk, plane) loop across CTAs; > 1 => fp32 red.add epilogue   // weight-tile ring: as many stages as fit 128 KB (TMA latency needs bytes in flight)
     short shift[P2P_MAX_TAPS];       // dh*Wp + dw
     unsigned char wtap[P2P_MAX_TAPS];
@@ -107,6 +110,61 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+
+// ---- coalesced epilogue stores --------------------------------------------------------------------------------------------
+// After tcgen05.ld a lane owns one accumulator ROW (32 lanes = 32 rows), so a direct v4 store touches 32 different 128-byte
+// lines with 16 bytes each and the LSU, not HBM, bounds the epilogue.  Each warp therefore transposes its 32-row chunk through
+// a private 4 KB shared-memory tile (16-byte pieces XOR-swizzled against bank conflicts) and stores rows cooperatively:
+// P lanes cover one row chunk of P*16 contiguous bytes, 32/P rows per instruction.
+template <int P> __device__ __forceinline__ int piece_swz(int row) {
+    return P == 8 ? (row & 7) : (P == 4 ? ((row >> 1) & 3) : (P == 2 ? ((row >> 2) & 1) : 0));
+}
+enum { EPI_ST = 0, EPI_RED = 1 };
+// regs: this lane's row chunk as P 16-byte pieces.  row_off: byte offset of this lane's row start (chunk column 0) in out;
+// okmask: ballot of valid rows; valid_bytes: bytes of the chunk inside the tensor (multiple of esz).
+template <int P>
+__device__ __forceinline__ void stage_store_chunk(uint32_t stage, int lane, const uint32_t* regs, long long row_off, unsigned okmask,
+                                                  char* out, int valid_bytes, int mode, int esz) {
+    __syncwarp();                               // the previous chunk's reads of the tile are done
+#pragma unroll
+    for (int p = 0; p < P; ++p)
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stage + (uint32_t)(lane * P + (p ^ piece_swz<P>(lane))) * 16u),
+                     "r"(regs[4 * p]), "r"(regs[4 * p + 1]), "r"(regs[4 * p + 2]), "r"(regs[4 * p + 3]) : "memory");
+    __syncwarp();
+    const int p = lane % P, r0 = lane / P;
+#pragma unroll
+    for (int k = 0; k < P; ++k) {
+        const int row = r0 + (32 / P) * k;
+        uint32_t v0, v1, v2, v3;
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v0), "=r"(v1), "=r"(v2), "=r"(v3)
+                     : "r"(stage + (uint32_t)(row * P + (p ^ piece_swz<P>(row))) * 16u));
+        const long long ro = __shfl_sync(0xffffffffu, row_off, row);
+        if (!((okmask >> row) & 1u)) continue;
+        char* dst = out + ro + p * 16;
+        if (p * 16 + 16 <= valid_bytes) {
+            if (mode == EPI_RED) red_add_v4(reinterpret_cast<float*>(dst), __uint_as_float(v0), __uint_as_float(v1), __uint_as_float(v2), __uint_as_float(v3));
+            else *reinterpret_cast<uint4*>(dst) = make_uint4(v0, v1, v2, v3);
+        } else if (p * 16 < valid_bytes) {      // ragged last piece of the tensor row
+            const uint32_t vv[4] = {v0, v1, v2, v3};
+            if (esz == 4) {
+                for (int i = 0; i < 4 && p * 16 + 4 * i < valid_bytes; ++i) {
+                    if (mode == EPI_RED) atomicAdd(reinterpret_cast<float*>(dst) + i, __uint_as_float(vv[i]));
+                    else reinterpret_cast<uint32_t*>(dst)[i] = vv[i];
+                }
+            } else {
+                for (int i = 0; i < 8 && p * 16 + 2 * i < valid_bytes; ++i)
+                    reinterpret_cast<uint16_t*>(dst)[i] = (uint16_t)(vv[i >> 1] >> ((i & 1) * 16));
+            }
+        }
+    }
+}
+__device__ __forceinline__ void stage_store(int P, uint32_t stage, int lane, const uint32_t* regs, long long row_off, unsigned okmask,
+                                            char* out, int valid_bytes, int mode, int esz) {
+    if (P == 8) stage_store_chunk<8>(stage, lane, regs, row_off, okmask, out, valid_bytes, mode, esz);
+    else if (P == 4) stage_store_chunk<4>(stage, lane, regs, row_off, okmask, out, valid_bytes, mode, esz);
+    else stage_store_chunk<2>(stage, lane, regs, row_off, okmask, out, valid_bytes, mode, esz);
+}
+
 // 128-byte-swizzle matrix descriptor; base_off = (start >> 7) & 7 for starts inside a 1024-byte swizzle atom
 __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t base_off) {
     return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
@@ -129,6 +187,7 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
     const uint32_t tmem_slot = bars + 8u * (8 + 2 * kBStagesMax);
     const uint32_t WB_STRIDE = (uint32_t)a.b_stage_bytes;
     const uint32_t bias_u32 = bars + 512;
+    const uint32_t epi_stage = bias_u32 + 2048;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int BN = a.BN, C = a.C, J = a.J;
@@ -276,6 +335,43 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
             mbar_wait(tfull(acc), (uint32_t)(v & 1));
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * 256;
+            if (a.fast_epi) {
+                const int esz = a.out_bf16 ? 2 : 4;
+                const unsigned okmask = __ballot_sync(0xffffffffu, rok);
+                const long long row_off = obase * esz;
+                const uint32_t stage = epi_stage + (uint32_t)(warp - 2) * 4096u;
+                const int mode = a.nsplit > 1 ? EPI_RED : EPI_ST;
+                for (int c2 = 0; c2 < BN; c2 += 32) {
+                    uint32_t r2[32];
+                    const bool two = c2 + 16 < BN;
+                    tmem_ld16(taddr + c2, *reinterpret_cast<uint32_t(*)[16]>(&r2[0]));
+                    if (two) tmem_ld16(taddr + c2 + 16, *reinterpret_cast<uint32_t(*)[16]>(&r2[16]));
+                    tmem_ld_wait();
+                    if (c2 >= c_count) break;
+                    const int ncol = two ? 32 : 16;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        if (4 * i < ncol) {
+                            const float4 bv = *reinterpret_cast<const float4*>(bs_ + c2 + 4 * i);
+                            r2[4 * i] = __float_as_uint(__uint_as_float(r2[4 * i]) + bv.x);
+                            r2[4 * i + 1] = __float_as_uint(__uint_as_float(r2[4 * i + 1]) + bv.y);
+                            r2[4 * i + 2] = __float_as_uint(__uint_as_float(r2[4 * i + 2]) + bv.z);
+                            r2[4 * i + 3] = __float_as_uint(__uint_as_float(r2[4 * i + 3]) + bv.w);
+                        }
+                    }
+                    int P = ncol / 4;
+                    if (a.out_bf16) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            const __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(r2[2 * i]), __uint_as_float(r2[2 * i + 1]));
+                            r2[i] = *reinterpret_cast<const uint32_t*>(&h);
+                        }
+                        P = ncol / 8;
+                    }
+                    const int valid = min(ncol, c_count - c2) * esz;
+                    stage_store(P, stage, lane, r2, row_off + (long long)c2 * esz, okmask, (char*)a.out, valid, mode, esz);
+                }
+            } else
             for (int c2 = 0; c2 < BN; c2 += 32) {
                 uint32_t r2[2][16];
                 tmem_ld16(taddr + c2, r2[0]);
@@ -385,7 +481,7 @@ __global__ void pad_nhwc_kernel(const T* __restrict__ x, T* __restrict__ xp, int
 constexpr int kGStagesMax = 8;
 constexpr int GA_BYTES = 2 * 8192;                  // [64 q][128 j]
 constexpr int GRING_BYTES = 3 * (GA_BYTES + kWinRowsMax * 128);     // 168 KB cut into stages of A tile + B window
-constexpr int GSMEM = GRING_BYTES + 1024 + 256;
+constexpr int GSMEM = GRING_BYTES + 1024 + 256 + EPI_STAGE_BYTES;
 constexpr int kMaxGroups = 8;
 
 struct WgradWinArgs {
@@ -398,6 +494,7 @@ struct WgradWinArgs {
     int ntaps, ngroups, atomic;
     int b_nboxes, b_rows_per_box;
     int stages, stage_bytes;
+    int fast_epi;
     int gbeg[kMaxGroups + 1];
     short ga[kMaxGroups], gb[kMaxGroups];
     short shift[32];
@@ -513,6 +610,24 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
             mbar_wait(tfull, (uint32_t)(li & 1));
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+            if (a.fast_epi) {
+                const unsigned okmask = __ballot_sync(0xffffffffu, rok);
+                const uint32_t stage = bars + 256 + (uint32_t)(warp - 2) * 4096u;
+                const int mode = a.atomic ? EPI_RED : EPI_ST;
+                for (int t = 0; t < a.ntaps; ++t) {
+                    const long long row_off = ((long long)a.wtap[t] * a.w_tap + (long long)j * a.C + c_begin) * 4;
+                    for (int c2 = 0; c2 < BN; c2 += 32) {
+                        uint32_t v2[32];
+                        const bool two = c2 + 16 < BN;
+                        tmem_ld16(taddr + t * BN + c2, *reinterpret_cast<uint32_t(*)[16]>(&v2[0]));
+                        if (two) tmem_ld16(taddr + t * BN + c2 + 16, *reinterpret_cast<uint32_t(*)[16]>(&v2[16]));
+                        tmem_ld_wait();
+                        if (c2 >= c_count) break;
+                        const int ncol = two ? 32 : 16;
+                        stage_store(ncol / 4, stage, lane, v2, row_off + (long long)c2 * 4, okmask, (char*)a.dw, min(ncol, c_count - c2) * 4, mode, 4);
+                    }
+                }
+            } else
             for (int t = 0; t < a.ntaps; ++t) {
                 float* o = a.dw + (long long)a.wtap[t] * a.w_tap + (long long)j * a.C + c_begin;
                 for (int c2 = 0; c2 < BN; c2 += 32) {
@@ -525,10 +640,22 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
                         const int c = c2 + hh * 16;
                         const uint32_t(&v)[16] = v2[hh];
                         if (!rok || c >= c_count) continue;
-                        if (c + 16 <= c_count && ((((uintptr_t)(o + c)) & 15) == 0)) {
+                        const bool vec = c + 16 <= c_count && ((((uintptr_t)(o + c)) & 15) == 0);
+                        if (!a.atomic) {            // sole writer of a tile the caller declared zero: plain stores
+                            if (vec) {
 #pragma unroll
-                            for (int i = 0; i < 4; ++i)      // red.add also when this CTA is the sole writer: a read-add-write
-                                red_add_v4(o + c + 4 * i, __uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),     // epilogue measured 1.7x slower
+                                for (int i = 0; i < 4; ++i)
+                                    reinterpret_cast<float4*>(o + c)[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                                                                                      __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+                            } else {
+#pragma unroll
+                                for (int i = 0; i < 16; ++i)
+                                    if (c + i < c_count) o[c + i] = __uint_as_float(v[i]);
+                            }
+                        } else if (vec) {           // red.add (a read-add-write epilogue measured 1.7x slower)
+#pragma unroll
+                            for (int i = 0; i < 4; ++i)
+                                red_add_v4(o + c + 4 * i, __uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
                                            __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
                         } else {
 #pragma unroll
@@ -689,6 +816,7 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
     a.out_bf16 = out_dtype == P2P_BF16;
     a.cpb = (C + 63) / 64;
     a.base_off_mode = g_window_base_off_mode;
+    a.fast_epi = ((long long)J * (a.out_bf16 ? 2 : 4)) % 16 == 0 && (((uintptr_t)out) & 15) == 0;
     {   // column tile: whole J when it fits 256 columns, else balanced multiples of 16
         const int nt = (J + 255) / 256;
         const int bn = ((J + nt - 1) / nt + 15) / 16 * 16;
@@ -768,7 +896,8 @@ extern "C" int p2p_conv_window(const void* xp, const void* weight, const float* 
 // taps must be grouped by (tap_a, tap_b).  ntaps * BN <= 512 TMEM columns: ntaps <= 32.
 extern "C" int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const void* bplanes, int n_bplanes, long long plane_rows,
                                      int Wp, int J, int C, float* dw, int wtaps_total, int ntaps, const int* tap_a,
-                                     const int* tap_b, const int* tap_dh, const int* tap_dw, const int* tap_w, void* stream) {
+                                     const int* tap_b, const int* tap_dh, const int* tap_dw, const int* tap_w, int dw_is_zero,
+                                     void* stream) {
     using namespace p2p;
     if (!aplanes || !bplanes || !dw || !tap_a || !tap_b || !tap_dh || !tap_dw || !tap_w) return fail(P2P_EINVAL, "null pointer argument");
     if (ntaps < 1 || ntaps > 32 || wtaps_total < 1) return fail(P2P_ENOTSUP, "window wgrad supports 1..32 taps, got %d", ntaps);
@@ -822,7 +951,8 @@ extern "C" int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const v
     if (nsplit < 1) nsplit = 1;
     a.kb_per_split = (a.total_kb + nsplit - 1) / nsplit;
     a.nsplit = (a.total_kb + a.kb_per_split - 1) / a.kb_per_split;
-    a.atomic = 1;                 // dW += : the caller may hand in a live gradient buffer
+    a.fast_epi = C % 4 == 0 && (((uintptr_t)dw) & 15) == 0;
+    a.atomic = !(dw_is_zero && a.nsplit == 1);    // dW += with red.add unless the buffer is known zero and the tile has one writer
     a.nwork = items * a.nsplit;
     if (int rc = encode_2d(&a.tm_a, aplanes, (unsigned long long)J, (unsigned long long)n_aplanes * plane_rows, 64, 64)) return rc;
     if (int rc = encode_2d(&a.tm_b, bplanes, (unsigned long long)C, (unsigned long long)n_bplanes * plane_rows, 64, (unsigned)a.b_rows_per_box)) return rc;

@@ -230,7 +230,7 @@ def _pad_weight(wq, Cout_p, Cin_p):
 
 # ---- stride-1 layers: TMA-fed shifted-window kernel (csrc/conv_window.cu) ------------------------------------------
 USE_WINDOW = True
-_WIN_ROWS_MAX = 320
+_WIN_ROWS_MAX = 312
 
 
 class _Shape:
@@ -326,7 +326,7 @@ def _window_passes(passes, x, wq, bias, out, wtaps_total, kind):
     return True
 
 
-def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None):
+def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None, fresh=False):
     """weight gradient of a layer call (its forward-type passes) as ONE launch of the window wgrad kernel:
     dW_t = sum over the padded grid of dout (laid out at the input's pitch) x shifted input window.  False if it does not fit."""
     if not USE_WINDOW or not passes or x.dtype != torch.bfloat16 or _lib.lib().p2p_conv_force_simple(-1) == 1:
@@ -378,7 +378,7 @@ def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None):
     shape = _Shape(N, 1, sum(P.gy * P.gx * P.ntaps for P in passes), J, 1, K, Hh, Wh)
     _timed("wgrad", shape, lambda: _lib.check(lib.p2p_conv_wgrad_window(
         _p(aplanes), s_out * s_out, _p(bplanes), s_in * s_in, rows, Wh, J, K, _p(dwp), wtaps_total, len(taps), ta, tb, th, tw, twt,
-        _stream())), umma=True)
+        int(fresh), _stream())), umma=True)
     return True
 
 
@@ -559,7 +559,7 @@ def _wgrad_1x1(a2d, b2d, rows, J, C, dw, Wp):
     one = (ctypes.c_int * 1)(0)
     shape = _Shape(1, 1, rows, J, 1, C, 1, rows)
     _timed("wgrad", shape, lambda: _lib.check(_lib.lib().p2p_conv_wgrad_window(
-        _p(a2d), 1, _p(b2d), 1, rows, Wp, J, C, _p(dw), 1, 1, one, one, one, one, one, _stream())), umma=True)
+        _p(a2d), 1, _p(b2d), 1, rows, Wp, J, C, _p(dw), 1, 1, one, one, one, one, one, 1, _stream())), umma=True)
 
 
 def _col_in_geometry(x, cfg, Cin, KH, KW):
@@ -775,13 +775,14 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
         if Cin != Cin0:
             dx = dx[..., :Cin0].contiguous()
     if need_dw:
-        direct = gphys is not None and thin is None and tuple(gphys.shape) == (KH, KW, Cout, Cin)
-        dwp = gphys if direct else torch.zeros((KH, KW, Cout, Cin), dtype=torch.float32, device=x.device)
+        direct = gphys is not None and thin is None and tuple(gphys.view.shape) == (KH, KW, Cout, Cin)
+        dwp = gphys.view if direct else torch.zeros((KH, KW, Cout, Cin), dtype=torch.float32, device=x.device)
+        fresh = gphys.first_write() if direct else True
         if cfg.transposed:
             wpasses = convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0]
         else:
             wpasses = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
-        if not _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None):
+        if not _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None, fresh):
             for P in wpasses:
                 _run_wgrad(P, x, dy, dwp)
         if direct:
@@ -855,6 +856,19 @@ def norm_act_backward(y, stats, dz, norm, act, slope):
 # ---------------------------------------------------------------------------------------------------
 # autograd Functions (x, outputs: NHWC)
 # ---------------------------------------------------------------------------------------------------
+class GradSink:
+    """a conv weight's slice of FusedAdam's flat gradient buffer (physical layout).  first_write() is True for the first
+    gradient written after the optimizer's zero_grad -- the kernels may then store instead of accumulate."""
+
+    def __init__(self, view, owner):
+        self.view, self.owner, self.epoch = view, owner, -1
+
+    def first_write(self):
+        fresh = self.epoch != self.owner.grad_epoch
+        self.epoch = self.owner.grad_epoch
+        return fresh
+
+
 class ConvBlockFn(torch.autograd.Function):
     """[ReflectionPad2d] Conv2d | ConvTranspose2d  ->  [InstanceNorm2d]  ->  [ReLU | LeakyReLU]  [+ residual]
     as ONE differentiable op.  In bf16 mode the pre-normalisation conv output stays fp32 inside the op (see

@@ -29,6 +29,7 @@ class FusedAdam:
         self.exp_avg_sq = torch.zeros(total, dtype=torch.float32, device=dev)
         self.flat_bf16 = torch.zeros(total, dtype=torch.bfloat16, device=dev)
         self.step_count = 0
+        self.grad_epoch = 0                                                # bumped by zero_grad (see ops.GradSink)
         self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)      # the authoritative step counter
         self.lr_dev = torch.full((1,), float(lr), dtype=torch.float32, device=dev)
         self._lr_on_dev = float(lr)
@@ -48,7 +49,7 @@ class FusedAdam:
                 p.data = self.flat[o:o + n].view(phys.shape).permute(*inv)
                 gview = self.flat_grad[o:o + n].view(phys.shape).permute(*inv)
                 conv.w16 = self.flat_bf16[o:o + n].view(phys.shape)
-                conv.gphys = self.flat_grad[o:o + n].view(phys.shape)       # wgrad kernels may accumulate here directly
+                conv.gphys = ops.GradSink(self.flat_grad[o:o + n].view(phys.shape), self)   # wgrad kernels write here directly
             else:
                 self.flat[o:o + n].copy_(p.data.reshape(-1))
                 p.data = self.flat[o:o + n].view(p.shape)
@@ -60,6 +61,7 @@ class FusedAdam:
 
     def zero_grad(self, set_to_none=False):
         self.flat_grad.zero_()
+        self.grad_epoch += 1
         for p, g in self._views:
             if p.grad is not g:
                 p.grad = g
