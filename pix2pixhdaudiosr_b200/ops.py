@@ -786,6 +786,7 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
             for P in wpasses:
                 _run_wgrad(P, x, dy, dwp)
         if direct:
+            gphys.written()
             return dx, None, db
         if thin is not None:
             dwp = dwp[:, :, :Cout0, :Cin0]
@@ -860,13 +861,19 @@ class GradSink:
     """a conv weight's slice of FusedAdam's flat gradient buffer (physical layout).  first_write() is True for the first
     gradient written after the optimizer's zero_grad -- the kernels may then store instead of accumulate."""
 
-    def __init__(self, view, owner):
-        self.view, self.owner, self.epoch = view, owner, -1
+    def __init__(self, view, owner, offset=0):
+        self.view, self.owner, self.epoch, self.offset = view, owner, -1, offset
 
     def first_write(self):
         fresh = self.epoch != self.owner.grad_epoch
         self.epoch = self.owner.grad_epoch
         return fresh
+
+    def written(self):
+        """the wgrad kernels of this weight are enqueued: data-parallel training may start reducing it (train.GradSync)"""
+        hook = getattr(self.owner, "grad_written_hook", None)
+        if hook is not None:
+            hook(self)
 
 
 class ConvBlockFn(torch.autograd.Function):

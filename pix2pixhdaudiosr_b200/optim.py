@@ -29,6 +29,7 @@ class FusedAdam:
         self.exp_avg_sq = torch.zeros(total, dtype=torch.float32, device=dev)
         self.flat_bf16 = torch.zeros(total, dtype=torch.bfloat16, device=dev)
         self.step_count = 0
+        self.grad_written_hook = None                                      # set by train.GradSync.attach_early
         self.grad_epoch = 0                                                # bumped by zero_grad (see ops.GradSink)
         self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)      # the authoritative step counter
         self.lr_dev = torch.full((1,), float(lr), dtype=torch.float32, device=dev)
@@ -49,7 +50,7 @@ class FusedAdam:
                 p.data = self.flat[o:o + n].view(phys.shape).permute(*inv)
                 gview = self.flat_grad[o:o + n].view(phys.shape).permute(*inv)
                 conv.w16 = self.flat_bf16[o:o + n].view(phys.shape)
-                conv.gphys = ops.GradSink(self.flat_grad[o:o + n].view(phys.shape), self)   # wgrad kernels write here directly
+                conv.gphys = ops.GradSink(self.flat_grad[o:o + n].view(phys.shape), self, o)   # wgrad kernels write here directly
             else:
                 self.flat[o:o + n].copy_(p.data.reshape(-1))
                 p.data = self.flat[o:o + n].view(p.shape)

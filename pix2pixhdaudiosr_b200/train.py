@@ -24,22 +24,52 @@ def assemble_losses(model, losses):
 
 
 class GradSync:
-    """average the flat gradient buffers over the data-parallel group (no-op for a single process)"""
+    """average the flat gradient buffers over the data-parallel group (no-op for a single process).
+
+    attach_early(optimizer): for an optimizer whose conv weights receive exactly ONE gradient per step (the generator's),
+    every large weight gradient is all-reduced as soon as its wgrad kernel is enqueued, so the transfer of the bulk of
+    the bytes (the 1536-channel residual blocks) overlaps the rest of the backward pass; start() then only reduces
+    what is left."""
+
+    EARLY_MIN = 1 << 20            # elements; smaller gradients travel with the final all-reduce
 
     def __init__(self, group=None):
         self.enabled = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
         self.group = group
         self.world = dist.get_world_size(group) if self.enabled else 1
+        self._early = {}           # optimizer id -> {"handles": [...], "ranges": [(offset, n), ...]}
+
+    def attach_early(self, optimizer):
+        if not self.enabled:
+            return
+        st = self._early[id(optimizer)] = {"handles": [], "ranges": []}
+
+        def hook(sink):
+            n = sink.view.numel()
+            if n >= self.EARLY_MIN:
+                st["handles"].append(dist.all_reduce(sink.view, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+                st["ranges"].append((sink.offset, n))
+        optimizer.grad_written_hook = hook
 
     def start(self, optimizer):
         if not self.enabled:
             return None
-        return dist.all_reduce(optimizer.flat_grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        st = self._early.get(id(optimizer))
+        if st is None or not st["ranges"]:
+            return [dist.all_reduce(optimizer.flat_grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True)]
+        handles, pos, total = st["handles"], 0, optimizer.flat_grad.numel()
+        for o, n in sorted(st["ranges"]) + [(total, 0)]:       # the gaps between the ranges already in flight
+            if o > pos:
+                handles.append(dist.all_reduce(optimizer.flat_grad[pos:o], op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+            pos = max(pos, o + n)
+        st["handles"], st["ranges"] = [], []
+        return handles
 
-    def finish(self, optimizer, handle):
-        if handle is None:
+    def finish(self, optimizer, handles):
+        if handles is None:
             return
-        handle.wait()                           # orders the current stream after the collective
+        for h in handles:
+            h.wait()                            # orders the current stream after the collective
         optimizer.grad_scale = 1.0 / self.world     # the averaging is folded into the Adam kernel's gradient read
 
 

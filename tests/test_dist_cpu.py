@@ -22,13 +22,21 @@ def _worker(rank, world, port, out):
     from pix2pixhdaudiosr_b200.train import GradSync, broadcast_parameters
     torch.manual_seed(rank)
     mk = lambda n: types.SimpleNamespace(flat=torch.randn(n), flat_bf16=torch.zeros(n, dtype=torch.bfloat16),
-                                         flat_grad=torch.randn(n), grad_scale=1.0)
+                                         flat_grad=torch.randn(n), grad_scale=1.0, grad_written_hook=None, grad_epoch=0)
     model = types.SimpleNamespace(optimizer_G=mk(1003), optimizer_D=mk(77))
     local_grads = [model.optimizer_G.flat_grad.clone(), model.optimizer_D.flat_grad.clone()]
     broadcast_parameters(model)
     sync = GradSync()
     assert sync.enabled and sync.world == world
+    # early path: two "large" weight gradients of G are reduced the moment they are written, the rest at start()
+    sync.EARLY_MIN = 100
+    sync.attach_early(model.optimizer_G)
+    from pix2pixhdaudiosr_b200.ops import GradSink
+    g = model.optimizer_G
+    for o, n in ((640, 200), (128, 256), (8, 16)):       # the last one is below EARLY_MIN: it must ride with the rest
+        GradSink(g.flat_grad[o:o + n], g, o).written()
     hG = sync.start(model.optimizer_G)
+    assert len(hG) == 2 + 3                               # 2 early ranges + the 3 gaps around them
     hD = sync.start(model.optimizer_D)           # both collectives in flight, as in train_step
     sync.finish(model.optimizer_G, hG)
     sync.finish(model.optimizer_D, hD)
