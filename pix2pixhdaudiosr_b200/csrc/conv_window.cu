@@ -48,7 +48,8 @@ struct WindowArgs {
     int BN, n_tiles, m_tiles, cpb;
     int out_bf16, b_mn_major;
     int base_off_mode;
-    int b_stages, b_stage_bytes;
+    int tps, b_tap_bytes;          // taps per ring stage (amortises the issuing thread's per-stage overhead), bytes of one tap tile
+    int b_stages, b_stage_bytes;   // weight ring: stages of tps tap tiles, as many as fit WRING_BYTES
     int fast_epi;                  // output rows 16-byte aligned: staged, coalesced epilogue stores
     int nsplit, ci_per_split;      // split of the (channel chunk, plane) loop across CTAs; > 1 => fp32 red.add epilogue   // weight-tile ring: as many stages as fit 128 KB (TMA latency needs bytes in flight)
     short shift[P2P_MAX_TAPS];       // dh*Wp + dw
@@ -185,7 +186,8 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
     auto tfull = [&](int i) { return bars + 8u * (4 + 2 * kBStagesMax + i); };
     auto tempty = [&](int i) { return bars + 8u * (6 + 2 * kBStagesMax + i); };
     const uint32_t tmem_slot = bars + 8u * (8 + 2 * kBStagesMax);
-    const uint32_t WB_STRIDE = (uint32_t)a.b_stage_bytes;
+    const uint32_t WB_STRIDE = (uint32_t)a.b_stage_bytes;       // = tps * TAP_STRIDE
+    const uint32_t TAP_STRIDE = (uint32_t)a.b_tap_bytes;
     const uint32_t bias_u32 = bars + 512;
     const uint32_t epi_stage = bias_u32 + 2048;
 
@@ -235,17 +237,22 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
                     for (int bx = 0; bx < a.nboxes; ++bx)
                         tma_load_2d(base + ab * WIN_BYTES + bx * a.rows_per_box * 128, &a.tm_x, c0,
                                     (int)((long long)pl * a.Q + q0 + (long long)bx * a.rows_per_box), afull(ab));
-                    for (int t = a.pbeg[u][pl]; t < a.pbeg[u][pl + 1]; ++t) {
+                    const int t_end = a.pbeg[u][pl + 1];
+                    for (int t0 = a.pbeg[u][pl]; t0 < t_end; t0 += a.tps) {       // one ring stage = up to tps taps
+                        const int nt_s = min(a.tps, t_end - t0);
                         const uint32_t s = bs;
                         mbar_wait(bempty(s), bph);
                         if (++bs == (uint32_t)kBStages) { bs = 0; bph ^= 1u; }
-                        mbar_expect_tx(bfull(s), b_bytes);
-                        const uint32_t dst = wbase + s * WB_STRIDE;
-                        if (!a.b_mn_major) {
-                            tma_load_2d(dst, &a.tm_w, c0, (int)a.wtap[t] * J + j0, bfull(s));
-                        } else {
-                            for (int jb = 0; jb * 64 < BN; ++jb)
-                                tma_load_2d(dst + jb * 8192, &a.tm_w, j0 + jb * 64, (int)a.wtap[t] * C + c0, bfull(s));
+                        mbar_expect_tx(bfull(s), b_bytes * (uint32_t)nt_s);
+                        for (int k = 0; k < nt_s; ++k) {
+                            const int t = t0 + k;
+                            const uint32_t dst = wbase + s * WB_STRIDE + (uint32_t)k * TAP_STRIDE;
+                            if (!a.b_mn_major) {
+                                tma_load_2d(dst, &a.tm_w, c0, (int)a.wtap[t] * J + j0, bfull(s));
+                            } else {
+                                for (int jb = 0; jb * 64 < BN; ++jb)
+                                    tma_load_2d(dst + jb * 8192, &a.tm_w, j0 + jb * 64, (int)a.wtap[t] * C + c0, bfull(s));
+                            }
                         }
                     }
                 }
@@ -282,18 +289,28 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
                     tc_fence_after();
                     const uint32_t win = base + ab * WIN_BYTES;
                     const int t_end = a.pbeg[u][pl + 1];
-                    for (int t = a.pbeg[u][pl]; t < t_end; ++t) {
+                    for (int t0 = a.pbeg[u][pl]; t0 < t_end; t0 += a.tps) {       // one ring stage = up to tps taps
+                        const int nt_s = min(a.tps, t_end - t0);
                         const uint32_t s = bs;
-                        const uint64_t ad = a_hi | (uint64_t)((win + (uint32_t)a.shift[t] * 128u) >> 4);
-                        const uint64_t bd = b_hi | (uint64_t)((wbase + s * WB_STRIDE) >> 4);
+                        const uint64_t bd0 = b_hi | (uint64_t)((wbase + s * WB_STRIDE) >> 4);
+                        uint64_t ad[4];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            ad[k] = a_hi | (uint64_t)((win + (uint32_t)a.shift[min(t0 + k, t_end - 1)] * 128u) >> 4);
                         mbar_wait(bfull(s), bph);
                         if (++bs == (uint32_t)kBStages) { bs = 0; bph ^= 1u; }
                         tc_fence_after();
                         if (elect_one()) {
-                            umma_bf16(d_tmem, ad, bd, idesc, accumulate);
-                            if (nk16 > 1) umma_bf16(d_tmem, ad + 2, bd + b_k16, idesc, 1);
-                            if (nk16 > 2) umma_bf16(d_tmem, ad + 4, bd + 2 * b_k16, idesc, 1);
-                            if (nk16 > 3) umma_bf16(d_tmem, ad + 6, bd + 3 * b_k16, idesc, 1);
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                if (k < nt_s) {
+                                    const uint64_t bd = bd0 + (uint64_t)(k * (TAP_STRIDE >> 4));
+                                    umma_bf16(d_tmem, ad[k], bd, idesc, k == 0 ? accumulate : 1u);
+                                    if (nk16 > 1) umma_bf16(d_tmem, ad[k] + 2, bd + b_k16, idesc, 1);
+                                    if (nk16 > 2) umma_bf16(d_tmem, ad[k] + 4, bd + 2 * b_k16, idesc, 1);
+                                    if (nk16 > 3) umma_bf16(d_tmem, ad[k] + 6, bd + 3 * b_k16, idesc, 1);
+                                }
+                            }
                             umma_commit(bempty(s));
                         }
                         __syncwarp();
@@ -471,6 +488,233 @@ __global__ void pad_nhwc_kernel(const T* __restrict__ x, T* __restrict__ xp, int
         if (sy >= 0 && sy < H && sx >= 0 && sx < W)
             v = reinterpret_cast<const uint4*>(x)[(((long long)n * H + sy) * W + sx) * C8 + c];
         reinterpret_cast<uint4*>(xp)[i] = v;
+    }
+}
+
+
+// ====================================================================================================================
+// Swapped form for layers with J <= 128 output channels.  Measured (scratch/mma_rate.cu): one tcgen05.mma of M = 128, K = 16
+// costs >= 105 cycles whatever N <= 192 is, so with the pixels on the M side a 96-channel layer can reach at most 48/105 of
+// the tensor peak.  Here the WEIGHT tile is the A operand (M = 128 output channels, rows >= J are don't-care) and 256 padded
+// pixels of the shifted window are the B operand (N = 256, 128 math cycles per instruction): D^T[j][pixel].  The epilogue
+// transposes 32 channels x 32 pixels through shared memory and stores 128 contiguous bytes per pixel and warp.
+// ====================================================================================================================
+constexpr int SBM = 256;                            // pixels per tile = N of the MMA
+constexpr int kSwapRowsMax = 400;                   // 256 + halo rows, 50 KB per window buffer
+constexpr int SWIN_BYTES = kSwapRowsMax * 128;
+constexpr int SW_TAP_BYTES = 16384;                 // [128 j][64 c] (K-major) or 2 x [64 c][64 j] (MN-major) bf16
+constexpr int kSwapStages = 6;
+constexpr int SWSMEM = 2 * SWIN_BYTES + kSwapStages * SW_TAP_BYTES + 1024 + 512 + 2 * SBM * 8 + EPI_STAGE_BYTES;
+static_assert(SWSMEM <= 232448, "swapped window kernel shared memory");
+
+__global__ void __launch_bounds__(kWThreads, 1) conv_window_swap_kernel(const __grid_constant__ WindowArgs a) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t wbase = base + 2 * SWIN_BYTES;
+    const uint32_t bars = wbase + kSwapStages * SW_TAP_BYTES;
+    auto afull = [&](int i) { return bars + 8u * i; };
+    auto aempty = [&](int i) { return bars + 8u * (2 + i); };
+    auto bfull = [&](int s) { return bars + 8u * (4 + s); };
+    auto bempty = [&](int s) { return bars + 8u * (4 + kSwapStages + s); };
+    auto tfull = [&](int i) { return bars + 8u * (4 + 2 * kSwapStages + i); };
+    auto tempty = [&](int i) { return bars + 8u * (6 + 2 * kSwapStages + i); };
+    const uint32_t tmem_slot = bars + 8u * (8 + 2 * kSwapStages);
+    const uint32_t table_u32 = bars + 512;                  // long long [2][256]: output element offset of each pixel, -1 = dropped
+    const uint32_t epi_stage = table_u32 + 2 * SBM * 8;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int C = a.C, J = a.J;
+    const uint32_t a_bytes = (uint32_t)a.nboxes * a.rows_per_box * 128u;
+
+    if (warp == 1) {
+        if (lane == 0) {
+            for (int i = 0; i < 2; ++i) { mbar_init(afull(i), 1); mbar_init(aempty(i), 1); mbar_init(tfull(i), 1); mbar_init(tempty(i), 128); }
+            for (int s = 0; s < kSwapStages; ++s) { mbar_init(bfull(s), 1); mbar_init(bempty(s), 1); }
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+    if (warp == 0) {
+        // ================================ TMA producer ================================
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_x) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_w) : "memory");
+            int ia = 0;
+            uint32_t bs = 0, bph = 1;
+            for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x) {
+                const int jt = (int)(w % a.n_tiles);
+                const long long mtu = w / a.n_tiles;
+                const int u = (int)(mtu / a.m_tiles);
+                const long long q0 = (mtu - (long long)u * a.m_tiles) * SBM;
+                const int j0 = jt * 128;
+                for (int ci = 0; ci < a.cpb * a.nplanes; ++ci, ++ia) {
+                    const int cc = ci / a.nplanes, pl = ci - cc * a.nplanes;
+                    const int c0 = cc * 64;
+                    const int ab = ia & 1;
+                    if (ia >= 2) mbar_wait(aempty(ab), (uint32_t)(((ia >> 1) - 1) & 1));
+                    mbar_expect_tx(afull(ab), a_bytes);
+                    for (int bx = 0; bx < a.nboxes; ++bx)
+                        tma_load_2d(base + ab * SWIN_BYTES + bx * a.rows_per_box * 128, &a.tm_x, c0,
+                                    (int)((long long)pl * a.Q + q0 + (long long)bx * a.rows_per_box), afull(ab));
+                    const int t_end = a.pbeg[u][pl + 1];
+                    for (int t = a.pbeg[u][pl]; t < t_end; ++t) {
+                        const uint32_t s = bs;
+                        mbar_wait(bempty(s), bph);
+                        if (++bs == (uint32_t)kSwapStages) { bs = 0; bph ^= 1u; }
+                        mbar_expect_tx(bfull(s), SW_TAP_BYTES);
+                        const uint32_t dst = wbase + s * SW_TAP_BYTES;
+                        if (!a.b_mn_major) {
+                            tma_load_2d(dst, &a.tm_w, c0, (int)a.wtap[t] * J + j0, bfull(s));
+                        } else {
+                            tma_load_2d(dst, &a.tm_w, j0, (int)a.wtap[t] * C + c0, bfull(s));
+                            tma_load_2d(dst + 8192, &a.tm_w, j0 + 64, (int)a.wtap[t] * C + c0, bfull(s));
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ================================ MMA issuer ================================
+        {
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a.b_mn_major << 15) | ((uint32_t)(SBM >> 3) << 17) |
+                                   ((uint32_t)(128 >> 4) << 24);
+            const uint64_t w_hi = a.b_mn_major ? make_desc(0, 8192, 1024, 0) : make_desc(0, 16, 1024, 0);     // weights: the A operand
+            const uint32_t w_k16 = a.b_mn_major ? (2048u >> 4) : (32u >> 4);
+            const uint64_t x_hi = make_desc(0, 16, 1024, 0);                                                  // window rows: the B operand
+            int ia = 0, li = 0;
+            uint32_t bs = 0, bph = 0;
+            for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
+                const int u = (int)((w / a.n_tiles) / a.m_tiles);
+                const int acc = li & 1, v = li >> 1;
+                if (v >= 1) mbar_wait(tempty(acc), (uint32_t)((v - 1) & 1));
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * 256;
+                uint32_t accumulate = 0;
+                for (int ci = 0; ci < a.cpb * a.nplanes; ++ci, ++ia) {
+                    const int cc = ci / a.nplanes, pl = ci - cc * a.nplanes;
+                    const int nk16 = min(64, C - cc * 64) >> 4;
+                    const int ab = ia & 1;
+                    mbar_wait(afull(ab), (uint32_t)((ia >> 1) & 1));
+                    tc_fence_after();
+                    const uint32_t win = base + ab * SWIN_BYTES;
+                    const int t_end = a.pbeg[u][pl + 1];
+                    for (int t = a.pbeg[u][pl]; t < t_end; ++t) {
+                        const uint32_t s = bs;
+                        const uint64_t xd = x_hi | (uint64_t)((win + (uint32_t)a.shift[t] * 128u) >> 4);
+                        const uint64_t wd = w_hi | (uint64_t)((wbase + s * SW_TAP_BYTES) >> 4);
+                        mbar_wait(bfull(s), bph);
+                        if (++bs == (uint32_t)kSwapStages) { bs = 0; bph ^= 1u; }
+                        tc_fence_after();
+                        if (elect_one()) {
+                            umma_bf16(d_tmem, wd, xd, idesc, accumulate);
+                            if (nk16 > 1) umma_bf16(d_tmem, wd + w_k16, xd + 2, idesc, 1);
+                            if (nk16 > 2) umma_bf16(d_tmem, wd + 2 * w_k16, xd + 4, idesc, 1);
+                            if (nk16 > 3) umma_bf16(d_tmem, wd + 3 * w_k16, xd + 6, idesc, 1);
+                            umma_commit(bempty(s));
+                        }
+                        __syncwarp();
+                        accumulate = 1;
+                    }
+                    if (elect_one()) umma_commit(aempty(ab));
+                    __syncwarp();
+                }
+                if (elect_one()) umma_commit(tfull(acc));
+                __syncwarp();
+            }
+        }
+        __syncwarp();
+    } else {
+        // ================================ epilogue ================================
+        const int quarter = warp & 3;                       // TMEM lanes 32*quarter .. +31 = output channels of this warp
+        const int et = (warp - 2) * 32 + lane;
+        const long long plane = (long long)a.Hp * a.Wp;
+        long long* table = reinterpret_cast<long long*>(smem_raw + (table_u32 - smem_u32(smem_raw)));
+        const uint32_t stage = epi_stage + (uint32_t)(warp - 2) * 4096u;
+        const int esz = a.out_bf16 ? 2 : 4;
+        int li = 0;
+        for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
+            const int jt = (int)(w % a.n_tiles);
+            const long long mtu = w / a.n_tiles;
+            const int u = (int)(mtu / a.m_tiles);
+            const long long mt = mtu - (long long)u * a.m_tiles;
+            const int acc = li & 1, v = li >> 1;
+            long long* tb = table + acc * SBM;
+            for (int i = et; i < SBM; i += 128) {           // where each of the tile's 256 padded pixels lands (or -1)
+                const long long q = mt * SBM + i;
+                long long off = -1;
+                if (q < a.Q) {
+                    const int n = (int)(q / plane);
+                    const int rem = (int)(q - (long long)n * plane);
+                    const int y = rem / a.Wp, x = rem - y * a.Wp;
+                    if (y < a.gy[u] && x < a.gx[u])
+                        off = (((long long)n * a.OHf + (y * a.oys + a.oyo[u])) * a.OWf + (x * a.oxs + a.oxo[u])) * J;
+                }
+                tb[i] = off;
+            }
+            const int jch = jt * 128 + quarter * 32 + lane;                 // this lane's output channel
+            const float bj = (a.bias && jch < J) ? __ldg(a.bias + jch) : 0.f;
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            mbar_wait(tfull(acc), (uint32_t)(v & 1));
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * 256;
+            const int jc = jt * 128 + quarter * 32 + (lane & 7) * 4;        // first of the 4 channels this lane stores
+            for (int c2 = 0; c2 < SBM; c2 += 32) {
+                uint32_t r[32];
+                tmem_ld16(taddr + c2, *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
+                tmem_ld16(taddr + c2 + 16, *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
+                tmem_ld_wait();
+                __syncwarp();                       // the previous chunk's reads of the tile are done
+#pragma unroll
+                for (int i = 0; i < 32; ++i)        // tile[pixel i][channel lane]
+                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(stage + (uint32_t)(i * 32 + lane) * 4u), "f"(__uint_as_float(r[i]) + bj) : "memory");
+                __syncwarp();
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const int pix = (lane >> 3) + 4 * k;
+                    float4 f;
+                    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(f.x), "=f"(f.y), "=f"(f.z), "=f"(f.w)
+                                 : "r"(stage + (uint32_t)(pix * 32 + (lane & 7) * 4) * 4u));
+                    const long long off = tb[c2 + pix];
+                    if (off < 0 || jc >= J) continue;
+                    char* dst = (char*)a.out + (off + jc) * esz;
+                    if (jc + 4 <= J) {
+                        if (a.out_bf16) {
+                            const __nv_bfloat162 h0 = __floats2bfloat162_rn(f.x, f.y), h1 = __floats2bfloat162_rn(f.z, f.w);
+                            uint2 t2;
+                            t2.x = *reinterpret_cast<const uint32_t*>(&h0);
+                            t2.y = *reinterpret_cast<const uint32_t*>(&h1);
+                            *reinterpret_cast<uint2*>(dst) = t2;
+                        } else {
+                            *reinterpret_cast<float4*>(dst) = f;
+                        }
+                    } else {
+                        const float fv[4] = {f.x, f.y, f.z, f.w};
+                        for (int i = 0; i < 4 && jc + i < J; ++i) {
+                            if (a.out_bf16) reinterpret_cast<__nv_bfloat16*>(dst)[i] = __float2bfloat16_rn(fv[i]);
+                            else reinterpret_cast<float*>(dst)[i] = fv[i];
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(tempty(acc));
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
     }
 }
 
@@ -799,12 +1043,22 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
         if (a.pbeg[u][nplanes] == a.pbeg[u][0]) return fail(P2P_EINVAL, "sub-pass %d has no taps", u);
     }
     if (t != ntaps) return fail(P2P_EINVAL, "taps must be grouped by sub-pass and sorted by plane");
-    a.win_rows = WBM + halo;
-    if (a.win_rows > kWinRowsMax) return fail(P2P_ENOTSUP, "window of %d rows exceeds the %d-row buffer", a.win_rows, kWinRowsMax);
+    // swapped form (weights on the M side, 256 pixels on the N side) for J <= 128: see conv_window_swap_kernel
+    static int swap_env = -1;
+    if (swap_env < 0) { const char* e = getenv("P2P_CONV_SWAP"); swap_env = (e && e[0] == '0') ? 0 : 1; }
+    a.Q = (long long)d->N * Hp * Wp;
+    const long long tiles256 = ((a.Q + SBM - 1) / SBM) * d->nsub * ((J + 127) / 128);
+    // measured per layer (gpurun_out/layers_swap.log vs layers_noswap.log): a win for J = 96 (res blocks: dgrad 253 -> 164 us per
+    // 4 calls), a loss for J <= 64 (fixed 256-pixel epilogue, 16 KB weight tiles) and mixed at J = 128
+    const bool swap = swap_env && J >= 96 && J < 128 && J % 4 == 0 && SBM + halo <= kSwapRowsMax && tiles256 >= 120 &&
+                      (((uintptr_t)out) & 15) == 0;
+    const int TR = swap ? SBM : WBM, rows_max = swap ? kSwapRowsMax : kWinRowsMax;
+    a.win_rows = TR + halo;
+    if (a.win_rows > rows_max) return fail(P2P_ENOTSUP, "window of %d rows exceeds the %d-row buffer", a.win_rows, rows_max);
     a.nboxes = (a.win_rows + 255) / 256;
     a.rows_per_box = (a.win_rows + a.nboxes - 1) / a.nboxes;
     a.rows_per_box = (a.rows_per_box + 7) / 8 * 8;          // keeps every box 1024-byte aligned
-    if (a.nboxes * a.rows_per_box > kWinRowsMax) return fail(P2P_ENOTSUP, "window boxes exceed the buffer");
+    if (a.nboxes * a.rows_per_box > rows_max) return fail(P2P_ENOTSUP, "window boxes exceed the buffer");
     const long long w_tap = d->w_tap, w_k = d->w_k, w_j = d->w_j;
     if (w_k == 1 && w_j % 8 == 0 && w_tap % 8 == 0) a.b_mn_major = 0;
     else if (w_j == 1 && w_k % 8 == 0 && w_tap % 8 == 0 && J % 8 == 0) a.b_mn_major = 1;
@@ -817,16 +1071,22 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
     a.cpb = (C + 63) / 64;
     a.base_off_mode = g_window_base_off_mode;
     a.fast_epi = ((long long)J * (a.out_bf16 ? 2 : 4)) % 16 == 0 && (((uintptr_t)out) & 15) == 0;
-    {   // column tile: whole J when it fits 256 columns, else balanced multiples of 16
+    if (swap) {
+        a.BN = 128;         // rows of the weight tile (output channels per MMA)
+    } else {   // column tile: whole J when it fits 256 columns, else balanced multiples of 16
         const int nt = (J + 255) / 256;
         const int bn = ((J + nt - 1) / nt + 15) / 16 * 16;
         a.BN = bn < 16 ? 16 : bn;
     }
     a.n_tiles = (J + a.BN - 1) / a.BN;
-    a.b_stage_bytes = a.b_mn_major ? ((a.BN + 63) / 64) * 8192 : ((a.BN * 128 + 1023) / 1024) * 1024;
+    a.b_tap_bytes = a.b_mn_major ? ((a.BN + 63) / 64) * 8192 : ((a.BN * 128 + 1023) / 1024) * 1024;
+    a.tps = WRING_BYTES / (3 * a.b_tap_bytes);          // keep >= 3 stages in flight
+    if (a.tps > 4) a.tps = 4;
+    if (a.tps < 1) a.tps = 1;
+    a.b_stage_bytes = a.tps * a.b_tap_bytes;
     a.b_stages = WRING_BYTES / a.b_stage_bytes;
     if (a.b_stages > kBStagesMax) a.b_stages = kBStagesMax;
-    const long long mt = (a.Q + WBM - 1) / WBM;
+    const long long mt = (a.Q + TR - 1) / TR;
     if (mt * a.nsub > 2000000000LL / a.n_tiles) return fail(P2P_ENOTSUP, "too many tiles");
     a.m_tiles = (int)mt;
     a.nwork = mt * a.n_tiles * a.nsub;
@@ -835,7 +1095,7 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     a.nsplit = 1;
     a.ci_per_split = a.cpb * nplanes;
-    if (!a.out_bf16 && a.nwork * 2 <= sms && a.cpb * nplanes >= 4) {
+    if (!swap && !a.out_bf16 && a.nwork * 2 <= sms && a.cpb * nplanes >= 4) {
         // few tiles (the 16x4-pixel bottleneck layers): split the channel loop so that one wave fills the chip; the
         // partial tiles meet in the fp32 output through red.add
         int ns = (int)(sms / a.nwork);
@@ -861,6 +1121,17 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
         configured = true;
     }
     const long long grid = a.nwork < sms ? a.nwork : sms;
+    if (swap) {
+        static bool configured_swap = false;
+        if (!configured_swap) {
+            if (cudaFuncSetAttribute(conv_window_swap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWSMEM) != cudaSuccess)
+                return check_launch("cudaFuncSetAttribute(conv_window_swap_kernel)");
+            configured_swap = true;
+        }
+        conv_window_swap_kernel<<<(unsigned)grid, kWThreads, SWSMEM, (cudaStream_t)stream>>>(a);
+        note_umma_launch();
+        return check_launch("conv_window_swap_kernel");
+    }
     conv_window_kernel<<<(unsigned)grid, kWThreads, WSMEM, (cudaStream_t)stream>>>(a);
     note_umma_launch();
     return check_launch("conv_window_kernel");
