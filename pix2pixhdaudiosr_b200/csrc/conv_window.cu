@@ -722,9 +722,12 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_swap_kernel(const __
 // dW[wtap_t][j][c] += sum_q A[a_plane_t][q][j] * B[b_plane_t][q + shift_t][c]: the reduction index q runs over the padded pixel
 // grid (A = dout laid out at the same pitch, zero where no output exists).  Both operands are MN-major (rows = q): A is one
 // TMA tile per 64-row block, B one shifted WINDOW shared by all taps of a group; every tap owns BN TMEM columns.
+// One tcgen05.mma costs >= 105 cycles whatever its N (scratch/mma_rate.cu), so the channel tile BN is made as wide as possible
+// (up to 256: the window is then BN/64 chunk boxes, LBO = bytes of one chunk) and the taps are cut into SETS of <= 512/BN taps;
+// a work item = (128 output channels, BN input channels, one tap set, one slice of the pixel blocks).
 constexpr int kGStagesMax = 8;
 constexpr int GA_BYTES = 2 * 8192;                  // [64 q][128 j]
-constexpr int GRING_BYTES = 3 * (GA_BYTES + kWinRowsMax * 128);     // 168 KB cut into stages of A tile + B window
+constexpr int GRING_BYTES = 196608;                 // 192 KB cut into stages of A tile + B window (all chunks)
 constexpr int GSMEM = GRING_BYTES + 1024 + 256 + EPI_STAGE_BYTES;
 constexpr int kMaxGroups = 8;
 
@@ -736,6 +739,8 @@ struct WgradWinArgs {
     long long w_tap;
     int J, C, BN, j_tiles, c_tiles, nsplit, kb_per_split, total_kb;
     int ntaps, ngroups, atomic;
+    int nsets, set_taps;     // taps [set * set_taps, min(ntaps, (set + 1) * set_taps)) share the TMEM columns of one work item
+    int nchunks, chunk_bytes;   // 64-channel boxes of the B window and the bytes of one
     int b_nboxes, b_rows_per_box;
     int stages, stage_bytes;
     int fast_epi;
@@ -783,22 +788,29 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
             uint32_t rs = 0, rph = 1;       // ring stage, parity of the "empty" wait (first lap passes at once)
             for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x) {
                 const int sp = (int)(w % a.nsplit);
-                const long long r = w / a.nsplit;
+                long long r = w / a.nsplit;
+                const int set = (int)(r % a.nsets);
+                r /= a.nsets;
                 const int ct = (int)(r % a.c_tiles), jt = (int)(r / a.c_tiles);
+                const int t_lo = set * a.set_taps, t_hi = min(a.ntaps, t_lo + a.set_taps);
+                const int nch = min(a.nchunks, (a.C - ct * BN + 63) / 64);      // chunks of this channel tile that exist
                 const int kb0 = sp * a.kb_per_split, kb1 = min(a.total_kb, kb0 + a.kb_per_split);
                 for (int kb = kb0; kb < kb1; ++kb)
                     for (int g = 0; g < a.ngroups; ++g) {
+                        if (max(a.gbeg[g], t_lo) >= min(a.gbeg[g + 1], t_hi)) continue;     // no tap of this set in the group
                         const uint32_t s = rs;
                         mbar_wait(empty(s), rph);
                         if (++rs == (uint32_t)kGStages) { rs = 0; rph ^= 1u; }
-                        mbar_expect_tx(full(s), GA_BYTES + b_bytes);
+                        mbar_expect_tx(full(s), GA_BYTES + b_bytes * (uint32_t)nch);
                         const uint32_t sa = base + s * GSTAGE, sb = sa + GA_BYTES;
                         const long long qa = (long long)a.ga[g] * a.Qs + (long long)kb * 64;
                         const long long qb = (long long)a.gb[g] * a.Qs + (long long)kb * 64;
                         tma_load_2d(sa, &a.tm_a, jt * 128, (int)qa, full(s));
                         tma_load_2d(sa + 8192, &a.tm_a, jt * 128 + 64, (int)qa, full(s));
-                        for (int bx = 0; bx < a.b_nboxes; ++bx)
-                            tma_load_2d(sb + bx * a.b_rows_per_box * 128, &a.tm_b, ct * BN, (int)(qb + (long long)bx * a.b_rows_per_box), full(s));
+                        for (int ch = 0; ch < nch; ++ch)
+                            for (int bx = 0; bx < a.b_nboxes; ++bx)
+                                tma_load_2d(sb + ch * a.chunk_bytes + bx * a.b_rows_per_box * 128, &a.tm_b, ct * BN + ch * 64,
+                                            (int)(qb + (long long)bx * a.b_rows_per_box), full(s));
                     }
             }
         }
@@ -808,15 +820,20 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) |
                                    ((uint32_t)(WBM >> 4) << 24);
             const uint64_t d_hi = make_desc(0, 8192, 1024, 0);      // both operands MN-major; +2048 B per k16
+            const uint64_t b_hi = make_desc(0, (uint32_t)a.chunk_bytes, 1024, 0);      // 64-channel blocks of the window: one chunk apart
             int li = 0;
             uint32_t rs = 0, rph = 0;
             for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
                 const int sp = (int)(w % a.nsplit);
+                const int set = (int)((w / a.nsplit) % a.nsets);
+                const int t_lo = set * a.set_taps, t_hi = min(a.ntaps, t_lo + a.set_taps);
                 const int kb0 = sp * a.kb_per_split, kb1 = min(a.total_kb, kb0 + a.kb_per_split);
                 if (li >= 1) mbar_wait(tempty, (uint32_t)((li - 1) & 1));
                 tc_fence_after();
                 for (int kb = kb0; kb < kb1; ++kb)
                     for (int g = 0; g < a.ngroups; ++g) {
+                        const int t_beg = max(a.gbeg[g], t_lo), t_end = min(a.gbeg[g + 1], t_hi);
+                        if (t_beg >= t_end) continue;
                         const uint32_t s = rs;
                         const uint32_t sa = base + s * GSTAGE, sb = sa + GA_BYTES;
                         const uint64_t ad = d_hi | (uint64_t)(sa >> 4);
@@ -824,11 +841,10 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
                         mbar_wait(full(s), rph);
                         if (++rs == (uint32_t)kGStages) { rs = 0; rph ^= 1u; }
                         tc_fence_after();
-                        const int t_end = a.gbeg[g + 1];
                         if (elect_one()) {
-                            for (int t = a.gbeg[g]; t < t_end; ++t) {
-                                const uint32_t d_tmem = tmem_base + t * BN;
-                                const uint64_t bd = d_hi | (uint64_t)((sb + (uint32_t)a.shift[t] * 128u) >> 4);
+                            for (int t = t_beg; t < t_end; ++t) {
+                                const uint32_t d_tmem = tmem_base + (t - t_lo) * BN;
+                                const uint64_t bd = b_hi | (uint64_t)((sb + (uint32_t)a.shift[t] * 128u) >> 4);
                                 umma_bf16(d_tmem, ad, bd, idesc, first);
                                 umma_bf16(d_tmem, ad + 128, bd + 128, idesc, 1);
                                 umma_bf16(d_tmem, ad + 256, bd + 256, idesc, 1);
@@ -847,8 +863,11 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
         const int quarter = warp & 3, row = quarter * 32 + lane;
         int li = 0;
         for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
-            const long long r = w / a.nsplit;
+            long long r = w / a.nsplit;
+            const int set = (int)(r % a.nsets);
+            r /= a.nsets;
             const int ct = (int)(r % a.c_tiles), jt = (int)(r / a.c_tiles);
+            const int t_lo = set * a.set_taps, t_hi = min(a.ntaps, t_lo + a.set_taps);
             const int j = jt * 128 + row, c_begin = ct * BN, c_count = min(BN, a.C - c_begin);
             const bool rok = j < a.J;
             mbar_wait(tfull, (uint32_t)(li & 1));
@@ -858,13 +877,13 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
                 const unsigned okmask = __ballot_sync(0xffffffffu, rok);
                 const uint32_t stage = bars + 256 + (uint32_t)(warp - 2) * 4096u;
                 const int mode = a.atomic ? EPI_RED : EPI_ST;
-                for (int t = 0; t < a.ntaps; ++t) {
+                for (int t = t_lo; t < t_hi; ++t) {
                     const long long row_off = ((long long)a.wtap[t] * a.w_tap + (long long)j * a.C + c_begin) * 4;
                     for (int c2 = 0; c2 < BN; c2 += 32) {
                         uint32_t v2[32];
                         const bool two = c2 + 16 < BN;
-                        tmem_ld16(taddr + t * BN + c2, *reinterpret_cast<uint32_t(*)[16]>(&v2[0]));
-                        if (two) tmem_ld16(taddr + t * BN + c2 + 16, *reinterpret_cast<uint32_t(*)[16]>(&v2[16]));
+                        tmem_ld16(taddr + (t - t_lo) * BN + c2, *reinterpret_cast<uint32_t(*)[16]>(&v2[0]));
+                        if (two) tmem_ld16(taddr + (t - t_lo) * BN + c2 + 16, *reinterpret_cast<uint32_t(*)[16]>(&v2[16]));
                         tmem_ld_wait();
                         if (c2 >= c_count) break;
                         const int ncol = two ? 32 : 16;
@@ -872,12 +891,12 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
                     }
                 }
             } else
-            for (int t = 0; t < a.ntaps; ++t) {
+            for (int t = t_lo; t < t_hi; ++t) {
                 float* o = a.dw + (long long)a.wtap[t] * a.w_tap + (long long)j * a.C + c_begin;
                 for (int c2 = 0; c2 < BN; c2 += 32) {
                     uint32_t v2[2][16];
-                    tmem_ld16(taddr + t * BN + c2, v2[0]);
-                    if (c2 + 16 < BN) tmem_ld16(taddr + t * BN + c2 + 16, v2[1]);
+                    tmem_ld16(taddr + (t - t_lo) * BN + c2, v2[0]);
+                    if (c2 + 16 < BN) tmem_ld16(taddr + (t - t_lo) * BN + c2 + 16, v2[1]);
                     tmem_ld_wait();
 #pragma unroll
                     for (int hh = 0; hh < 2; ++hh) {
@@ -1177,13 +1196,6 @@ extern "C" int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const v
     if ((long long)(n_aplanes > n_bplanes ? n_aplanes : n_bplanes) * plane_rows > 2000000000LL) return fail(P2P_ENOTSUP, "too many rows");
     WgradWinArgs a;
     a.dw = dw; a.Qs = plane_rows; a.J = J; a.C = C; a.ntaps = ntaps; a.w_tap = (long long)J * C;
-    int bn = (512 / ntaps) / 16 * 16;
-    if (bn > 64) bn = 64;
-    if (bn > (C + 15) / 16 * 16) bn = (C + 15) / 16 * 16;
-    if (bn < 16) return fail(P2P_ENOTSUP, "too many taps for the TMEM columns");
-    a.BN = bn;
-    a.j_tiles = (J + 127) / 128;
-    a.c_tiles = (C + bn - 1) / bn;
     int halo = 0, ng = 0;
     for (int t = 0; t < ntaps; ++t) {
         if (tap_a[t] < 0 || tap_a[t] >= n_aplanes || tap_b[t] < 0 || tap_b[t] >= n_bplanes || tap_dh[t] < 0 || tap_dw[t] < 0)
@@ -1209,15 +1221,33 @@ extern "C" int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const v
     a.b_nboxes = (brows + 255) / 256;
     a.b_rows_per_box = ((brows + a.b_nboxes - 1) / a.b_nboxes + 7) / 8 * 8;
     if (a.b_nboxes * a.b_rows_per_box > kWinRowsMax) return fail(P2P_ENOTSUP, "window boxes exceed the buffer");
-    a.stage_bytes = GA_BYTES + a.b_nboxes * a.b_rows_per_box * 128;
+    a.chunk_bytes = ((a.b_nboxes * a.b_rows_per_box * 128 + 1023) / 1024) * 1024;
+    // channel tile: as wide as two ring stages allow (fewer, wider MMAs), balanced over C; then taps per set = 512 / BN columns
+    const int Cr = (C + 15) / 16 * 16;
+    int max_chunks = (GRING_BYTES / 2 - GA_BYTES) / a.chunk_bytes;
+    if (max_chunks > 4) max_chunks = 4;
+    if (max_chunks < 1) return fail(P2P_ENOTSUP, "window too large for the stage ring");
+    const int bn_cap = max_chunks * 64;
+    const int nct = (Cr + bn_cap - 1) / bn_cap;
+    int bn = ((Cr + nct - 1) / nct + 15) / 16 * 16;
+    if (bn > bn_cap) bn = bn_cap;
+    a.BN = bn;
+    a.nchunks = (bn + 63) / 64;
+    a.j_tiles = (J + 127) / 128;
+    a.c_tiles = (C + bn - 1) / bn;
+    const int tmax = 512 / bn;
+    a.nsets = (ntaps + tmax - 1) / tmax;
+    a.set_taps = (ntaps + a.nsets - 1) / a.nsets;
+    a.nsets = (ntaps + a.set_taps - 1) / a.set_taps;
+    a.stage_bytes = GA_BYTES + a.nchunks * a.chunk_bytes;
     a.stages = GRING_BYTES / a.stage_bytes;
     if (a.stages > kGStagesMax) a.stages = kGStagesMax;
     a.total_kb = (int)(plane_rows / 64);
-    const long long items = (long long)a.j_tiles * a.c_tiles;
+    const long long items = (long long)a.j_tiles * a.c_tiles * a.nsets;
     int sms = 148, dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    int nsplit = (int)((sms + items - 1) / items);         // one wave: every extra split is another pass of atomics over dW
+    int nsplit = (int)(sms / items);                       // at most one wave: every extra split is another pass of atomics over dW
     if (nsplit > a.total_kb / 2) nsplit = a.total_kb / 2;
     if (nsplit < 1) nsplit = 1;
     a.kb_per_split = (a.total_kb + nsplit - 1) / nsplit;
