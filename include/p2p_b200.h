@@ -141,6 +141,9 @@ typedef struct {
     signed char tap_sub[P2P_MAX_TAPS], tap_plane[P2P_MAX_TAPS];
     short tap_dh[P2P_MAX_TAPS], tap_dw[P2P_MAX_TAPS];
     unsigned char tap_w[P2P_MAX_TAPS];
+    int wrap;   /* != 0: taps may read past their sub-pass grid (y + dh >= Hp wraps into the next rows / image of the flattened
+                 * plane): the caller guarantees those pixels hold zeros.  Used by the input-gradient pass that shares the
+                 * weight-gradient's copy of dout (dout at the pitch of the padded input, zero prefix before the first image) */
 } p2p_conv_window_desc;
 int p2p_pad_planes(const void* x, void* planes, int N, int H, int W, int C, int pt, int pl, int Hh, int Wh, int s,
                    long long plane_rows /* >= N*Hh*Wh; the tail of every plane is zero-filled */, int reflect /* s == 1 only */,

@@ -39,7 +39,8 @@ class WindowDesc(ctypes.Structure):
                 ("wtaps_total", _i), ("w_tap", _ll), ("w_k", _ll), ("w_j", _ll), ("nsub", _i), ("oys", _i), ("oxs", _i),
                 ("gy", _i * 4), ("gx", _i * 4), ("oyo", _i * 4), ("oxo", _i * 4), ("ntaps", _i),
                 ("tap_sub", _c.c_byte * MAX_TAPS), ("tap_plane", _c.c_byte * MAX_TAPS),
-                ("tap_dh", _c.c_short * MAX_TAPS), ("tap_dw", _c.c_short * MAX_TAPS), ("tap_w", _c.c_ubyte * MAX_TAPS)]
+                ("tap_dh", _c.c_short * MAX_TAPS), ("tap_dw", _c.c_short * MAX_TAPS), ("tap_w", _c.c_ubyte * MAX_TAPS),
+                ("wrap", _i)]
 
 
 _SIGS.update({

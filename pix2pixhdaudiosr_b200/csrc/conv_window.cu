@@ -1047,7 +1047,8 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
         for (int p = 0; p < nplanes; ++p) {
             a.pbeg[u][p] = t;
             while (t < ntaps && d->tap_sub[t] == u && d->tap_plane[t] == p) {
-                if (d->tap_dh[t] < 0 || d->tap_dw[t] < 0 || d->tap_dh[t] + a.gy[u] > Hp || d->tap_dw[t] + a.gx[u] > Wp)
+                if (d->tap_dh[t] < 0 || d->tap_dw[t] < 0 ||
+                    (!d->wrap && (d->tap_dh[t] + a.gy[u] > Hp || d->tap_dw[t] + a.gx[u] > Wp)))
                     return fail(P2P_EINVAL, "tap %d reads outside its plane", t);
                 if (d->tap_w[t] >= d->wtaps_total) return fail(P2P_EINVAL, "weight tap out of range");
                 const int sh = d->tap_dh[t] * Wp + d->tap_dw[t];
@@ -1127,7 +1128,9 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
             a.nwork *= a.nsplit;
         }
     }
-    if (int rc = encode_2d(&a.tm_x, planes, (unsigned long long)C, (unsigned long long)nplanes * a.Q, 64, (unsigned)a.rows_per_box)) return rc;
+    // wrap mode: the last image's rows are reached through shifts past row Q (the caller's buffer holds Q + halo rows)
+    if (int rc = encode_2d(&a.tm_x, planes, (unsigned long long)C, (unsigned long long)nplanes * a.Q + (d->wrap ? halo : 0), 64,
+                           (unsigned)a.rows_per_box)) return rc;
     if (!a.b_mn_major) {
         if (int rc = encode_2d(&a.tm_w, weight, (unsigned long long)C, (unsigned long long)d->wtaps_total * J, 64, (unsigned)a.BN)) return rc;
     } else {
@@ -1168,7 +1171,7 @@ extern "C" int p2p_conv_window(const void* xp, const void* weight, const float* 
     d.nplanes = 1; d.N = N; d.Hp = Hp; d.Wp = Wp; d.C = C;
     d.OHf = Hp - KH + 1; d.OWf = Wp - KW + 1; d.J = J;
     d.wtaps_total = KH * KW; d.w_tap = w_tap; d.w_k = w_k; d.w_j = w_j;
-    d.nsub = 1; d.oys = d.oxs = 1;
+    d.nsub = 1; d.oys = d.oxs = 1; d.wrap = 0;
     for (int u = 0; u < 4; ++u) { d.gy[u] = d.OHf; d.gx[u] = d.OWf; d.oyo[u] = d.oxo[u] = 0; }
     d.ntaps = KH * KW;
     for (int i = 0; i < KH; ++i)

@@ -326,7 +326,49 @@ def _window_passes(passes, x, wq, bias, out, wtaps_total, kind):
     return True
 
 
-def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None, fresh=False):
+def _dy_wrap(dy, Hh, Wh, KH, KW):
+    """dy [N,OH,OW,J] laid out at the pitch of the padded input ([N,Hh,Wh] grid, dy at its top-left, zeros elsewhere) in a
+    buffer of P64 + rows64 + P64 rows whose first and last P64 >= (KH-1)*Wh + KW-1 rows are zero -> (key, buffer, P64)"""
+    N, OH, OW, J = dy.shape
+    rows = _rows64(N * Hh * Wh)
+    P64 = _rows64((KH - 1) * Wh + KW - 1)
+    buf = torch.empty((P64 + rows + P64, J), dtype=dy.dtype, device=dy.device)      # zero prefix | dy grid | zero suffix
+    buf[:P64].zero_()
+    buf[P64 + rows:].zero_()
+    _lib.check(_lib.lib().p2p_pad_planes(_p(dy), _p(buf[P64:]), N, OH, OW, J, 0, 0, Hh, Wh, 1, rows, 0, _DT[dy.dtype], _stream()))
+    return (Hh, Wh, rows, J), buf, P64
+
+
+def _dgrad_wrap(dy_shared, wq, dtype, N, H, W, p, KH, KW, Cout, Cin, reflect):
+    """input gradient of a stride-1 convolution from the shared dy copy: output on the padded grid (reflection: folded by the
+    caller) or directly [N,H,W,Cin] (zero padding)"""
+    (Hh, Wh, rows, J), buf, P64 = dy_shared
+    P = (KH - 1) * Wh + (KW - 1)
+    off = P64 - P + (0 if reflect else p * Wh + p)
+    d = _lib.WindowDesc()
+    d.nplanes, d.N, d.Hp, d.Wp, d.C = 1, N, Hh, Wh, Cout
+    gy, gx = (Hh, Wh) if reflect else (H, W)
+    d.OHf, d.OWf, d.J = gy, gx, Cin
+    d.wtaps_total, d.w_tap, d.w_k, d.w_j = KH * KW, Cout * Cin, Cin, 1
+    d.nsub, d.oys, d.oxs, d.wrap = 1, 1, 1, 1
+    d.gy[0], d.gx[0], d.oyo[0], d.oxo[0] = gy, gx, 0, 0
+    t = 0
+    for a in range(KH):
+        for b in range(KW):
+            d.tap_sub[t], d.tap_plane[t], d.tap_dh[t], d.tap_dw[t] = 0, 0, a, b
+            d.tap_w[t] = (KH - 1 - a) * KW + (KW - 1 - b)
+            t += 1
+    d.ntaps = t
+    few = _few_tiles(N * Hh * Wh, Cin, 1, (Cout + 63) // 64)
+    out = torch.empty((N, gy, gx, Cin), dtype=torch.float32 if few else dtype, device=buf.device)
+    planes = buf[off:]
+    _timed("dgrad", _Shape(N, gy, gx, Cin, KH * KW, Cout, Hh, Wh),
+           lambda: _lib.check(_lib.lib().p2p_conv_window_run(ctypes.byref(d), _p(planes), _p(wq), None, _p(out), _DT[out.dtype],
+                                                            _stream())), umma=True)
+    return out if out.dtype == dtype else out.to(dtype)
+
+
+def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None, fresh=False, dy_shared=None):
     """weight gradient of a layer call (its forward-type passes) as ONE launch of the window wgrad kernel:
     dW_t = sum over the padded grid of dout (laid out at the input's pitch) x shifted input window.  False if it does not fit."""
     if not USE_WINDOW or not passes or x.dtype != torch.bfloat16 or _lib.lib().p2p_conv_force_simple(-1) == 1:
@@ -371,8 +413,11 @@ def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None, fresh=False):
     else:
         bplanes = torch.empty((s_in * s_in, rows, C), dtype=x.dtype, device=x.device)
         _lib.check(lib.p2p_pad_planes(_p(x), _p(bplanes), N, H, W, C, pt, pl, Hh, Wh, s_in, rows, int(reflect), _DT[x.dtype], _stream()))
-    aplanes = torch.empty((s_out * s_out, rows, J), dtype=dy.dtype, device=dy.device)
-    _lib.check(lib.p2p_pad_planes(_p(dy), _p(aplanes), N, dy.shape[1], dy.shape[2], J, 0, 0, Hh, Wh, s_out, rows, 0, _DT[dy.dtype], _stream()))
+    if dy_shared is not None and s_out == 1 and dy_shared[0] == (Hh, Wh, rows, J):
+        aplanes = dy_shared[1][dy_shared[2]: dy_shared[2] + rows]       # the copy the input-gradient pass already made
+    else:
+        aplanes = torch.empty((s_out * s_out, rows, J), dtype=dy.dtype, device=dy.device)
+        _lib.check(lib.p2p_pad_planes(_p(dy), _p(aplanes), N, dy.shape[1], dy.shape[2], J, 0, 0, Hh, Wh, s_out, rows, 0, _DT[dy.dtype], _stream()))
     IntArr = ctypes.c_int * len(taps)
     ta, tb, th, tw, twt = (IntArr(*[q[i] for q in taps]) for i in range(5))
     shape = _Shape(N, 1, sum(P.gy * P.gx * P.ntaps for P in passes), J, 1, K, Hh, Wh)
@@ -715,6 +760,7 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
     wphys, Cout, Cin, KH, KW = _phys(weight, cfg)
     assert dy.dtype == x.dtype and dy.is_contiguous()
     dx = dw = db = None
+    dy_shared = None
     if need_db:
         db = _bias_grad(dy, Cout)
     col = _colable(x, cfg, Cin, Cout, KH, KW)
@@ -753,7 +799,15 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
         else:
             q = (KH - 1) if cfg.pad_mode == PAD_REFLECT else (KH - 1 - cfg.pad)      # zero margin around dy
             OHd, OWd = dy.shape[1], dy.shape[2]
-            if (cfg.stride == 1 and KH == KW and q >= 0
+            p = cfg.pad
+            if (cfg.stride == 1 and KH == KW and q >= 0 and p > 0 and need_dw and thin is None and USE_WINDOW
+                    and _window_ok(x.dtype, Cout, Cin, KH, KW, H + 2 * p, W + 2 * p, True)):
+                # ONE copy of dy serves both gradients: dy at the pitch of the padded input (what the wgrad kernel wants)
+                # behind a zero prefix; the flipped-tap window reads wrap into the zero margins of the previous row / image
+                dy_shared = _dy_wrap(dy, H + 2 * p, W + 2 * p, KH, KW)
+                buf = _dgrad_wrap(dy_shared, wq, x.dtype, N, H, W, p, KH, KW, Cout, Cin, cfg.pad_mode == PAD_REFLECT)
+                passes = []
+            elif (cfg.stride == 1 and KH == KW and q >= 0
                     and _window_ok(x.dtype, Cout, Cin, KH, KW, OHd + 2 * q, OWd + 2 * q, True)):
                 dyp = pad_nhwc(dy, q, q, q, q, False) if q else dy
                 buf = conv_window(dyp, wq, None, x.dtype, KH, KW, Cin, True, Cout * Cin, Cin, 1, "dgrad")
@@ -782,7 +836,7 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
             wpasses = convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0]
         else:
             wpasses = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
-        if not _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None, fresh):
+        if not _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None, fresh, dy_shared):
             for P in wpasses:
                 _run_wgrad(P, x, dy, dwp)
         if direct:
