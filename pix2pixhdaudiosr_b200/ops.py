@@ -2,6 +2,7 @@
 and torch.autograd.Function wrappers that call the C ABI (include/p2p_b200.h).  Internal activation layout is
 NHWC ([N,H,W,C] contiguous); dtype float32 (exact path) or bfloat16 (tensor-core path)."""
 import ctypes
+import os
 
 import torch
 
@@ -326,15 +327,24 @@ def _window_passes(passes, x, wq, bias, out, wtaps_total, kind):
     return True
 
 
+_WRAP_BUFFERS = {}
+
+
 def _dy_wrap(dy, Hh, Wh, KH, KW):
     """dy [N,OH,OW,J] laid out at the pitch of the padded input ([N,Hh,Wh] grid, dy at its top-left, zeros elsewhere) in a
     buffer of P64 + rows64 + P64 rows whose first and last P64 >= (KH-1)*Wh + KW-1 rows are zero -> (key, buffer, P64)"""
     N, OH, OW, J = dy.shape
     rows = _rows64(N * Hh * Wh)
     P64 = _rows64((KH - 1) * Wh + KW - 1)
-    buf = torch.empty((P64 + rows + P64, J), dtype=dy.dtype, device=dy.device)      # zero prefix | dy grid | zero suffix
-    buf[:P64].zero_()
-    buf[P64 + rows:].zero_()
+    key = (dy.device, dy.dtype, P64, rows, J)
+    buf = _WRAP_BUFFERS.get(key)
+    if buf is None or torch.cuda.is_current_stream_capturing() != _WRAP_BUFFERS.get(("capturing", key), False):
+        # zero prefix | dy grid | zero suffix; the margins are written once, the grid (and its zero tail) by every call.
+        # The buffer is reused by later calls of the same geometry: the two gradient passes that read it are enqueued on the
+        # same stream before the next layer overwrites it.  (One buffer per capture state: a CUDA graph keeps its own.)
+        buf = torch.zeros((P64 + rows + P64, J), dtype=dy.dtype, device=dy.device)
+        _WRAP_BUFFERS[key] = buf
+        _WRAP_BUFFERS[("capturing", key)] = torch.cuda.is_current_stream_capturing()
     _lib.check(_lib.lib().p2p_pad_planes(_p(dy), _p(buf[P64:]), N, OH, OW, J, 0, 0, Hh, Wh, 1, rows, 0, _DT[dy.dtype], _stream()))
     return (Hh, Wh, rows, J), buf, P64
 
@@ -911,6 +921,9 @@ def norm_act_backward(y, stats, dz, norm, act, slope):
 # ---------------------------------------------------------------------------------------------------
 # autograd Functions (x, outputs: NHWC)
 # ---------------------------------------------------------------------------------------------------
+NORM_BIAS_GRAD = os.environ.get("P2P_NORM_BIAS_GRAD", "0") == "1"
+
+
 class GradSink:
     """a conv weight's slice of FusedAdam's flat gradient buffer (physical layout).  first_write() is True for the first
     gradient written after the optimizer's zero_grad -- the kernels may then store instead of accumulate."""
@@ -953,6 +966,7 @@ class ConvBlockFn(torch.autograd.Function):
         ctx.save_for_backward(x, weight, w16, ysave, stats)
         ctx.cfg = (cfg, norm, act, slope, bias is not None, res is not None, plain)
         ctx.gphys = gphys
+        ctx.bias_n = bias.numel() if bias is not None else 0
         return z
 
     @staticmethod
@@ -961,8 +975,13 @@ class ConvBlockFn(torch.autograd.Function):
         cfg, norm, act, slope, has_bias, has_res, plain = ctx.cfg
         dz = dz.contiguous()
         dy = dz if plain else norm_act_backward(y, stats, dz, norm, act, slope)
+        # a bias in front of InstanceNorm2d(affine=False) has an exactly zero gradient (the mean subtraction removes it; the
+        # reference's autograd returns rounding noise of ~1e-7 relative size): not computed unless P2P_NORM_BIAS_GRAD=1
+        need_db = has_bias and ctx.needs_input_grad[2] and (not norm or NORM_BIAS_GRAD)
         dx, dw, db = conv_backward(x, weight, w16, dy, cfg, ctx.needs_input_grad[0], ctx.needs_input_grad[1],
-                                   has_bias and ctx.needs_input_grad[2], ctx.gphys, ctx.xpad)
+                                   need_db, ctx.gphys, ctx.xpad)
+        if has_bias and ctx.needs_input_grad[2] and not need_db and ctx.gphys is None:
+            db = torch.zeros(ctx.bias_n, dtype=torch.float32, device=x.device)    # no flat gradient buffer behind .grad: give autograd the zero
         return dx, dw, db, None, (dz if has_res else None), None, None, None, None, None, None
 
 
