@@ -135,15 +135,14 @@ __global__ void __launch_bounds__(256) in_stats_v4_kernel(const T* __restrict__ 
         float shift[4];
         ld4(base, shift);
         int r = r0 + threadIdx.y;
-        for (; r + 8 < r1; r += 16) {
-            float v[4], u[4];
-            ld4(base + (long long)r * C, v);
-            ld4(base + (long long)(r + 8) * C, u);
+        for (; r + 24 < r1; r += 32) {           // four rows in flight per thread
+            float v[4][4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float d = v[i] - shift[i], e = u[i] - shift[i];
-                a[i] += d + e; b[i] += d * d + e * e;
-            }
+            for (int u = 0; u < 4; ++u) ld4(base + (long long)(r + 8 * u) * C, v[u]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { const float d = v[u][i] - shift[i]; a[i] += d; b[i] += d * d; }
         }
         for (; r < r1; r += 8) {
             float v[4];
@@ -169,6 +168,7 @@ template <typename TY, typename T>
 __global__ void __launch_bounds__(256) in_apply_v4_kernel(const TY* __restrict__ y, const T* __restrict__ res, T* __restrict__ z,
                                                           const float* __restrict__ stats, unsigned HWC4, unsigned C4,
                                                           unsigned total4, int norm, int act, float slope) {
+#pragma unroll 2
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
         float v[4];
         ld4(y + 4ll * i, v);
@@ -204,7 +204,24 @@ __global__ void __launch_bounds__(256) in_bwd_stats_v4_kernel(const TY* __restri
         const float4* sp = reinterpret_cast<const float4*>(stats + ((long long)n * C + cg * 4) * 2);
         const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
         const float mean[4] = {s0.x, s0.z, s1.x, s1.z}, rstd[4] = {s0.y, s0.w, s1.y, s1.w};
-        for (int r = r0 + threadIdx.y; r < r1; r += 8) {
+        int r = r0 + threadIdx.y;
+        for (; r + 24 < r1; r += 32) {           // four rows in flight per thread
+            float v[4][4], g[4][4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                ld4(y + off + (long long)(r + 8 * u) * C, v[u]);
+                ld4(dz + off + (long long)(r + 8 * u) * C, g[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float xh = (v[u][i] - mean[i]) * rstd[i];
+                    const float gg = g[u][i] * act_grad(xh, act, slope);
+                    a[i] += gg; b[i] += gg * xh;
+                }
+        }
+        for (; r < r1; r += 8) {
             float v[4], g[4];
             ld4(y + off + (long long)r * C, v);
             ld4(dz + off + (long long)r * C, g);
@@ -233,6 +250,7 @@ __global__ void __launch_bounds__(256) in_bwd_apply_v4_kernel(const TY* __restri
                                                               const T* __restrict__ dz, const float* __restrict__ work,
                                                               T* __restrict__ dy, unsigned HWC4, unsigned C4, unsigned total4,
                                                               float inv, int norm, int act, float slope) {
+#pragma unroll 2
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
         float v[4], g[4], o[4];
         ld4(y + 4ll * i, v);
