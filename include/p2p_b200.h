@@ -157,6 +157,9 @@ int p2p_pad_planes(const void* x, void* planes, int N, int H, int W, int C, int 
 int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const void* bplanes, int n_bplanes, long long plane_rows, int Wp,
                           int J, int C, float* dw, int wtaps_total, int ntaps, const int* tap_a, const int* tap_b,
                           const int* tap_dh, const int* tap_dw, const int* tap_w, int dw_is_zero, void* stream);
+/* Debug hook: builds with -DP2P_WINDOW_TIMING write, per CTA, the MMA warp's cycles {waiting for the window, waiting for weight
+ * stages, issuing, waiting for the accumulator, stages, total, tiles, -} to buf (8 x int64 per CTA); a no-op otherwise. */
+int p2p_conv_window_debug_buffer(long long* buf);
 int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* planes, const void* weight, const float* bias, void* out,
                         int out_dtype, void* stream);
 /* Adjoint of reflection padding: dx[n,h,w,c] = sum of dxp over the padded positions that mirror onto (h,w).

@@ -4,7 +4,7 @@ import ctypes
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libp2p_b200.so")
+LIB_PATH = os.environ.get("P2P_LIB_PATH") or os.path.join(_PKG, "libp2p_b200.so")      # override: instrumented builds (profiles/)
 
 _c = ctypes
 _SIGS = {
@@ -52,6 +52,7 @@ _SIGS.update({
     "p2p_conv_window": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _vp]),
     "p2p_pad_planes": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _ll, _i, _i, _vp]),
     "p2p_conv_wgrad_window": (_i, [_vp, _i, _vp, _i, _ll, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
+    "p2p_conv_window_debug_buffer": (_i, [_vp]),
     "p2p_conv_window_run": (_i, [_c.POINTER(WindowDesc), _vp, _vp, _vp, _vp, _i, _vp]),
     "p2p_bias_grad": (_i, [_vp, _vp, _ll, _i, _i, _vp]),
     "p2p_reflect_pad_fold": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),

@@ -29,7 +29,12 @@ constexpr int WIN_BYTES = kWinRowsMax * 128;
 constexpr int WB_BYTES = 256 * 128;                 // one weight tile: up to 256 output channels x 64 channels
 constexpr int WRING_BYTES = 4 * WB_BYTES;             // 128 KB of weight tiles in flight, cut into b_stage_bytes stages
 constexpr int EPI_STAGE_BYTES = 4 * 4096;           // one 32-row x 128-byte transposition tile per epilogue warp
-constexpr int WSMEM = 2 * WIN_BYTES + WRING_BYTES + 1024 + 512 + 2048 + EPI_STAGE_BYTES;     // + barriers + 2 x 256 staged bias values
+constexpr int kWinThreads = 320;                    // conv_window_kernel: TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter)
+constexpr int WEPI_STAGE_BYTES = 8 * 4096;
+constexpr int WDATA_BYTES = 2 * WIN_BYTES + WRING_BYTES - 16384;     // two window buffers + the weight ring, carved per launch (win_bytes)
+constexpr int WSMEM = WDATA_BYTES + 1024 + 512 + 32 * kBStagesMax + 2048 + WEPI_STAGE_BYTES;     // + barriers + stage records + 2 x 256 staged bias values
+// stage-record flags (written by the producer, read by the MMA warp)
+constexpr uint32_t REC_TILE_FIRST = 1u << 8, REC_CHUNK_FIRST = 1u << 9, REC_CHUNK_LAST = 1u << 10, REC_TILE_LAST = 1u << 11, REC_LAST = 1u << 12;
 static_assert(WSMEM <= 232448, "window kernel shared memory");
 constexpr int kWThreads = 192;
 
@@ -51,6 +56,10 @@ struct WindowArgs {
     int tps, b_tap_bytes;          // taps per ring stage (amortises the issuing thread's per-stage overhead), bytes of one tap tile
     int b_stages, b_stage_bytes;   // weight ring: stages of tps tap tiles, as many as fit WRING_BYTES
     int fast_epi;                  // output rows 16-byte aligned: staged, coalesced epilogue stores
+    long long* dbg;                // P2P_WINDOW_TIMING builds: per CTA {wait A, wait B, issue, wait TMEM, stages, total} cycles of the MMA warp
+    int mrep;                      // 128-row MMAs per weight tile (1 or 2): a work item covers 128*mrep padded pixels
+    int win_bytes;                 // bytes of one window buffer (multiple of 1024); the ring gets WDATA_BYTES - 2*win_bytes
+    int acc_slots, half_cols;      // TMEM: accumulator slots of 256 (or 512) columns, column stride between the two row halves
     int nsplit, ci_per_split;      // split of the (channel chunk, plane) loop across CTAs; > 1 => fp32 red.add epilogue   // weight-tile ring: as many stages as fit 128 KB (TMA latency needs bytes in flight)
     short shift[P2P_MAX_TAPS];       // dh*Wp + dw
     unsigned char wtap[P2P_MAX_TAPS];
@@ -172,11 +181,57 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
            ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46) | ((uint64_t)(base_off & 7) << 49) | (2ull << 61);
 }
 
-__global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_constant__ WindowArgs a) {
+// the MMAs of one weight-ring stage: up to 4 taps x up to 4 k16 steps, each against MREP 128-row halves of the window (the
+// halves share the weight tile, so it is written to shared memory once per 128*MREP pixels)
+template <int MREP>
+__device__ __forceinline__ void issue_stage(uint32_t d_tmem, uint32_t half_cols, uint32_t a_hi, uint32_t b_hi, uint32_t al0, uint32_t al1,
+                                            uint32_t al2, uint32_t al3, uint32_t bl, uint32_t b_k16, uint32_t b_tap, uint32_t idesc,
+                                            uint32_t meta, uint32_t accumulate) {
+    auto mk = [](uint32_t hi, uint32_t lo) { return ((uint64_t)hi << 32) | lo; };
+    constexpr uint32_t A_HALF = (128u * 128u) >> 4;         // descriptor advance to the second 128 window rows
+    const uint32_t al[4] = {al0, al1, al2, al3};
+    if ((meta & 63u) == (4u | (4u << 3))) {                 // the common stage: 4 taps x 64 channels, no predicates
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t bk = bl + (uint32_t)k * b_tap;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+#pragma unroll
+                for (int h = 0; h < MREP; ++h)
+                    umma_bf16(d_tmem + h * half_cols, mk(a_hi, al[k] + 2 * j + h * A_HALF), mk(b_hi, bk + j * b_k16), idesc,
+                              (k | j) == 0 ? accumulate : 1u);
+            }
+        }
+    } else {
+        const uint32_t nt_s = meta & 7u, nk16 = (meta >> 3) & 7u;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if ((uint32_t)k < nt_s) {
+                const uint32_t bk = bl + (uint32_t)k * b_tap;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if ((uint32_t)j < nk16) {
+#pragma unroll
+                        for (int h = 0; h < MREP; ++h)
+                            umma_bf16(d_tmem + h * half_cols, mk(a_hi, al[k] + 2 * j + h * A_HALF), mk(b_hi, bk + j * b_k16), idesc,
+                                      (k | j) == 0 ? accumulate : 1u);
+                    }
+                }
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __grid_constant__ WindowArgs a) {
     extern __shared__ uint8_t smem_raw[];
+#ifdef P2P_WINDOW_TIMING
+    long long g_entry;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_entry));
+#endif
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t wbase = base + 2 * WIN_BYTES;
-    const uint32_t bars = wbase + WRING_BYTES;
+    const uint32_t win_bytes = (uint32_t)a.win_bytes;
+    const uint32_t wbase = base + 2 * win_bytes;
+    const uint32_t bars = base + WDATA_BYTES;
     const int kBStages = a.b_stages;
     // barriers: afull[2] aempty[2] bfull[16] bempty[16] tfull[2] tempty[2], then the TMEM base word
     auto afull = [&](int i) { return bars + 8u * i; };
@@ -188,7 +243,8 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
     const uint32_t tmem_slot = bars + 8u * (8 + 2 * kBStagesMax);
     const uint32_t WB_STRIDE = (uint32_t)a.b_stage_bytes;       // = tps * TAP_STRIDE
     const uint32_t TAP_STRIDE = (uint32_t)a.b_tap_bytes;
-    const uint32_t bias_u32 = bars + 512;
+    const uint32_t recs = bars + 512;                           // one 32-byte stage record per weight-ring stage
+    const uint32_t bias_u32 = recs + 32 * kBStagesMax;
     const uint32_t epi_stage = bias_u32 + 2048;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -198,7 +254,7 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
 
     if (warp == 1) {
         if (lane == 0) {
-            for (int i = 0; i < 2; ++i) { mbar_init(afull(i), 1); mbar_init(aempty(i), 1); mbar_init(tfull(i), 1); mbar_init(tempty(i), 128); }
+            for (int i = 0; i < 2; ++i) { mbar_init(afull(i), 1); mbar_init(aempty(i), 1); mbar_init(tfull(i), 1); mbar_init(tempty(i), 256); }
             for (int s = 0; s < kBStages; ++s) { mbar_init(bfull(s), 1); mbar_init(bempty(s), 1); }
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
@@ -214,39 +270,56 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
 
     if (warp == 0) {
         // ================================ TMA producer ================================
+        // Besides the loads, the producer writes one 32-byte record per weight-ring stage (A/B descriptor low words, tap and
+        // k16 counts, tile/chunk boundary flags) so that the MMA warp's loop is flat: wait, read the record, issue.  Measured
+        // with -DP2P_WINDOW_TIMING: the nested schedule walk in the issuing warp cost as many cycles as the MMAs themselves.
         if (lane == 0) {
             asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_x) : "memory");
             asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_w) : "memory");
+            const uint32_t a_lo = (uint32_t)make_desc(0, 16, 1024, 0);
+            const uint32_t b_lo = (uint32_t)(a.b_mn_major ? make_desc(0, 8192, 1024, 0) : make_desc(0, 16, 1024, 0));
             int ia = 0;                     // window loads issued so far
             uint32_t bs = 0, bph = 1;       // weight ring: stage, parity of the "empty" wait (first lap passes at once)
-            for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x) {
-                const int nt = (int)(w % a.n_tiles);
-                const long long wr = w / a.n_tiles;
-                const int sp = (int)(wr % a.nsplit);
-                const long long mtu = wr / a.nsplit;
-                const int u = (int)(mtu / a.m_tiles);
-                const long long q0 = (mtu - (long long)u * a.m_tiles) * WBM;
-                const int j0 = nt * BN;
-                const int ci1 = min(a.cpb * a.nplanes, (sp + 1) * a.ci_per_split);
-                for (int ci = sp * a.ci_per_split; ci < ci1; ++ci, ++ia) {
+            const uint32_t nwork = (uint32_t)a.nwork, n_tiles = (uint32_t)a.n_tiles, nsplit = (uint32_t)a.nsplit;
+            for (uint32_t w = blockIdx.x; w < nwork; w += gridDim.x) {
+                const uint32_t nt = w % n_tiles, wr = w / n_tiles;
+                const uint32_t sp = wr % nsplit, mtu = wr / nsplit;
+                const int u = (int)(mtu / (uint32_t)a.m_tiles);
+                const int q0 = (int)(mtu - (uint32_t)u * (uint32_t)a.m_tiles) * (WBM * a.mrep);
+                const int j0 = (int)nt * BN;
+                const int ci0 = (int)sp * a.ci_per_split, ci1 = min(a.cpb * a.nplanes, ((int)sp + 1) * a.ci_per_split);
+                const uint32_t f_last_tile = (w + gridDim.x >= nwork) ? REC_LAST : 0u;
+                for (int ci = ci0; ci < ci1; ++ci, ++ia) {
                     const int cc = ci / a.nplanes, pl = ci - cc * a.nplanes;
                     const int c0 = cc * 64;
+                    const uint32_t nk16 = (uint32_t)(min(64, C - c0) >> 4);
                     const int ab = ia & 1;
+                    const uint32_t win = base + ab * win_bytes;
                     if (ia >= 2) mbar_wait(aempty(ab), (uint32_t)(((ia >> 1) - 1) & 1));
                     mbar_expect_tx(afull(ab), a_bytes);
                     for (int bx = 0; bx < a.nboxes; ++bx)
-                        tma_load_2d(base + ab * WIN_BYTES + bx * a.rows_per_box * 128, &a.tm_x, c0,
-                                    (int)((long long)pl * a.Q + q0 + (long long)bx * a.rows_per_box), afull(ab));
-                    const int t_end = a.pbeg[u][pl + 1];
-                    for (int t0 = a.pbeg[u][pl]; t0 < t_end; t0 += a.tps) {       // one ring stage = up to tps taps
+                        tma_load_2d(win + bx * a.rows_per_box * 128, &a.tm_x, c0, pl * (int)a.Q + q0 + bx * a.rows_per_box, afull(ab));
+                    const int t_beg = a.pbeg[u][pl], t_end = a.pbeg[u][pl + 1];
+                    for (int t0 = t_beg; t0 < t_end; t0 += a.tps) {       // one ring stage = up to tps taps
                         const int nt_s = min(a.tps, t_end - t0);
                         const uint32_t s = bs;
+                        uint32_t meta = (uint32_t)nt_s | (nk16 << 3);
+                        if (t0 == t_beg) meta |= REC_CHUNK_FIRST | (ci == ci0 ? REC_TILE_FIRST : 0u);
+                        if (t0 + a.tps >= t_end) meta |= REC_CHUNK_LAST | (ci == ci1 - 1 ? (REC_TILE_LAST | f_last_tile) : 0u);
+                        uint32_t alo[4];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            alo[k] = a_lo | ((win + (uint32_t)a.shift[min(t0 + k, t_end - 1)] * 128u) >> 4);
+                        const uint32_t stage_base = wbase + s * WB_STRIDE;
                         mbar_wait(bempty(s), bph);
                         if (++bs == (uint32_t)kBStages) { bs = 0; bph ^= 1u; }
-                        mbar_expect_tx(bfull(s), b_bytes * (uint32_t)nt_s);
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(recs + 32u * s), "r"(alo[0]), "r"(alo[1]), "r"(alo[2]),
+                                     "r"(alo[3]) : "memory");
+                        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(recs + 32u * s + 16u), "r"(meta), "r"(b_lo | (stage_base >> 4)) : "memory");
+                        mbar_expect_tx(bfull(s), b_bytes * (uint32_t)nt_s);         // release: the record is visible to the waiter
                         for (int k = 0; k < nt_s; ++k) {
                             const int t = t0 + k;
-                            const uint32_t dst = wbase + s * WB_STRIDE + (uint32_t)k * TAP_STRIDE;
+                            const uint32_t dst = stage_base + (uint32_t)k * TAP_STRIDE;
                             if (!a.b_mn_major) {
                                 tma_load_2d(dst, &a.tm_w, c0, (int)a.wtap[t] * J + j0, bfull(s));
                             } else {
@@ -261,104 +334,127 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
         __syncwarp();
     } else if (warp == 1) {
         // ================================ MMA issuer ================================
-        {   // the whole warp walks the schedule (keeps every value warp-uniform); one elected lane issues
+        // the whole warp walks the records (keeps every value warp-uniform); one elected lane issues
+        if (blockIdx.x < a.nwork) {
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a.b_mn_major << 16) | ((uint32_t)(BN >> 3) << 17) |
                                    ((uint32_t)(WBM >> 4) << 24);
-            // descriptors: everything but the 14-bit start address is loop invariant; per-k16 advance is an add on the
-            // low word (+32 B along K for K-major tiles, +2048 B for MN-major weight tiles)
-            const uint64_t a_hi = make_desc(0, 16, 1024, 0);
-            const uint64_t b_hi = a.b_mn_major ? make_desc(0, 8192, 1024, 0) : make_desc(0, 16, 1024, 0);
+            // descriptors: the high words are loop invariant, the low words come from the stage record; per-k16 advance is an
+            // add on the low word (+32 B along K for K-major tiles, +2048 B for MN-major weight tiles)
+            const uint32_t a_hi = (uint32_t)(make_desc(0, 16, 1024, 0) >> 32);
+            const uint32_t b_hi = (uint32_t)((a.b_mn_major ? make_desc(0, 8192, 1024, 0) : make_desc(0, 16, 1024, 0)) >> 32);
             const uint32_t b_k16 = a.b_mn_major ? (2048u >> 4) : (32u >> 4);
+            const uint32_t b_tap = TAP_STRIDE >> 4;
             int ia = 0, li = 0;
             uint32_t bs = 0, bph = 0;       // weight ring: stage, parity of the "full" wait
-            for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
-                const long long wr = w / a.n_tiles;
-                const int sp = (int)(wr % a.nsplit);
-                const int u = (int)((wr / a.nsplit) / a.m_tiles);
-                const int acc = li & 1, v = li >> 1;
-                if (v >= 1) mbar_wait(tempty(acc), (uint32_t)((v - 1) & 1));
-                tc_fence_after();
-                const uint32_t d_tmem = tmem_base + acc * 256;
-                uint32_t accumulate = 0;
-                const int ci1 = min(a.cpb * a.nplanes, (sp + 1) * a.ci_per_split);
-                for (int ci = sp * a.ci_per_split; ci < ci1; ++ci, ++ia) {
-                    const int cc = ci / a.nplanes, pl = ci - cc * a.nplanes;
-                    const int nk16 = min(64, C - cc * 64) >> 4;
-                    const int ab = ia & 1;
-                    mbar_wait(afull(ab), (uint32_t)((ia >> 1) & 1));
-                    tc_fence_after();
-                    const uint32_t win = base + ab * WIN_BYTES;
-                    const int t_end = a.pbeg[u][pl + 1];
-                    for (int t0 = a.pbeg[u][pl]; t0 < t_end; t0 += a.tps) {       // one ring stage = up to tps taps
-                        const int nt_s = min(a.tps, t_end - t0);
-                        const uint32_t s = bs;
-                        const uint64_t bd0 = b_hi | (uint64_t)((wbase + s * WB_STRIDE) >> 4);
-                        uint64_t ad[4];
-#pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            ad[k] = a_hi | (uint64_t)((win + (uint32_t)a.shift[min(t0 + k, t_end - 1)] * 128u) >> 4);
-                        mbar_wait(bfull(s), bph);
-                        if (++bs == (uint32_t)kBStages) { bs = 0; bph ^= 1u; }
-                        tc_fence_after();
-                        if (elect_one()) {
-#pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                if (k < nt_s) {
-                                    const uint64_t bd = bd0 + (uint64_t)(k * (TAP_STRIDE >> 4));
-                                    umma_bf16(d_tmem, ad[k], bd, idesc, k == 0 ? accumulate : 1u);
-                                    if (nk16 > 1) umma_bf16(d_tmem, ad[k] + 2, bd + b_k16, idesc, 1);
-                                    if (nk16 > 2) umma_bf16(d_tmem, ad[k] + 4, bd + 2 * b_k16, idesc, 1);
-                                    if (nk16 > 3) umma_bf16(d_tmem, ad[k] + 6, bd + 3 * b_k16, idesc, 1);
-                                }
-                            }
-                            umma_commit(bempty(s));
-                        }
-                        __syncwarp();
-                        accumulate = 1;
-                    }
-                    if (elect_one()) umma_commit(aempty(ab));
-                    __syncwarp();
+            uint32_t d_tmem = tmem_base, accumulate = 0;
+#ifdef P2P_WINDOW_TIMING
+            // running checkpoints: every cycle of the warp between loop entry and exit lands in exactly one bucket
+            long long c_wa = 0, c_wb = 0, c_is = 0, c_wt = 0, c_n = 0, c_sh = 0;
+            const long long c_t0 = clock64();
+            long long c_last = c_t0;
+            long long g_loop0;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_loop0));
+#define CP(dst) { const long long now_ = clock64(); dst += now_ - c_last; c_last = now_; }
+#else
+#define CP(dst)
+#endif
+            const uint32_t slot_mask = (uint32_t)a.acc_slots - 1u, slot_shift = (uint32_t)a.acc_slots >> 1;      // 1 or 2 slots
+            const uint32_t half_cols = (uint32_t)a.half_cols;
+            for (;;) {
+                const uint32_t s = bs;
+                CP(c_sh);
+                mbar_wait(bfull(s), bph);
+                CP(c_wb);
+                if (++bs == (uint32_t)kBStages) { bs = 0; bph ^= 1u; }
+                uint32_t al0, al1, al2, al3, meta, bl;
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(al0), "=r"(al1), "=r"(al2), "=r"(al3) : "r"(recs + 32u * s) : "memory");
+                asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(meta), "=r"(bl) : "r"(recs + 32u * s + 16u) : "memory");
+                if (meta & REC_TILE_FIRST) {
+                    const uint32_t acc = (uint32_t)li & slot_mask, v = (uint32_t)li >> slot_shift;
+                    if (v >= 1) mbar_wait(tempty(acc), (v - 1) & 1u);
+                    d_tmem = tmem_base + acc * 256;
+                    accumulate = 0;
+                    CP(c_wt);
                 }
-                if (elect_one()) umma_commit(tfull(acc));
+                if (meta & REC_CHUNK_FIRST) {
+                    mbar_wait(afull(ia & 1), (uint32_t)((ia >> 1) & 1));
+                    CP(c_wa);
+                }
+                tc_fence_after();
+                if (elect_one()) {
+                    if (a.mrep == 2) issue_stage<2>(d_tmem, half_cols, a_hi, b_hi, al0, al1, al2, al3, bl, b_k16, b_tap, idesc, meta, accumulate);
+                    else issue_stage<1>(d_tmem, half_cols, a_hi, b_hi, al0, al1, al2, al3, bl, b_k16, b_tap, idesc, meta, accumulate);
+                    umma_commit(bempty(s));
+                    if (meta & REC_CHUNK_LAST) umma_commit(aempty(ia & 1));
+                    if (meta & REC_TILE_LAST) umma_commit(tfull((uint32_t)li & slot_mask));
+                }
                 __syncwarp();
+                accumulate = 1;
+                if (meta & REC_CHUNK_LAST) ++ia;
+                if (meta & REC_TILE_LAST) ++li;
+#ifdef P2P_WINDOW_TIMING
+                ++c_n;
+#endif
+                CP(c_is);
+                if (meta & REC_LAST) break;
             }
+#ifdef P2P_WINDOW_TIMING
+            if (a.dbg && lane == 0) {
+                long long* o = a.dbg + 8ll * blockIdx.x;
+                long long g_loop1;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_loop1));
+                o[0] = c_wa; o[1] = c_wb; o[2] = c_is; o[3] = c_wt; o[4] = c_n; o[5] = clock64() - c_t0; o[6] = li;
+                o[7] = ((g_loop0 - g_entry) << 32) | (g_loop1 - g_loop0);       // ns: entry -> loop start | loop duration
+                long long* o2 = a.dbg + 9ll * gridDim.x + 8ll * blockIdx.x;
+                o2[0] = 0; o2[1] = 0; o2[2] = c_sh; o2[3] = 0; o2[4] = 0;
+            }
+#endif
         }
         __syncwarp();
     } else {
         // ================================ epilogue ================================
+        // eight warps: two per TMEM lane quarter.  With two row halves (mrep = 2) group g takes half g; with one, the groups
+        // take alternate 32-column chunks.
         const int quarter = warp & 3, row = quarter * 32 + lane;
-        const int et = (warp - 2) * 32 + lane;            // 0..127 over the epilogue warps
-        const long long plane = (long long)a.Hp * a.Wp;
+        const int ewarp = warp - 2, g = ewarp >> 2;
+        const int et = ewarp * 32 + lane;                 // 0..255 over the epilogue warps
+        const int half_lo = a.mrep == 2 ? g : 0, half_hi = a.mrep == 2 ? g + 1 : 1;
+        const int c2_lo = a.mrep == 2 ? 0 : 32 * g, c2_step = a.mrep == 2 ? 32 : 64;
+        const uint32_t plane = (uint32_t)(a.Hp * a.Wp);     // the host keeps every row index below 2^31: 32-bit divisions throughout
         float* bias_s = reinterpret_cast<float*>(smem_raw + (bias_u32 - smem_u32(smem_raw)));
         int li = 0;
-        for (long long w = blockIdx.x; w < a.nwork; w += gridDim.x, ++li) {
-            const int nt = (int)(w % a.n_tiles);
-            const long long wr = w / a.n_tiles;
-            const int sp = (int)(wr % a.nsplit);
-            const long long mtu = wr / a.nsplit;
-            const int u = (int)(mtu / a.m_tiles);
-            const long long mt = mtu - (long long)u * a.m_tiles;
-            const int acc = li & 1, v = li >> 1;
+        const uint32_t nwork = (uint32_t)a.nwork, n_tiles = (uint32_t)a.n_tiles, nsplit = (uint32_t)a.nsplit;
+        for (uint32_t w = blockIdx.x; w < nwork; w += gridDim.x, ++li) {
+            const int nt = (int)(w % n_tiles);
+            const uint32_t wr = w / n_tiles;
+            const int sp = (int)(wr % nsplit);
+            const uint32_t mtu = wr / nsplit;
+            const int u = (int)(mtu / (uint32_t)a.m_tiles);
+            const uint32_t mt = mtu - (uint32_t)u * (uint32_t)a.m_tiles;
+            const int acc = li & (a.acc_slots - 1), v = li >> (a.acc_slots >> 1);
             const int c_begin = nt * BN, c_count = min(BN, J - c_begin);
-            float* bs_ = bias_s + acc * 256;
-            for (int c = et; c < BN; c += 128) bs_[c] = (a.bias && sp == 0 && c < c_count) ? __ldg(a.bias + c_begin + c) : 0.f;
-            const long long q = mt * WBM + row;
+            float* bs_ = bias_s + (li & 1) * 256;
+            for (int c = et; c < BN; c += 256) bs_[c] = (a.bias && sp == 0 && c < c_count) ? __ldg(a.bias + c_begin + c) : 0.f;
+            for (int half = half_lo; half < half_hi; ++half) {
+            const uint32_t q = (mt * (uint32_t)a.mrep + (uint32_t)half) * WBM + row;
             const int n = (int)(q / plane);
-            const int rem = (int)(q - (long long)n * plane);
+            const int rem = (int)(q - (uint32_t)n * plane);
             const int y = rem / a.Wp, x = rem - y * a.Wp;
-            const bool rok = q < a.Q && y < a.gy[u] && x < a.gx[u];
+            const bool rok = (long long)q < a.Q && y < a.gy[u] && x < a.gx[u];
             const long long obase = (((long long)n * a.OHf + (y * a.oys + a.oyo[u])) * a.OWf + (x * a.oxs + a.oxo[u])) * J + c_begin;
-            asm volatile("bar.sync 1, 128;" ::: "memory");      // bias staged (double-buffered by accumulator slot)
-            mbar_wait(tfull(acc), (uint32_t)(v & 1));
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * 256;
+            if (half == half_lo) {
+                asm volatile("bar.sync 1, 256;" ::: "memory");      // bias staged (double-buffered by tile parity)
+                mbar_wait(tfull(acc), (uint32_t)(v & 1));
+                tc_fence_after();
+            }
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * 256 + half * a.half_cols;
             if (a.fast_epi) {
                 const int esz = a.out_bf16 ? 2 : 4;
                 const unsigned okmask = __ballot_sync(0xffffffffu, rok);
                 const long long row_off = obase * esz;
-                const uint32_t stage = epi_stage + (uint32_t)(warp - 2) * 4096u;
+                const uint32_t stage = epi_stage + (uint32_t)ewarp * 4096u;
                 const int mode = a.nsplit > 1 ? EPI_RED : EPI_ST;
-                for (int c2 = 0; c2 < BN; c2 += 32) {
+                for (int c2 = c2_lo; c2 < BN; c2 += c2_step) {
                     uint32_t r2[32];
                     const bool two = c2 + 16 < BN;
                     tmem_ld16(taddr + c2, *reinterpret_cast<uint32_t(*)[16]>(&r2[0]));
@@ -389,7 +485,7 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
                     stage_store(P, stage, lane, r2, row_off + (long long)c2 * esz, okmask, (char*)a.out, valid, mode, esz);
                 }
             } else
-            for (int c2 = 0; c2 < BN; c2 += 32) {
+            for (int c2 = c2_lo; c2 < BN; c2 += c2_step) {
                 uint32_t r2[2][16];
                 tmem_ld16(taddr + c2, r2[0]);
                 if (c2 + 16 < BN) tmem_ld16(taddr + c2 + 16, r2[1]);
@@ -448,6 +544,7 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
                     }
                 }
             }
+            }
             tc_fence_before();
             mbar_arrive(tempty(acc));
         }
@@ -455,6 +552,13 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_kernel(const __grid_
 
     tc_fence_before();
     __syncthreads();
+#ifdef P2P_WINDOW_TIMING
+    if (a.dbg && tid == 0) {
+        long long g_exit;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_exit));
+        a.dbg[8ll * gridDim.x + blockIdx.x] = g_exit - g_entry;             // ns: whole CTA lifetime
+    }
+#endif
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
@@ -971,11 +1075,17 @@ int encode_2d(CUtensorMap* tm, const void* ptr, unsigned long long inner, unsign
     return P2P_OK;
 }
 
+long long* g_window_dbg = nullptr;    // P2P_WINDOW_TIMING builds only (p2p_conv_window_debug_buffer)
 int g_window_base_off_mode = 0;     // measured on B200: shifted starts need base_offset 0 (absolute-address swizzle)
 
 }  // namespace
 void note_umma_launch();
 }  // namespace p2p
+
+extern "C" int p2p_conv_window_debug_buffer(long long* buf) {    // 8 x int64 per CTA; only read by -DP2P_WINDOW_TIMING builds
+    p2p::g_window_dbg = buf;
+    return 0;
+}
 
 extern "C" int p2p_conv_window_base_off_mode(int mode) {
     const int old = p2p::g_window_base_off_mode;
@@ -1065,20 +1175,52 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
     if (t != ntaps) return fail(P2P_EINVAL, "taps must be grouped by sub-pass and sorted by plane");
     // swapped form (weights on the M side, 256 pixels on the N side) for J <= 128: see conv_window_swap_kernel
     static int swap_env = -1;
-    if (swap_env < 0) { const char* e = getenv("P2P_CONV_SWAP"); swap_env = (e && e[0] == '0') ? 0 : 1; }
+    if (swap_env < 0) { const char* e = getenv("P2P_CONV_SWAP"); swap_env = (e && e[0] == '1') ? 1 : 0; }      // opt-in since the 256-row tiles below: 9.15 vs 9.19 ms per step
     a.Q = (long long)d->N * Hp * Wp;
     const long long tiles256 = ((a.Q + SBM - 1) / SBM) * d->nsub * ((J + 127) / 128);
     // measured per layer (gpurun_out/layers_swap.log vs layers_noswap.log): a win for J = 96 (res blocks: dgrad 253 -> 164 us per
     // 4 calls), a loss for J <= 64 (fixed 256-pixel epilogue, 16 KB weight tiles) and mixed at J = 128
     const bool swap = swap_env && J >= 96 && J < 128 && J % 4 == 0 && SBM + halo <= kSwapRowsMax && tiles256 >= 120 &&
                       (((uintptr_t)out) & 15) == 0;
-    const int TR = swap ? SBM : WBM, rows_max = swap ? kSwapRowsMax : kWinRowsMax;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // column tile: whole J when it fits 256 columns, else balanced multiples of 16 (swapped form: 128 weight rows per MMA)
+    {
+        const int nt = (J + 255) / 256;
+        const int bn = ((J + nt - 1) / nt + 15) / 16 * 16;
+        a.BN = swap ? 128 : (bn < 16 ? 16 : bn);
+    }
+    a.n_tiles = (J + a.BN - 1) / a.BN;
+    // Two 128-row MMAs per weight tile (mrep = 2) halve the weight bytes TMA writes into shared memory per pixel.  The kernel
+    // is bound by the shared-memory port (MMA operand reads + TMA fills + epilogue staging, 128 B/clk), see DESIGN.md section 6,
+    // so this pays whenever the longer tiles still fill the chip: rounds(256-row tiles) * 2 * 0.8 < rounds(128-row tiles).
+    static int mrep_env = -1;
+    if (mrep_env < 0) { const char* e = getenv("P2P_CONV_MREP"); mrep_env = (e && e[0] == '1') ? 1 : 2; }
+    a.mrep = 1;
+    if (!swap && mrep_env == 2) {
+        const long long w1 = ((a.Q + 127) / 128) * a.n_tiles * d->nsub, w2 = ((a.Q + 255) / 256) * a.n_tiles * d->nsub;
+        const long long r1 = (w1 + sms - 1) / sms, r2 = (w2 + sms - 1) / sms;
+        const int nb2 = (256 + halo + 255) / 256, rpb2 = ((256 + halo + nb2 - 1) / nb2 + 7) / 8 * 8;
+        const int rows2 = (nb2 * rpb2 * 128 + 1023) / 1024 * 1024;         // bytes of one 256-row window buffer, box-rounded
+        const int tap_bytes_k = ((a.BN * 128 + 1023) / 1024) * 1024, tap_bytes_mn = ((a.BN + 63) / 64) * 8192;
+        const int tap_max = tap_bytes_k > tap_bytes_mn ? tap_bytes_k : tap_bytes_mn;
+        if (w1 * 2 > sms && r2 * 16 < r1 * 10 && WDATA_BYTES - 2 * rows2 >= 3 * tap_max) a.mrep = 2;
+    }
+    const int TR = swap ? SBM : WBM * a.mrep, rows_max = swap ? kSwapRowsMax : (WDATA_BYTES / 2) / 128;
     a.win_rows = TR + halo;
-    if (a.win_rows > rows_max) return fail(P2P_ENOTSUP, "window of %d rows exceeds the %d-row buffer", a.win_rows, rows_max);
+    if (a.win_rows > rows_max || (!swap && a.mrep == 1 && a.win_rows > kWinRowsMax))
+        return fail(P2P_ENOTSUP, "window of %d rows exceeds the %d-row buffer", a.win_rows, rows_max);
+    a.win_bytes = (a.win_rows * 128 + 1023) / 1024 * 1024;
+    a.half_cols = a.BN <= 128 ? 128 : 256;
+    a.acc_slots = (a.mrep == 2 && a.BN > 128) ? 1 : 2;
     a.nboxes = (a.win_rows + 255) / 256;
     a.rows_per_box = (a.win_rows + a.nboxes - 1) / a.nboxes;
     a.rows_per_box = (a.rows_per_box + 7) / 8 * 8;          // keeps every box 1024-byte aligned
     if (a.nboxes * a.rows_per_box > rows_max) return fail(P2P_ENOTSUP, "window boxes exceed the buffer");
+    if (!swap && a.nboxes * a.rows_per_box * 128 > a.win_bytes) {
+        a.win_bytes = (a.nboxes * a.rows_per_box * 128 + 1023) / 1024 * 1024;
+    }
     const long long w_tap = d->w_tap, w_k = d->w_k, w_j = d->w_j;
     if (w_k == 1 && w_j % 8 == 0 && w_tap % 8 == 0) a.b_mn_major = 0;
     else if (w_j == 1 && w_k % 8 == 0 && w_tap % 8 == 0 && J % 8 == 0) a.b_mn_major = 1;
@@ -1091,28 +1233,21 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
     a.cpb = (C + 63) / 64;
     a.base_off_mode = g_window_base_off_mode;
     a.fast_epi = ((long long)J * (a.out_bf16 ? 2 : 4)) % 16 == 0 && (((uintptr_t)out) & 15) == 0;
-    if (swap) {
-        a.BN = 128;         // rows of the weight tile (output channels per MMA)
-    } else {   // column tile: whole J when it fits 256 columns, else balanced multiples of 16
-        const int nt = (J + 255) / 256;
-        const int bn = ((J + nt - 1) / nt + 15) / 16 * 16;
-        a.BN = bn < 16 ? 16 : bn;
-    }
-    a.n_tiles = (J + a.BN - 1) / a.BN;
+    a.dbg = g_window_dbg;
     a.b_tap_bytes = a.b_mn_major ? ((a.BN + 63) / 64) * 8192 : ((a.BN * 128 + 1023) / 1024) * 1024;
-    a.tps = WRING_BYTES / (3 * a.b_tap_bytes);          // keep >= 3 stages in flight
+    const int ring_bytes = swap ? WRING_BYTES : WDATA_BYTES - 2 * a.win_bytes;
+    a.tps = ring_bytes / (3 * a.b_tap_bytes);          // keep >= 3 stages in flight
     if (a.tps > 4) a.tps = 4;
     if (a.tps < 1) a.tps = 1;
     a.b_stage_bytes = a.tps * a.b_tap_bytes;
-    a.b_stages = WRING_BYTES / a.b_stage_bytes;
+    a.b_stages = ring_bytes / a.b_stage_bytes;
     if (a.b_stages > kBStagesMax) a.b_stages = kBStagesMax;
+    if (a.b_stages < 2) return fail(P2P_ENOTSUP, "weight ring too small for this window");
     const long long mt = (a.Q + TR - 1) / TR;
     if (mt * a.nsub > 2000000000LL / a.n_tiles) return fail(P2P_ENOTSUP, "too many tiles");
+    if ((long long)nplanes * a.Q + halo + TR > 2000000000LL) return fail(P2P_ENOTSUP, "too many rows for 32-bit row indices");
     a.m_tiles = (int)mt;
     a.nwork = mt * a.n_tiles * a.nsub;
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     a.nsplit = 1;
     a.ci_per_split = a.cpb * nplanes;
     if (!swap && !a.out_bf16 && a.nwork * 2 <= sms && a.cpb * nplanes >= 4) {
@@ -1154,7 +1289,7 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
         note_umma_launch();
         return check_launch("conv_window_swap_kernel");
     }
-    conv_window_kernel<<<(unsigned)grid, kWThreads, WSMEM, (cudaStream_t)stream>>>(a);
+    conv_window_kernel<<<(unsigned)grid, kWinThreads, WSMEM, (cudaStream_t)stream>>>(a);
     note_umma_launch();
     return check_launch("conv_window_kernel");
 }

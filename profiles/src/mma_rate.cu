@@ -58,6 +58,43 @@ __global__ void k(long long* out, int N, int mode, int iters, int shift_rows, in
     __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
 }
+// W warps (one elected thread each) issue concurrently to disjoint accumulators: is the ~105-cycle cost per issuing thread or per SM?
+__global__ void k2(long long* out, int N, int iters, int W) {
+    extern __shared__ uint8_t raw[];
+    const uint32_t base = (smem_u32(raw) + 1023u) & ~1023u;
+    const uint32_t sa = base, sb = base + 64 * 1024, bar = base + 160 * 1024, slot = bar + 64;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < 40 * 1024; i += blockDim.x) reinterpret_cast<uint32_t*>(raw)[i] = 0x3c003c00u;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp == 0) {
+        if (tid == 0) { for (int i = 0; i < 4; ++i) mbar_init(bar + 8 * i, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+        __syncwarp();
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    uint32_t tmem;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem) : "r"(slot));
+    long long t0 = clock64();
+    if (warp < W && (tid & 31) == 0) {
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((128u >> 4) << 24);
+        const uint64_t ad0 = make_desc(sa, 16, 1024), bd0 = make_desc(sb, 16, 1024);
+        const uint32_t d = tmem + (uint32_t)(warp * N);
+        for (int it = 0; it < iters; ++it) {
+            umma_bf16(d, ad0, bd0, idesc, 1);
+            umma_bf16(d, ad0 + 2, bd0 + 2, idesc, 1);
+            umma_bf16(d, ad0 + 4, bd0 + 4, idesc, 1);
+            umma_bf16(d, ad0 + 6, bd0 + 6, idesc, 1);
+        }
+        umma_commit(bar + 8 * warp);
+        mbar_wait(bar + 8 * warp, 0);
+    }
+    __syncthreads();
+    if (tid == 0) out[blockIdx.x] = clock64() - t0;
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+}
 int main() {
     long long* d; cudaMalloc(&d, 148 * 8);
     cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -78,6 +115,18 @@ int main() {
                 printf("commit_every %3d  A %s  B %s  N %3d  independent accumulators %d : %7.1f cyc/MMA  (math floor %d)\n", ce, (mode & 1) ? "MN" : "K ", (mode & 2) ? "MN" : "K ", N, nacc,
                        (double)mx / (iters * 4.0), 128 * N / 256);
             }
+        }
+    printf("\nW issuing warps per CTA, each 512 groups of 4 MMAs to its own accumulator: cycles per MMA counted over ALL warps' MMAs\n");
+    cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    for (int N : {48, 96, 128})
+        for (int W : {1, 2, 4}) {
+            if (W * N > 512) continue;
+            k2<<<148, 128, 200 * 1024>>>(d, N, iters, W);
+            cudaError_t e = cudaDeviceSynchronize();
+            if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
+            long long h[148]; cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
+            long long mx = 0; for (int i = 0; i < 148; ++i) mx = h[i] > mx ? h[i] : mx;
+            printf("N %3d  issuing warps %d : %7.1f cyc/MMA (math floor %d)\n", N, W, (double)mx / (iters * 4.0 * W), 128 * N / 256);
         }
     return 0;
 }
