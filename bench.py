@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- the driver's measurement contract for the hot path (see DESIGN.md "Measurement").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload train|mdct]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload train|train_time|mdct]
 
 One JSON line on stdout (rank 0).
 Workload "train" (default; BASELINE.json configs[2]): one step = one full G3L2-ngf48 optimisation step
@@ -35,7 +35,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="train", choices=["train", "mdct"])
+    ap.add_argument("--workload", default="train", choices=["train", "train_time", "mdct"])
     ap.add_argument("--batch", type=int, default=None, help="segments per GPU per step (train: 8, mdct: 512)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -298,8 +298,8 @@ def run_ours(args):
 def main():
     args = parse_args()
     if args.batch is None:
-        args.batch = 8 if args.workload == "train" else 512
-    if args.workload == "train":
+        args.batch = 8 if args.workload.startswith("train") else 512
+    if args.workload.startswith("train"):
         from bench_train import run_train, run_train_reference
         (run_train_reference if args.impl == "reference" else run_train)(args)
     elif args.impl == "reference":

@@ -118,7 +118,9 @@ def run_train(args):
     import io
     torch.manual_seed(1234)
     with contextlib.redirect_stdout(io.StringIO()):
-        model = create_model(options.g3l2_opt(gpu_ids=[local], batchSize=B, precision=args.precision))
+        # --workload train_time: BASELINE.json configs[3] (train_script.sh:93, 96: --use_time_D --lambda_time 10 --use_match_loss)
+        extra = dict(use_time_D=True, use_match_loss=True, lambda_time=10.0) if args.workload == "train_time" else {}
+        model = create_model(options.g3l2_opt(gpu_ids=[local], batchSize=B, precision=args.precision, **extra))
     broadcast_parameters(model)
     sync = GradSync()
     if os.environ.get("P2P_EARLY_SYNC", "0") == "1":      # measured slower at 8 GPUs (12.7 vs 12.1 ms/step): off by default
@@ -211,7 +213,9 @@ def run_train(args):
             "metric": METRIC, "value": round(B * world * K / (total_ms * 1e-3), 2), "unit": "samples/s", "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": round(step_ms, 3), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
-            "config": {"workload": WORKLOAD % (B, B), "global_batch": B * world, "parallelism": f"dp{world}",
+            "config": {"workload": WORKLOAD % (B, B) + ("; + time-domain D on [%d,2,128,1024] frames and frame-match loss "
+                                                          "(--use_time_D --lambda_time 10 --use_match_loss)" % B if extra else ""),
+                       "global_batch": B * world, "parallelism": f"dp{world}",
                        "launch": "eager" if args.no_graph else "one CUDA graph replay per step",
                        "l2": "per-step working set (0.31 GB bf16 weights + 0.65 GB fp32 master + activations) exceeds the 126 MB L2; no flush",
                        "weights": "random init N(0,0.02), seed 1234; mask_mode mode2; Adam lr 2e-4 beta1 0.5",

@@ -246,6 +246,30 @@ int p2p_spectro_decode(const void* x, long long sb, long long sc, long long sh, 
                        const float* pha, float* coef, int B, int channels, int F, int M, float alpha, float min_value,
                        float gain, int dtype, void* stream);
 
+/* ---- time-domain side of the loss path (models/pix2pixHD_model.py:251-258, 314-320, 375-387, 408-415) ------------
+ * p2p_frame_window: frames[b,f,n] = window[n] * x_pad[b, f*hop + n], x_pad = audio shifted right by `offset` zeros and
+ *   zero-extended -- the windowed frames MDCT2.forward(signal, return_ola=True) returns (models/mdct.py:497-503), which
+ *   to_spectro stores in norm_param['frames'] (pix2pixHD_model.py:143-145, 227).
+ * p2p_frames_db_fwd / _bwd: out = 20 log10(max(|gain * window[n] * frames[r,n]|, min_value)) - 20 over `rows` frames of
+ *   N samples (discriminate_time_D :317-318 fused with sqrt(up_ratio-1) * window * frames of :375); window may be NULL
+ *   (then only the gain applies).  _bwd: dframes = dout * d out / d frames (zero below the clamp).
+ * p2p_frame_match (:408-415): weight * mean_{b, f < F-1, i < N/2}((y[b,f,N/2+i] w[i] - y[b,f+1,i] w[N/2+i])^2).  Value
+ *   mode: loss != NULL (atomically accumulated: zero it first); gradient mode: dframes != NULL receives
+ *   gscale * (*gscale_dev if non-NULL) * d loss / d y.  Both may be requested in one call.
+ * p2p_spectro_decode_bwd: gradient of p2p_spectro_decode with channels == 2 (to_frames / to_audio in the loss path):
+ *   dcoef [B,F,M] -> dx [B,M,F,2] fp32 channels-last; x, strides, norm, alpha, gain as in the forward call. */
+int p2p_frame_window(const float* audio, const float* window, float* frames, int B, long long T, int F, int hop, int win,
+                     long long offset, void* stream);
+int p2p_frames_db_fwd(const float* frames, const float* window, float gain, float* out, long long rows, int N,
+                      float min_value, void* stream);
+int p2p_frames_db_bwd(const float* frames, const float* window, float gain, const float* dout, float* dframes,
+                      long long rows, int N, float min_value, void* stream);
+int p2p_frame_match(const float* frames, const float* window, float weight, float* loss, float* dframes, float gscale,
+                    const float* gscale_dev, int B, int F, int N, void* stream);
+int p2p_spectro_decode_bwd(const void* x, long long sb, long long sc, long long sh, long long sw, const float* norm,
+                           const float* dcoef, float* dx, int B, int F, int M, float alpha, float gain, int dtype,
+                           void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -6,6 +6,8 @@ a functional restatement, on plain torch CPU ops, of
     models/networks.py:68-110    GANLoss (LSGAN branch)                             -> gan_loss()
     models/pix2pixHD_model.py:142-227, 229-249   to_spectro / denormalize / to_audio -> to_spectro(), to_audio()
     models/pix2pixHD_model.py:331-435            forward (GAN + feature matching)   -> model_losses()
+    models/pix2pixHD_model.py:251-258, 314-320, 375-387, 408-415   to_frames, time-domain D, frame match
+                                                                   -> to_frames(), frames_of(), time_losses(), match_loss()
     train.py:155-184             loss assembly, two backward passes, two Adam steps -> TrainState.step()
 
 working directly on reference-format state_dicts (same keys, same shapes).  Only tests/, __graft_entry__.smoke()
@@ -13,8 +15,9 @@ and bench.py's cpu_baseline / --impl reference legs may import this file.
 
 Parity pinned: tests/test_oracle_nets.py checks it against the reference's own outputs committed under
 tests/golden/ (nets_ref.npz: network outputs and gradients; model_ref.npz: encoded images, first-step losses and
-gradients, weights after the first Adam step, 200-step loss curve, inference + reconstructed audio), all produced by
-importing /root/reference in the build container (tests/golden/make_golden_nets.py, make_golden_model.py).
+gradients, weights after the first Adam step, 200-step loss curve, inference + reconstructed audio; model_time_ref.npz:
+the same step with --use_time_D --use_match_loss), all produced by importing /root/reference in the build container
+(tests/golden/make_golden_nets.py, make_golden_model.py, make_golden_model_time.py).
 """
 import math
 
@@ -156,6 +159,8 @@ def to_spectro(audio, cfg, mask):
     pha = torch.sign(spectro)
     hi, lo = logs.max(), logs.min()
     norm = {'max': hi, 'min': lo, 'mean': logs.mean(), 'std': logs.var().sqrt()}
+    if cfg.get('use_time_D'):
+        norm['frames'] = frames_of(audio, cfg)
     logs = (logs - lo) / (hi - lo)
     if mask:
         size = logs.size()
@@ -173,6 +178,61 @@ def to_audio(log_spectro, norm, cfg):
     w = M4.kbdwin(cfg['win_length'])
     y = M4.imdct4_forward(spec.permute(0, 2, 1).double().numpy(), w, cfg['n_fft'], cfg['hop_length'], True)
     return math.sqrt(cfg['up_ratio'] - 1) * torch.from_numpy(y.astype(np.float32)).reshape(spec.shape[0], 1, 1, -1)
+
+
+# ---- time-domain side (frames) ---------------------------------------------------------------------------
+def frames_of(audio, cfg):
+    """the windowed frames [B, F, win] MDCT2.forward(signal, return_ola=True) hands back (models/mdct.py:377-394; the
+    same pad / unfold / window lines open MDCT4.forward, :488-503)"""
+    hop, win = cfg['hop_length'], cfg['win_length']
+    start_pad = hop                                               # center=True
+    r = len(audio) % hop
+    end_pad = start_pad + (hop - r if r else 0)
+    x = F.pad(audio, (start_pad, end_pad))
+    return x.unfold(-1, win, hop) * torch.from_numpy(M4.kbdwin(win).astype(np.float32))
+
+
+def decode_coefficients(log_spectro, norm, cfg):
+    """denormalize + explicit decode + permute (pix2pixHD_model.py:229-232, 253-257), differentiable"""
+    s = log_spectro.abs() * (norm['max'] - norm['min']) + norm['min']
+    amp = 10.0 * torch.pow(10.0, 0.05 * s) - cfg['min_value']
+    spec = (amp[..., 0, :, :] - amp[..., 1, :, :]) / (2 * cfg['alpha'] - 1)
+    return spec.permute(0, 2, 1)
+
+
+def to_frames(log_spectro, norm, cfg):
+    """pix2pixHD_model.py:251-258 with `_idct` = IMDCT4's per-frame inverse (models/mdct.py:547-549, twiddles :539-540)
+    scaled 8/n_fft: IDCT_2N is twice the frame IMDCT2 windows and overlap-adds (mdct.py:440), IMDCT4 overlap-adds
+    (4/n_fft) * this frame (mdct.py:560).  Differentiable torch restatement, float64 inside, float32 out."""
+    N = cfg['n_fft']
+    X = decode_coefficients(log_spectro, norm, cfg).double()
+    exp1 = torch.exp(-1j * (math.pi / (2 * N) + math.pi / 4) * torch.arange(1, N, 2, dtype=torch.float64))
+    exp2 = torch.exp(-1j * math.pi / (2 * N) * torch.arange(0, 2 * N, 2, dtype=torch.float64))
+    y = torch.real(torch.fft.fft(exp1 * X, n=N) * exp2)
+    return (8.0 / N * y).float()
+
+
+def match_loss(sr_frames, cfg):
+    """pix2pixHD_model.py:408-415"""
+    half = cfg['win_length'] // 2
+    w = torch.from_numpy(M4.kbdwin(cfg['win_length']).astype(np.float32))
+    a = sr_frames[..., :-1, half:] * w[:half]
+    b = sr_frames[..., 1:, :half] * w[half:]
+    return ((a - b) ** 2).mean() * cfg['lambda_mat']
+
+
+def time_losses(sdT, lr_frames, hr_frames, sr_frames, cfg):
+    """pix2pixHD_model.py:375-387 with discriminate_time_D (:314-320) -> (G_GAN_t, D_real_t, D_fake_t)"""
+    d, amin = cfg['D'], cfg['min_value']
+    w = torch.from_numpy(M4.kbdwin(cfg['win_length']).astype(np.float32))
+    run = lambda x: discriminator(x, sdT, d['num_D'], d['n_layers_D'], False)
+    sr = (math.sqrt(cfg['up_ratio'] - 1) * w * sr_frames).unsqueeze(1)
+    lr, hr = lr_frames.unsqueeze(1), hr_frames.unsqueeze(1)
+    db = lambda x: _db(x.abs(), amin)
+    loss_D_fake_t = gan_loss(run(torch.cat((db(lr), db(sr.detach())), dim=1)), False) * cfg['lambda_time']
+    loss_D_real_t = gan_loss(run(torch.cat((db(lr), db(hr)), dim=1)), True) * cfg['lambda_time']
+    loss_G_t = gan_loss(run(torch.cat((lr, sr), dim=1)), True) * cfg['lambda_time']       # :386: raw frames, no dB
+    return loss_G_t, loss_D_real_t, loss_D_fake_t
 
 
 # ---- model + optimisation step ---------------------------------------------------------------------------
@@ -194,26 +254,41 @@ def model_losses(sdG, sdD, lr_spectro, hr_spectro, cfg):
 
 
 class TrainState:
-    """weights + two Adam optimisers (pix2pixHD_model.py:131, 140) stepping as train.py:155-184 does"""
+    """weights + two Adam optimisers (pix2pixHD_model.py:131, 140) stepping as train.py:155-184 does; with sdT (the
+    time-domain discriminator's weights, cfg['use_time_D']) and / or cfg['use_match_loss'] the frame losses of
+    pix2pixHD_model.py:375-387, 408-415 join loss_G / loss_D as train.py:159-160 adds them"""
 
-    def __init__(self, sdG, sdD, cfg, lr=2e-4, beta1=0.5):
+    def __init__(self, sdG, sdD, cfg, lr=2e-4, beta1=0.5, sdT=None):
         self.cfg = cfg
         self.G = {k: v.clone().float().requires_grad_(True) for k, v in sdG.items()}
         self.D = {k: v.clone().float().requires_grad_(True) for k, v in sdD.items()}
+        self.T = {k: v.clone().float().requires_grad_(True) for k, v in (sdT or {}).items()}
         self.opt_G = torch.optim.Adam(list(self.G.values()), lr=lr, betas=(beta1, 0.999))
-        self.opt_D = torch.optim.Adam(list(self.D.values()), lr=lr, betas=(beta1, 0.999))
+        self.opt_D = torch.optim.Adam(list(self.D.values()) + list(self.T.values()), lr=lr, betas=(beta1, 0.999))
 
     def step(self, lr_audio, hr_audio, spectros=None):
         cfg = self.cfg
+        lnorm = hnorm = None
         if spectros is None:
             with torch.no_grad():
-                hs, _, _ = to_spectro(hr_audio, cfg, False)
-                ls, _, _ = to_spectro(lr_audio, cfg, True)
+                hs, _, hnorm = to_spectro(hr_audio, cfg, False)
+                ls, _, lnorm = to_spectro(lr_audio, cfg, True)
         else:
             ls, hs = spectros
         g_gan, g_feat, d_real, d_fake, sr = model_losses(self.G, self.D, ls, hs, cfg)
         loss_D = (d_fake + d_real) * 0.5
         loss_G = g_gan + g_feat
+        extra = {}
+        if cfg.get('use_time_D') or cfg.get('use_match_loss'):
+            sr_frames = to_frames(sr, lnorm, cfg)
+            if cfg.get('use_match_loss'):
+                extra['G_mat'] = match_loss(sr_frames, cfg)
+                loss_G = loss_G + extra['G_mat']
+            if cfg.get('use_time_D'):
+                g_t, d_real_t, d_fake_t = time_losses(self.T, lnorm['frames'], hnorm['frames'], sr_frames, cfg)
+                extra.update(G_GAN_t=g_t, D_real_t=d_real_t, D_fake_t=d_fake_t)
+                loss_G = loss_G + g_t
+                loss_D = loss_D + (d_fake_t + d_real_t) * 0.5
         self.opt_G.zero_grad()
         loss_G.backward()
         gG = {k: v.grad.clone() for k, v in self.G.items()}
@@ -221,8 +296,10 @@ class TrainState:
         self.opt_D.zero_grad()
         loss_D.backward()
         gD = {k: v.grad.clone() for k, v in self.D.items()}
+        self.last_gT = {k: v.grad.clone() for k, v in self.T.items()}
+        self.last_extra = {k: float(v.detach()) for k, v in extra.items()}
         self.opt_D.step()
-        return [float(g_gan), float(g_feat), float(d_real), float(d_fake)], sr.detach(), gG, gD
+        return [float(g_gan.detach()), float(g_feat.detach()), float(d_real.detach()), float(d_fake.detach())], sr.detach(), gG, gD
 
 
 def random_state_dicts(ngf=48, ndf=64, input_nc=2, output_nc=2, n_down=4, n_blocks_global=3, n_blocks_local=2, num_D=2,

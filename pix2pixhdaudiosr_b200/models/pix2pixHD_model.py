@@ -9,8 +9,11 @@ Differences from the reference, all deliberate:
 * the three per-step `.cpu().numpy()` copies of pix2pixHD_model.py:418-432 only happen when `infer` is set;
 * the generator's pass through D runs with detached D weights (the reference computes and discards those
   weight gradients, train.py:164-176);
-* the time-domain discriminator / frame-match options (`use_time_D`, `use_match_loss`, `use_hifigan_D`), the
-  instance-feature encoder and VGG loss are not built.
+* `use_time_D` / `use_match_loss` (pix2pixHD_model.py:375-387, 408-415) run on MDCT4's own frames: the shipped model
+  takes them from MDCT2(return_ola) / IDCT_2N; here `norm_param['frames']` are the windowed frames of mdct.py:497-503
+  and `to_frames` is IMDCT4's per-frame inverse before window and overlap-add (mdct.py:547-549) times 8/n_fft, i.e.
+  twice the frame IMDCT4 windows and overlap-adds -- the relation IDCT_2N has to IMDCT2 (mdct.py:440);
+* `use_hifigan_D`, the instance-feature encoder and the VGG loss are not built.
 """
 import ctypes
 import math
@@ -22,7 +25,7 @@ from ..optim import FusedAdam
 from ..util.util import kbdwin
 from . import networks
 from .base_model import BaseModel
-from .mdct import IMDCT4, MDCT4
+from .mdct import IMDCT4, MDCT4, _Plan, _SynthesisFn
 
 
 def _p(t):
@@ -46,9 +49,16 @@ class Pix2PixHDModel(BaseModel):
 
     def initialize(self, opt):
         BaseModel.initialize(self, opt)
-        for flag in ('use_time_D', 'use_match_loss', 'use_hifigan_D', 'instance_feat', 'label_feat'):
+        for flag in ('use_hifigan_D', 'instance_feat', 'label_feat'):
             if getattr(opt, flag, False):
                 raise NotImplementedError('--%s is outside the path built so far (DESIGN.md §5)' % flag)
+        self.use_frames = bool(opt.isTrain and (opt.use_time_D or opt.use_match_loss))
+        if self.use_frames:
+            if not opt.explicit_encoding:
+                raise ValueError('use_time_D / use_match_loss need explicit_encoding: to_frames returns None otherwise '
+                                 '(pix2pixHD_model.py:251-258)')
+            if opt.win_length != opt.n_fft:
+                raise NotImplementedError('use_time_D / use_match_loss: win_length must equal n_fft')
         if getattr(opt, 'transform', 'mdct4') != 'mdct4':
             raise NotImplementedError('transform %r: only MDCT4/IMDCT4 is built (MDCT2 is SURVEY §8f N1)' % opt.transform)
         if not opt.no_vgg_loss and opt.isTrain:
@@ -66,6 +76,9 @@ class Pix2PixHDModel(BaseModel):
                            device=self.device)
         self._imdct = IMDCT4(n_fft=opt.n_fft, hop_length=opt.hop_length, win_length=opt.win_length, window=self.window,
                              device=self.device)
+        # to_frames: the synthesis kernel with hop = win = n_fft and a window of ones gives the F frames side by side;
+        # a second plan carries sqrt(up_ratio-1) * window (:375)
+        self._frame_plan = self._frame_plan_scaled = None
 
         # networks (:42-60)
         netG_input_nc = input_nc + (0 if opt.no_instance else 1)
@@ -78,6 +91,9 @@ class Pix2PixHDModel(BaseModel):
                 netD_input_nc = input_nc + opt.output_nc + (0 if opt.no_instance else 1)
                 self.netD = networks.define_D(netD_input_nc, opt.ndf, opt.n_layers_D, opt.norm, opt.no_lsgan, opt.num_D,
                                               not opt.no_ganFeat_loss, gpu_ids=self.gpu_ids)
+                if opt.use_time_D:      # :64-65
+                    self.time_D = networks.define_D(2, opt.ndf, opt.n_layers_D, opt.norm, opt.no_lsgan, opt.num_D, False,
+                                                    gpu_ids=self.gpu_ids)
         finally:
             networks.set_default_precision('fp32')
         if opt.verbose:
@@ -88,6 +104,8 @@ class Pix2PixHDModel(BaseModel):
             self.load_network(self.netG, 'G', opt.which_epoch, pretrained_path)
             if self.isTrain:
                 self.load_network(self.netD, 'D', opt.which_epoch, pretrained_path)
+                if opt.use_time_D:
+                    self.load_network(self.time_D, 'time_D', opt.which_epoch, pretrained_path)
 
         if self.isTrain:
             self.old_lr = opt.lr
@@ -103,6 +121,8 @@ class Pix2PixHDModel(BaseModel):
                 params = list(self.netG.parameters())
             print('Total number of parameters of G: %d' % (sum([param.numel() for param in params])))
             d_params = list(self.netD.parameters())
+            if opt.use_time_D:          # :137-138
+                d_params += list(self.time_D.parameters())
             print('Total number of parameters of D: %d' % (sum([param.numel() for param in d_params])))
             if len(self.gpu_ids) > 0:
                 self.optimizer_G = FusedAdam(params, lr=opt.lr, betas=(opt.beta1, 0.999))
@@ -133,10 +153,15 @@ class Pix2PixHDModel(BaseModel):
         """audio [B,T] -> (log_spectro [B,C,H,W] in [0,1], pha [B,1,H,W], norm_param); H = bins, W = frames.
         The returned images are channels-last in memory (what the conv kernels read) behind NCHW shapes."""
         opt = self.opt
-        spec = self._mdct(audio.to(self.device))                        # [B, F, M] fp32, kernel: mdct4_analysis
+        audio = audio.to(self.device)
+        spec = self._mdct(audio)                                        # [B, F, M] fp32, kernel: mdct4_analysis
         if spec.dim() != 3:
             raise ValueError('to_spectro expects audio shaped [B, T]')
         B, F, M = spec.shape
+        frames = None
+        if getattr(opt, 'use_time_D', False):                           # :143-145: the windowed frames, [B, F, win]
+            start_pad, _ = self._mdct.pads(int(len(audio)))
+            frames = ops.frame_window(audio, self._mdct.window.to(audio.device, torch.float32), F, opt.hop_length, start_pad)
         C = 2 if opt.explicit_encoding else 1
         dev = spec.device
         logs = torch.empty((B, M, F, C), dtype=torch.float32, device=dev)
@@ -162,7 +187,7 @@ class Pix2PixHDModel(BaseModel):
             noise = self._mask_noise(B, mask_size, F, C, dev) if mask_size > 0 else None
         _lib.check(lib.p2p_spectro_normalize(_p(logs), _p(work), _p(norm), _p(noise), B, F, M, C, mask_size,
                                              int(bool(mask) and mask_size > 0), _stream()))
-        norm_param = {'max': norm[0], 'min': norm[1], 'mean': norm[2], 'std': norm[3], 'frames': None}
+        norm_param = {'max': norm[0], 'min': norm[1], 'mean': norm[2], 'std': norm[3], 'frames': frames}
         return logs.permute(0, 3, 1, 2), pha, norm_param
 
     def _decode(self, log_spectro, norm_param, pha, gain):
@@ -204,6 +229,39 @@ class Pix2PixHDModel(BaseModel):
             coef = self._decode(log_spectro, norm_param, pha, math.sqrt(self.up_ratio - 1))
             return self._imdct(coef)
 
+    def _decode_with_grad(self, log_spectro, norm_param):
+        """denormalize + explicit decode + permute (:229-232, 253-257) -> coefficients [B, F, M], differentiable"""
+        log_spectro = log_spectro.to(self.device)
+        norm = torch.stack((norm_param['max'], norm_param['min'])).to(log_spectro.device, torch.float32)
+        return ops.SpectroDecodeFn.apply(log_spectro, norm, self.opt.alpha, self.opt.min_value, 1.0)
+
+    def _frames_from_coef(self, coef, plan):
+        """synthesis kernel at hop = win = n_fft: no overlap, the F frames land side by side -> [B, F, n_fft]"""
+        B, F, _ = coef.shape
+        N = self.opt.n_fft
+        return _SynthesisFn.apply(coef, plan, F * N, 0, 8.0 / N).view(B, F, N)
+
+    def _frame_plans(self):
+        if self._frame_plan is None:
+            N = self.opt.n_fft
+            self._frame_plan = _Plan(N, N, N, torch.ones(N))
+            self._frame_plan_scaled = _Plan(N, N, N, math.sqrt(self.up_ratio - 1) * self.window.detach().cpu().float())
+        return self._frame_plan, self._frame_plan_scaled
+
+    def to_frames(self, log_spectro, norm_param):
+        """spectrogram image -> per-frame time signals [B, F, n_fft] with a gradient (:251-258): decode kernel +
+        synthesis kernel (no window, no overlap-add)"""
+        if not self.opt.explicit_encoding:
+            return None
+        return self._frames_from_coef(self._decode_with_grad(log_spectro, norm_param), self._frame_plans()[0])
+
+    def discriminate_time_D(self, label_frames, test_frames):
+        """time-domain discriminator on dB(|label|), dB(|test.detach()|) stacked on channels (:314-320); frames [B,1,F,N]"""
+        amin = self.opt.min_value
+        label = ops.FramesDbFn.apply(label_frames, None, 1.0, amin)
+        test = ops.FramesDbFn.apply(test_frames.detach(), None, 1.0, amin)
+        return self.time_D.forward(torch.cat((label, test), dim=1))
+
     def encode_input(self, lr_audio, inst_map=None, hr_audio=None, feat_map=None):
         if hr_audio is not None:
             with torch.no_grad():
@@ -234,15 +292,40 @@ class Pix2PixHDModel(BaseModel):
         pred_fake = self.netD.forward(torch.cat((lr_spectro, sr_result.float()), dim=1), needs_wgrad=False)
         loss_G_GAN = self.criterionGAN(pred_fake, True)
 
+        # time-domain GAN on frames (:375-387)
+        loss_G_GAN_time = loss_D_real_time = loss_D_fake_time = 0
+        sr_coef = self._decode_with_grad(sr_result, lr_norm_param) if self.use_frames else None
+        if opt.use_time_D:
+            # sqrt(up_ratio-1) * window * to_frames(sr): the window rides in the synthesis kernel
+            sr_frames = self._frames_from_coef(sr_coef, self._frame_plans()[1]).unsqueeze(1)
+            lr_frames = lr_norm_param['frames'].unsqueeze(1)
+            hr_frames = hr_norm_param['frames'].unsqueeze(1)
+            pred_fake_frames = self.discriminate_time_D(lr_frames, sr_frames)
+            loss_D_fake_time = self.criterionGAN(pred_fake_frames, False) * opt.lambda_time
+            pred_real_frames = self.discriminate_time_D(lr_frames, hr_frames)
+            loss_D_real_time = self.criterionGAN(pred_real_frames, True) * opt.lambda_time
+            # the generator's pass (:386 feeds the frames themselves, without the dB map): gradients reach G through
+            # time_D's activations only; its weight gradients are discarded upstream (train.py:164-176)
+            _pred_fake_frames = self.time_D.forward(torch.cat((lr_frames, sr_frames), dim=1), needs_wgrad=False)
+            loss_G_GAN_time = self.criterionGAN(_pred_fake_frames, True) * opt.lambda_time
+
         loss_G_GAN_Feat = 0
         if not opt.no_ganFeat_loss:
             loss_G_GAN_Feat = networks.feature_matching_loss(pred_fake, pred_real, opt.num_D, opt.n_layers_D, opt.lambda_feat)
+
+        # frame-match loss (:408-415): adjacent frames must agree on their overlap
+        loss_G_match = 0
+        if opt.explicit_encoding and opt.use_match_loss:
+            raw_frames = self._frames_from_coef(sr_coef, self._frame_plans()[0])
+            loss_G_match = ops.FrameMatchFn.apply(raw_frames, self._mdct.window.to(raw_frames.device, torch.float32),
+                                                  float(opt.lambda_mat))
 
         if infer:   # the visualiser's host copies (:418-432) -- only when the caller asked for the image
             self.current_lable = lr_spectro.detach()[0].float().mean(0).cpu().numpy() if opt.explicit_encoding else lr_spectro.detach().cpu().numpy()[0, 0]
             self.current_generated = sr_result.detach()[0].float().mean(0).cpu().numpy() if opt.explicit_encoding else sr_result.detach().float().cpu().numpy()[0, 0]
             self.current_real = hr_spectro.detach()[0].float().mean(0).cpu().numpy() if opt.explicit_encoding else hr_spectro.detach().cpu().numpy()[0, 0]
-        return [self.loss_filter(loss_G_GAN, loss_G_GAN_Feat, 0, 0, 0, 0, 0, loss_D_real, loss_D_fake),
+        return [self.loss_filter(loss_G_GAN, loss_G_GAN_Feat, 0, loss_G_match, loss_G_GAN_time, loss_D_real_time,
+                                 loss_D_fake_time, loss_D_real, loss_D_fake),
                 None if not infer else sr_result]
 
     def inference(self, lr_audio, inst):
@@ -254,6 +337,8 @@ class Pix2PixHDModel(BaseModel):
     def save(self, which_epoch):
         self.save_network(self.netG, 'G', which_epoch, self.gpu_ids)
         self.save_network(self.netD, 'D', which_epoch, self.gpu_ids)
+        if getattr(self.opt, 'use_time_D', False):
+            self.save_network(self.time_D, 'time_D', which_epoch, self.gpu_ids)
 
     def update_fixed_params(self):
         """after niter_fix_global epochs also train the global generator (:521-531)"""

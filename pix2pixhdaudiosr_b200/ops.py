@@ -1094,6 +1094,99 @@ class L1Fn(torch.autograd.Function):
         return da, None, None
 
 
+class FramesDbFn(torch.autograd.Function):
+    """dB(|gain * window * frames|) = amplitude_to_DB(|.|, 20, min_value, 1) of discriminate_time_D
+    (pix2pixHD_model.py:317-318) fused with the sqrt(up_ratio-1) * window scaling of :375; frames [..., N] fp32."""
+
+    @staticmethod
+    def forward(ctx, frames, window, gain, min_value):
+        _need_cuda(frames, window)
+        frames = frames.to(torch.float32).contiguous()
+        out = torch.empty_like(frames)
+        N = frames.shape[-1]
+        _lib.check(_lib.lib().p2p_frames_db_fwd(_p(frames), _p(window), gain, _p(out), frames.numel() // N, N, min_value, _stream()))
+        ctx.save_for_backward(frames, window)
+        ctx.cfg = (gain, min_value)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        frames, window = ctx.saved_tensors
+        gain, min_value = ctx.cfg
+        dout = dout.to(torch.float32).contiguous()
+        dframes = torch.empty_like(frames)
+        N = frames.shape[-1]
+        _lib.check(_lib.lib().p2p_frames_db_bwd(_p(frames), _p(window), gain, _p(dout), _p(dframes), frames.numel() // N, N,
+                                                min_value, _stream()))
+        return dframes, None, None, None
+
+
+class FrameMatchFn(torch.autograd.Function):
+    """weight * MSE(frames[:, :-1, half:] * w[:half], frames[:, 1:, :half] * w[half:]) (pix2pixHD_model.py:408-415)."""
+
+    @staticmethod
+    def forward(ctx, frames, window, weight):
+        _need_cuda(frames, window)
+        frames = frames.to(torch.float32).contiguous()
+        B, F, N = frames.shape
+        loss = torch.zeros((), dtype=torch.float32, device=frames.device)
+        _lib.check(_lib.lib().p2p_frame_match(_p(frames), _p(window), weight, _p(loss), None, 0.0, None, B, F, N, _stream()))
+        ctx.save_for_backward(frames, window)
+        ctx.weight = weight
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        frames, window = ctx.saved_tensors
+        B, F, N = frames.shape
+        dframes = torch.empty_like(frames)
+        g = g.to(torch.float32).contiguous()
+        _lib.check(_lib.lib().p2p_frame_match(_p(frames), _p(window), ctx.weight, None, _p(dframes), 1.0, _p(g), B, F, N, _stream()))
+        return dframes, None, None
+
+
+class SpectroDecodeFn(torch.autograd.Function):
+    """denormalize + explicit +/- decode + permute(0,2,1) (pix2pixHD_model.py:229-237, 246-248) with a gradient:
+    x [B,2,M,F] image (any strides, fp32 or bf16) -> coefficients [B,F,M] fp32.  The gradient comes back as a
+    channels-last buffer behind an NCHW shape, in x's dtype."""
+
+    @staticmethod
+    def forward(ctx, x, norm, alpha, min_value, gain):
+        _need_cuda(x, norm)
+        B, C, M, F = x.shape
+        assert C == 2, "the differentiable decode is the explicit-encoding branch"
+        coef = torch.empty((B, F, M), dtype=torch.float32, device=x.device)
+        sb, sc, sh, sw = x.stride()
+        _lib.check(_lib.lib().p2p_spectro_decode(_p(x), sb, sc, sh, sw, _p(norm), None, _p(coef), B, C, F, M, alpha, min_value,
+                                                 gain, _DT[x.dtype], _stream()))
+        ctx.save_for_backward(x, norm)
+        ctx.cfg = (alpha, gain)
+        return coef
+
+    @staticmethod
+    def backward(ctx, dcoef):
+        x, norm = ctx.saved_tensors
+        alpha, gain = ctx.cfg
+        B, C, M, F = x.shape
+        dcoef = dcoef.to(torch.float32).contiguous()
+        dx = torch.empty((B, M, F, 2), dtype=torch.float32, device=x.device)
+        sb, sc, sh, sw = x.stride()
+        _lib.check(_lib.lib().p2p_spectro_decode_bwd(_p(x), sb, sc, sh, sw, _p(norm), _p(dcoef), _p(dx), B, F, M, alpha, gain,
+                                                     _DT[x.dtype], _stream()))
+        return dx.permute(0, 3, 1, 2).to(x.dtype), None, None, None, None
+
+
+def frame_window(audio, window, n_frames, hop, offset):
+    """windowed frames [B, F, win] of a zero-padded signal (models/mdct.py:497-503)"""
+    _need_cuda(audio, window)
+    audio = audio.to(torch.float32).contiguous()
+    B, T = audio.shape
+    win = window.numel()
+    frames = torch.empty((B, n_frames, win), dtype=torch.float32, device=audio.device)
+    _lib.check(_lib.lib().p2p_frame_window(_p(audio), _p(window), _p(frames), B, T, n_frames, hop, win, offset, _stream()))
+    return frames
+
+
 def adam_step(w, g, m, v, w16, lr, beta1, beta2, eps, step):
     _need_cuda(w, g, m, v)
     assert w.is_contiguous() and g.is_contiguous() and w.dtype == torch.float32 and g.dtype == torch.float32
