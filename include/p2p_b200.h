@@ -270,6 +270,23 @@ int p2p_spectro_decode_bwd(const void* x, long long sb, long long sc, long long 
                            const float* dcoef, float* dx, int B, int F, int M, float alpha, float gain, int dtype,
                            void* stream);
 
+/* ---- MDCT2 / IMDCT2: the DCT-II lapped transform (models/mdct.py:352-454 with dct/dct_native.py:7-67) -------------
+ *   DCT_2N_native(u)[k]  = (2/N) sum_n u[n] cos(pi (2n+1) k / (2N));   IDCT_2N_native(X)[n] = X[0] + 2 sum_{k>=1} X[k] cos(.)
+ * p2p_mdct2_analysis:  spec[b,f,k] = scale * c0_k * DCT_2N(window * x_pad[b, f*hop : f*hop+win], zero-extended to n_fft)[k]
+ * p2p_mdct2_synthesis: out[b, s - crop_left] = scale * sum_f window[n] * (2 sum_k c0_k spec[b,f,k] cos(pi (2n+1) k / (2 n_fft))),
+ *                      n = s - f*hop in [0, win), s in [crop_left, crop_left + T_out)
+ * with c0_0 = c0 and c0_k = 1 for k > 0.  MDCT2.forward = analysis(scale 1, c0 1); IMDCT2.forward = synthesis(scale 1/2,
+ * c0 1/2); their autograd adjoints are synthesis(1/n_fft, 1) and analysis(n_fft/2, 1/2).  x_pad is x shifted right by
+ * `offset` zeros and zero-extended.  x [B,T], spec [B,F,n_fft], window [win], all fp32 device pointers; tables: device
+ * copy of p2p_mdct2_fill_tables(n_fft) (p2p_mdct2_table_words(n_fft) 4-byte words, computed in double on the host).
+ * n_fft: power of two in [4, 4096]; 1 <= hop <= win <= n_fft. */
+int p2p_mdct2_table_words(int n_fft);
+int p2p_mdct2_fill_tables(int n_fft, void* host_tables);
+int p2p_mdct2_analysis(const float* x, float* spec, const float* window, const void* tables, int B, int64_t T, int F,
+                       int n_fft, int hop, int win, int64_t offset, float scale, float c0, void* stream);
+int p2p_mdct2_synthesis(const float* spec, float* out, const float* window, const void* tables, int B, int F, int64_t T_out,
+                        int n_fft, int hop, int win, int64_t crop_left, float scale, float c0, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -73,6 +73,10 @@ _SIGS.update({
     "p2p_spectro_encode": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _vp]),
     "p2p_spectro_normalize": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_spectro_decode": (_i, [_vp, _ll, _ll, _ll, _ll, _vp, _vp, _vp, _i, _i, _i, _i, _f, _f, _f, _i, _vp]),
+    "p2p_mdct2_table_words": (_i, [_i]),
+    "p2p_mdct2_fill_tables": (_i, [_i, _vp]),
+    "p2p_mdct2_analysis": (_i, [_vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _i, _ll, _f, _f, _vp]),
+    "p2p_mdct2_synthesis": (_i, [_vp, _vp, _vp, _vp, _i, _i, _ll, _i, _i, _i, _ll, _f, _f, _vp]),
     "p2p_frame_window": (_i, [_vp, _vp, _vp, _i, _ll, _i, _i, _i, _ll, _vp]),
     "p2p_frames_db_fwd": (_i, [_vp, _vp, _f, _vp, _ll, _i, _f, _vp]),
     "p2p_frames_db_bwd": (_i, [_vp, _vp, _f, _vp, _vp, _ll, _i, _f, _vp]),

@@ -1,0 +1,253 @@
+// MDCT2 / IMDCT2 (the DCT-II lapped transform the shipped Pix2PixHDModel wires) as two fused kernels.
+//
+// Replaces models/mdct.py:377-398 (MDCT2.forward: pad, frame, window, zero-extend, DCT_2N_native) and :432-454
+// (IMDCT2.forward: IDCT_2N_native / 2, window, fold, crop) plus dct/dct_native.py:7-67.  What the reference computes
+// (verified numerically against it, tests/golden/make_golden_mdct2.py):
+//     DCT_2N_native(u)[k]  = (2/N) sum_n u[n] cos(pi (2n+1) k / (2N))
+//     IDCT_2N_native(X)[n] = X[0] + 2 sum_{k>=1} X[k] cos(pi (2n+1) k / (2N))        (so IDCT(DCT(u)) = 2u)
+// with a 2N-point rfft / irfft of a zero-extended row.  Here (Makhoul): one N-point complex FFT in shared memory on the
+// even/odd-reordered row v[n] = u[2n], v[N-1-n] = u[2n+1]:  sum_n u[n] cos(pi (2n+1) k / (2N)) = Re(e^{-j pi k/(2N)} FFT_N(v)[k]);
+// the inverse runs the same forward FFT on c_k X[k] e^{-j pi k/(2N)} and keeps the real part.  Both directions take
+// (scale, c0): c0 multiplies bin 0, which makes each kernel the other's adjoint (autograd) as well:
+//     analysis(scale, c0):  X[k] = scale * c0_k * (2/N) * sum_n w[n] x[f hop + n] cos(.)
+//     synthesis(scale, c0): out  = scale * crop(OLA_hop(w[n] * 2 sum_k c0_k X[k] cos(.)))     c0_0 = c0, c0_k = 1 (k > 0)
+//   MDCT2 = analysis(1, 1); IMDCT2 = synthesis(1/2, 1/2); d MDCT2 / dx = synthesis(1/N, 1); d IMDCT2 / dX = analysis(N/2, 1/2).
+// Layout: signal [B,T] fp32, coefficients [B,F,N] fp32 (bins fastest).  Bound: HBM (4 B in + 8 B out per sample at
+// hop = N/2); the shared-memory complex FFT of a real row does twice the necessary butterflies (next: two frames per
+// complex FFT / the register FFT of mdct4_fast.cuh).
+#include "common.cuh"
+#include "smem_fft.cuh"
+#include <cmath>
+#include <cstdint>
+
+namespace p2p {
+namespace {
+
+using smemfft::kThreads;
+using smemfft::cmul;
+using smemfft::fft_rows_inplace;
+
+struct Tables2 {          // 5N words: tw[N] complex | roots[N] complex | perm[N] int
+    const float2* tw;     // e^{-j pi k / (2N)}
+    const float2* roots;  // e^{-2 pi j m / N}
+    const int* perm;      // position p after the in-place DIF passes holds FFT bin perm[p]
+};
+
+__device__ __forceinline__ Tables2 make_tables2(const void* t, int N) {
+    const float* f = reinterpret_cast<const float*>(t);
+    Tables2 r;
+    r.tw = reinterpret_cast<const float2*>(f);
+    r.roots = reinterpret_cast<const float2*>(f + 2 * N);
+    r.perm = reinterpret_cast<const int*>(f + 4 * N);
+    return r;
+}
+
+// grid (ceil(F/fpb), B).  smem: sig[(fpb-1)*hop+win] | win_s[win] | z[fpb*N] (float2) | o[fpb*N]
+__global__ void __launch_bounds__(kThreads)
+mdct2_analysis_kernel(const float* __restrict__ x, float* __restrict__ spec, const float* __restrict__ window,
+                      const void* __restrict__ tables, long long T, int F, int N, int hop, int win, long long offset,
+                      float scale, float c0, int fpb) {
+    extern __shared__ __align__(16) float smem[];
+    const int f0 = blockIdx.x * fpb;
+    const int nfr = min(fpb, F - f0);
+    const int span = (nfr - 1) * hop + win;
+    const int span_max = (fpb - 1) * hop + win;
+    float* sig = smem;
+    float* win_s = sig + ((span_max + 3) & ~3);
+    float2* z = reinterpret_cast<float2*>(win_s + ((win + 3) & ~3));
+    float* o = reinterpret_cast<float*>(z + fpb * N);
+    const Tables2 tb = make_tables2(tables, N);
+
+    const float* xb = x + (long long)blockIdx.y * T;
+    const long long t0 = (long long)f0 * hop - offset;
+    for (int i = threadIdx.x; i < span; i += kThreads) {
+        const long long t = t0 + i;
+        sig[i] = (t >= 0 && t < T) ? __ldg(xb + t) : 0.f;
+    }
+    for (int i = threadIdx.x; i < win; i += kThreads) win_s[i] = __ldg(window + i);
+    __syncthreads();
+
+    // v[p] = u[2p] (p < N/2), u[2(N-1-p)+1] otherwise; u = window * frame, zero beyond win
+    const int hN = N >> 1;
+    for (int w = threadIdx.x; w < nfr * N; w += kThreads) {
+        const int fl = w / N;
+        const int p = w - fl * N;
+        const int i = p < hN ? 2 * p : 2 * (N - 1 - p) + 1;
+        const float* s = sig + fl * hop;
+        z[w] = make_float2(i < win ? s[i] * win_s[i] : 0.f, 0.f);
+    }
+    __syncthreads();
+
+    fft_rows_inplace(z, nfr, N, tb.roots);
+
+    const float sc = scale * 2.f / (float)N;
+    for (int w = threadIdx.x; w < nfr * N; w += kThreads) {
+        const int fl = w / N;
+        const int p = w - fl * N;
+        const int k = tb.perm[p];
+        const float2 t = tb.tw[k];
+        const float2 v = z[w];
+        o[fl * N + k] = (k == 0 ? sc * c0 : sc) * (v.x * t.x - v.y * t.y);
+    }
+    __syncthreads();
+
+    float* dst = spec + ((long long)blockIdx.y * F + f0) * N;
+    const int total = nfr * N;
+    if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+        const float4* o4 = reinterpret_cast<const float4*>(o);
+        float4* d4 = reinterpret_cast<float4*>(dst);
+        for (int i = threadIdx.x; i < (total >> 2); i += kThreads) d4[i] = o4[i];
+    } else {
+        for (int i = threadIdx.x; i < total; i += kThreads) dst[i] = o[i];
+    }
+}
+
+// grid (ceil(T_out/chunk), B).  Each CTA owns `chunk` output samples and transforms every frame that overlaps them, so
+// the overlap-add is a deterministic gather (no atomics, each sample written once).
+// smem: win_s[win] | z[nfmax*N] (float2) | t[nfmax*N]
+__global__ void __launch_bounds__(kThreads)
+mdct2_synthesis_kernel(const float* __restrict__ spec, float* __restrict__ out, const float* __restrict__ window,
+                       const void* __restrict__ tables, int F, long long T_out, int N, int hop, int win,
+                       long long crop_left, float scale, float c0, int chunk, int nfmax) {
+    extern __shared__ __align__(16) float smem[];
+    float* win_s = smem;
+    float2* z = reinterpret_cast<float2*>(win_s + ((win + 3) & ~3));
+    float* t = reinterpret_cast<float*>(z + nfmax * N);
+    const Tables2 tb = make_tables2(tables, N);
+
+    const long long s_lo = (long long)blockIdx.x * chunk + crop_left;            // OLA coordinates
+    const long long s_hi = min((long long)(blockIdx.x + 1) * chunk, T_out) + crop_left;  // exclusive
+    long long fl_ = (s_lo - win + 1 + hop - 1);
+    fl_ = fl_ > 0 ? fl_ / hop : 0;                                               // ceil, clamped at 0
+    const int f_lo = (int)min(fl_, (long long)F);
+    const int f_hi = (int)min((s_hi - 1) / hop, (long long)F - 1);              // inclusive
+    const int nfr = max(0, f_hi - f_lo + 1);
+
+    for (int i = threadIdx.x; i < win; i += kThreads) win_s[i] = __ldg(window + i);
+    const float* src = spec + ((long long)blockIdx.y * F + f_lo) * N;
+    for (int w = threadIdx.x; w < nfr * N; w += kThreads) {
+        const int k = w % N;
+        const float2 tw = tb.tw[k];
+        const float xv = __ldg(src + w) * (k == 0 ? c0 : 1.f);
+        z[w] = make_float2(xv * tw.x, xv * tw.y);
+    }
+    __syncthreads();
+
+    fft_rows_inplace(z, nfr, N, tb.roots);
+
+    // v[n] = Re Z[n]; y[2n] = 2 v[n] (n < N/2), y[2(N-1-n)+1] = 2 v[n] otherwise
+    const int hN = N >> 1;
+    for (int w = threadIdx.x; w < nfr * N; w += kThreads) {
+        const int fl = w / N;
+        const int p = w - fl * N;
+        const int n = tb.perm[p];
+        const int i = n < hN ? 2 * n : 2 * (N - 1 - n) + 1;
+        t[fl * N + i] = 2.f * z[w].x;
+    }
+    __syncthreads();
+
+    float* ob = out + (long long)blockIdx.y * T_out;
+    const int n_out = (int)(s_hi - s_lo);
+    for (int i = threadIdx.x; i < n_out; i += kThreads) {
+        const long long s = s_lo + i;
+        long long a = s - win + 1 + hop - 1;                                     // frames with 0 <= s - f*hop < win
+        int fa = (int)(a > 0 ? a / hop : 0);
+        fa = max(fa, f_lo);
+        const int fb = (int)min(s / hop, (long long)f_hi);
+        float acc = 0.f;
+        for (int f = fa; f <= fb; ++f) {
+            const int n = (int)(s - (long long)f * hop);
+            acc += win_s[n] * t[(f - f_lo) * N + n];
+        }
+        ob[s - crop_left] = scale * acc;
+    }
+}
+
+constexpr int kMaxSmem2 = 227 * 1024;
+
+int check_geometry2(int n_fft, int hop, int win) {
+    if (!is_pow2(n_fft) || n_fft < 4 || n_fft > 4096)
+        return fail(P2P_ENOTSUP, "n_fft must be a power of two in [4, 4096], got %d", n_fft);
+    if (win < 1 || win > n_fft) return fail(P2P_EINVAL, "win_length %d must be in [1, n_fft=%d]", win, n_fft);
+    if (hop < 1 || hop > win) return fail(P2P_EINVAL, "hop_length %d must be in [1, win_length=%d]", hop, win);
+    return P2P_OK;
+}
+
+template <typename K>
+int ensure_smem2(K kernel, size_t bytes) {
+    if (bytes > (size_t)kMaxSmem2) return fail(P2P_ENOTSUP, "needs %zu B of shared memory", bytes);
+    if (bytes > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        if (e != cudaSuccess) return fail(P2P_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    }
+    return P2P_OK;
+}
+
+}  // namespace
+}  // namespace p2p
+
+extern "C" int p2p_mdct2_table_words(int n_fft) {
+    if (!p2p::is_pow2(n_fft) || n_fft < 4 || n_fft > 4096)
+        return p2p::fail(P2P_ENOTSUP, "n_fft must be a power of two in [4, 4096], got %d", n_fft);
+    return 5 * n_fft;
+}
+
+extern "C" int p2p_mdct2_fill_tables(int n_fft, void* host_tables) {
+    const int words = p2p_mdct2_table_words(n_fft);
+    if (words < 0) return words;
+    if (!host_tables) return p2p::fail(P2P_EINVAL, "host_tables is null");
+    const int N = n_fft;
+    float* f = static_cast<float*>(host_tables);
+    int* perm = reinterpret_cast<int*>(f + 4 * N);
+    const double pi = 3.14159265358979323846264338327950288;
+    for (int k = 0; k < N; ++k) {
+        const double a = -pi * k / (2.0 * N), c = -2.0 * pi * k / N;
+        f[2 * k] = (float)cos(a);           f[2 * k + 1] = (float)sin(a);
+        f[2 * N + 2 * k] = (float)cos(c);   f[2 * N + 2 * k + 1] = (float)sin(c);
+        perm[k] = p2p::smemfft::dif_position_to_bin(k, N);
+    }
+    return P2P_OK;
+}
+
+extern "C" int p2p_mdct2_analysis(const float* x, float* spec, const float* window, const void* tables, int B, int64_t T,
+                                  int F, int n_fft, int hop, int win, int64_t offset, float scale, float c0, void* stream) {
+    using namespace p2p;
+    if (int rc = check_geometry2(n_fft, hop, win)) return rc;
+    if (B < 0 || T < 0 || F < 0) return fail(P2P_EINVAL, "negative size B=%d T=%lld F=%d", B, (long long)T, F);
+    if (B == 0 || F == 0) return P2P_OK;
+    if (!spec || !window || !tables || (!x && T > 0)) return fail(P2P_EINVAL, "null pointer argument");
+    if (B > 65535) return fail(P2P_ENOTSUP, "B=%d exceeds 65535 rows per launch", B);
+    int fpb = 4096 / n_fft; if (fpb < 1) fpb = 1; if (fpb > 32) fpb = 32; if (fpb > F) fpb = F;
+    const int span_max = (fpb - 1) * hop + win;
+    const size_t smem = 4ull * (((span_max + 3) & ~3) + ((win + 3) & ~3) + 2 * fpb * n_fft + fpb * n_fft);
+    if (int rc = ensure_smem2(mdct2_analysis_kernel, smem)) return rc;
+    dim3 grid((F + fpb - 1) / fpb, B);
+    mdct2_analysis_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(x, spec, window, tables, (long long)T, F, n_fft, hop,
+                                                                         win, (long long)offset, scale, c0, fpb);
+    return check_launch("mdct2_analysis_kernel");
+}
+
+extern "C" int p2p_mdct2_synthesis(const float* spec, float* out, const float* window, const void* tables, int B, int F,
+                                   int64_t T_out, int n_fft, int hop, int win, int64_t crop_left, float scale, float c0,
+                                   void* stream) {
+    using namespace p2p;
+    if (int rc = check_geometry2(n_fft, hop, win)) return rc;
+    if (B < 0 || T_out < 0 || F < 0 || crop_left < 0)
+        return fail(P2P_EINVAL, "negative size B=%d T_out=%lld F=%d crop_left=%lld", B, (long long)T_out, F, (long long)crop_left);
+    if (B == 0 || T_out == 0) return P2P_OK;
+    if (!out || !window || !tables || (!spec && F > 0)) return fail(P2P_EINVAL, "null pointer argument");
+    if (B > 65535) return fail(P2P_ENOTSUP, "B=%d exceeds 65535 rows per launch", B);
+    const int overlap = (win + hop - 1) / hop;            // frames covering one sample
+    int nf_target = 4096 / n_fft; if (nf_target < 2) nf_target = 2;
+    int hpb = nf_target - overlap; if (hpb < 1) hpb = 1;
+    const int chunk = hpb * hop;
+    int nfmax = (chunk + win - 2) / hop + 1; if (nfmax > F) nfmax = F; if (nfmax < 1) nfmax = 1;
+    const size_t smem = 4ull * (((win + 3) & ~3) + 2 * nfmax * n_fft + nfmax * n_fft);
+    if (int rc = ensure_smem2(mdct2_synthesis_kernel, smem)) return rc;
+    const long long nchunks = (T_out + chunk - 1) / chunk;
+    if (nchunks > 2147483647LL) return fail(P2P_ENOTSUP, "T_out too large");
+    dim3 grid((unsigned)nchunks, B);
+    mdct2_synthesis_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(spec, out, window, tables, F, (long long)T_out, n_fft,
+                                                                          hop, win, (long long)crop_left, scale, c0, chunk, nfmax);
+    return check_launch("mdct2_synthesis_kernel");
+}

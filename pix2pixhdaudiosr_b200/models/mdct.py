@@ -206,3 +206,130 @@ class IMDCT4(nn.Module):
         crop_left, t_out = self.out_geometry(spec.shape[1])
         out = _SynthesisFn.apply(spec, self._plan, t_out, crop_left, 4.0 / self.n_fft)
         return out.reshape(spec.shape[0], 1, 1, t_out)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# MDCT2 / IMDCT2 (reference: models/mdct.py:352-454 with dct/dct_native.py:7-67) on csrc/mdct2.cu
+# ----------------------------------------------------------------------------------------------------------------
+class _Plan2(_Plan):
+    """geometry + device-resident window and DCT-II tables (p2p_mdct2_fill_tables)"""
+
+    def on(self, device):
+        key = (device.type, device.index)
+        if key not in self._dev:
+            lib = _lib.lib()
+            words = lib.p2p_mdct2_table_words(self.n_fft)
+            if words < 0:
+                _lib.check(words)
+            host = torch.empty(words, dtype=torch.int32)
+            _lib.check(lib.p2p_mdct2_fill_tables(self.n_fft, ctypes.c_void_p(host.data_ptr())))
+            self._dev[key] = (self.window_cpu.to(device), host.to(device))
+        return self._dev[key]
+
+
+def _analysis2(x, plan, n_frames, offset, scale, c0):
+    _require_cuda(x, "mdct2 analysis")
+    x = x.to(torch.float32).contiguous()
+    B, T = x.shape
+    window, tables = plan.on(x.device)
+    spec = torch.empty((B, n_frames, plan.n_fft), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().p2p_mdct2_analysis(
+            x.data_ptr(), spec.data_ptr(), window.data_ptr(), tables.data_ptr(), B, T, n_frames,
+            plan.n_fft, plan.hop, plan.win, offset, scale, c0, _stream()))
+    return spec
+
+
+def _synthesis2(spec, plan, t_out, crop_left, scale, c0):
+    _require_cuda(spec, "mdct2 synthesis")
+    spec = spec.to(torch.float32).contiguous()
+    B, n_frames, _ = spec.shape
+    window, tables = plan.on(spec.device)
+    out = torch.empty((B, t_out), dtype=torch.float32, device=spec.device)
+    with torch.cuda.device(spec.device):
+        _lib.check(_lib.lib().p2p_mdct2_synthesis(
+            spec.data_ptr(), out.data_ptr(), window.data_ptr(), tables.data_ptr(), B, n_frames, t_out,
+            plan.n_fft, plan.hop, plan.win, crop_left, scale, c0, _stream()))
+    return out
+
+
+class _Analysis2Fn(torch.autograd.Function):
+    """spec = scale * diag(c0) D W frame(x), D = DCT_2N; adjoint = synthesis(scale / n_fft, 2 c0 ... ) -- see csrc/mdct2.cu:
+    the synthesis kernel computes 2 sum_k c0_k X[k] cos(.), so D^T diag(c0) g = (1/n_fft) * synthesis-sum with the same c0."""
+
+    @staticmethod
+    def forward(ctx, x, plan, n_frames, offset, scale, c0):
+        ctx.plan, ctx.offset, ctx.scale, ctx.c0, ctx.T = plan, offset, scale, c0, x.shape[-1]
+        return _analysis2(x, plan, n_frames, offset, scale, c0)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _Synthesis2Fn.apply(g, ctx.plan, ctx.T, ctx.offset, ctx.scale / ctx.plan.n_fft, ctx.c0), None, None, None, None, None
+
+
+class _Synthesis2Fn(torch.autograd.Function):
+    """out = scale * crop(OLA(W E diag(c0) spec)), E[n,k] = 2 cos(.); adjoint = analysis(scale * n_fft, c0)
+    (E^T u = n_fft * DCT_2N(u))."""
+
+    @staticmethod
+    def forward(ctx, spec, plan, t_out, crop_left, scale, c0):
+        ctx.plan, ctx.crop_left, ctx.scale, ctx.c0, ctx.F = plan, crop_left, scale, c0, spec.shape[1]
+        return _synthesis2(spec, plan, t_out, crop_left, scale, c0)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _Analysis2Fn.apply(g, ctx.plan, ctx.F, ctx.crop_left, ctx.scale * ctx.plan.n_fft, ctx.c0), None, None, None, None, None
+
+
+class MDCT2(MDCT4):
+    """models/mdct.py:352-398.  `dct_op` is accepted for signature compatibility (the reference asserts it is callable);
+    the transform itself is always DCT_2N_native's (dct/dct_native.py:7-33), fused with framing and windowing.
+    forward(signal, return_ola=False) -> [B, F, n_fft] (and the windowed frames [B, F, win] when return_ola)."""
+
+    def __init__(self, n_fft=2048, hop_length=None, win_length=None, window=None, center=True, pad_mode='constant',
+                 device='cuda', dct_op=None) -> None:
+        super().__init__(n_fft, hop_length, win_length, window, center, pad_mode, device)
+        assert dct_op is None or callable(dct_op)
+        self.dct = dct_op
+        self._plan = _Plan2(self.n_fft, self.hop_length, self.win_length, self.window)
+
+    def forward(self, signal, return_ola=False):
+        start_pad, end_pad = self.pads(int(len(signal)))
+        lead, T = signal.shape[:-1], signal.shape[-1]
+        x = signal.to(self.device, torch.float32).reshape(-1, T)
+        if self.pad_mode != 'constant':
+            x = F_.pad(x, (start_pad, end_pad), mode=self.pad_mode)
+            offset = 0
+        else:
+            offset = start_pad
+        padded = T + start_pad + end_pad
+        if padded < self.win_length:
+            raise RuntimeError('maximum size for tensor at dimension %d is %d but size is %d'
+                               % (signal.dim() - 1, padded, self.win_length))
+        n_frames = (padded - self.win_length) // self.hop_length + 1
+        spec = _Analysis2Fn.apply(x, self._plan, n_frames, offset, 1.0, 1.0).reshape(*lead, n_frames, self.n_fft)
+        if not return_ola:
+            return spec
+        from .. import ops
+        window, _ = self._plan.on(x.device)
+        frames = ops.frame_window(x.detach(), window, n_frames, self.hop_length, offset)
+        return spec, frames.reshape(*lead, n_frames, self.win_length)
+
+
+class IMDCT2(IMDCT4):
+    """models/mdct.py:401-454: IDCT_2N_native(X) / 2 -> window -> overlap-add -> crop; result [B,1,1,T]."""
+
+    def __init__(self, n_fft=2048, hop_length=None, win_length=None, window=None, center=True, pad_mode='constant',
+                 out_length=None, device='cuda', idct_op=None) -> None:
+        super().__init__(n_fft, hop_length, win_length, window, center, pad_mode, out_length, device)
+        assert idct_op is None or callable(idct_op)
+        self.idct = idct_op
+        self._plan = _Plan2(self.n_fft, self.hop_length, self.win_length, self.window)
+
+    def forward(self, signal):
+        assert signal.dim() == 3, 'Only tensors shaped in BHW are supported, got tensor of shape %s' % (str(signal.size()))
+        assert signal.size()[-1] == self.n_fft, 'The last dim of input tensor should match the n_fft. Expected %d ,got %d' % (self.n_fft, signal.size()[-1])
+        spec = signal.to(self.device, torch.float32)
+        crop_left, t_out = self.out_geometry(spec.shape[1])
+        out = _Synthesis2Fn.apply(spec, self._plan, t_out, crop_left, 0.5, 0.5)
+        return out.reshape(spec.shape[0], 1, 1, t_out)
