@@ -36,6 +36,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="train", choices=["train", "train_time", "mdct"])
+    ap.add_argument("--transform", default="mdct4", choices=["mdct4", "mdct2"],
+                    help="train workloads: the lapped transform in front of the networks (mdct2 = the shipped wiring)")
     ap.add_argument("--batch", type=int, default=None, help="segments per GPU per step (train: 8, mdct: 512)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -9,10 +9,10 @@ WORKLOAD = ("G3L2 ngf48 LocalEnhancer + 2-scale D (ndf 64), GAN + feature matchi
             "(train.py:148-184), batch %d x 65024-sample 48 kHz segments per GPU -> [%d,2,512,128] MDCT4 spectrograms")
 
 
-def synth_audio(B, seed):
+def synth_audio(B, seed, T=None):
     import torch
     g = torch.Generator().manual_seed(seed)
-    hr = 0.1 * torch.randn(B, T_SEG, generator=g)
+    hr = 0.1 * torch.randn(B, T or T_SEG, generator=g)
     lr = 0.5 * (hr + torch.roll(hr, 1, dims=1))             # a crude low-pass stands in for the 8 kHz resample
     return lr, hr
 
@@ -120,12 +120,18 @@ def run_train(args):
     with contextlib.redirect_stdout(io.StringIO()):
         # --workload train_time: BASELINE.json configs[3] (train_script.sh:93, 96: --use_time_D --lambda_time 10 --use_match_loss)
         extra = dict(use_time_D=True, use_match_loss=True, lambda_time=10.0) if args.workload == "train_time" else {}
+        t_seg = T_SEG
+        if getattr(args, "transform", "mdct4") == "mdct2":
+            # the recipe exactly as generated/GEN_VCTK_G3L2_48ngf/opt.txt wires it: MDCT2 n_fft 512 / hop 256 on 32 512-sample
+            # segments -> the same [B,2,512,128] image
+            t_seg = 127 * 256
+            extra.update(transform="mdct2", n_fft=512, hop_length=256, win_length=512, segment_length=t_seg)
         model = create_model(options.g3l2_opt(gpu_ids=[local], batchSize=B, precision=args.precision, **extra))
     broadcast_parameters(model)
     sync = GradSync()
     if os.environ.get("P2P_EARLY_SYNC", "0") == "1":      # measured slower at 8 GPUs (12.7 vs 12.1 ms/step): off by default
         sync.attach_early(model.optimizer_G)
-    lr_host, hr_host = synth_audio(B, 1000 + rank)
+    lr_host, hr_host = synth_audio(B, 1000 + rank, t_seg)
     lr_host, hr_host = lr_host.pin_memory(), hr_host.pin_memory()
     lr_d, hr_d = lr_host.to(dev), hr_host.to(dev)
 
@@ -215,6 +221,7 @@ def run_train(args):
             "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
             "config": {"workload": WORKLOAD % (B, B) + ("; + time-domain D on [%d,2,128,1024] frames and frame-match loss "
                                                           "(--use_time_D --lambda_time 10 --use_match_loss)" % B if extra else ""),
+                       "transform": getattr(args, "transform", "mdct4") + (" (n_fft 512, hop 256, 32512-sample segments)" if t_seg != T_SEG else ""),
                        "global_batch": B * world, "parallelism": f"dp{world}",
                        "launch": "eager" if args.no_graph else "one CUDA graph replay per step",
                        "l2": "per-step working set (0.31 GB bf16 weights + 0.65 GB fp32 master + activations) exceeds the 126 MB L2; no flush",
@@ -235,7 +242,7 @@ def run_train(args):
                             "TFLOPs": round(v[1] / (v[2] * 1e-3) / 1e12, 1) if v[2] > 0 else None}
                         for k, v in sorted(classes.items())},
             "e2e": {"value": round(B * world * K / (e2e_ms * 1e-3), 2), "unit": "samples/s",
-                    "h2d_bytes_per_step": 2 * B * T_SEG * 4 * world, "d2h_bytes_per_step": 4 * len(names) * world,
+                    "h2d_bytes_per_step": 2 * B * t_seg * 4 * world, "d2h_bytes_per_step": 4 * len(names) * world,
                     "ms_per_step": round(e2e_ms / K, 3)},
             "gpu_launches": int(launches), "clocks": clk,
         }

@@ -25,6 +25,7 @@ import numpy as np
 import torch
 import torch.nn.functional as F
 
+from . import mdct2_oracle as M2
 from . import mdct4_oracle as M4
 
 
@@ -147,7 +148,10 @@ def to_spectro(audio, cfg, mask):
     """pix2pixHD_model.py:142-227 with the transform = MDCT4 (float64 numpy oracle, cast to float32 like MDCT2's
     output); mask_mode None (zeros) is the deterministic variant the fixtures use"""
     w = M4.kbdwin(cfg['win_length'])
-    spec = M4.mdct4_forward(audio.numpy(), w, cfg['n_fft'], cfg['hop_length'], True, signal_len=len(audio))
+    if cfg.get('transform', 'mdct4') == 'mdct2':        # the shipped wiring (pix2pixHD_model.py:37-38)
+        spec = M2.mdct2_forward(audio.numpy(), w, cfg['n_fft'], cfg['hop_length'], True, signal_len=len(audio))
+    else:
+        spec = M4.mdct4_forward(audio.numpy(), w, cfg['n_fft'], cfg['hop_length'], True, signal_len=len(audio))
     spectro = torch.from_numpy(spec.astype(np.float32)).unsqueeze(1).permute(0, 1, 3, 2)
     a, amin = cfg['alpha'], cfg['min_value']
     if cfg['explicit_encoding']:
@@ -176,7 +180,8 @@ def to_audio(log_spectro, norm, cfg):
     amp = 10.0 * torch.pow(10.0, 0.05 * s) - cfg['min_value']          # DB_to_amplitude(., 10, 0.5) - min_value
     spec = (amp[..., 0, :, :] - amp[..., 1, :, :]) / (2 * cfg['alpha'] - 1)
     w = M4.kbdwin(cfg['win_length'])
-    y = M4.imdct4_forward(spec.permute(0, 2, 1).double().numpy(), w, cfg['n_fft'], cfg['hop_length'], True)
+    inverse = M2.imdct2_forward if cfg.get('transform', 'mdct4') == 'mdct2' else M4.imdct4_forward
+    y = inverse(spec.permute(0, 2, 1).double().numpy(), w, cfg['n_fft'], cfg['hop_length'], True)
     return math.sqrt(cfg['up_ratio'] - 1) * torch.from_numpy(y.astype(np.float32)).reshape(spec.shape[0], 1, 1, -1)
 
 
@@ -206,6 +211,10 @@ def to_frames(log_spectro, norm, cfg):
     (4/n_fft) * this frame (mdct.py:560).  Differentiable torch restatement, float64 inside, float32 out."""
     N = cfg['n_fft']
     X = decode_coefficients(log_spectro, norm, cfg).double()
+    if cfg.get('transform', 'mdct4') == 'mdct2':        # `_idct` = IDCT_2N_native as shipped (dct_native.py:44-67)
+        n = torch.arange(N, dtype=torch.float64)
+        C = torch.cos(math.pi * (2 * n[None, :] + 1) * n[:, None] / (2 * N))       # [k, n]
+        return (2.0 * X @ C - X[..., :1]).float()
     exp1 = torch.exp(-1j * (math.pi / (2 * N) + math.pi / 4) * torch.arange(1, N, 2, dtype=torch.float64))
     exp2 = torch.exp(-1j * math.pi / (2 * N) * torch.arange(0, 2 * N, 2, dtype=torch.float64))
     y = torch.real(torch.fft.fft(exp1 * X, n=N) * exp2)

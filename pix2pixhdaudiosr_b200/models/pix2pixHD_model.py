@@ -4,7 +4,8 @@ losses, with the same `forward(lr_audio, inst, hr_audio, feat, infer)` / `infere
 loss order and `optimizer_G` / `optimizer_D` attributes, executed by the sm_100a kernels behind include/p2p_b200.h.
 
 Differences from the reference, all deliberate:
-* the transform is MDCT4/IMDCT4 (SURVEY H1; the shipped model wires MDCT2 -- README.md:133 invites MDCT4);
+* the transform is MDCT4/IMDCT4 by default (README.md:133 invites it); `opt.transform = 'mdct2'` selects what
+  the shipped model wires (MDCT2 / IMDCT2 / IDCT_2N_native, :35-40) -- then every line below is the reference's;
 * `opt.fp16` selects bf16 storage with fp32 accumulation / master weights instead of fp16 autocast + GradScaler;
 * the three per-step `.cpu().numpy()` copies of pix2pixHD_model.py:418-432 only happen when `infer` is set;
 * the generator's pass through D runs with detached D weights (the reference computes and discards those
@@ -25,7 +26,8 @@ from ..optim import FusedAdam
 from ..util.util import kbdwin
 from . import networks
 from .base_model import BaseModel
-from .mdct import IMDCT4, MDCT4, _Plan, _SynthesisFn
+from ..dct.dct_native import DCT_2N_native, IDCT_2N_native
+from .mdct import IMDCT2, IMDCT4, MDCT2, MDCT4, _Plan, _Plan2, _Synthesis2Fn, _SynthesisFn
 
 
 def _p(t):
@@ -59,8 +61,9 @@ class Pix2PixHDModel(BaseModel):
                                  '(pix2pixHD_model.py:251-258)')
             if opt.win_length != opt.n_fft:
                 raise NotImplementedError('use_time_D / use_match_loss: win_length must equal n_fft')
-        if getattr(opt, 'transform', 'mdct4') != 'mdct4':
-            raise NotImplementedError('transform %r: only MDCT4/IMDCT4 is built (MDCT2 is SURVEY §8f N1)' % opt.transform)
+        self.transform = getattr(opt, 'transform', 'mdct4')
+        if self.transform not in ('mdct4', 'mdct2'):
+            raise ValueError("transform %r: 'mdct4' (SURVEY H1) or 'mdct2' (what the shipped model wires, :35-40)" % self.transform)
         if not opt.no_vgg_loss and opt.isTrain:
             raise NotImplementedError('the VGG loss is deprecated for audio (README.md:18): pass no_vgg_loss=True')
         if opt.pool_size > 0:
@@ -72,10 +75,17 @@ class Pix2PixHDModel(BaseModel):
         # lapped transform (pix2pixHD_model.py:35-40)
         self.up_ratio = opt.hr_sampling_rate / opt.lr_sampling_rate
         self.window = kbdwin(opt.win_length)
-        self._mdct = MDCT4(n_fft=opt.n_fft, hop_length=opt.hop_length, win_length=opt.win_length, window=self.window,
-                           device=self.device)
-        self._imdct = IMDCT4(n_fft=opt.n_fft, hop_length=opt.hop_length, win_length=opt.win_length, window=self.window,
-                             device=self.device)
+        if self.transform == 'mdct2':       # :37-40 as shipped: DCT-II frames of n_fft bins
+            self._dct, self._idct = DCT_2N_native(), IDCT_2N_native()
+            self._mdct = MDCT2(n_fft=opt.n_fft, hop_length=opt.hop_length, win_length=opt.win_length, window=self.window,
+                               device=self.device, dct_op=self._dct)
+            self._imdct = IMDCT2(n_fft=opt.n_fft, hop_length=opt.hop_length, win_length=opt.win_length, window=self.window,
+                                 device=self.device, idct_op=self._idct)
+        else:
+            self._mdct = MDCT4(n_fft=opt.n_fft, hop_length=opt.hop_length, win_length=opt.win_length, window=self.window,
+                               device=self.device)
+            self._imdct = IMDCT4(n_fft=opt.n_fft, hop_length=opt.hop_length, win_length=opt.win_length, window=self.window,
+                                 device=self.device)
         # to_frames: the synthesis kernel with hop = win = n_fft and a window of ones gives the F frames side by side;
         # a second plan carries sqrt(up_ratio-1) * window (:375)
         self._frame_plan = self._frame_plan_scaled = None
@@ -239,13 +249,16 @@ class Pix2PixHDModel(BaseModel):
         """synthesis kernel at hop = win = n_fft: no overlap, the F frames land side by side -> [B, F, n_fft]"""
         B, F, _ = coef.shape
         N = self.opt.n_fft
+        if self.transform == 'mdct2':       # IDCT_2N_native on every frame (:257)
+            return _Synthesis2Fn.apply(coef, plan, F * N, 0, 1.0, 0.5).view(B, F, N)
         return _SynthesisFn.apply(coef, plan, F * N, 0, 8.0 / N).view(B, F, N)
 
     def _frame_plans(self):
         if self._frame_plan is None:
             N = self.opt.n_fft
-            self._frame_plan = _Plan(N, N, N, torch.ones(N))
-            self._frame_plan_scaled = _Plan(N, N, N, math.sqrt(self.up_ratio - 1) * self.window.detach().cpu().float())
+            P = _Plan2 if self.transform == 'mdct2' else _Plan
+            self._frame_plan = P(N, N, N, torch.ones(N))
+            self._frame_plan_scaled = P(N, N, N, math.sqrt(self.up_ratio - 1) * self.window.detach().cpu().float())
         return self._frame_plan, self._frame_plan_scaled
 
     def to_frames(self, log_spectro, norm_param):

@@ -28,7 +28,9 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 STEPS = 40
 
 
-def main():
+def main(shipped_mdct2=False, out_name="model_time_ref.npz"):
+    """shipped_mdct2=True (make_golden_model_mdct2.py): the reference model exactly as shipped -- MDCT2 / IMDCT2 /
+    IDCT_2N_native, nothing replaced"""
     MDCT4, IMDCT4, kbdwin = import_reference()
     tmp = tempfile.mkdtemp()
     sys.argv = ['train.py', '--checkpoints_dir', tmp] + ARGS + ['--use_time_D', '--use_match_loss', '--lambda_time', '10']
@@ -59,8 +61,9 @@ def main():
             y = torch.real(torch.fft.fft(im.exp1 * x.double(), n=im.n_fft) * im.exp2)
             return (8.0 / im.n_fft * y).float()
 
-    model._mdct = Mdct4WithFrames()
-    model._idct = FrameInverse()
+    if not shipped_mdct2:
+        model._mdct = Mdct4WithFrames()
+        model._idct = FrameInverse()
     out = {}
     for tag, net in (("G0/", model.netG), ("D0/", model.netD), ("T0/", model.time_D)):
         for k, v in net.state_dict().items():
@@ -95,6 +98,9 @@ def main():
             out["sr0"] = generated.detach().numpy()
             with torch.no_grad():
                 ls, pha, npar = model.to_spectro(lr, mask=True)
+                hs, _, _ = model.to_spectro(hr, mask=False)
+                out["lr_spectro0"], out["hr_spectro0"], out["lr_pha0"] = ls.numpy(), hs.numpy(), pha.numpy()
+                out["lr_norm0"] = np.array([float(npar[k]) for k in ('max', 'min', 'mean', 'std')])
                 out["lr_frames0"] = npar['frames'].numpy()
                 out["sr_frames0"] = model.to_frames(generated.detach(), npar).numpy()
             for tag, net in (("G1/", model.netG), ("D1/", model.netD), ("T1/", model.time_D)):
@@ -104,7 +110,14 @@ def main():
             print(i, dict(zip(names, curve[-1])))
     out["loss_names"] = np.array(names)
     out["curve"] = np.array(curve, np.float64)
-    np.savez_compressed(os.path.join(HERE, "model_time_ref.npz"), **out)
+    lr, hr = batch(STEPS)
+    sr, pha, npar, ls = model.inference(lr, None)
+    out["inf_sr"] = sr.numpy()
+    if shipped_mdct2:
+        out["inf_audio"] = model.to_audio(sr, npar, pha).numpy()
+    for k, v in model.netG.state_dict().items():
+        out["GN/" + k] = v.numpy().copy()
+    np.savez_compressed(os.path.join(HERE, out_name), **out)
     print("params T", sum(p.numel() for p in model.time_D.parameters()), "frames", out["sr_frames0"].shape)
 
 

@@ -27,13 +27,20 @@ CFG = {'n_fft': 128, 'hop_length': 64, 'win_length': 128, 'alpha': 0.6, 'min_val
 NAMES = ['G_GAN', 'G_GAN_Feat', 'G_mat', 'G_GAN_t', 'D_real_t', 'D_fake_t', 'D_real', 'D_fake']
 
 
-@pytest.fixture(scope="module")
-def ref():
-    return np.load(os.path.join(ROOT, "tests", "golden", "model_time_ref.npz"))
+# 'mdct4': the reference model with its two transform hooks switched to MDCT4 (make_golden_model_time.py);
+# 'mdct2': the reference model exactly as shipped, nothing replaced (make_golden_model_mdct2.py)
+GOLDEN = {"mdct4": "model_time_ref.npz", "mdct2": "model_mdct2_ref.npz"}
 
 
-def time_opt(**kw):
-    return tiny_opt(use_time_D=True, use_match_loss=True, lambda_time=10.0, lambda_mat=10.0, **kw)
+@pytest.fixture(scope="module", params=["mdct4", "mdct2"])
+def ref(request):
+    r = dict(np.load(os.path.join(ROOT, "tests", "golden", GOLDEN[request.param])))
+    r["transform"] = request.param
+    return r
+
+
+def time_opt(ref, **kw):
+    return tiny_opt(use_time_D=True, use_match_loss=True, lambda_time=10.0, lambda_mat=10.0, transform=ref["transform"], **kw)
 
 
 # ---- kernels ---------------------------------------------------------------------------------------------------
@@ -131,13 +138,13 @@ def test_spectro_decode_gradient(dtype):
 # ---- model -----------------------------------------------------------------------------------------------------
 def _load(model, ref):
     for tag, net in (("G0/", model.netG), ("D0/", model.netD), ("T0/", model.time_D)):
-        net.load_state_dict({k[len(tag):]: torch.from_numpy(ref[k]) for k in ref.files if k.startswith(tag)})
+        net.load_state_dict({k[len(tag):]: torch.from_numpy(ref[k]) for k in ref if k.startswith(tag)})
     for opt in (model.optimizer_G, model.optimizer_D):
         opt.flat_bf16.copy_(opt.flat)
 
 
 def test_to_frames_matches_reference(ref):
-    model = create_model(time_opt())
+    model = create_model(time_opt(ref))
     assert model.loss_names == NAMES == list(ref["loss_names"])
     lr, _ = batch(0)
     _, _, npar = model.to_spectro(lr, mask=True)
@@ -149,7 +156,7 @@ def test_to_frames_matches_reference(ref):
 
 def test_first_step_with_time_D_matches_reference(ref):
     """all eight losses, every gradient of G, D and time_D, and the weights after the first Adam steps (exact fp32 path)"""
-    model = create_model(time_opt())
+    model = create_model(time_opt(ref))
     _load(model, ref)
     lr, hr = batch(0)
     losses, sr = model(lr, None, hr, None, infer=True)
@@ -185,7 +192,7 @@ def test_first_step_with_time_D_matches_reference(ref):
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
 def test_time_D_loss_curve(ref, precision):
     """40 optimisation steps with --use_time_D --use_match_loss from the reference's seeded weights"""
-    model = create_model(time_opt(precision=precision))
+    model = create_model(time_opt(ref, precision=precision))
     _load(model, ref)
     curve = []
     for i in range(40):
@@ -212,10 +219,23 @@ def test_time_D_loss_curve(ref, precision):
     assert abs(np.log(curve[-10:, mat].mean() / want[-10:, mat].mean())) < np.log(1.5)
 
 
-def test_time_D_step_in_a_cuda_graph():
+def test_inference_and_to_audio_match_shipped_reference(ref):
+    if ref["transform"] != "mdct2":
+        pytest.skip("the MDCT4 variant's inference is covered by test_model_gpu.py")
+    model = create_model(time_opt(ref))
+    model.netG.load_state_dict({k[3:]: torch.from_numpy(ref[k]) for k in ref if k.startswith("GN/")})
+    lr, _ = batch(40)
+    sr, pha, npar, ls = model.inference(lr, None)
+    assert relerr(sr.float().cpu().numpy(), ref["inf_sr"]) < 5e-3
+    audio = model.to_audio(torch.from_numpy(ref["inf_sr"]).cuda(), npar, pha)
+    assert tuple(audio.shape) == ref["inf_audio"].shape
+    assert relerr(audio.cpu().numpy(), ref["inf_audio"]) < 2e-3
+
+
+def test_time_D_step_in_a_cuda_graph(ref):
     """the config-4 step is capturable (no host sync inside) and replays to finite losses"""
     from pix2pixhdaudiosr_b200.train import GraphedTrainStep
-    model = create_model(time_opt(precision="bf16"))
+    model = create_model(time_opt(ref, precision="bf16"))
     lr, hr = batch(0)
     step = GraphedTrainStep(model, lr.cuda(), hr.cuda())
     for i in range(3):
