@@ -93,15 +93,28 @@ class Conv2d(_ConvBase):
         self.in_channels, self.out_channels = in_channels, out_channels
         self.kernel_size, self.stride, self.padding = int(kernel_size), int(stride), int(padding)
         k = self.kernel_size
+        self.tswap = False
         self._init_params((out_channels, in_channels, k, k), in_channels * k * k, (2, 3, 0, 1))
+
+    def set_transposed_image(self):
+        """this layer will be run on spatially transposed images (MultiscaleDiscriminator(transposed_image=True)): store
+        the weight [KW][KH][Cout][Cin] behind the same logical [Cout, Cin, KH, KW] parameter (state_dict unchanged).
+        Call before the optimiser re-homes the parameter."""
+        if self.tswap:
+            return
+        phys = self.weight.data.permute(3, 2, 0, 1).contiguous()
+        self.weight = nn.Parameter(phys.permute(2, 3, 1, 0))
+        self._perm = (3, 2, 0, 1)
+        self.weight._p2p_conv = self
+        self.w16, self.gphys, self.tswap = None, None, True
 
     def run(self, x, reflect_pad=0, needs_wgrad=True, norm=None, act_mod=None, res=None):
         """conv [+ InstanceNorm] [+ activation] [+ residual] as one fused op"""
         if reflect_pad:
             assert self.padding == 0
-            cfg = ops.ConvCfg(False, self.stride, reflect_pad, ops.PAD_REFLECT)
+            cfg = ops.ConvCfg(False, self.stride, reflect_pad, ops.PAD_REFLECT, tswap=self.tswap)
         else:
-            cfg = ops.ConvCfg(False, self.stride, self.padding, ops.PAD_ZERO)
+            cfg = ops.ConvCfg(False, self.stride, self.padding, ops.PAD_ZERO, tswap=self.tswap)
         return _conv_block(self, x, cfg, needs_wgrad, norm, act_mod, res)
 
     def extra_repr(self):
@@ -407,8 +420,12 @@ class MultiscaleDiscriminator(nn.Module):
     """networks.py:292-331: num_D PatchGANs on an average-pooled pyramid; finest scale first in the result."""
 
     def __init__(self, input_nc, ndf=64, n_layers=3, norm_layer=InstanceNorm2d, use_sigmoid=False, num_D=3,
-                 getIntermFeat=False):
+                 getIntermFeat=False, transposed_image=False):
         super().__init__()
+        # transposed_image: run every layer on the spatially transposed image (exact: square kernels, symmetric stride,
+        # padding and pooling).  For wide images (the time-domain D's [frames, n_fft] maps) this puts the short axis on
+        # the fast dimension, which the shifted-window conv kernels need (halo = (K-1) * padded width rows).
+        self.transposed_image = transposed_image
         self.num_D = num_D
         self.n_layers = n_layers
         self.getIntermFeat = getIntermFeat
@@ -420,22 +437,30 @@ class MultiscaleDiscriminator(nn.Module):
             else:
                 setattr(self, 'layer' + str(i), netD.model)
         self.act_dtype = _DEFAULT_DTYPE
+        if transposed_image:
+            for m in self.modules():
+                if isinstance(m, Conv2d):
+                    m.set_transposed_image()
+
+    def _out(self, x):
+        y = _to_nchw(x)
+        return y.transpose(2, 3) if self.transposed_image else y
 
     def singleD_forward(self, model, x, needs_wgrad=True):
         if self.getIntermFeat:
             result = []
             for i in range(len(model)):
                 x = run_layers(model[i], x, needs_wgrad)
-                result.append(_to_nchw(x))
+                result.append(self._out(x))
             return result
-        return [_to_nchw(run_layers(model, x, needs_wgrad))]
+        return [self._out(run_layers(model, x, needs_wgrad))]
 
     def forward(self, input, needs_wgrad=True):
         """needs_wgrad=False runs with detached weights: the generator's pass through D, whose weight gradients
         the reference computes and then discards (train.py:164-176)."""
         num_D = self.num_D
         result = []
-        x = _to_nhwc(input, self.act_dtype)
+        x = _to_nhwc(input.transpose(2, 3) if self.transposed_image else input, self.act_dtype)
         for i in range(num_D):
             if self.getIntermFeat:
                 model = [getattr(self, 'scale' + str(num_D - 1 - i) + '_layer' + str(j)) for j in range(self.n_layers + 2)]
@@ -447,10 +472,11 @@ class MultiscaleDiscriminator(nn.Module):
         return result
 
 
-def define_D(input_nc, ndf, n_layers_D, norm='instance', use_sigmoid=False, num_D=1, getIntermFeat=False, gpu_ids=[]):
-    """networks.py:46-54"""
+def define_D(input_nc, ndf, n_layers_D, norm='instance', use_sigmoid=False, num_D=1, getIntermFeat=False, gpu_ids=[],
+             transposed_image=False):
+    """networks.py:46-54 (transposed_image: see MultiscaleDiscriminator; results and state_dict are unchanged)"""
     norm_layer = get_norm_layer(norm_type=norm)
-    netD = MultiscaleDiscriminator(input_nc, ndf, n_layers_D, norm_layer, use_sigmoid, num_D, getIntermFeat)
+    netD = MultiscaleDiscriminator(input_nc, ndf, n_layers_D, norm_layer, use_sigmoid, num_D, getIntermFeat, transposed_image)
     if len(gpu_ids) > 0:
         assert (torch.cuda.is_available())
         netD.cuda(gpu_ids[0])

@@ -102,8 +102,9 @@ class Pix2PixHDModel(BaseModel):
                 self.netD = networks.define_D(netD_input_nc, opt.ndf, opt.n_layers_D, opt.norm, opt.no_lsgan, opt.num_D,
                                               not opt.no_ganFeat_loss, gpu_ids=self.gpu_ids)
                 if opt.use_time_D:      # :64-65
+                    # its [frames, n_fft] maps are wide: run it on the transposed image (same results, same state_dict)
                     self.time_D = networks.define_D(2, opt.ndf, opt.n_layers_D, opt.norm, opt.no_lsgan, opt.num_D, False,
-                                                    gpu_ids=self.gpu_ids)
+                                                    gpu_ids=self.gpu_ids, transposed_image=True)
         finally:
             networks.set_default_precision('fp32')
         if opt.verbose:

@@ -179,10 +179,13 @@ def _run_pass(P, x, w, bias, out, kind="fwd"):
 
 class ConvCfg:
     """static description of one conv / transposed-conv layer call"""
-    __slots__ = ("transposed", "stride", "pad", "pad_mode", "out_pad")
+    __slots__ = ("transposed", "stride", "pad", "pad_mode", "out_pad", "tswap")
 
-    def __init__(self, transposed=False, stride=1, pad=0, pad_mode=PAD_ZERO, out_pad=0):
+    def __init__(self, transposed=False, stride=1, pad=0, pad_mode=PAD_ZERO, out_pad=0, tswap=False):
         self.transposed, self.stride, self.pad, self.pad_mode, self.out_pad = transposed, stride, pad, pad_mode, out_pad
+        # tswap: the layer runs on the spatially TRANSPOSED image (conv(x^T, w^T) = conv(x, w)^T for square kernels with
+        # symmetric stride / padding); its weight is stored [KW][KH][Cout][Cin], so the kernels see an ordinary layer
+        self.tswap = tswap
 
 
 def _phys(weight, cfg):
@@ -190,11 +193,22 @@ def _phys(weight, cfg):
     if cfg.transposed:
         Cin, Cout, KH, KW = weight.shape
         w = weight.permute(2, 3, 1, 0)
+    elif cfg.tswap:
+        Cout, Cin, KH, KW = weight.shape
+        assert KH == KW
+        w = weight.permute(3, 2, 0, 1)
     else:
         Cout, Cin, KH, KW = weight.shape
         w = weight.permute(2, 3, 0, 1)
     assert w.is_contiguous(), "conv weights must be stored [KH][KW][Cout][Cin]"
     return w, Cout, Cin, KH, KW
+
+
+def _dw_logical(dwp, cfg):
+    """physical weight gradient [K0][K1][Cout][Cin] -> the logical [Cout, Cin, KH, KW] view autograd expects"""
+    if dwp is None:
+        return None
+    return dwp.permute(2, 3, 1, 0) if cfg.tswap else dwp.permute(2, 3, 0, 1)
 
 
 def _ceil16(c):
@@ -777,20 +791,20 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
     if col == "in" and (not need_dx or cfg.pad_mode == PAD_ZERO or cfg.pad == 0):
         dx, dwp = _col_in_backward(x, _weight_for(x, wphys, w16) if need_dx else None, dy, cfg, Cin, Cout, KH, KW, need_dx,
                                    need_dw, xpad)
-        return dx, (dwp.permute(2, 3, 0, 1) if dwp is not None else None), db
+        return dx, _dw_logical(dwp, cfg), db
     if col == "out":
         dx, dwp = _col_out_backward(x, _weight_for(x, wphys, w16) if need_dx else None, dy, cfg, Cin, Cout, KH, KW, need_dx,
                                     need_dw, xpad)
-        return dx, (dwp.permute(2, 3, 0, 1) if dwp is not None else None), db
+        return dx, _dw_logical(dwp, cfg), db
     pk = _packable(x, cfg, Cin, Cout, KH, KW)
     if pk is not None and (pk == "out" or not need_dx):
         dx, dwp = _packed_backward(pk, x, _weight_for(x, wphys, w16) if need_dx else None, dy, cfg, Cin, Cout, KH, KW,
                                    need_dx, need_dw, xpad)
-        return dx, (dwp.permute(2, 3, 0, 1) if dwp is not None else None), db
+        return dx, _dw_logical(dwp, cfg), db
     pk_dw = pk == "in" and need_dw         # thin-input layer that also needs dx: dW packed, dx through the padded path
     if pk_dw:
         _, dwp = _packed_backward(pk, x, None, dy, cfg, Cin, Cout, KH, KW, False, True, xpad)
-        dw = dwp.permute(2, 3, 0, 1)
+        dw = _dw_logical(dwp, cfg)
         need_dw = False
     Cin0, Cout0 = Cin, Cout
     thin = _thin(x, Cin, Cout)
@@ -854,7 +868,7 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
             return dx, None, db
         if thin is not None:
             dwp = dwp[:, :, :Cout0, :Cin0]
-        dw = dwp.permute(3, 2, 0, 1) if cfg.transposed else dwp.permute(2, 3, 0, 1)
+        dw = dwp.permute(3, 2, 0, 1) if cfg.transposed else _dw_logical(dwp, cfg)
     return dx, dw, db
 
 

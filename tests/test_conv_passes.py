@@ -90,3 +90,23 @@ def test_reflect_fold_is_adjoint_of_reflect_pad():
         g = torch.randn_like(xp)
         (gx,) = torch.autograd.grad(xp, x, g)
         assert np.allclose(E.fold_reflect(_nhwc(g), p), _nhwc(gx), atol=1e-12)
+
+
+def test_transposed_image_discriminator_keeps_the_reference_state_dict():
+    """MultiscaleDiscriminator(transposed_image=True) stores every conv weight [KW][KH][Cout][Cin] behind the same
+    logical parameter: same keys / shapes / values in state_dict, physical buffer contiguous and transposed"""
+    import torch
+    from pix2pixhdaudiosr_b200.models import networks
+    torch.manual_seed(3)
+    a = networks.define_D(2, 8, 3, 'instance', False, 2, False, gpu_ids=[])
+    b = networks.define_D(2, 8, 3, 'instance', False, 2, False, gpu_ids=[], transposed_image=True)
+    sa, sb = a.state_dict(), b.state_dict()
+    assert list(sa) == list(sb) and all(sa[k].shape == sb[k].shape for k in sa)
+    b.load_state_dict(sa)
+    for (ka, ma), (kb, mb) in zip(a.named_modules(), b.named_modules()):
+        if isinstance(ma, networks.Conv2d):
+            assert mb.tswap and not ma.tswap
+            assert torch.equal(ma.weight.data, mb.weight.data)
+            pa, pb = ma.physical_weight(), mb.physical_weight()
+            assert pa.is_contiguous() and pb.is_contiguous()
+            assert torch.equal(pb, pa.transpose(0, 1))
