@@ -29,35 +29,40 @@ def main():
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6550.0
     flush = torch.empty(64 << 20, dtype=torch.float32, device=dev)
     rows = []
+    mdct2 = "--mdct2" in sys.argv               # the DCT-II lapped transform (MDCT2 / IMDCT2): n_fft bins per frame
+    bins = (lambda n: n) if mdct2 else (lambda n: n // 2)
+    ana = (lambda x, plan, F, sp: pm._analysis2(x, plan, F, sp, 1.0, 1.0)) if mdct2 else (lambda x, plan, F, sp: pm._analysis(x, plan, F, sp, 1.0))
+    syn = ((lambda s, plan, T_out, crop, n: pm._synthesis2(s, plan, T_out, crop, 0.5, 0.5)) if mdct2
+           else (lambda s, plan, T_out, crop, n: pm._synthesis(s, plan, T_out, crop, 4.0 / n)))
     for n_fft in (256, 512, 1024, 2048, 4096):
         hop = n_fft // 2
-        m = pm.MDCT4(n_fft, hop, n_fft, kbdwin, True, device=dev)
-        im = pm.IMDCT4(n_fft, hop, n_fft, kbdwin, True, device=dev)
-        for B_total in (1, 4, 16, 64, 256, 1024):
+        m = (pm.MDCT2 if mdct2 else pm.MDCT4)(n_fft, hop, n_fft, kbdwin, True, device=dev)
+        im = (pm.IMDCT2 if mdct2 else pm.IMDCT4)(n_fft, hop, n_fft, kbdwin, True, device=dev)
+        for B_total in ((1, 16, 256, 1024) if mdct2 else (1, 4, 16, 64, 256, 1024)):
             B = max(1, B_total // world)            # per rank (B_total < world: every rank runs one segment)
             x = 0.1 * torch.randn(B, T, device=dev)
             sp, ep = m.pads(B)
             F = (T + sp + ep - n_fft) // hop + 1
             crop, T_out = im.out_geometry(F)
-            ba = B * (4 * T + 4 * F * (n_fft // 2))
-            bs = B * (4 * F * (n_fft // 2) + 4 * T_out)
+            ba = B * (4 * T + 4 * F * bins(n_fft))
+            bs = B * (4 * F * bins(n_fft) + 4 * T_out)
             reps = 20 if ba < 64e6 else 8
             need_flush = ba < 2 * L2_BYTES
             for _ in range(3):
-                spec = pm._analysis(x, m._plan, F, sp, 1.0)
-                y = pm._synthesis(spec, m._plan, T_out, crop, 4.0 / n_fft)
+                spec = ana(x, m._plan, F, sp)
+                y = syn(spec, m._plan, T_out, crop, n_fft)
             ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(reps)]
             torch.cuda.synchronize()
             for e in ev:
                 if need_flush:
                     flush.fill_(1.0)
                 e[0].record()
-                spec = pm._analysis(x, m._plan, F, sp, 1.0)
+                spec = ana(x, m._plan, F, sp)
                 e[1].record()
                 if need_flush:
                     flush.fill_(2.0)
                 e[2].record()
-                y = pm._synthesis(spec, m._plan, T_out, crop, 4.0 / n_fft)
+                y = syn(spec, m._plan, T_out, crop, n_fft)
                 e[3].record()
             torch.cuda.synchronize()
             ms = torch.tensor([sorted(e[0].elapsed_time(e[1]) for e in ev)[reps // 2],
@@ -72,7 +77,7 @@ def main():
                          "l2_flushed": need_flush, "roundtrip_max_abs_err": err})
             del x, spec, y
     if rank == 0:
-        print(json.dumps({"n_gpus": world, "T": T, "hbm_peak_GBps_per_gpu": peak, "rows": rows}))
+        print(json.dumps({"transform": "mdct2" if mdct2 else "mdct4", "n_gpus": world, "T": T, "hbm_peak_GBps_per_gpu": peak, "rows": rows}))
         print("| n_fft | segments | MDCT4 ms | GB/s (frac of %d-GPU peak) | IMDCT4 ms | GB/s (frac) |" % world, file=sys.stderr)
         print("|---|---|---|---|---|---|", file=sys.stderr)
         for r in rows:
