@@ -13,8 +13,8 @@
 //     synthesis(scale, c0): out  = scale * crop(OLA_hop(w[n] * 2 sum_k c0_k X[k] cos(.)))     c0_0 = c0, c0_k = 1 (k > 0)
 //   MDCT2 = analysis(1, 1); IMDCT2 = synthesis(1/2, 1/2); d MDCT2 / dx = synthesis(1/N, 1); d IMDCT2 / dX = analysis(N/2, 1/2).
 // Layout: signal [B,T] fp32, coefficients [B,F,N] fp32 (bins fastest).  Bound: HBM (4 B in + 8 B out per sample at
-// hop = N/2); the shared-memory complex FFT of a real row does twice the necessary butterflies (next: two frames per
-// complex FFT / the register FFT of mdct4_fast.cuh).
+// hop = N/2).  Two real frames share one complex FFT (real / imaginary lanes); next: the register FFT + TMA prefetch
+// structure of mdct4_fast.cuh.
 #include "common.cuh"
 #include "smem_fft.cuh"
 #include <cmath>
@@ -27,10 +27,11 @@ using smemfft::kThreads;
 using smemfft::cmul;
 using smemfft::fft_rows_inplace;
 
-struct Tables2 {          // 5N words: tw[N] complex | roots[N] complex | perm[N] int
+struct Tables2 {          // 6N words: tw[N] complex | roots[N] complex | perm[N] int | inv[N] int
     const float2* tw;     // e^{-j pi k / (2N)}
     const float2* roots;  // e^{-2 pi j m / N}
     const int* perm;      // position p after the in-place DIF passes holds FFT bin perm[p]
+    const int* inv;       // FFT bin k sits at position inv[k]
 };
 
 __device__ __forceinline__ Tables2 make_tables2(const void* t, int N) {
@@ -39,24 +40,28 @@ __device__ __forceinline__ Tables2 make_tables2(const void* t, int N) {
     r.tw = reinterpret_cast<const float2*>(f);
     r.roots = reinterpret_cast<const float2*>(f + 2 * N);
     r.perm = reinterpret_cast<const int*>(f + 4 * N);
+    r.inv = reinterpret_cast<const int*>(f + 5 * N);
     return r;
 }
 
-// grid (ceil(F/fpb), B).  smem: sig[(fpb-1)*hop+win] | win_s[win] | z[fpb*N] (float2) | o[fpb*N]
+// Two real frames share one complex FFT (frame A on the real lane, frame B on the imaginary lane):
+//   FFT(vA + j vB)[k] = VA[k] + j VB[k],  VA[k] = (Z[k] + conj Z[N-k]) / 2,  VB[k] = -j (Z[k] - conj Z[N-k]) / 2.
+// grid (ceil(F/fpb), B), fpb even.  smem: sig[(fpb-1)*hop+win] | win_s[win] | z[(fpb/2)*N] (float2)
 __global__ void __launch_bounds__(kThreads)
 mdct2_analysis_kernel(const float* __restrict__ x, float* __restrict__ spec, const float* __restrict__ window,
-                      const void* __restrict__ tables, long long T, int F, int N, int hop, int win, long long offset,
-                      float scale, float c0, int fpb) {
+                      const void* __restrict__ tables, long long T, int F, int N, int lgN, int hop, int win,
+                      long long offset, float scale, float c0, int fpb) {
     extern __shared__ __align__(16) float smem[];
     const int f0 = blockIdx.x * fpb;
     const int nfr = min(fpb, F - f0);
+    const int npair = (nfr + 1) >> 1;
     const int span = (nfr - 1) * hop + win;
     const int span_max = (fpb - 1) * hop + win;
     float* sig = smem;
     float* win_s = sig + ((span_max + 3) & ~3);
     float2* z = reinterpret_cast<float2*>(win_s + ((win + 3) & ~3));
-    float* o = reinterpret_cast<float*>(z + fpb * N);
     const Tables2 tb = make_tables2(tables, N);
+    const int mask = N - 1;
 
     const float* xb = x + (long long)blockIdx.y * T;
     const long long t0 = (long long)f0 * hop - offset;
@@ -69,51 +74,54 @@ mdct2_analysis_kernel(const float* __restrict__ x, float* __restrict__ spec, con
 
     // v[p] = u[2p] (p < N/2), u[2(N-1-p)+1] otherwise; u = window * frame, zero beyond win
     const int hN = N >> 1;
-    for (int w = threadIdx.x; w < nfr * N; w += kThreads) {
-        const int fl = w / N;
-        const int p = w - fl * N;
+    for (int w = threadIdx.x; w < npair * N; w += kThreads) {
+        const int pr = w >> lgN;
+        const int p = w & mask;
         const int i = p < hN ? 2 * p : 2 * (N - 1 - p) + 1;
-        const float* s = sig + fl * hop;
-        z[w] = make_float2(i < win ? s[i] * win_s[i] : 0.f, 0.f);
+        float a = 0.f, b = 0.f;
+        if (i < win) {
+            const float wv = win_s[i];
+            a = sig[(2 * pr) * hop + i] * wv;
+            if (2 * pr + 1 < nfr) b = sig[(2 * pr + 1) * hop + i] * wv;
+        }
+        z[w] = make_float2(a, b);
     }
     __syncthreads();
 
-    fft_rows_inplace(z, nfr, N, tb.roots);
+    fft_rows_inplace(z, npair, N, tb.roots);
 
-    const float sc = scale * 2.f / (float)N;
-    for (int w = threadIdx.x; w < nfr * N; w += kThreads) {
-        const int fl = w / N;
-        const int p = w - fl * N;
-        const int k = tb.perm[p];
-        const float2 t = tb.tw[k];
-        const float2 v = z[w];
-        o[fl * N + k] = (k == 0 ? sc * c0 : sc) * (v.x * t.x - v.y * t.y);
-    }
-    __syncthreads();
-
+    // natural-order bins: coalesced table reads and stores, the digit reversal is a shared-memory gather
+    const float sc = scale / (float)N;               // (2/N) * the 1/2 of the split
     float* dst = spec + ((long long)blockIdx.y * F + f0) * N;
-    const int total = nfr * N;
-    if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-        const float4* o4 = reinterpret_cast<const float4*>(o);
-        float4* d4 = reinterpret_cast<float4*>(dst);
-        for (int i = threadIdx.x; i < (total >> 2); i += kThreads) d4[i] = o4[i];
-    } else {
-        for (int i = threadIdx.x; i < total; i += kThreads) dst[i] = o[i];
+    for (int w = threadIdx.x; w < npair * N; w += kThreads) {
+        const int pr = w >> lgN;
+        const int k = w & mask;
+        const float2 a = z[(pr << lgN) + __ldg(tb.inv + k)];
+        const float2 m = z[(pr << lgN) + __ldg(tb.inv + ((N - k) & mask))];
+        const float2 t = __ldg(tb.tw + k);
+        const float s = k == 0 ? sc * c0 : sc;
+        // VA = (a + conj m), VB = -j (a - conj m)   (the 1/2 lives in sc)
+        const float2 va = make_float2(a.x + m.x, a.y - m.y);
+        const float2 vb = make_float2(a.y + m.y, m.x - a.x);
+        dst[(long long)(2 * pr) * N + k] = s * (va.x * t.x - va.y * t.y);
+        if (2 * pr + 1 < nfr) dst[(long long)(2 * pr + 1) * N + k] = s * (vb.x * t.x - vb.y * t.y);
     }
 }
 
 // grid (ceil(T_out/chunk), B).  Each CTA owns `chunk` output samples and transforms every frame that overlaps them, so
-// the overlap-add is a deterministic gather (no atomics, each sample written once).
-// smem: win_s[win] | z[nfmax*N] (float2) | t[nfmax*N]
+// the overlap-add is a deterministic gather (no atomics, each sample written once).  Frames are paired on one complex
+// FFT: h[k] = tw[k] (X[k] + j X[N-k]) / 2 (h[0] = c0 X[0]) is Hermitian, so FFT(hA + j hB) = vA + j vB with both real.
+// smem: win_s[win] | z[ceil(nfmax/2)*N] (float2) | t[nfmax*N]
 __global__ void __launch_bounds__(kThreads)
 mdct2_synthesis_kernel(const float* __restrict__ spec, float* __restrict__ out, const float* __restrict__ window,
-                       const void* __restrict__ tables, int F, long long T_out, int N, int hop, int win,
+                       const void* __restrict__ tables, int F, long long T_out, int N, int lgN, int hop, int win,
                        long long crop_left, float scale, float c0, int chunk, int nfmax) {
     extern __shared__ __align__(16) float smem[];
     float* win_s = smem;
     float2* z = reinterpret_cast<float2*>(win_s + ((win + 3) & ~3));
-    float* t = reinterpret_cast<float*>(z + nfmax * N);
+    float* t = reinterpret_cast<float*>(z + ((nfmax + 1) >> 1) * N);
     const Tables2 tb = make_tables2(tables, N);
+    const int mask = N - 1;
 
     const long long s_lo = (long long)blockIdx.x * chunk + crop_left;            // OLA coordinates
     const long long s_hi = min((long long)(blockIdx.x + 1) * chunk, T_out) + crop_left;  // exclusive
@@ -122,27 +130,54 @@ mdct2_synthesis_kernel(const float* __restrict__ spec, float* __restrict__ out, 
     const int f_lo = (int)min(fl_, (long long)F);
     const int f_hi = (int)min((s_hi - 1) / hop, (long long)F - 1);              // inclusive
     const int nfr = max(0, f_hi - f_lo + 1);
+    const int npair = (nfr + 1) >> 1;
 
     for (int i = threadIdx.x; i < win; i += kThreads) win_s[i] = __ldg(window + i);
-    const float* src = spec + ((long long)blockIdx.y * F + f_lo) * N;
-    for (int w = threadIdx.x; w < nfr * N; w += kThreads) {
-        const int k = w % N;
-        const float2 tw = tb.tw[k];
-        const float xv = __ldg(src + w) * (k == 0 ? c0 : 1.f);
-        z[w] = make_float2(xv * tw.x, xv * tw.y);
+    {   // coalesced load of the coefficient rows into t
+        const float* src = spec + ((long long)blockIdx.y * F + f_lo) * N;
+        const int total = nfr * N;
+        if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+            const float4* s4 = reinterpret_cast<const float4*>(src);
+            float4* t4 = reinterpret_cast<float4*>(t);
+            for (int i = threadIdx.x; i < (total >> 2); i += kThreads) t4[i] = __ldg(s4 + i);
+        } else {
+            for (int i = threadIdx.x; i < total; i += kThreads) t[i] = __ldg(src + i);
+        }
     }
     __syncthreads();
 
-    fft_rows_inplace(z, nfr, N, tb.roots);
+    for (int w = threadIdx.x; w < npair * N; w += kThreads) {
+        const int pr = w >> lgN;
+        const int k = w & mask;
+        const float* ta = t + ((2 * pr) << lgN);
+        const bool hb = 2 * pr + 1 < nfr;
+        const float* tbp = ta + N;
+        float2 ha, hbv;
+        if (k == 0) {
+            ha = make_float2(c0 * ta[0], 0.f);
+            hbv = make_float2(hb ? c0 * tbp[0] : 0.f, 0.f);
+        } else {
+            const float2 tw = __ldg(tb.tw + k);
+            const float ak = ta[k], am = ta[N - k];
+            ha = make_float2(0.5f * (tw.x * ak - tw.y * am), 0.5f * (tw.x * am + tw.y * ak));
+            const float bk = hb ? tbp[k] : 0.f, bm = hb ? tbp[N - k] : 0.f;
+            hbv = make_float2(0.5f * (tw.x * bk - tw.y * bm), 0.5f * (tw.x * bm + tw.y * bk));
+        }
+        z[w] = make_float2(ha.x - hbv.y, ha.y + hbv.x);
+    }
+    __syncthreads();
 
-    // v[n] = Re Z[n]; y[2n] = 2 v[n] (n < N/2), y[2(N-1-n)+1] = 2 v[n] otherwise
+    fft_rows_inplace(z, npair, N, tb.roots);
+
+    // position p holds v[n], n = perm[p]; y[2n] = 2 v[n] (n < N/2), y[2(N-1-n)+1] = 2 v[n] otherwise
     const int hN = N >> 1;
-    for (int w = threadIdx.x; w < nfr * N; w += kThreads) {
-        const int fl = w / N;
-        const int p = w - fl * N;
-        const int n = tb.perm[p];
+    for (int w = threadIdx.x; w < npair * N; w += kThreads) {
+        const int pr = w >> lgN;
+        const int n = __ldg(tb.perm + (w & mask));
         const int i = n < hN ? 2 * n : 2 * (N - 1 - n) + 1;
-        t[fl * N + i] = 2.f * z[w].x;
+        const float2 v = z[w];
+        t[((2 * pr) << lgN) + i] = 2.f * v.x;
+        if (2 * pr + 1 < nfr) t[((2 * pr + 1) << lgN) + i] = 2.f * v.y;
     }
     __syncthreads();
 
@@ -157,11 +192,13 @@ mdct2_synthesis_kernel(const float* __restrict__ spec, float* __restrict__ out, 
         float acc = 0.f;
         for (int f = fa; f <= fb; ++f) {
             const int n = (int)(s - (long long)f * hop);
-            acc += win_s[n] * t[(f - f_lo) * N + n];
+            acc += win_s[n] * t[((f - f_lo) << lgN) + n];
         }
         ob[s - crop_left] = scale * acc;
     }
 }
+
+inline int ilog2i(int v) { int l = 0; while ((1 << l) < v) ++l; return l; }
 
 constexpr int kMaxSmem2 = 227 * 1024;
 
@@ -189,7 +226,7 @@ int ensure_smem2(K kernel, size_t bytes) {
 extern "C" int p2p_mdct2_table_words(int n_fft) {
     if (!p2p::is_pow2(n_fft) || n_fft < 4 || n_fft > 4096)
         return p2p::fail(P2P_ENOTSUP, "n_fft must be a power of two in [4, 4096], got %d", n_fft);
-    return 5 * n_fft;
+    return 6 * n_fft;
 }
 
 extern "C" int p2p_mdct2_fill_tables(int n_fft, void* host_tables) {
@@ -199,6 +236,7 @@ extern "C" int p2p_mdct2_fill_tables(int n_fft, void* host_tables) {
     const int N = n_fft;
     float* f = static_cast<float*>(host_tables);
     int* perm = reinterpret_cast<int*>(f + 4 * N);
+    int* inv = perm + N;
     const double pi = 3.14159265358979323846264338327950288;
     for (int k = 0; k < N; ++k) {
         const double a = -pi * k / (2.0 * N), c = -2.0 * pi * k / N;
@@ -206,6 +244,7 @@ extern "C" int p2p_mdct2_fill_tables(int n_fft, void* host_tables) {
         f[2 * N + 2 * k] = (float)cos(c);   f[2 * N + 2 * k + 1] = (float)sin(c);
         perm[k] = p2p::smemfft::dif_position_to_bin(k, N);
     }
+    for (int p = 0; p < N; ++p) inv[perm[p]] = p;
     return P2P_OK;
 }
 
@@ -217,13 +256,13 @@ extern "C" int p2p_mdct2_analysis(const float* x, float* spec, const float* wind
     if (B == 0 || F == 0) return P2P_OK;
     if (!spec || !window || !tables || (!x && T > 0)) return fail(P2P_EINVAL, "null pointer argument");
     if (B > 65535) return fail(P2P_ENOTSUP, "B=%d exceeds 65535 rows per launch", B);
-    int fpb = 4096 / n_fft; if (fpb < 1) fpb = 1; if (fpb > 32) fpb = 32; if (fpb > F) fpb = F;
+    int fpb = 8192 / n_fft; if (fpb < 2) fpb = 2; if (fpb > 32) fpb = 32;      // even: frames are transformed in pairs
     const int span_max = (fpb - 1) * hop + win;
-    const size_t smem = 4ull * (((span_max + 3) & ~3) + ((win + 3) & ~3) + 2 * fpb * n_fft + fpb * n_fft);
+    const size_t smem = 4ull * (((span_max + 3) & ~3) + ((win + 3) & ~3) + 2 * (fpb / 2) * n_fft);
     if (int rc = ensure_smem2(mdct2_analysis_kernel, smem)) return rc;
     dim3 grid((F + fpb - 1) / fpb, B);
-    mdct2_analysis_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(x, spec, window, tables, (long long)T, F, n_fft, hop,
-                                                                         win, (long long)offset, scale, c0, fpb);
+    mdct2_analysis_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(x, spec, window, tables, (long long)T, F, n_fft,
+                                                                         ilog2i(n_fft), hop, win, (long long)offset, scale, c0, fpb);
     return check_launch("mdct2_analysis_kernel");
 }
 
@@ -238,16 +277,16 @@ extern "C" int p2p_mdct2_synthesis(const float* spec, float* out, const float* w
     if (!out || !window || !tables || (!spec && F > 0)) return fail(P2P_EINVAL, "null pointer argument");
     if (B > 65535) return fail(P2P_ENOTSUP, "B=%d exceeds 65535 rows per launch", B);
     const int overlap = (win + hop - 1) / hop;            // frames covering one sample
-    int nf_target = 4096 / n_fft; if (nf_target < 2) nf_target = 2;
+    int nf_target = 8192 / n_fft; if (nf_target < 2) nf_target = 2;
     int hpb = nf_target - overlap; if (hpb < 1) hpb = 1;
     const int chunk = hpb * hop;
     int nfmax = (chunk + win - 2) / hop + 1; if (nfmax > F) nfmax = F; if (nfmax < 1) nfmax = 1;
-    const size_t smem = 4ull * (((win + 3) & ~3) + 2 * nfmax * n_fft + nfmax * n_fft);
+    const size_t smem = 4ull * (((win + 3) & ~3) + 2 * ((nfmax + 1) / 2) * n_fft + nfmax * n_fft);
     if (int rc = ensure_smem2(mdct2_synthesis_kernel, smem)) return rc;
     const long long nchunks = (T_out + chunk - 1) / chunk;
     if (nchunks > 2147483647LL) return fail(P2P_ENOTSUP, "T_out too large");
     dim3 grid((unsigned)nchunks, B);
     mdct2_synthesis_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(spec, out, window, tables, F, (long long)T_out, n_fft,
-                                                                          hop, win, (long long)crop_left, scale, c0, chunk, nfmax);
+                                                                          ilog2i(n_fft), hop, win, (long long)crop_left, scale, c0, chunk, nfmax);
     return check_launch("mdct2_synthesis_kernel");
 }
