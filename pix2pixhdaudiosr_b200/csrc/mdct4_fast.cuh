@@ -29,6 +29,10 @@ struct Cfg {
     static constexpr int XW = 2 * V * (P + 1);       // words of one exchange region (row stride P+1)
     static constexpr int XREG = XW + ((P == 8 && XW % 32 == 0) ? 16 : 0);
     static constexpr bool TABLES_IN_SMEM = (L <= 512);   // pre/post twiddles; else read through L1
+    // (V,P) = (16,8) (n_fft 512): with the post table in shared memory the analysis kernel needs 115 920 B per CTA, 208 B
+    // more than two CTAs per SM allow; its 1 KB post table is read through L1 instead (16 instead of 8 warps per SM)
+    static constexpr bool POST_IN_SMEM = TABLES_IN_SMEM && !(V == 16 && P == 8);
+    static constexpr int TBF = TABLES_IN_SMEM ? (POST_IN_SMEM ? 6 * L : 4 * L) : 0;   // floats of tables in shared memory
     static constexpr bool XTW_IN_REGS = (V <= 16);       // exchange twiddles live in registers
     static constexpr int XV = XTW_IN_REGS ? V : 1;
     static constexpr int WS = N + ROWPAD;            // signed window, same padded layout as a frame
@@ -37,7 +41,7 @@ struct Cfg {
     static constexpr int OFF_WS = 2 * SIG;
     static constexpr int OFF_X = OFF_WS + ((WS + 3) & ~3);
     static constexpr int OFF_TB = OFF_X + kWarps * G * XREG;
-    static constexpr int OFF_BAR = OFF_TB + (TABLES_IN_SMEM ? 6 * L : 0);
+    static constexpr int OFF_BAR = OFF_TB + TBF;
     static constexpr size_t SMEM_BYTES = 4ull * OFF_BAR + 16;
 };
 
@@ -176,7 +180,7 @@ __device__ __forceinline__ void fft_core(float2 (&z)[C::V], float* __restrict__ 
         const float2* pk = post + k1;
 #pragma unroll
         for (int k2 = 0; k2 < P; ++k2) {
-            const float2 y = cmulf(b[brev<P>(k2)], ldt<C::TABLES_IN_SMEM>(pk + V * k2));
+            const float2 y = cmulf(b[brev<P>(k2)], ldt<C::POST_IN_SMEM>(pk + V * k2));
             re_[m][k2] = y.x;
             nim[m][k2] = -y.y;
         }
@@ -252,10 +256,10 @@ __device__ __forceinline__ void setup_tables(float* tb, const float* gt, int c, 
             const int n1 = i / C::P, jj = i % C::P;
             t2[i] = __ldg(gpre + i);                                          // pre
             t2[L + i] = __ldg(gpre + C::P * pi_rev<C>(n1, c) + jj);            // pre_f: reversed register order
-            t2[2 * L + i] = __ldg(post + i);                                  // post
+            if constexpr (C::POST_IN_SMEM) t2[2 * L + i] = __ldg(post + i);   // post
         }
         pre_lane = t2 + (ln.flip ? L : 0) + ln.j;
-        post = t2 + 2 * L;
+        if constexpr (C::POST_IN_SMEM) post = t2 + 2 * L;
     }
     if constexpr (C::XTW_IN_REGS) {
 #pragma unroll
@@ -319,7 +323,7 @@ struct SynCfg {
     static constexpr int BUF = ROWS * C::ROW;                       // floats per coefficient buffer
     static constexpr int OFF_X = 2 * BUF;
     static constexpr int OFF_TB = OFF_X + kWarps * C::G * C::XREG;
-    static constexpr int OFF_BAR = OFF_TB + (C::TABLES_IN_SMEM ? 6 * C::L : 0);
+    static constexpr int OFF_BAR = OFF_TB + C::TBF;
     static constexpr size_t SMEM_BYTES = 4ull * OFF_BAR + 16;
     static constexpr int G4 = C::M / 4;                             // float4 groups per hop slot
     static constexpr int NQ = G4 > kThreads ? G4 / kThreads : 1;    // window register sets per thread
