@@ -299,6 +299,8 @@ def run_ours(args):
 
 def main():
     args = parse_args()
+    # NCCL writes its debug lines (e.g. "NCCL version ..." under NCCL_DEBUG=VERSION) to stdout: keep stdout = ONE JSON line
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     if args.batch is None:
         args.batch = 8 if args.workload.startswith("train") else 512
     if args.workload.startswith("train"):
