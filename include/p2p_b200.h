@@ -287,6 +287,14 @@ int p2p_mdct2_analysis(const float* x, float* spec, const float* window, const v
 int p2p_mdct2_synthesis(const float* spec, float* out, const float* window, const void* tables, int B, int F, int64_t T_out,
                         int n_fft, int hop, int win, int64_t crop_left, float scale, float c0, void* stream);
 
+/* ---- device-side resampling for the data path (data/audio_dataset.py:56-58 -> torchaudio.functional.resample) ---------
+ * out[b, i*new_freq + j] = sum_{k < 2*width+orig} bank[j, k] * x_pad[b, i*orig + k], x_pad = x shifted right by `width`
+ * zeros and zero-extended; orig / new_freq already divided by their gcd; bank [new_freq, 2*width+orig] fp32 on the
+ * device (the windowed-sinc filter bank of torchaudio's _get_sinc_resample_kernel, built by the caller);
+ * T_out <= ceil(new_freq * T / orig). */
+int p2p_resample(const float* x, const float* bank, float* out, int B, long long T, long long T_out, int orig, int new_freq,
+                 int width, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

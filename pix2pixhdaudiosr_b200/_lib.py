@@ -77,6 +77,7 @@ _SIGS.update({
     "p2p_mdct2_fill_tables": (_i, [_i, _vp]),
     "p2p_mdct2_analysis": (_i, [_vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _i, _ll, _f, _f, _vp]),
     "p2p_mdct2_synthesis": (_i, [_vp, _vp, _vp, _vp, _i, _i, _ll, _i, _i, _i, _ll, _f, _f, _vp]),
+    "p2p_resample": (_i, [_vp, _vp, _vp, _i, _ll, _ll, _i, _i, _i, _vp]),
     "p2p_frame_window": (_i, [_vp, _vp, _vp, _i, _ll, _i, _i, _i, _ll, _vp]),
     "p2p_frames_db_fwd": (_i, [_vp, _vp, _f, _vp, _ll, _i, _f, _vp]),
     "p2p_frames_db_bwd": (_i, [_vp, _vp, _f, _vp, _vp, _ll, _i, _f, _vp]),
