@@ -11,7 +11,7 @@ namespace p2p {
 namespace {
 
 constexpr int kTh = 256;
-constexpr int kMaxBank = 12288;      // floats of filter bank staged in shared memory (48 KB)
+constexpr int kMaxBank = 28160;      // floats of filter bank staged in shared memory (110 KB: two CTAs per SM)
 
 __global__ void __launch_bounds__(kTh) resample_kernel(const float* __restrict__ x, const float* __restrict__ bank,
                                                        float* __restrict__ out, long long T, long long T_out, int orig,
@@ -54,9 +54,16 @@ extern "C" int p2p_resample(const float* x, const float* bank, float* out, int B
     if ((T_out - 1) / new_freq > T / orig) return fail(P2P_EINVAL, "T_out=%lld exceeds what %lld input samples produce", T_out, T);
     const long long words = (long long)new_freq * K;
     const int in_smem = words <= kMaxBank;
-    long long blocks = (T_out + kTh - 1) / kTh;
+    // a CTA stages the whole bank: with a large bank (e.g. 44.1 -> 48 kHz: 160 phases x 161 taps = 103 KB) it has to
+    // amortise that over many outputs (64 per thread), with a small one (48 <-> 8 kHz: 80-90 words) one per thread
+    const long long per_cta = (long long)kTh * (words > 2048 ? 64 : 1);
+    long long blocks = (T_out + per_cta - 1) / per_cta;
     if (blocks > 148 * 16) blocks = 148 * 16;
     dim3 grid((unsigned)blocks, B);
+    if (in_smem && words * 4 > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(resample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(words * 4));
+        if (e != cudaSuccess) return fail(P2P_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    }
     resample_kernel<<<grid, kTh, in_smem ? words * 4 : 0, (cudaStream_t)stream>>>(x, bank, out, T, T_out, orig, new_freq, width, K, in_smem);
     return check_launch("resample_kernel");
 }
