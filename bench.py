@@ -299,8 +299,11 @@ def run_ours(args):
 
 def main():
     args = parse_args()
-    # NCCL writes its debug lines (e.g. "NCCL version ..." under NCCL_DEBUG=VERSION) to stdout: keep stdout = ONE JSON line
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # Native libraries write to file descriptor 1 (NCCL prints "NCCL version ..." there): keep stdout = ONE JSON line by
+    # pointing fd 1 at stderr and giving Python's own stdout a private copy of the original descriptor
+    sys.stdout.flush()
+    sys.stdout = os.fdopen(os.dup(1), "w", buffering=1)
+    os.dup2(2, 1)
     if args.batch is None:
         args.batch = 8 if args.workload.startswith("train") else 512
     if args.workload.startswith("train"):
