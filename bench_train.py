@@ -9,6 +9,16 @@ WORKLOAD = ("G3L2 ngf48 LocalEnhancer + 2-scale D (ndf 64), GAN + feature matchi
             "(train.py:148-184), batch %d x 65024-sample 48 kHz segments per GPU -> [%d,2,512,128] MDCT4 spectrograms")
 
 
+def workload_name(args):
+    """the `config.workload` string, identical in both arms"""
+    B = args.batch
+    name = WORKLOAD % (B, B)
+    if args.workload == "train_time":
+        name += ("; + time-domain D on [%d,2,128,%d] frames and frame-match loss "
+                 "(--use_time_D --lambda_time 10 --use_match_loss)" % (B, 512 if getattr(args, "transform", "mdct4") == "mdct2" else 1024))
+    return name
+
+
 def synth_audio(B, seed, T=None):
     import torch
     g = torch.Generator().manual_seed(seed)
@@ -51,7 +61,7 @@ def _mdct_roofline(dev, steps=10, B=512, T=130816):
             "hbm_peak_GBps": peak, "peak_source": src}
 
 
-def cpu_train_step_seconds(batch=1, steps=1):
+def cpu_train_step_seconds(batch=1, steps=1, workload="train", transform="mdct4"):
     """the oracle port of the reference's optimisation step (oracle/pix2pixhd_oracle.py: plain torch CPU ops on
     reference-format state_dicts) on all host threads; returns (seconds per step, threads)"""
     import torch
@@ -62,9 +72,16 @@ def cpu_train_step_seconds(batch=1, steps=1):
            'up_ratio': 6.0, 'lambda_feat': 10.0,
            'G': {'netG': 'local', 'n_downsample_global': 4, 'n_blocks_global': 3, 'n_local_enhancers': 1, 'n_blocks_local': 2},
            'D': {'num_D': 2, 'n_layers_D': 3}}
+    sdT, t_seg = None, None
+    if transform == "mdct2":                # the shipped wiring: n_fft 512 / hop 256 on 32 512-sample segments
+        cfg.update(transform="mdct2", n_fft=512, hop_length=256, win_length=512)
+        t_seg = 127 * 256
+    if workload == "train_time":            # config 4: + time-domain D on frames + frame-match loss
+        cfg.update(use_time_D=True, use_match_loss=True, lambda_time=10.0, lambda_mat=10.0)
+        sdT = O.random_time_D_state_dict()
     sdG, sdD = O.random_state_dicts()
-    st = O.TrainState(sdG, sdD, cfg)
-    lr, hr = synth_audio(batch, 7)
+    st = O.TrainState(sdG, sdD, cfg, sdT=sdT)
+    lr, hr = synth_audio(batch, 7, t_seg)
     t = []
     for _ in range(steps):
         t0 = time.perf_counter()
@@ -80,7 +97,8 @@ def run_train_reference(args):
     if int(os.environ.get("RANK", "0")) != 0:
         return
     steps = max(1, min(args.steps, 6))
-    sec, threads = cpu_train_step_seconds(batch=1, steps=steps + min(args.warmup, 1))
+    sec, threads = cpu_train_step_seconds(batch=1, steps=steps + min(args.warmup, 1), workload=args.workload,
+                                           transform=getattr(args, "transform", "mdct4"))
     val = round(1.0 / sec, 5)
     sample = (f"batch 1 (bounded sample of the batch-{args.batch} step), {steps} timed step(s) of the requested "
               f"{args.steps}, oracle/pix2pixhd_oracle.py on {threads} threads")
@@ -88,7 +106,7 @@ def run_train_reference(args):
         "impl": "reference", "metric": METRIC, "value": val, "unit": "samples/s", "n_gpus": args.gpus, "steps": steps,
         "warmup": min(args.warmup, 1), "ms_per_step": round(sec * 1e3, 1), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD % (args.batch, args.batch), "sample": sample},
+        "config": {"workload": workload_name(args), "transform": getattr(args, "transform", "mdct4"), "sample": sample},
         "cpu_baseline": {"value": val, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
@@ -219,8 +237,7 @@ def run_train(args):
             "metric": METRIC, "value": round(B * world * K / (total_ms * 1e-3), 2), "unit": "samples/s", "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": round(step_ms, 3), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
-            "config": {"workload": WORKLOAD % (B, B) + ("; + time-domain D on [%d,2,128,1024] frames and frame-match loss "
-                                                          "(--use_time_D --lambda_time 10 --use_match_loss)" % B if extra else ""),
+            "config": {"workload": workload_name(args),
                        "transform": getattr(args, "transform", "mdct4") + (" (n_fft 512, hop 256, 32512-sample segments)" if t_seg != T_SEG else ""),
                        "global_batch": B * world, "parallelism": f"dp{world}",
                        "launch": "eager" if args.no_graph else "one CUDA graph replay per step",
@@ -250,7 +267,7 @@ def run_train(args):
         torch.cuda.empty_cache()
         out["mdct4"] = _mdct_roofline(dev)
         if world == 1 and not args.no_cpu_baseline:
-            sec, threads = cpu_train_step_seconds(batch=1, steps=1)
+            sec, threads = cpu_train_step_seconds(batch=1, steps=1, workload=args.workload, transform=getattr(args, "transform", "mdct4"))
             out["cpu_baseline"] = {"value": round(1.0 / sec, 5), "unit": "samples/s", "cores": threads, "kind": "port",
                                    "sample": "one optimisation step at batch 1 (bounded sample of the batch-8 step), "
                                              "oracle/pix2pixhd_oracle.py (torch CPU restatement of networks.py / "

@@ -353,3 +353,20 @@ def random_state_dicts(ngf=48, ndf=64, input_nc=2, output_nc=2, n_down=4, n_bloc
             add(sdD, f'scale{s}_layer{j}.0', cout, prev, 4)
             prev, nf = cout, min(nf * 2, 512)
     return sdG, sdD
+
+
+def random_time_D_state_dict(ndf=64, num_D=2, n_layers_D=3, seed=4321):
+    """time_D = define_D(2, ndf, n_layers_D, ..., num_D, getIntermFeat=False) (pix2pixHD_model.py:64-65): keys
+    layer{s}.{0,2,5,8,11}.*; same N(0, 0.02) draw as random_state_dicts.  For timing and smoke runs only."""
+    g = torch.Generator().manual_seed(seed)
+    sd = {}
+    idx = [0] + [2 + 3 * k for k in range(n_layers_D + 1)]
+    for s in range(num_D):
+        nf, prev = ndf, 2
+        for j, i in enumerate(idx):
+            cout = 1 if j == n_layers_D + 1 else nf
+            sd[f'layer{s}.{i}.weight'] = torch.randn((cout, prev, 4, 4), generator=g) * 0.02
+            bound = 1 / math.sqrt(prev * 16)
+            sd[f'layer{s}.{i}.bias'] = (torch.rand(cout, generator=g) * 2 - 1) * bound
+            prev, nf = cout, min(nf * 2, 512)
+    return sd
