@@ -64,3 +64,74 @@ def test_mdct2_matches_reference(ref, case):
     y = O2.imdct2_forward(ref[case + "/spec"], w, n_fft, hop, center)
     assert y.shape == ref[case + "/y"].shape
     assert relerr(y, ref[case + "/y"]) < 2e-6
+
+
+# ---- host side of csrc/mdct2.cu: the tables the C ABI fills, and the kernels' index formulas restated in numpy -----
+def _tables(N):
+    import ctypes
+    from pix2pixhdaudiosr_b200 import _lib
+    lib = _lib.lib()
+    words = lib.p2p_mdct2_table_words(N)
+    assert words == 6 * N
+    buf = np.zeros(words, np.int32)
+    assert lib.p2p_mdct2_fill_tables(N, ctypes.c_void_p(buf.ctypes.data)) == 0
+    f = buf.view(np.float32)
+    tw = f[0:2 * N:2] + 1j * f[1:2 * N:2]
+    roots = f[2 * N:4 * N:2] + 1j * f[2 * N + 1:4 * N:2]
+    return tw.astype(np.complex128), roots.astype(np.complex128), buf[4 * N:5 * N].copy(), buf[5 * N:6 * N].copy()
+
+
+def _dif_fft(z, roots):
+    """the in-place radix-4 (+ final radix-2) DIF passes of csrc/smem_fft.cuh: natural-order in, permuted out"""
+    z = z.copy()
+    L = len(z)
+    S = L
+    while S >= 4:
+        q = S // 4
+        step = L // S
+        for blk in range(L // S):
+            for j in range(q):
+                p = blk * S + j
+                a0, a1, a2, a3 = z[p], z[p + q], z[p + 2 * q], z[p + 3 * q]
+                s02, d02, s13, d13 = a0 + a2, a0 - a2, a1 + a3, a1 - a3
+                z[p] = s02 + s13
+                z[p + q] = (d02 - 1j * d13) * roots[step * j]
+                z[p + 2 * q] = (s02 - s13) * roots[step * 2 * j]
+                z[p + 3 * q] = (d02 + 1j * d13) * roots[step * 3 * j]
+        S = q
+    if S == 2:
+        for r in range(L // 2):
+            a0, a1 = z[2 * r], z[2 * r + 1]
+            z[2 * r], z[2 * r + 1] = a0 + a1, a0 - a1
+    return z
+
+
+@pytest.mark.parametrize("N", [4, 8, 64, 512])
+def test_kernel_algorithm_with_the_library_tables(N):
+    """paired-frame Makhoul DCT-II / its inverse exactly as mdct2_analysis_kernel / mdct2_synthesis_kernel index them,
+    on the tables p2p_mdct2_fill_tables produces (host-only call: no GPU needed)"""
+    tw, roots, perm, inv = _tables(N)
+    assert sorted(perm) == list(range(N)) and all(inv[perm[p]] == p for p in range(N))
+    assert np.abs(tw - np.exp(-1j * np.pi * np.arange(N) / (2 * N))).max() < 1e-7
+    rng = np.random.default_rng(N)
+    uA, uB = rng.standard_normal(N), rng.standard_normal(N)
+    idx = np.array([2 * p if p < N // 2 else 2 * (N - 1 - p) + 1 for p in range(N)])
+    Z = _dif_fft(uA[idx] + 1j * uB[idx], roots)
+    assert np.abs(Z[inv] - np.fft.fft(uA[idx] + 1j * uB[idx])).max() < 1e-5 * N        # position inv[k] holds bin k
+    k = np.arange(N)
+    a, m = Z[inv[k]], Z[inv[(N - k) % N]]
+    va, vb = a + np.conj(m), -1j * (a - np.conj(m))
+    XA, XB = (va * tw).real / N, (vb * tw).real / N
+    assert relerr(XA, O2.dct_2n(uA)) < 1e-5 and relerr(XB, O2.dct_2n(uB)) < 1e-5
+    # inverse: h[k] = tw[k] (X[k] + j X[N-k]) / 2, h[0] = c0 X[0]; FFT(hA + j hB) = vA + j vB; y[idx(n)] = 2 v[n]
+    def h(X, c0):
+        out = 0.5 * tw * (X + 1j * X[(N - k) % N])
+        out[0] = c0 * X[0]
+        return out
+    V = _dif_fft(h(XA, 0.5) + 1j * h(XB, 0.5), roots)
+    yA, yB = np.zeros(N), np.zeros(N)
+    for p in range(N):
+        n = perm[p]
+        yA[idx[n]], yB[idx[n]] = 2 * V[p].real, 2 * V[p].imag
+    assert relerr(yA, O2.idct_2n(XA)) < 1e-5 and relerr(yB, O2.idct_2n(XB)) < 1e-5
+    assert relerr(yA, 2 * uA) < 1e-5                                                    # IDCT(DCT(u)) = 2u
