@@ -110,3 +110,21 @@ def test_transposed_image_discriminator_keeps_the_reference_state_dict():
             pa, pb = ma.physical_weight(), mb.physical_weight()
             assert pa.is_contiguous() and pb.is_contiguous()
             assert torch.equal(pb, pa.transpose(0, 1))
+
+
+def test_time_domain_discriminator_layers_take_the_window_form_only_when_transposed():
+    """time_D sees [frames = 128, n_fft = 1024] maps: with the long axis fastest the halo (K-1) * padded width exceeds the
+    shifted-window kernel's 312 rows; transposed (what define_D(..., transposed_image=True) runs) every layer fits"""
+    import torch
+    from pix2pixhdaudiosr_b200 import ops
+    for (H, W, Cin, Cout, stride) in [(1024, 128, 64, 128, 2), (513, 65, 128, 256, 2), (257, 33, 256, 512, 1)]:
+        fwd_t = ops.conv_fwd_passes(8, H, W, Cin, Cout, 4, 4, stride, 2, ops.PAD_ZERO)
+        fwd_w = ops.conv_fwd_passes(8, W, H, Cin, Cout, 4, 4, stride, 2, ops.PAD_ZERO)
+        if stride == 1:
+            assert ops._window_ok(torch.bfloat16, Cin, Cout, 4, 4, H + 4, W + 4, False) or not ops.USE_WINDOW
+            assert not ops._window_ok(torch.bfloat16, Cin, Cout, 4, 4, W + 4, H + 4, False)
+        else:
+            assert ops._plan_window_passes(fwd_t, torch.bfloat16) is not None
+            assert ops._plan_window_passes(fwd_w, torch.bfloat16) is None
+        dg_t = ops.conv_dgrad_passes(8, H, W, Cin, Cout, 4, 4, stride, 2, ops.PAD_ZERO)
+        assert dg_t
