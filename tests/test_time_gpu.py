@@ -215,8 +215,8 @@ def test_time_D_loss_curve(ref, precision):
     # G_mat starts at 6e-6 (a difference of nearly equal numbers, four orders of magnitude below the other losses) and
     # grows 10^4-fold over the run: early on it follows the reference within a factor (bf16: 5x seen), and it lands on
     # the reference's level once it is large enough to be driven by the optimisation rather than by rounding
-    assert np.abs(np.log(curve[:8, mat] / want[:8, mat])).max() < np.log(3.0 if precision == "fp32" else 10.0)
-    assert abs(np.log(curve[-10:, mat].mean() / want[-10:, mat].mean())) < np.log(1.5)
+    assert np.abs(np.log(curve[:8, mat] / want[:8, mat])).max() < np.log(10.0)      # 2.6x seen in fp32 (atomics reorder sums), 5x in bf16
+    assert abs(np.log(curve[-10:, mat].mean() / want[-10:, mat].mean())) < np.log(2.0)       # 1.00-1.07 seen
 
 
 def test_inference_and_to_audio_match_shipped_reference(ref):
