@@ -33,6 +33,10 @@ const char* p2p_last_error(void);
 int p2p_abi_version(void);
 /* Number of kernel launches this process has issued through the entry points below (bench.py's gpu_launches). */
 long long p2p_kernel_launches(void);
+/* Deterministic mode (also: environment P2P_DETERMINISTIC=1): every floating-point reduction runs with one writer per
+ * address -- no split-K / split-pixel red.add between CTAs, single-chunk statistics, single-CTA loss sums -- so results are
+ * bit-reproducible run to run, at lower parallelism on the few-tile layers.  on < 0 only queries.  Returns the old value. */
+int p2p_set_deterministic(int on);
 
 /* ---- MDCT4 / IMDCT4 ------------------------------------------------------------------------
  * M = n_fft/2 bins, L = M/2 = complex FFT length.  n_fft: power of two, 16..4096.
@@ -144,6 +148,8 @@ typedef struct {
     int wrap;   /* != 0: taps may read past their sub-pass grid (y + dh >= Hp wraps into the next rows / image of the flattened
                  * plane): the caller guarantees those pixels hold zeros.  Used by the input-gradient pass that shares the
                  * weight-gradient's copy of dout (dout at the pitch of the padded input, zero prefix before the first image) */
+    long long plane_rows;   /* rows between consecutive planes; 0 = N*Hp*Wp (densely packed).  The window weight-gradient kernel
+                             * wants planes of a multiple of 64 rows with a zero tail: one copy then serves both passes */
 } p2p_conv_window_desc;
 int p2p_pad_planes(const void* x, void* planes, int N, int H, int W, int C, int pt, int pl, int Hh, int Wh, int s,
                    long long plane_rows /* >= N*Hh*Wh; the tail of every plane is zero-filled */, int reflect /* s == 1 only */,
@@ -162,6 +168,25 @@ int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const void* bplane
 int p2p_conv_window_debug_buffer(long long* buf);
 int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* planes, const void* weight, const float* bias, void* out,
                         int out_dtype, void* stream);
+/* The same launches with InstanceNorm's statistics taken in the epilogue (replaces the separate reduction over the conv
+ * output that models/networks.py:190-207's `norm_layer` implies): stats [N][J][2] fp32 is zeroed and then receives, per
+ * (image, output channel), the sum and the sum of squares of (out - bias) over the written pixels.  Needs an fp32 output,
+ * J % 4 == 0 and an unsplit channel loop (enough tiles to fill the chip): P2P_ENOTSUP otherwise, nothing launched. */
+int p2p_conv_window_stats(const void* xp, const void* weight, const float* bias, void* out, int N, int Hp, int Wp, int C, int J,
+                          int KH, int KW, int flip, long long w_tap, long long w_k, long long w_j, int out_dtype, float* stats,
+                          void* stream);
+int p2p_conv_window_run_stats(const p2p_conv_window_desc* d, const void* planes, const void* weight, const float* bias, void* out,
+                              int out_dtype, float* stats, void* stream);
+/* z = act(InstanceNorm(y)) + res written DIRECTLY as the next convolution's input: s*s planes of plane_rows rows x C bf16 in
+ * the geometry of p2p_pad_planes (plane (a,b)[n,yy,xx,:] = z[n, s*yy+a-pt, s*xx+b-pl, :], zero or -- s == 1 -- reflection
+ * outside, zero tail), and optionally the plain bf16 NHWC tensor z_out too.  y [N,H,W,C] of y_dtype.  stats_in [N,C,2]:
+ * raw_mode 1 = the (sum, sum of squares) of (y - bias) from p2p_conv_window_*_stats, stats_out [N,C,2] then receives
+ * (mean, rstd) for p2p_instnorm_act_bwd; raw_mode 0 = (mean, rstd) already.  res: bf16 with element strides per image / row /
+ * pixel (channels contiguous) or NULL.  C % 8 == 0. */
+int p2p_instnorm_act_planes(const void* y, const float* bias, const float* stats_in, int raw_mode, float* stats_out,
+                            const void* res, long long res_sn, long long res_sh, long long res_sw, void* planes, void* z_out,
+                            int N, int H, int W, int C, int pt, int pl, int Hh, int Wh, int s, long long plane_rows, int reflect,
+                            int norm, int act, float slope, float eps, int y_dtype, void* stream);
 /* Adjoint of reflection padding: dx[n,h,w,c] = sum of dxp over the padded positions that mirror onto (h,w).
  * dxp is [N, H+2p, W+2p, C], dx is [N,H,W,C]. */
 int p2p_reflect_pad_fold(const void* dxp, void* dx, int N, int H, int W, int C, int p, int dtype, void* stream);
@@ -198,6 +223,8 @@ int p2p_instnorm_act_fwd(const void* y, const void* res, void* z, float* stats, 
  * work: fp32 scratch [N,C,2] (ignored when norm == 0). */
 int p2p_instnorm_act_bwd(const void* y, const float* stats, const void* dz, void* dy, float* work, int N,
                          long long HW, int C, int norm, int act, float slope, int y_dtype, int dtype, void* stream);
+/* stats [N,C,2] = (mean, rstd) of y [N,HW,C] alone: the reduction half of p2p_instnorm_act_fwd, for p2p_instnorm_act_planes. */
+int p2p_instnorm_stats(const void* y, float* stats, int N, long long HW, int C, float eps, int y_dtype, void* stream);
 
 /* AvgPool2d(3, stride 2, padding 1, count_include_pad=False), NHWC. OH=(H-1)/2+1, OW=(W-1)/2+1. */
 int p2p_avgpool3s2_fwd(const void* x, void* y, int N, int H, int W, int C, int dtype, void* stream);

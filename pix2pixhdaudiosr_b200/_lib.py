@@ -11,6 +11,7 @@ _SIGS = {
     "p2p_last_error": (_c.c_char_p, []),
     "p2p_abi_version": (_c.c_int, []),
     "p2p_kernel_launches": (_c.c_longlong, []),
+    "p2p_set_deterministic": (_c.c_int, [_c.c_int]),
     "p2p_mdct4_force_general": (_c.c_int, [_c.c_int]),
     "p2p_mdct4_table_words": (_c.c_int, [_c.c_int]),
     "p2p_mdct4_fill_tables": (_c.c_int, [_c.c_int, _c.c_void_p]),
@@ -40,7 +41,7 @@ class WindowDesc(ctypes.Structure):
                 ("gy", _i * 4), ("gx", _i * 4), ("oyo", _i * 4), ("oxo", _i * 4), ("ntaps", _i),
                 ("tap_sub", _c.c_byte * MAX_TAPS), ("tap_plane", _c.c_byte * MAX_TAPS),
                 ("tap_dh", _c.c_short * MAX_TAPS), ("tap_dw", _c.c_short * MAX_TAPS), ("tap_w", _c.c_ubyte * MAX_TAPS),
-                ("wrap", _i)]
+                ("wrap", _i), ("plane_rows", _ll)]
 
 
 _SIGS.update({
@@ -54,6 +55,9 @@ _SIGS.update({
     "p2p_conv_wgrad_window": (_i, [_vp, _i, _vp, _i, _ll, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "p2p_conv_window_debug_buffer": (_i, [_vp]),
     "p2p_conv_window_run": (_i, [_c.POINTER(WindowDesc), _vp, _vp, _vp, _vp, _i, _vp]),
+    "p2p_conv_window_stats": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _vp, _vp]),
+    "p2p_conv_window_run_stats": (_i, [_c.POINTER(WindowDesc), _vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "p2p_instnorm_act_planes": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _ll, _ll, _ll, _vp, _vp] + [_i] * 9 + [_ll, _i, _i, _i, _f, _f, _i, _vp]),
     "p2p_bias_grad": (_i, [_vp, _vp, _ll, _i, _i, _vp]),
     "p2p_reflect_pad_fold": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_pack_in": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
@@ -64,6 +68,7 @@ _SIGS.update({
     "p2p_pack_dy_full": (_i, [_vp, _vp] + [_i] * 7 + [_ll, _vp]),
     "p2p_instnorm_act_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _f, _f, _i, _i, _vp]),
     "p2p_instnorm_act_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _f, _i, _i, _vp]),
+    "p2p_instnorm_stats": (_i, [_vp, _vp, _i, _ll, _i, _f, _i, _vp]),
     "p2p_avgpool3s2_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "p2p_avgpool3s2_bwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "p2p_tanh_fwd": (_i, [_vp, _vp, _ll, _i, _vp]),

@@ -10,8 +10,17 @@ long long& launch_counter() {
     static long long n = 0;
     return n;
 }
+int& deterministic_flag() {
+    static int f = -1;
+    return f;
+}
 }  // namespace p2p
 
 extern "C" const char* p2p_last_error(void) { return p2p::error_slot(); }
-extern "C" int p2p_abi_version(void) { return 2; }
+extern "C" int p2p_abi_version(void) { return 3; }
+extern "C" int p2p_set_deterministic(int on) {      // negative only queries; returns the old value
+    const int old = p2p::deterministic() ? 1 : 0;
+    if (on >= 0) p2p::deterministic_flag() = on ? 1 : 0;
+    return old;
+}
 extern "C" long long p2p_kernel_launches(void) { return p2p::launch_counter(); }

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include "../../include/p2p_b200.h"
 
 namespace p2p {
@@ -24,6 +25,16 @@ inline int check_launch(const char* what) {
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(P2P_ECUDA, "%s: %s", what, cudaGetErrorString(e));
     return P2P_OK;
+}
+
+int& deterministic_flag();      // -1 = not read yet (defined in c_abi.cu; env P2P_DETERMINISTIC, p2p_set_deterministic)
+// Deterministic mode: no kernel lets several CTAs add floating-point partial results into one address in an order that
+// depends on scheduling (split-K / split-pixel red.add, multi-chunk statistics and loss atomics): every reduction runs
+// with one writer per address, at lower parallelism.  Results are then bit-reproducible run to run.
+inline bool deterministic() {
+    int& f = deterministic_flag();
+    if (f < 0) { const char* e = getenv("P2P_DETERMINISTIC"); f = (e && e[0] == '1') ? 1 : 0; }
+    return f != 0;
 }
 
 inline bool is_pow2(long long v) { return v > 0 && (v & (v - 1)) == 0; }

@@ -188,7 +188,7 @@ int conv_wgrad_simple_launch(const p2p_conv_pass* P, const void* in, const void*
     long long S = (148LL * 4) / ((long long)gk * gj * P->ntaps);
     const long long maxS = (M + 255) / 256;
     if (S > maxS) S = maxS;
-    if (S < 1) S = 1;
+    if (S < 1 || deterministic()) S = 1;        // one CTA per (tap, k tile, j tile): its atomicAdd is the only write of the call
     if ((long long)P->ntaps * S > 65535) S = 65535 / P->ntaps;
     long long mchunk = (M + S - 1) / S;
     mchunk = (mchunk + BK - 1) / BK * BK;

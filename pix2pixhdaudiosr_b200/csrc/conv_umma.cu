@@ -514,7 +514,7 @@ int conv_forward_umma(const p2p_conv_pass* P, const void* in, const void* weight
     for (int bn = 16; bn <= 256; bn += 16) {
         const long long nt = (P->J + bn - 1) / bn;
         if (bn > 16 && nt == (P->J + bn - 17) / (bn - 16)) continue;     // a narrower tile covers J equally
-        const int max_split = can_split ? (a.total_kb >= 8 ? a.total_kb / 4 : 1) : 1;
+        const int max_split = (can_split && !deterministic()) ? (a.total_kb >= 8 ? a.total_kb / 4 : 1) : 1;
         for (int sp = 1; sp <= max_split; sp = sp < 4 ? sp + 1 : sp * 2) {
             const long long items = mt * nt * sp;
             const long long rounds = (items + sms - 1) / sms;
@@ -562,7 +562,7 @@ int conv_wgrad_umma(const p2p_conv_pass* P, const void* in, const void* dout, fl
         nsplit = (int)((2LL * sm_count() + tiles - 1) / tiles);
         const int max_split = a.total_kb / 4;
         if (nsplit > max_split) nsplit = max_split;
-        if (nsplit < 1) nsplit = 1;
+        if (nsplit < 1 || deterministic()) nsplit = 1;
     }
     a.kb_per_split = (a.total_kb + nsplit - 1) / nsplit;
     a.nsplit = (a.total_kb + a.kb_per_split - 1) / a.kb_per_split;

@@ -43,7 +43,10 @@ struct WindowArgs {
     CUtensorMap tm_w;        // weights: K-major [taps*J rows][C] box [64][BN]; MN-major [taps*K rows][J] box [64][64]
     const float* bias;
     void* out;
+    float* stats;            // optional [N][J][2] fp32, zeroed by the host: per (image, channel) sum and sum of squares of the
+                             // bias-free accumulators over the valid output pixels (InstanceNorm statistics from the epilogue)
     long long Q;             // GEMM rows = padded pixels of one plane
+    long long Qp;            // rows between consecutive planes (>= Q)
     int N, Hp, Wp, C, J;
     int OHf, OWf, oys, oxs;  // output tensor extent and scatter stride: pixel (y*oys+oyo, x*oxs+oxo)
     int ntaps, nplanes, nsub;
@@ -107,6 +110,50 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint6
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+// ---- CTA pairs (tcgen05 cta_group::2): one MMA covers 2 x 128 rows, each CTA holds half of the B tile ------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t saddr, uint32_t rank) {      // shared::cluster address of `saddr` in CTA `rank`
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx_cluster(uint32_t cbar, uint32_t bytes) {     // cbar: shared::cluster address
+    asm volatile("mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [%0], %1;" ::"r"(cbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cbar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cbar) : "memory");
+}
+// TMA load into this CTA's shared memory whose completion is signalled on the LEADER CTA's barrier (cbar: shared::cluster address)
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* tm, int c0, int c1, uint32_t cbar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+        "l"(tm), "r"(c0), "r"(c1), "r"(cbar) : "memory");
+}
+__device__ __forceinline__ void umma2_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc),
+        "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma2_commit(uint32_t bar) {        // arrives on `bar` (same offset) in BOTH CTAs of the pair
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+                 "h"((uint16_t)3) : "memory");
+}
+template <int CG> __device__ __forceinline__ void umma_cg(uint32_t d, uint64_t ad, uint64_t bd, uint32_t idesc, uint32_t acc) {
+    if constexpr (CG == 2) umma2_bf16(d, ad, bd, idesc, acc); else umma_bf16(d, ad, bd, idesc, acc);
+}
+template <int CG> __device__ __forceinline__ void commit_cg(uint32_t bar) {
+    if constexpr (CG == 2) umma2_commit(bar); else umma_commit(bar);
+}
+
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
@@ -132,9 +179,12 @@ template <int P> __device__ __forceinline__ int piece_swz(int row) {
 enum { EPI_ST = 0, EPI_RED = 1 };
 // regs: this lane's row chunk as P 16-byte pieces.  row_off: byte offset of this lane's row start (chunk column 0) in out;
 // okmask: ballot of valid rows; valid_bytes: bytes of the chunk inside the tensor (multiple of esz).
+// st: statistics target of this chunk's first column (nullptr: none), &stats[(n*J + column) * 2], valid when all valid rows of
+// the warp belong to image n; bias4: shared-memory address of the chunk's staged bias values (statistics are taken of v - bias).
 template <int P>
 __device__ __forceinline__ void stage_store_chunk(uint32_t stage, int lane, const uint32_t* regs, long long row_off, unsigned okmask,
-                                                  char* out, int valid_bytes, int mode, int esz) {
+                                                  char* out, int valid_bytes, int mode, int esz, float* st = nullptr,
+                                                  const float* bias4 = nullptr) {
     __syncwarp();                               // the previous chunk's reads of the tile are done
 #pragma unroll
     for (int p = 0; p < P; ++p)
@@ -142,6 +192,11 @@ __device__ __forceinline__ void stage_store_chunk(uint32_t stage, int lane, cons
                      "r"(regs[4 * p]), "r"(regs[4 * p + 1]), "r"(regs[4 * p + 2]), "r"(regs[4 * p + 3]) : "memory");
     __syncwarp();
     const int p = lane % P, r0 = lane / P;
+    float sa[4] = {0.f, 0.f, 0.f, 0.f}, sq[4] = {0.f, 0.f, 0.f, 0.f}, bb[4] = {0.f, 0.f, 0.f, 0.f};
+    if (st) {
+        const float4 b4 = *reinterpret_cast<const float4*>(bias4 + p * 4);
+        bb[0] = b4.x; bb[1] = b4.y; bb[2] = b4.z; bb[3] = b4.w;
+    }
 #pragma unroll
     for (int k = 0; k < P; ++k) {
         const int row = r0 + (32 / P) * k;
@@ -150,6 +205,12 @@ __device__ __forceinline__ void stage_store_chunk(uint32_t stage, int lane, cons
                      : "r"(stage + (uint32_t)(row * P + (p ^ piece_swz<P>(row))) * 16u));
         const long long ro = __shfl_sync(0xffffffffu, row_off, row);
         if (!((okmask >> row) & 1u)) continue;
+        if (st) {           // fp32 pieces: this lane sees the same 4 columns in every row it reads
+            const float d0 = __uint_as_float(v0) - bb[0], d1 = __uint_as_float(v1) - bb[1], d2 = __uint_as_float(v2) - bb[2],
+                        d3 = __uint_as_float(v3) - bb[3];
+            sa[0] += d0; sa[1] += d1; sa[2] += d2; sa[3] += d3;
+            sq[0] += d0 * d0; sq[1] += d1 * d1; sq[2] += d2 * d2; sq[3] += d3 * d3;
+        }
         char* dst = out + ro + p * 16;
         if (p * 16 + 16 <= valid_bytes) {
             if (mode == EPI_RED) red_add_v4(reinterpret_cast<float*>(dst), __uint_as_float(v0), __uint_as_float(v1), __uint_as_float(v2), __uint_as_float(v3));
@@ -167,11 +228,27 @@ __device__ __forceinline__ void stage_store_chunk(uint32_t stage, int lane, cons
             }
         }
     }
+    if (st) {               // lanes p, p + P, ... hold partial sums of the same 4 columns: fold them, one lane per piece adds
+#pragma unroll
+        for (int o = P; o < 32; o <<= 1) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                sa[i] += __shfl_xor_sync(0xffffffffu, sa[i], o);
+                sq[i] += __shfl_xor_sync(0xffffffffu, sq[i], o);
+            }
+        }
+        if (r0 == 0 && p * 16 + 16 <= valid_bytes) {
+            float* t = st + p * 8;          // [column][sum, sum of squares]
+            red_add_v4(t, sa[0], sq[0], sa[1], sq[1]);
+            red_add_v4(t + 4, sa[2], sq[2], sa[3], sq[3]);
+        }
+    }
 }
 __device__ __forceinline__ void stage_store(int P, uint32_t stage, int lane, const uint32_t* regs, long long row_off, unsigned okmask,
-                                            char* out, int valid_bytes, int mode, int esz) {
-    if (P == 8) stage_store_chunk<8>(stage, lane, regs, row_off, okmask, out, valid_bytes, mode, esz);
-    else if (P == 4) stage_store_chunk<4>(stage, lane, regs, row_off, okmask, out, valid_bytes, mode, esz);
+                                            char* out, int valid_bytes, int mode, int esz, float* st = nullptr,
+                                            const float* bias4 = nullptr) {
+    if (P == 8) stage_store_chunk<8>(stage, lane, regs, row_off, okmask, out, valid_bytes, mode, esz, st, bias4);
+    else if (P == 4) stage_store_chunk<4>(stage, lane, regs, row_off, okmask, out, valid_bytes, mode, esz, st, bias4);
     else stage_store_chunk<2>(stage, lane, regs, row_off, okmask, out, valid_bytes, mode, esz);
 }
 
@@ -183,7 +260,7 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
 
 // the MMAs of one weight-ring stage: up to 4 taps x up to 4 k16 steps, each against MREP 128-row halves of the window (the
 // halves share the weight tile, so it is written to shared memory once per 128*MREP pixels)
-template <int MREP>
+template <int MREP, int CG>
 __device__ __forceinline__ void issue_stage(uint32_t d_tmem, uint32_t half_cols, uint32_t a_hi, uint32_t b_hi, uint32_t al0, uint32_t al1,
                                             uint32_t al2, uint32_t al3, uint32_t bl, uint32_t b_k16, uint32_t b_tap, uint32_t idesc,
                                             uint32_t meta, uint32_t accumulate) {
@@ -198,7 +275,7 @@ __device__ __forceinline__ void issue_stage(uint32_t d_tmem, uint32_t half_cols,
             for (int j = 0; j < 4; ++j) {
 #pragma unroll
                 for (int h = 0; h < MREP; ++h)
-                    umma_bf16(d_tmem + h * half_cols, mk(a_hi, al[k] + 2 * j + h * A_HALF), mk(b_hi, bk + j * b_k16), idesc,
+                    umma_cg<CG>(d_tmem + h * half_cols, mk(a_hi, al[k] + 2 * j + h * A_HALF), mk(b_hi, bk + j * b_k16), idesc,
                               (k | j) == 0 ? accumulate : 1u);
             }
         }
@@ -213,7 +290,7 @@ __device__ __forceinline__ void issue_stage(uint32_t d_tmem, uint32_t half_cols,
                     if ((uint32_t)j < nk16) {
 #pragma unroll
                         for (int h = 0; h < MREP; ++h)
-                            umma_bf16(d_tmem + h * half_cols, mk(a_hi, al[k] + 2 * j + h * A_HALF), mk(b_hi, bk + j * b_k16), idesc,
+                            umma_cg<CG>(d_tmem + h * half_cols, mk(a_hi, al[k] + 2 * j + h * A_HALF), mk(b_hi, bk + j * b_k16), idesc,
                                       (k | j) == 0 ? accumulate : 1u);
                     }
                 }
@@ -222,8 +299,14 @@ __device__ __forceinline__ void issue_stage(uint32_t d_tmem, uint32_t half_cols,
     }
 }
 
+// CG = 2: the CTAs of a pair (cluster of 2) each own 128*mrep window rows and half of every weight tile; the leader's MMA warp
+// issues tcgen05.mma.cta_group::2 (M = 256) for both.  Measured (profiles/r02_mma_rate_cg2.txt): 46-50 cycles per MMA for
+// N <= 96 against 93 for cta_group::1 -- the per-instruction floor that capped the 96-channel layers at half the tensor peak.
+template <int CG>
 __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __grid_constant__ WindowArgs a) {
     extern __shared__ uint8_t smem_raw[];
+    const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
+    const uint32_t cid = blockIdx.x / CG, ncl = gridDim.x / CG;          // pair index / number of pairs: the work-item stride
 #ifdef P2P_WINDOW_TIMING
     long long g_entry;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g_entry));
@@ -250,23 +333,34 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int BN = a.BN, C = a.C, J = a.J;
     const uint32_t a_bytes = (uint32_t)a.nboxes * a.rows_per_box * 128u;
-    const uint32_t b_bytes = a.b_mn_major ? (uint32_t)((BN + 63) / 64) * 8192u : (uint32_t)BN * 128u;
+    const int BNL = BN / CG;                                             // weight-tile columns held by this CTA
+    const uint32_t b_bytes = a.b_mn_major ? (uint32_t)((BNL + 63) / 64) * 8192u : (uint32_t)BNL * 128u;
 
     if (warp == 1) {
         if (lane == 0) {
-            for (int i = 0; i < 2; ++i) { mbar_init(afull(i), 1); mbar_init(aempty(i), 1); mbar_init(tfull(i), 1); mbar_init(tempty(i), 256); }
-            for (int s = 0; s < kBStages; ++s) { mbar_init(bfull(s), 1); mbar_init(bempty(s), 1); }
+            // full barriers live in the leader: one arrive.expect_tx per CTA of the pair; empty / tfull barriers are local and
+            // receive the (multicast) commit; tempty collects one arrive per epilogue warp of every CTA
+            for (int i = 0; i < 2; ++i) { mbar_init(afull(i), CG); mbar_init(aempty(i), 1); mbar_init(tfull(i), 1); mbar_init(tempty(i), 8 * CG); }
+            for (int s = 0; s < kBStages; ++s) { mbar_init(bfull(s), CG); mbar_init(bempty(s), 1); }
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
         __syncwarp();
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if constexpr (CG == 2) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
     __syncthreads();
+    if constexpr (CG == 2) cluster_sync_all();          // the peer's barriers are initialised before anything arrives on them
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    // barrier addresses as seen from this CTA for arrivals that must land in the leader
+    auto lead = [&](uint32_t bar) { return CG == 2 ? mapa_rank(bar, 0) : bar; };
 
     if (warp == 0) {
         // ================================ TMA producer ================================
@@ -281,14 +375,14 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
             int ia = 0;                     // window loads issued so far
             uint32_t bs = 0, bph = 1;       // weight ring: stage, parity of the "empty" wait (first lap passes at once)
             const uint32_t nwork = (uint32_t)a.nwork, n_tiles = (uint32_t)a.n_tiles, nsplit = (uint32_t)a.nsplit;
-            for (uint32_t w = blockIdx.x; w < nwork; w += gridDim.x) {
+            for (uint32_t w = cid; w < nwork; w += ncl) {
                 const uint32_t nt = w % n_tiles, wr = w / n_tiles;
                 const uint32_t sp = wr % nsplit, mtu = wr / nsplit;
                 const int u = (int)(mtu / (uint32_t)a.m_tiles);
-                const int q0 = (int)(mtu - (uint32_t)u * (uint32_t)a.m_tiles) * (WBM * a.mrep);
-                const int j0 = (int)nt * BN;
+                const int q0 = (int)((mtu - (uint32_t)u * (uint32_t)a.m_tiles) * CG + rank) * (WBM * a.mrep);
+                const int j0 = (int)nt * BN + (int)rank * BNL;
                 const int ci0 = (int)sp * a.ci_per_split, ci1 = min(a.cpb * a.nplanes, ((int)sp + 1) * a.ci_per_split);
-                const uint32_t f_last_tile = (w + gridDim.x >= nwork) ? REC_LAST : 0u;
+                const uint32_t f_last_tile = (w + ncl >= nwork) ? REC_LAST : 0u;
                 for (int ci = ci0; ci < ci1; ++ci, ++ia) {
                     const int cc = ci / a.nplanes, pl = ci - cc * a.nplanes;
                     const int c0 = cc * 64;
@@ -296,9 +390,16 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
                     const int ab = ia & 1;
                     const uint32_t win = base + ab * win_bytes;
                     if (ia >= 2) mbar_wait(aempty(ab), (uint32_t)(((ia >> 1) - 1) & 1));
-                    mbar_expect_tx(afull(ab), a_bytes);
-                    for (int bx = 0; bx < a.nboxes; ++bx)
-                        tma_load_2d(win + bx * a.rows_per_box * 128, &a.tm_x, c0, pl * (int)a.Q + q0 + bx * a.rows_per_box, afull(ab));
+                    if constexpr (CG == 2) {
+                        const uint32_t fb = lead(afull(ab));
+                        mbar_expect_tx_cluster(fb, a_bytes);
+                        for (int bx = 0; bx < a.nboxes; ++bx)
+                            tma_load_2d_pair(win + bx * a.rows_per_box * 128, &a.tm_x, c0, pl * (int)a.Qp + q0 + bx * a.rows_per_box, fb);
+                    } else {
+                        mbar_expect_tx(afull(ab), a_bytes);
+                        for (int bx = 0; bx < a.nboxes; ++bx)
+                            tma_load_2d(win + bx * a.rows_per_box * 128, &a.tm_x, c0, pl * (int)a.Qp + q0 + bx * a.rows_per_box, afull(ab));
+                    }
                     const int t_beg = a.pbeg[u][pl], t_end = a.pbeg[u][pl + 1];
                     for (int t0 = t_beg; t0 < t_end; t0 += a.tps) {       // one ring stage = up to tps taps
                         const int nt_s = min(a.tps, t_end - t0);
@@ -316,6 +417,20 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
                         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(recs + 32u * s), "r"(alo[0]), "r"(alo[1]), "r"(alo[2]),
                                      "r"(alo[3]) : "memory");
                         asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(recs + 32u * s + 16u), "r"(meta), "r"(b_lo | (stage_base >> 4)) : "memory");
+                        if constexpr (CG == 2) {
+                            const uint32_t fb = lead(bfull(s));
+                            mbar_expect_tx_cluster(fb, b_bytes * (uint32_t)nt_s);       // release: the leader's record is visible to the waiter
+                            for (int k = 0; k < nt_s; ++k) {
+                                const int t = t0 + k;
+                                const uint32_t dst = stage_base + (uint32_t)k * TAP_STRIDE;
+                                if (!a.b_mn_major) {
+                                    tma_load_2d_pair(dst, &a.tm_w, c0, (int)a.wtap[t] * J + j0, fb);
+                                } else {
+                                    for (int jb = 0; jb * 64 < BNL; ++jb)
+                                        tma_load_2d_pair(dst + jb * 8192, &a.tm_w, j0 + jb * 64, (int)a.wtap[t] * C + c0, fb);
+                                }
+                            }
+                        } else {
                         mbar_expect_tx(bfull(s), b_bytes * (uint32_t)nt_s);         // release: the record is visible to the waiter
                         for (int k = 0; k < nt_s; ++k) {
                             const int t = t0 + k;
@@ -327,6 +442,7 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
                                     tma_load_2d(dst + jb * 8192, &a.tm_w, j0 + jb * 64, (int)a.wtap[t] * C + c0, bfull(s));
                             }
                         }
+                        }
                     }
                 }
             }
@@ -335,9 +451,9 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
     } else if (warp == 1) {
         // ================================ MMA issuer ================================
         // the whole warp walks the records (keeps every value warp-uniform); one elected lane issues
-        if (blockIdx.x < a.nwork) {
+        if (cid < a.nwork && rank == 0) {
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a.b_mn_major << 16) | ((uint32_t)(BN >> 3) << 17) |
-                                   ((uint32_t)(WBM >> 4) << 24);
+                                   ((uint32_t)((WBM * CG) >> 4) << 24);
             // descriptors: the high words are loop invariant, the low words come from the stage record; per-k16 advance is an
             // add on the low word (+32 B along K for K-major tiles, +2048 B for MN-major weight tiles)
             const uint32_t a_hi = (uint32_t)(make_desc(0, 16, 1024, 0) >> 32);
@@ -382,11 +498,11 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
                 }
                 tc_fence_after();
                 if (elect_one()) {
-                    if (a.mrep == 2) issue_stage<2>(d_tmem, half_cols, a_hi, b_hi, al0, al1, al2, al3, bl, b_k16, b_tap, idesc, meta, accumulate);
-                    else issue_stage<1>(d_tmem, half_cols, a_hi, b_hi, al0, al1, al2, al3, bl, b_k16, b_tap, idesc, meta, accumulate);
-                    umma_commit(bempty(s));
-                    if (meta & REC_CHUNK_LAST) umma_commit(aempty(ia & 1));
-                    if (meta & REC_TILE_LAST) umma_commit(tfull((uint32_t)li & slot_mask));
+                    if (a.mrep == 2) issue_stage<2, CG>(d_tmem, half_cols, a_hi, b_hi, al0, al1, al2, al3, bl, b_k16, b_tap, idesc, meta, accumulate);
+                    else issue_stage<1, CG>(d_tmem, half_cols, a_hi, b_hi, al0, al1, al2, al3, bl, b_k16, b_tap, idesc, meta, accumulate);
+                    commit_cg<CG>(bempty(s));
+                    if (meta & REC_CHUNK_LAST) commit_cg<CG>(aempty(ia & 1));
+                    if (meta & REC_TILE_LAST) commit_cg<CG>(tfull((uint32_t)li & slot_mask));
                 }
                 __syncwarp();
                 accumulate = 1;
@@ -424,13 +540,13 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
         float* bias_s = reinterpret_cast<float*>(smem_raw + (bias_u32 - smem_u32(smem_raw)));
         int li = 0;
         const uint32_t nwork = (uint32_t)a.nwork, n_tiles = (uint32_t)a.n_tiles, nsplit = (uint32_t)a.nsplit;
-        for (uint32_t w = blockIdx.x; w < nwork; w += gridDim.x, ++li) {
+        for (uint32_t w = cid; w < nwork; w += ncl, ++li) {
             const int nt = (int)(w % n_tiles);
             const uint32_t wr = w / n_tiles;
             const int sp = (int)(wr % nsplit);
             const uint32_t mtu = wr / nsplit;
             const int u = (int)(mtu / (uint32_t)a.m_tiles);
-            const uint32_t mt = mtu - (uint32_t)u * (uint32_t)a.m_tiles;
+            const uint32_t mt = (mtu - (uint32_t)u * (uint32_t)a.m_tiles) * CG + rank;
             const int acc = li & (a.acc_slots - 1), v = li >> (a.acc_slots >> 1);
             const int c_begin = nt * BN, c_count = min(BN, J - c_begin);
             float* bs_ = bias_s + (li & 1) * 256;
@@ -454,6 +570,13 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
                 const long long row_off = obase * esz;
                 const uint32_t stage = epi_stage + (uint32_t)ewarp * 4096u;
                 const int mode = a.nsplit > 1 ? EPI_RED : EPI_ST;
+                // InstanceNorm statistics: the warp's valid rows normally lie in one image (n_lo == n_hi): column sums through
+                // the staged tile; a warp that straddles two images adds row by row
+                int n_lo = 0, n_hi = 0;
+                if (a.stats && okmask) {
+                    n_lo = __reduce_min_sync(0xffffffffu, rok ? n : 0x7fffffff);
+                    n_hi = __reduce_max_sync(0xffffffffu, rok ? n : -1);
+                }
                 for (int c2 = c2_lo; c2 < BN; c2 += c2_step) {
                     uint32_t r2[32];
                     const bool two = c2 + 16 < BN;
@@ -482,7 +605,23 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
                         P = ncol / 8;
                     }
                     const int valid = min(ncol, c_count - c2) * esz;
-                    stage_store(P, stage, lane, r2, row_off + (long long)c2 * esz, okmask, (char*)a.out, valid, mode, esz);
+                    float* st = nullptr;
+                    if (a.stats && okmask) {
+                        if (n_lo == n_hi) {
+                            st = a.stats + ((long long)n_lo * J + c_begin + c2) * 2;
+                        } else if (rok) {           // rare: per-row adds (r2 holds acc + bias in fp32 here: stats only with fp32 output)
+                            float* t = a.stats + ((long long)n * J + c_begin + c2) * 2;
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) {          // compile-time register indices: r2 must not move to local memory
+                                if (i < ncol && c2 + i < c_count) {
+                                    const float d = __uint_as_float(r2[i]) - bs_[c2 + i];
+                                    atomicAdd(t + 2 * i, d);
+                                    atomicAdd(t + 2 * i + 1, d * d);
+                                }
+                            }
+                        }
+                    }
+                    stage_store(P, stage, lane, r2, row_off + (long long)c2 * esz, okmask, (char*)a.out, valid, mode, esz, st, bs_ + c2);
                 }
             } else
             for (int c2 = c2_lo; c2 < BN; c2 += c2_step) {
@@ -546,12 +685,17 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
             }
             }
             tc_fence_before();
-            mbar_arrive(tempty(acc));
+            __syncwarp();
+            if (lane == 0) {            // one arrival per epilogue warp, on the leader's barrier (its MMA warp reuses the slot)
+                if constexpr (CG == 2) mbar_arrive_cluster(lead(tempty(acc)));
+                else mbar_arrive(tempty(acc));
+            }
         }
     }
 
     tc_fence_before();
     __syncthreads();
+    if constexpr (CG == 2) cluster_sync_all();          // no CTA of the pair leaves (or frees TMEM) while the other still signals it
 #ifdef P2P_WINDOW_TIMING
     if (a.dbg && tid == 0) {
         long long g_exit;
@@ -561,7 +705,8 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
 #endif
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+        if constexpr (CG == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
     }
 }
 
@@ -667,7 +812,7 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_window_swap_kernel(const __
                     mbar_expect_tx(afull(ab), a_bytes);
                     for (int bx = 0; bx < a.nboxes; ++bx)
                         tma_load_2d(base + ab * SWIN_BYTES + bx * a.rows_per_box * 128, &a.tm_x, c0,
-                                    (int)((long long)pl * a.Q + q0 + (long long)bx * a.rows_per_box), afull(ab));
+                                    (int)((long long)pl * a.Qp + q0 + (long long)bx * a.rows_per_box), afull(ab));
                     const int t_end = a.pbeg[u][pl + 1];
                     for (int t = a.pbeg[u][pl]; t < t_end; ++t) {
                         const uint32_t s = bs;
@@ -1128,8 +1273,19 @@ extern "C" int p2p_pad_planes(const void* x, void* planes, int N, int H, int W, 
 }
 
 // General form (include/p2p_b200.h: p2p_conv_window_desc): up to 4 sub-passes (output parities) share the planes.
+extern "C" int p2p_conv_window_run_stats(const p2p_conv_window_desc* d, const void* planes, const void* weight, const float* bias,
+                                         void* out, int out_dtype, float* stats, void* stream);
 extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* planes, const void* weight, const float* bias,
                                    void* out, int out_dtype, void* stream) {
+    return p2p_conv_window_run_stats(d, planes, weight, bias, out, out_dtype, nullptr, stream);
+}
+
+// stats (optional): [N][J][2] fp32, written by this call (zeroed, then accumulated by the epilogue): per (image, output channel)
+// sum and sum of squares of (out - bias) over the output pixels -- InstanceNorm's statistics without a second pass over `out`.
+// Needs an fp32 output with J % 4 == 0 and enough tiles to fill the chip (no channel-loop split): P2P_ENOTSUP otherwise, with
+// nothing launched.
+extern "C" int p2p_conv_window_run_stats(const p2p_conv_window_desc* d, const void* planes, const void* weight, const float* bias,
+                                         void* out, int out_dtype, float* stats, void* stream) {
     using namespace p2p;
     if (!d || !planes || !weight || !out) return fail(P2P_EINVAL, "null pointer argument");
     const int ntaps = d->ntaps, nplanes = d->nplanes, C = d->C, J = d->J, Hp = d->Hp, Wp = d->Wp;
@@ -1141,7 +1297,9 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
     a.OHf = d->OHf; a.OWf = d->OWf; a.oys = d->oys; a.oxs = d->oxs;
     a.ntaps = ntaps; a.nplanes = nplanes; a.nsub = d->nsub;
     a.Q = (long long)d->N * Hp * Wp;
-    if ((long long)nplanes * a.Q > 2000000000LL) return fail(P2P_ENOTSUP, "too many rows");
+    a.Qp = d->plane_rows > 0 ? d->plane_rows : a.Q;
+    if (a.Qp < a.Q) return fail(P2P_EINVAL, "plane_rows smaller than N*Hp*Wp");
+    if ((long long)nplanes * a.Qp > 2000000000LL) return fail(P2P_ENOTSUP, "too many rows");
     for (int u = 0; u < 4; ++u) {
         a.gy[u] = a.gx[u] = a.oyo[u] = a.oxo[u] = 0;
         for (int p = 0; p <= 4; ++p) a.pbeg[u][p] = 0;
@@ -1192,6 +1350,11 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
         a.BN = swap ? 128 : (bn < 16 ? 16 : bn);
     }
     a.n_tiles = (J + a.BN - 1) / a.BN;
+    // CTA pairs (tcgen05 cta_group::2, see conv_window_kernel): on by default; P2P_CONV_CG=1 keeps single CTAs (A/B measurements)
+    static int cg_env = -1;
+    if (cg_env < 0) { const char* e = getenv("P2P_CONV_CG"); cg_env = (e && e[0] == '1') ? 1 : 2; }
+    const int CG = (!swap && cg_env == 2 && sms % 2 == 0) ? 2 : 1;
+    const int slots = sms / CG;                 // CTAs (CG = 1) or CTA pairs (CG = 2) resident at once
     // Two 128-row MMAs per weight tile (mrep = 2) halve the weight bytes TMA writes into shared memory per pixel.  The kernel
     // is bound by the shared-memory port (MMA operand reads + TMA fills + epilogue staging, 128 B/clk), see DESIGN.md section 6,
     // so this pays whenever the longer tiles still fill the chip: rounds(256-row tiles) * 2 * 0.8 < rounds(128-row tiles).
@@ -1199,13 +1362,14 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
     if (mrep_env < 0) { const char* e = getenv("P2P_CONV_MREP"); mrep_env = (e && e[0] == '1') ? 1 : 2; }
     a.mrep = 1;
     if (!swap && mrep_env == 2) {
-        const long long w1 = ((a.Q + 127) / 128) * a.n_tiles * d->nsub, w2 = ((a.Q + 255) / 256) * a.n_tiles * d->nsub;
-        const long long r1 = (w1 + sms - 1) / sms, r2 = (w2 + sms - 1) / sms;
+        const long long w1 = ((a.Q + 128 * CG - 1) / (128 * CG)) * a.n_tiles * d->nsub, w2 = ((a.Q + 256 * CG - 1) / (256 * CG)) * a.n_tiles * d->nsub;
+        const long long r1 = (w1 + slots - 1) / slots, r2 = (w2 + slots - 1) / slots;
         const int nb2 = (256 + halo + 255) / 256, rpb2 = ((256 + halo + nb2 - 1) / nb2 + 7) / 8 * 8;
         const int rows2 = (nb2 * rpb2 * 128 + 1023) / 1024 * 1024;         // bytes of one 256-row window buffer, box-rounded
-        const int tap_bytes_k = ((a.BN * 128 + 1023) / 1024) * 1024, tap_bytes_mn = ((a.BN + 63) / 64) * 8192;
+        const int bnl = a.BN / CG;
+        const int tap_bytes_k = ((bnl * 128 + 1023) / 1024) * 1024, tap_bytes_mn = ((bnl + 63) / 64) * 8192;
         const int tap_max = tap_bytes_k > tap_bytes_mn ? tap_bytes_k : tap_bytes_mn;
-        if (w1 * 2 > sms && r2 * 16 < r1 * 10 && WDATA_BYTES - 2 * rows2 >= 3 * tap_max) a.mrep = 2;
+        if (w1 * 2 > slots && r2 * 16 < r1 * 10 && WDATA_BYTES - 2 * rows2 >= 3 * tap_max) a.mrep = 2;
     }
     const int TR = swap ? SBM : WBM * a.mrep, rows_max = swap ? kSwapRowsMax : (WDATA_BYTES / 2) / 128;
     a.win_rows = TR + halo;
@@ -1229,12 +1393,15 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
         return fail(P2P_ENOTSUP, "weights must be densely packed per tap");
     a.bias = bias;
     a.out = out;
+    a.stats = stats;
     a.out_bf16 = out_dtype == P2P_BF16;
     a.cpb = (C + 63) / 64;
     a.base_off_mode = g_window_base_off_mode;
     a.fast_epi = ((long long)J * (a.out_bf16 ? 2 : 4)) % 16 == 0 && (((uintptr_t)out) & 15) == 0;
     a.dbg = g_window_dbg;
-    a.b_tap_bytes = a.b_mn_major ? ((a.BN + 63) / 64) * 8192 : ((a.BN * 128 + 1023) / 1024) * 1024;
+    const int BNL = a.BN / CG;                  // weight-tile columns per CTA
+    if (CG == 2 && (a.BN % 16 != 0)) return fail(P2P_ENOTSUP, "CTA pairs need a column tile that is a multiple of 16");
+    a.b_tap_bytes = a.b_mn_major ? ((BNL + 63) / 64) * 8192 : ((BNL * 128 + 1023) / 1024) * 1024;
     const int ring_bytes = swap ? WRING_BYTES : WDATA_BYTES - 2 * a.win_bytes;
     a.tps = ring_bytes / (3 * a.b_tap_bytes);          // keep >= 3 stages in flight
     if (a.tps > 4) a.tps = 4;
@@ -1243,17 +1410,20 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
     a.b_stages = ring_bytes / a.b_stage_bytes;
     if (a.b_stages > kBStagesMax) a.b_stages = kBStagesMax;
     if (a.b_stages < 2) return fail(P2P_ENOTSUP, "weight ring too small for this window");
-    const long long mt = (a.Q + TR - 1) / TR;
+    const long long mt = swap ? (a.Q + TR - 1) / TR : (a.Q + (long long)TR * CG - 1) / ((long long)TR * CG);      // row tiles per CTA (pair)
     if (mt * a.nsub > 2000000000LL / a.n_tiles) return fail(P2P_ENOTSUP, "too many tiles");
-    if ((long long)nplanes * a.Q + halo + TR > 2000000000LL) return fail(P2P_ENOTSUP, "too many rows for 32-bit row indices");
+    if ((long long)nplanes * a.Qp + halo + (long long)TR * CG > 2000000000LL) return fail(P2P_ENOTSUP, "too many rows for 32-bit row indices");
     a.m_tiles = (int)mt;
     a.nwork = mt * a.n_tiles * a.nsub;
     a.nsplit = 1;
     a.ci_per_split = a.cpb * nplanes;
-    if (!swap && !a.out_bf16 && a.nwork * 2 <= sms && a.cpb * nplanes >= 4) {
+    const bool may_split = !swap && !a.out_bf16 && a.nwork * 2 <= slots && a.cpb * nplanes >= 4 && !deterministic();
+    if (may_split && stats)
+        return fail(P2P_ENOTSUP, "epilogue statistics are not available for split channel loops (few-tile layers)");
+    if (may_split) {
         // few tiles (the 16x4-pixel bottleneck layers): split the channel loop so that one wave fills the chip; the
         // partial tiles meet in the fp32 output through red.add
-        int ns = (int)(sms / a.nwork);
+        int ns = (int)(slots / a.nwork);
         if (ns > a.cpb * nplanes / 2) ns = a.cpb * nplanes / 2;
         a.ci_per_split = (a.cpb * nplanes + ns - 1) / ns;
         a.nsplit = (a.cpb * nplanes + a.ci_per_split - 1) / a.ci_per_split;
@@ -1263,33 +1433,49 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
             a.nwork *= a.nsplit;
         }
     }
+    if (stats) {
+        if (swap || a.out_bf16 || !a.fast_epi || a.nsplit > 1 || deterministic())
+            return fail(P2P_ENOTSUP, "epilogue statistics need an fp32 output with J %% 4 == 0 and an unsplit channel loop");
+        if (cudaMemsetAsync(stats, 0, sizeof(float) * 2 * (size_t)d->N * J, (cudaStream_t)stream) != cudaSuccess)
+            return check_launch("cudaMemsetAsync(stats)");
+    }
     // wrap mode: the last image's rows are reached through shifts past row Q (the caller's buffer holds Q + halo rows)
-    if (int rc = encode_2d(&a.tm_x, planes, (unsigned long long)C, (unsigned long long)nplanes * a.Q + (d->wrap ? halo : 0), 64,
+    if (int rc = encode_2d(&a.tm_x, planes, (unsigned long long)C, (unsigned long long)(nplanes - 1) * a.Qp + a.Q + (d->wrap ? halo : 0), 64,
                            (unsigned)a.rows_per_box)) return rc;
     if (!a.b_mn_major) {
-        if (int rc = encode_2d(&a.tm_w, weight, (unsigned long long)C, (unsigned long long)d->wtaps_total * J, 64, (unsigned)a.BN)) return rc;
+        if (int rc = encode_2d(&a.tm_w, weight, (unsigned long long)C, (unsigned long long)d->wtaps_total * J, 64, (unsigned)BNL)) return rc;
     } else {
         if (int rc = encode_2d(&a.tm_w, weight, (unsigned long long)J, (unsigned long long)d->wtaps_total * C, 64, 64)) return rc;
     }
-    static bool configured = false;
-    if (!configured) {
-        if (cudaFuncSetAttribute(conv_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WSMEM) != cudaSuccess)
+    static bool configured[64] = {};            // the attribute is per device
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
+        if (cudaFuncSetAttribute(conv_window_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, WSMEM) != cudaSuccess ||
+            cudaFuncSetAttribute(conv_window_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, WSMEM) != cudaSuccess ||
+            cudaFuncSetAttribute(conv_window_swap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWSMEM) != cudaSuccess)
             return check_launch("cudaFuncSetAttribute(conv_window_kernel)");
-        configured = true;
+        configured[dev] = true;
     }
-    const long long grid = a.nwork < sms ? a.nwork : sms;
+    const long long grid = (a.nwork < slots ? a.nwork : slots) * CG;
     if (swap) {
-        static bool configured_swap = false;
-        if (!configured_swap) {
-            if (cudaFuncSetAttribute(conv_window_swap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SWSMEM) != cudaSuccess)
-                return check_launch("cudaFuncSetAttribute(conv_window_swap_kernel)");
-            configured_swap = true;
-        }
         conv_window_swap_kernel<<<(unsigned)grid, kWThreads, SWSMEM, (cudaStream_t)stream>>>(a);
         note_umma_launch();
         return check_launch("conv_window_swap_kernel");
     }
-    conv_window_kernel<<<(unsigned)grid, kWinThreads, WSMEM, (cudaStream_t)stream>>>(a);
+    if (CG == 2) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)grid);
+        cfg.blockDim = dim3(kWinThreads);
+        cfg.dynamicSmemBytes = WSMEM;
+        cfg.stream = (cudaStream_t)stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (cudaLaunchKernelEx(&cfg, conv_window_kernel<2>, a) != cudaSuccess) return check_launch("conv_window_kernel<2> (cluster launch)");
+    } else {
+        conv_window_kernel<1><<<(unsigned)grid, kWinThreads, WSMEM, (cudaStream_t)stream>>>(a);
+    }
     note_umma_launch();
     return check_launch("conv_window_kernel");
 }
@@ -1297,16 +1483,25 @@ extern "C" int p2p_conv_window_run(const p2p_conv_window_desc* d, const void* pl
 // out[n,y,x,j] (+bias) = sum_{dh<KH, dw<KW} sum_c xp[n, y+dh, x+dw, c] * Wt[c, j],  y < OH = Hp-KH+1, x < OW = Wp-KW+1.
 // weight tap index = flip ? (KH-1-dh)*KW + (KW-1-dw) : dh*KW + dw; element (tap, c, j) at tap*w_tap + c*w_k + j*w_j with
 // either w_k == 1 (K-major) or w_j == 1 (MN-major, the transposed read used for input gradients).
+extern "C" int p2p_conv_window_stats(const void* xp, const void* weight, const float* bias, void* out, int N, int Hp, int Wp, int C,
+                                     int J, int KH, int KW, int flip, long long w_tap, long long w_k, long long w_j, int out_dtype,
+                                     float* stats, void* stream);
 extern "C" int p2p_conv_window(const void* xp, const void* weight, const float* bias, void* out, int N, int Hp, int Wp, int C,
                                int J, int KH, int KW, int flip, long long w_tap, long long w_k, long long w_j, int out_dtype,
                                void* stream) {
+    return p2p_conv_window_stats(xp, weight, bias, out, N, Hp, Wp, C, J, KH, KW, flip, w_tap, w_k, w_j, out_dtype, nullptr, stream);
+}
+
+extern "C" int p2p_conv_window_stats(const void* xp, const void* weight, const float* bias, void* out, int N, int Hp, int Wp, int C,
+                                     int J, int KH, int KW, int flip, long long w_tap, long long w_k, long long w_j, int out_dtype,
+                                     float* stats, void* stream) {
     using namespace p2p;
     if (KH < 1 || KW < 1 || KH * KW > P2P_MAX_TAPS || Hp < KH || Wp < KW) return fail(P2P_EINVAL, "bad window geometry");
     p2p_conv_window_desc d;
     d.nplanes = 1; d.N = N; d.Hp = Hp; d.Wp = Wp; d.C = C;
     d.OHf = Hp - KH + 1; d.OWf = Wp - KW + 1; d.J = J;
     d.wtaps_total = KH * KW; d.w_tap = w_tap; d.w_k = w_k; d.w_j = w_j;
-    d.nsub = 1; d.oys = d.oxs = 1; d.wrap = 0;
+    d.nsub = 1; d.oys = d.oxs = 1; d.wrap = 0; d.plane_rows = 0;
     for (int u = 0; u < 4; ++u) { d.gy[u] = d.OHf; d.gx[u] = d.OWf; d.oyo[u] = d.oxo[u] = 0; }
     d.ntaps = KH * KW;
     for (int i = 0; i < KH; ++i)
@@ -1315,7 +1510,7 @@ extern "C" int p2p_conv_window(const void* xp, const void* weight, const float* 
             d.tap_sub[t] = 0; d.tap_plane[t] = 0; d.tap_dh[t] = (short)i; d.tap_dw[t] = (short)j;
             d.tap_w[t] = (unsigned char)(flip ? (KH - 1 - i) * KW + (KW - 1 - j) : t);
         }
-    return p2p_conv_window_run(&d, xp, weight, bias, out, out_dtype, stream);
+    return p2p_conv_window_run_stats(&d, xp, weight, bias, out, out_dtype, stats, stream);
 }
 
 // dW[tap_w[t]][j][c] (fp32, [wtaps_total][J][C], caller-zeroed) += sum over the padded grid of
@@ -1387,7 +1582,7 @@ extern "C" int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const v
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int nsplit = (int)(sms / items);                       // at most one wave: every extra split is another pass of atomics over dW
     if (nsplit > a.total_kb / 2) nsplit = a.total_kb / 2;
-    if (nsplit < 1) nsplit = 1;
+    if (nsplit < 1 || deterministic()) nsplit = 1;
     a.kb_per_split = (a.total_kb + nsplit - 1) / nsplit;
     a.nsplit = (a.total_kb + a.kb_per_split - 1) / a.kb_per_split;
     a.fast_epi = C % 4 == 0 && (((uintptr_t)dw) & 15) == 0;

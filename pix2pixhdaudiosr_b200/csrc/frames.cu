@@ -164,7 +164,7 @@ extern "C" int p2p_frame_match(const float* frames, const float* window, float w
     if (!frames || !window) return fail(P2P_EINVAL, "null pointer argument");
     const long long total = (long long)B * F * N;
     const float inv_cnt = 1.f / ((float)B * (float)(F - 1) * (float)(N / 2));
-    frame_match_kernel<<<grid_for(total, 592), kTh, 0, (cudaStream_t)stream>>>(frames, window, weight, loss, dframes,
+    frame_match_kernel<<<(loss && deterministic()) ? 1 : grid_for(total, 592), kTh, 0, (cudaStream_t)stream>>>(frames, window, weight, loss, dframes,
                                                                              gscale * weight * inv_cnt, gscale_dev, F, N, total, inv_cnt);
     return check_launch("frame_match_kernel");
 }

@@ -502,6 +502,7 @@ inline int ew_grid(long long n) {
     return (int)(b < 1 ? 1 : (b > cap ? cap : b));
 }
 inline int split_for(long long rows, int base_ctas) {      // chunks of the row dimension so that ~4 CTAs/SM exist
+    if (deterministic()) return 1;                         // one writer per statistic
     long long s = (148LL * 4 + base_ctas - 1) / base_ctas;
     const long long maxs = (rows + 63) / 64;
     if (s > maxs) s = maxs;
@@ -546,6 +547,30 @@ extern "C" int p2p_instnorm_act_fwd(const void* y, const void* res, void* z, flo
             in_apply_kernel<TY, T><<<ew_grid(total), kEw, 0, st>>>((const TY*)y, (const T*)res, (T*)z, stats, HW, C, total, norm, act, slope);
     });
     return check_launch("instnorm_act_fwd");
+}
+
+// stats [N,C,2] = (mean, rstd) of y [N,HW,C] alone (the reduction half of p2p_instnorm_act_fwd), for callers that apply the
+// normalisation with p2p_instnorm_act_planes
+extern "C" int p2p_instnorm_stats(const void* y, float* stats, int N, long long HW, int C, float eps, int y_dtype, void* stream) {
+    if (N < 0 || HW < 0 || C < 0) return fail(P2P_EINVAL, "negative size");
+    if ((long long)N * HW * C == 0) return P2P_OK;
+    if (!y || !stats) return fail(P2P_EINVAL, "null pointer argument");
+    if (N > 65535) return fail(P2P_ENOTSUP, "N=%d too large", N);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(stats, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
+    P2P_DISPATCH_DTYPE(y_dtype, TY, {
+        if (C % 4 == 0 && HW < 2000000000LL && vec4_ok(y, sizeof(TY)) && vec4_ok(stats, 4)) {
+            const int cb = (C / 4 + 31) / 32, S = split_for(HW, cb * N);
+            const int chunk = (int)((HW + S - 1) / S);
+            in_stats_v4_kernel<TY><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, (int)HW, C, chunk);
+        } else {
+            const int cb = (C + 31) / 32, S = split_for(HW, cb * N);
+            const long long chunk = (HW + S - 1) / S;
+            in_stats_kernel<TY><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, HW, C, chunk);
+        }
+        in_finalize_kernel<TY><<<(N * C + 255) / 256, 256, 0, st>>>((const TY*)y, stats, HW, C, N * C, eps);
+    });
+    return check_launch("instnorm_stats");
 }
 
 extern "C" int p2p_instnorm_act_bwd(const void* y, const float* stats, const void* dz, void* dy, float* work, int N,
@@ -642,7 +667,7 @@ extern "C" int p2p_loss_mse_const(const void* x, float target, float weight, flo
                                   const float* gscale_dev, long long n, int dtype, void* stream) {
     if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
     const float gcoef = gscale * weight * 2.f / (float)n;
-    const int grid = ew_grid(n) > 592 ? 592 : ew_grid(n);
+    const int grid = (loss && deterministic()) ? 1 : (ew_grid(n) > 592 ? 592 : ew_grid(n));
     P2P_DISPATCH_DTYPE(dtype, T, mse_const_kernel<T><<<grid, kEw, 0, (cudaStream_t)stream>>>((const T*)x, target, weight, loss, (T*)dx, gcoef, gscale_dev, n));
     return check_launch("loss_mse_const");
 }
@@ -651,7 +676,7 @@ extern "C" int p2p_loss_l1(const void* a, const void* b, float weight, float* lo
                            const float* gscale_dev, long long n, int dtype, void* stream) {
     if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
     const float gcoef = gscale * weight / (float)n;
-    const int grid = ew_grid(n) > 592 ? 592 : ew_grid(n);
+    const int grid = (loss && deterministic()) ? 1 : (ew_grid(n) > 592 ? 592 : ew_grid(n));
     P2P_DISPATCH_DTYPE(dtype, T, l1_kernel<T><<<grid, kEw, 0, (cudaStream_t)stream>>>((const T*)a, (const T*)b, weight, loss, (T*)da, gcoef, gscale_dev, n));
     return check_launch("loss_l1");
 }

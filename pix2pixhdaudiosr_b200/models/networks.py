@@ -108,14 +108,17 @@ class Conv2d(_ConvBase):
         self.weight._p2p_conv = self
         self.w16, self.gphys, self.tswap = None, None, True
 
-    def run(self, x, reflect_pad=0, needs_wgrad=True, norm=None, act_mod=None, res=None):
-        """conv [+ InstanceNorm] [+ activation] [+ residual] as one fused op"""
+    def cfg_for(self, reflect_pad=0):
         if reflect_pad:
             assert self.padding == 0
-            cfg = ops.ConvCfg(False, self.stride, reflect_pad, ops.PAD_REFLECT, tswap=self.tswap)
-        else:
-            cfg = ops.ConvCfg(False, self.stride, self.padding, ops.PAD_ZERO, tswap=self.tswap)
-        return _conv_block(self, x, cfg, needs_wgrad, norm, act_mod, res)
+            return ops.ConvCfg(False, self.stride, reflect_pad, ops.PAD_REFLECT, tswap=self.tswap)
+        return ops.ConvCfg(False, self.stride, self.padding, ops.PAD_ZERO, tswap=self.tswap)
+
+    def run(self, x, reflect_pad=0, needs_wgrad=True, norm=None, act_mod=None, res=None, consumer=None, want_plain=False):
+        """conv [+ InstanceNorm] [+ activation] [+ residual] as one fused op; `consumer` = (conv module, ConvCfg) of the layer
+        that reads the result (its padded input planes are then written directly), want_plain: the result must be a plain
+        contiguous NHWC tensor (it is also handed out as a feature map)"""
+        return _conv_block(self, x, self.cfg_for(reflect_pad), needs_wgrad, norm, act_mod, res, consumer, want_plain)
 
     def extra_repr(self):
         return f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, stride={self.stride}, padding={self.padding}"
@@ -131,9 +134,11 @@ class ConvTranspose2d(_ConvBase):
         # torch computes fan_in of a [Cin, Cout, k, k] transposed-conv weight as size(1) * k * k
         self._init_params((in_channels, out_channels, k, k), out_channels * k * k, (2, 3, 1, 0))
 
-    def run(self, x, needs_wgrad=True, norm=None, act_mod=None, res=None):
-        cfg = ops.ConvCfg(True, self.stride, self.padding, ops.PAD_ZERO, self.output_padding)
-        return _conv_block(self, x, cfg, needs_wgrad, norm, act_mod, res)
+    def cfg_for(self, reflect_pad=0):
+        return ops.ConvCfg(True, self.stride, self.padding, ops.PAD_ZERO, self.output_padding)
+
+    def run(self, x, needs_wgrad=True, norm=None, act_mod=None, res=None, consumer=None, want_plain=False):
+        return _conv_block(self, x, self.cfg_for(), needs_wgrad, norm, act_mod, res, consumer, want_plain)
 
     def extra_repr(self):
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, stride={self.stride}, "
@@ -149,14 +154,44 @@ def _act_code(act_mod):
     return ops.ACT_NONE, 0.0
 
 
-def _conv_block(conv, x, cfg, needs_wgrad, norm, act_mod, res):
+def _conv_block(conv, x, cfg, needs_wgrad, norm, act_mod, res, consumer=None, want_plain=False):
     w = conv.weight if needs_wgrad else conv.weight.detach()
     b = conv.bias if needs_wgrad else conv.bias.detach()
     if x.dtype == torch.bfloat16 and (conv.w16 is None or conv.w16.device != x.device):
         conv.sync_shadow()
     act, slope = _act_code(act_mod)
-    return ops.ConvBlockFn.apply(x, w, b, conv.w16, res, cfg, norm is not None, act, slope,
-                                 norm.eps if norm is not None else 0.0, conv.gphys if needs_wgrad else None)
+    out_plan = None
+    if consumer is not None:
+        cmod, ccfg = consumer
+        out_plan = lambda shape, dtype: ops.plan_input_layout(shape, dtype, cmod.weight, ccfg)      # noqa: E731
+    z, layout = ops.ConvBlockFn.apply(x, w, b, conv.w16, res, cfg, norm is not None, act, slope,
+                                      norm.eps if norm is not None else 0.0, conv.gphys if needs_wgrad else None,
+                                      getattr(x, "_p2p_layout", None), out_plan, want_plain)
+    if layout is not None:
+        z._p2p_layout = layout          # (key, planes): this tensor already exists as its consumer's padded input
+    return z
+
+
+def _consumer_of(mods):
+    """the convolution a module (list) starts with -> (conv module, ConvCfg), or None"""
+    if isinstance(mods, nn.Sequential):
+        mods = list(mods)
+    elif not isinstance(mods, (list, tuple)):
+        mods = [mods]
+    if not mods:
+        return None
+    m = mods[0]
+    if isinstance(m, nn.Sequential):
+        return _consumer_of(list(m) + list(mods[1:]))
+    if isinstance(m, ResnetBlock):
+        return _consumer_of(list(m.conv_block))
+    if isinstance(m, ReflectionPad2d):
+        if len(mods) > 1 and isinstance(mods[1], Conv2d):
+            return mods[1], mods[1].cfg_for(m.padding)
+        return None
+    if isinstance(m, (Conv2d, ConvTranspose2d)):
+        return m, m.cfg_for()
+    return None
 
 
 def weights_init(m):
@@ -194,15 +229,18 @@ def _take_norm_act(mods, i):
     return norm, act, i
 
 
-def run_layers(mods, x, needs_wgrad=True, res_last=None):
+def run_layers(mods, x, needs_wgrad=True, res_last=None, next_consumer=None, want_plain=False):
     """Execute a reference-shaped module list.  Conv [+IN] [+act] runs as one fused op; `res_last` is added in
-    the last conv block of the list (LocalEnhancer's `model_downsample(input_i) + output_prev`)."""
+    the last conv block of the list (LocalEnhancer's `model_downsample(input_i) + output_prev`).  `next_consumer`: the
+    module(s) that will read this list's result (lets the last block write its consumer's padded input directly);
+    `want_plain`: the list's result is also used as a plain tensor (a discriminator feature map)."""
     mods = list(mods)
     i = 0
     while i < len(mods):
         m = mods[i]
         if isinstance(m, nn.Sequential):
-            x = run_layers(m, x, needs_wgrad)
+            x = run_layers(m, x, needs_wgrad, next_consumer=mods[i + 1:] if i + 1 < len(mods) else next_consumer,
+                           want_plain=want_plain and i + 1 == len(mods))
             i += 1
         elif isinstance(m, (ReflectionPad2d, Conv2d, ConvTranspose2d)):
             pad = 0
@@ -211,11 +249,15 @@ def run_layers(mods, x, needs_wgrad=True, res_last=None):
                 assert isinstance(m, Conv2d), "ReflectionPad2d must be followed by Conv2d"
                 i += 1
             norm, act, i = _take_norm_act(mods, i + 1)
-            res = res_last if i == len(mods) else None
+            last = i == len(mods)
+            res = res_last if last else None
+            consumer = _consumer_of(mods[i:]) if not last else (_consumer_of(next_consumer) if next_consumer is not None else None)
+            plain = want_plain and last
             if isinstance(m, Conv2d):
-                x = m.run(x, reflect_pad=pad, needs_wgrad=needs_wgrad, norm=norm, act_mod=act, res=res)
+                x = m.run(x, reflect_pad=pad, needs_wgrad=needs_wgrad, norm=norm, act_mod=act, res=res, consumer=consumer,
+                          want_plain=plain)
             else:
-                x = m.run(x, needs_wgrad=needs_wgrad, norm=norm, act_mod=act, res=res)
+                x = m.run(x, needs_wgrad=needs_wgrad, norm=norm, act_mod=act, res=res, consumer=consumer, want_plain=plain)
             if res is not None:
                 res_last = None
         elif isinstance(m, InstanceNorm2d):
@@ -228,7 +270,9 @@ def run_layers(mods, x, needs_wgrad=True, res_last=None):
             x = ops.TanhFn.apply(x)
             i += 1
         elif isinstance(m, ResnetBlock):
-            x = m.run(x, needs_wgrad)
+            last = i + 1 == len(mods)
+            consumer = _consumer_of(mods[i + 1:]) if not last else (_consumer_of(next_consumer) if next_consumer is not None else None)
+            x = m.run(x, needs_wgrad, consumer)
             i += 1
         else:
             raise NotImplementedError(f"no kernel for module {type(m).__name__}")
@@ -268,10 +312,11 @@ class ResnetBlock(nn.Module):
                                         ReLU(True), ReflectionPad2d(1), Conv2d(dim, dim, kernel_size=3, padding=0),
                                         norm_layer(dim))
 
-    def run(self, x, needs_wgrad=True):
+    def run(self, x, needs_wgrad=True, consumer=None):
         cb = self.conv_block
-        h = cb[1].run(x, reflect_pad=cb[0].padding, needs_wgrad=needs_wgrad, norm=cb[2], act_mod=cb[3])
-        return cb[5].run(h, reflect_pad=cb[4].padding, needs_wgrad=needs_wgrad, norm=cb[6], act_mod=None, res=x)
+        h = cb[1].run(x, reflect_pad=cb[0].padding, needs_wgrad=needs_wgrad, norm=cb[2], act_mod=cb[3],
+                      consumer=(cb[5], cb[5].cfg_for(cb[4].padding)))
+        return cb[5].run(h, reflect_pad=cb[4].padding, needs_wgrad=needs_wgrad, norm=cb[6], act_mod=None, res=x, consumer=consumer)
 
     def forward(self, x):
         return _to_nchw(self.run(_to_nhwc(x, _act_dtype(self))))
@@ -347,7 +392,7 @@ class LocalEnhancer(nn.Module):
             model_upsample = getattr(self, 'model' + str(n) + '_2')
             input_i = input_downsampled[self.n_local_enhancers - n]
             # model_downsample ends with IN + ReLU: fuse `+ output_prev` into that pass (networks.py:180)
-            h = run_layers(model_downsample, input_i, res_last=output_prev)
+            h = run_layers(model_downsample, input_i, res_last=output_prev, next_consumer=model_upsample)
             output_prev = run_layers(model_upsample, h)
         return _to_nchw(output_prev)
 
@@ -410,7 +455,8 @@ class NLayerDiscriminator(nn.Module):
         if self.getIntermFeat:
             res = []
             for n in range(self.n_layers + 2):
-                x = run_layers(getattr(self, 'model' + str(n)), x)
+                nxt = getattr(self, 'model' + str(n + 1)) if n < self.n_layers + 1 else None
+                x = run_layers(getattr(self, 'model' + str(n)), x, next_consumer=nxt, want_plain=True)
                 res.append(_to_nchw(x))
             return res
         return _to_nchw(run_layers(self.model, x))
@@ -450,7 +496,7 @@ class MultiscaleDiscriminator(nn.Module):
         if self.getIntermFeat:
             result = []
             for i in range(len(model)):
-                x = run_layers(model[i], x, needs_wgrad)
+                x = run_layers(model[i], x, needs_wgrad, next_consumer=model[i + 1] if i + 1 < len(model) else None, want_plain=True)
                 result.append(self._out(x))
             return result
         return [self._out(run_layers(model, x, needs_wgrad))]

@@ -306,8 +306,15 @@ def _plan_window_passes(passes, dtype):
     return dict(s=s, pt=pt, pl=pl, Hh=Hh, Wh=Wh, subs=subs)
 
 
-def _window_passes(passes, x, wq, bias, out, wtaps_total, kind):
-    """run all passes of a layer call as ONE launch of the shifted-window kernel; False (nothing launched) if they do not fit"""
+def _planes_key(pl, N, C):
+    """(pt, pl, Hh, Wh, rows, reflect, s, C): the layout of a layer's padded input planes (what _window_wgrad compares)"""
+    return (pl["pt"], pl["pl"], pl["Hh"], pl["Wh"], _rows64(N * pl["Hh"] * pl["Wh"]), False, pl["s"], C)
+
+
+def _window_passes(passes, x, wq, bias, out, wtaps_total, kind, aux=None, xin=None, stats=None):
+    """run all passes of a layer call as ONE launch of the shifted-window kernel; False (nothing launched) if they do not fit.
+    xin: (key, planes) written by the producer of x (skips the padding copy); aux: list that receives (key, planes) for the
+    weight-gradient pass; stats: [N,J,2] fp32 buffer for the epilogue's InstanceNorm sums (returns "stats" when they were taken)"""
     if not USE_WINDOW or not passes or _lib.lib().p2p_conv_force_simple(-1) == 1:
         return False
     pl = _plan_window_passes(passes, x.dtype)
@@ -315,11 +322,20 @@ def _window_passes(passes, x, wq, bias, out, wtaps_total, kind):
         return False
     N, H, W, C = x.shape
     s, P0 = pl["s"], passes[0]
-    planes = torch.empty((s * s, N, pl["Hh"], pl["Wh"], C), dtype=x.dtype, device=x.device)
-    _lib.check(_lib.lib().p2p_pad_planes(_p(x), _p(planes), N, H, W, C, pl["pt"], pl["pl"], pl["Hh"], pl["Wh"], s,
-                                         N * pl["Hh"] * pl["Wh"], 0, _DT[x.dtype], _stream()))
+    key = _planes_key(pl, N, C)
+    rows = key[4]
+    if xin is not None and xin[0] == key:
+        planes = xin[1]
+    else:
+        x = x.contiguous()
+        planes = torch.empty((s * s, rows, C), dtype=x.dtype, device=x.device)
+        _lib.check(_lib.lib().p2p_pad_planes(_p(x), _p(planes), N, H, W, C, pl["pt"], pl["pl"], pl["Hh"], pl["Wh"], s,
+                                             rows, 0, _DT[x.dtype], _stream()))
+    if aux is not None:
+        aux.append((key, planes))
     d = _lib.WindowDesc()
     d.nplanes, d.N, d.Hp, d.Wp, d.C = s * s, N, pl["Hh"], pl["Wh"], C
+    d.plane_rows = rows
     d.OHf, d.OWf, d.J = P0.OH, P0.OW, P0.J
     d.wtaps_total, d.w_tap, d.w_k, d.w_j = wtaps_total, P0.w_tap, P0.w_k, P0.w_j
     d.nsub, d.oys, d.oxs = len(passes), P0.oys, P0.oxs
@@ -332,13 +348,20 @@ def _window_passes(passes, x, wq, bias, out, wtaps_total, kind):
     d.ntaps = t
     shape = _Shape(N, 1, sum(P.gy * P.gx * P.ntaps for P in passes), P0.J, 1, C, pl["Hh"], pl["Wh"])
     run = out
-    if out.dtype != torch.float32 and _few_tiles(N * pl["Hh"] * pl["Wh"], P0.J, len(passes), (C + 63) // 64 * s * s):
+    few = _few_tiles(N * pl["Hh"] * pl["Wh"], P0.J, len(passes), (C + 63) // 64 * s * s)
+    if out.dtype != torch.float32 and few:
         run = torch.empty(out.shape, dtype=torch.float32, device=out.device)
-    _timed(kind, shape, lambda: _lib.check(_lib.lib().p2p_conv_window_run(ctypes.byref(d), _p(planes), _p(wq), _p(bias), _p(run),
-                                                                          _DT[run.dtype], _stream())), umma=True)
+    take = stats is not None and not few and run.dtype == torch.float32 and P0.J % 4 == 0 and not deterministic()
+    _timed(kind, shape, lambda: _lib.check(_lib.lib().p2p_conv_window_run_stats(ctypes.byref(d), _p(planes), _p(wq), _p(bias), _p(run),
+                                                                                _DT[run.dtype], _p(stats) if take else None,
+                                                                                _stream())), umma=True)
     if run is not out:
         out.copy_(run)
-    return True
+    return "stats" if take else True
+
+
+def deterministic():
+    return _lib.lib().p2p_set_deterministic(-1) == 1
 
 
 _WRAP_BUFFERS = {}
@@ -436,6 +459,7 @@ def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None, fresh=False, dy_sh
         bplanes = xpad[1]                   # the forward pass's padded copy
     else:
         bplanes = torch.empty((s_in * s_in, rows, C), dtype=x.dtype, device=x.device)
+        x = x.contiguous()
         _lib.check(lib.p2p_pad_planes(_p(x), _p(bplanes), N, H, W, C, pt, pl, Hh, Wh, s_in, rows, int(reflect), _DT[x.dtype], _stream()))
     if dy_shared is not None and s_out == 1 and dy_shared[0] == (Hh, Wh, rows, J):
         aplanes = dy_shared[1][dy_shared[2]: dy_shared[2] + rows]       # the copy the input-gradient pass already made
@@ -456,15 +480,21 @@ def _few_tiles(rows, J, nsub, chunks):
     return ((rows + 127) // 128) * ((J + 255) // 256) * nsub * 2 <= 148 and chunks >= 4
 
 
-def conv_window(xp, wq, bias, out_dtype, KH, KW, J, flip, w_tap, w_k, w_j, kind, shape=None):
+def conv_window(xp, wq, bias, out_dtype, KH, KW, J, flip, w_tap, w_k, w_j, kind, shape=None, stats=None):
+    """stats: optional [N,J,2] fp32 buffer; when the launch can take InstanceNorm's sums in its epilogue it does and the call
+    returns (out, True), else (out, False).  Without `stats` only `out` is returned."""
     N, Hp, Wp, C = shape if shape is not None else xp.shape
     OH, OW = Hp - KH + 1, Wp - KW + 1
-    run_dtype = torch.float32 if _few_tiles(N * Hp * Wp, J, 1, (C + 63) // 64) else out_dtype
+    few = _few_tiles(N * Hp * Wp, J, 1, (C + 63) // 64)
+    run_dtype = torch.float32 if few else out_dtype
     out = torch.empty((N, OH, OW, J), dtype=run_dtype, device=xp.device)
+    take = stats is not None and not few and run_dtype == torch.float32 and J % 4 == 0 and not deterministic()
     _timed(kind, _Shape(N, OH, OW, J, KH * KW, C, Hp, Wp),
-           lambda: _lib.check(_lib.lib().p2p_conv_window(_p(xp), _p(wq), _p(bias), _p(out), N, Hp, Wp, C, J, KH, KW, int(flip),
-                                                         w_tap, w_k, w_j, _DT[run_dtype], _stream())), umma=True)
-    return out if run_dtype == out_dtype else out.to(out_dtype)
+           lambda: _lib.check(_lib.lib().p2p_conv_window_stats(_p(xp), _p(wq), _p(bias), _p(out), N, Hp, Wp, C, J, KH, KW, int(flip),
+                                                               w_tap, w_k, w_j, _DT[run_dtype], _p(stats) if take else None,
+                                                               _stream())), umma=True)
+    out = out if run_dtype == out_dtype else out.to(out_dtype)
+    return out if stats is None else (out, take)
 
 
 # ---- thin layers (2-4 channels on one side): fold the kernel's columns into the channel dimension ---------------------
@@ -542,7 +572,7 @@ def _pack_dy(dy, KW, Cout, Wp):
     return out
 
 
-def _packed_forward(kind, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux=None):
+def _packed_forward(kind, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux=None, xin=None):
     if kind == "in":
         xpk, wpk, P, (OH, OW) = _packed_in_operands(x, wq, cfg, Cin, Cout, KH, KW)
         if aux is not None:
@@ -552,8 +582,11 @@ def _packed_forward(kind, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux=No
         return y
     N = x.shape[0]
     P, (Hp, Wp, OH, OW) = _packed_out_geometry(x, cfg, Cin, Cout, KH, KW)
-    xp = _pad_rows64(x, cfg.pad, cfg.pad_mode == PAD_REFLECT) if (Cin * x.element_size()) % 16 == 0 else \
-        _pad_hw(x, cfg.pad, cfg.pad_mode == PAD_REFLECT)
+    if xin is not None:
+        xp = xin[1].view(-1, Cin)           # written in this layout by the producer (plan_input_layout)
+    else:
+        xp = _pad_rows64(x, cfg.pad, cfg.pad_mode == PAD_REFLECT) if (Cin * x.element_size()) % 16 == 0 else \
+            _pad_hw(x, cfg.pad, cfg.pad_mode == PAD_REFLECT)
     if aux is not None:
         aux.append(("packed_out", xp))
     ypk = torch.empty((N, OH, Wp, 16), dtype=torch.float32, device=x.device)
@@ -590,7 +623,7 @@ def _packed_backward(kind, x, wq, dy, cfg, Cin, Cout, KH, KW, need_dx, need_dw, 
         else:
             dx = buf[:, p: p + H, p: p + W, :].contiguous() if p else buf
     if need_dw:
-        xp = xpad[1] if xpad is not None and xpad[0] == "packed_out" else _pad_hw(x, cfg.pad, cfg.pad_mode == PAD_REFLECT)
+        xp = xpad[1] if xpad is not None and xpad[0] == "packed_out" else _pad_hw(x.contiguous(), cfg.pad, cfg.pad_mode == PAD_REFLECT)
         dwk = torch.zeros((KH, 16, Cin), dtype=torch.float32, device=x.device)
         _run_wgrad(P, xp, dypk, dwk)
         dwp = dwk[:, :KW * Cout].reshape(KH, KW, Cout, Cin)
@@ -653,14 +686,19 @@ def _im2col(x, cfg, Cin, KH, KW):
     return xcol
 
 
-def _col_in_forward(x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux):
+def _col_in_forward(x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux, stats=None):
+    """-> (y, stats_taken)"""
     N, H, W, s, p, OH, OW, Kc = _col_in_geometry(x, cfg, Cin, KH, KW)
     xcol = _im2col(x, cfg, Cin, KH, KW)
     if aux is not None:
         aux.append(("col_in", xcol))
+    if stats is not None and xcol.shape[0] == N * OH * OW:      # (a zero row tail would be counted as output pixels)
+        return _with_ratio(KH * KW * Cin / float(Kc),
+                           lambda: conv_window(xcol, _col_weight(wq, Kc), bias, out_dtype, 1, 1, Cout, False, Cout * Kc, 1, Kc, "fwd",
+                                               (N, OH, OW, Kc), stats))
     return _with_ratio(KH * KW * Cin / float(Kc),
                        lambda: conv_window(xcol, _col_weight(wq, Kc), bias, out_dtype, 1, 1, Cout, False, Cout * Kc, 1, Kc, "fwd",
-                                           (N, OH, OW, Kc)))
+                                           (N, OH, OW, Kc))), False
 
 
 def _col_in_backward(x, wq, dy, cfg, Cin, Cout, KH, KW, need_dx, need_dw, xpad):
@@ -712,7 +750,7 @@ def _col_out_backward(x, wq, dy, cfg, Cin, Cout, KH, KW, need_dx, need_dw, xpad)
         if xpad is not None and xpad[0] == "packed_out" and xpad[1].shape[0] == rows:
             xp = xpad[1]
         else:
-            xp = _pad_rows64(x, p, cfg.pad_mode == PAD_REFLECT)
+            xp = _pad_rows64(x.contiguous(), p, cfg.pad_mode == PAD_REFLECT)
         dwfull = torch.zeros((Kc, Cin), dtype=torch.float32, device=x.device)
         _with_ratio(ratio, lambda: _wgrad_1x1(dyfull, xp, rows, Kc, Cin, dwfull, Wp))
         dwp = dwfull[:KH * KW * Cout].reshape(KH, KW, Cout, Cin)
@@ -730,18 +768,57 @@ def _pad_rows64(x, p, reflect):
 
 
 
-def _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux=None):
-    """nn.Conv2d (+ nn.ReflectionPad2d) / nn.ConvTranspose2d forward, NHWC (networks.py:145-154, 190-207, 223-246, 340-361)"""
+def plan_input_layout(shape, dtype, weight, cfg):
+    """The layout (pt, pl, Hh, Wh, rows, reflect, s, C) of the padded planes conv_forward builds from an input of this shape,
+    or None when the layer does not read padded planes (thin / unpadded / non-window layers).  A producer that writes its
+    output in this layout (norm_act_forward_planes) saves the padding copy: pass the buffer as conv_forward(xin=(key, planes))."""
+    if dtype != torch.bfloat16 or not USE_WINDOW or _lib.lib().p2p_conv_force_simple(-1) == 1:
+        return None
+    N, H, W, Cx = shape
+    _, Cout, Cin, KH, KW = _phys(weight, cfg)
+    if Cx != Cin or (Cin * 2) % 16 != 0:
+        return None
+    x_meta = torch.empty(0, dtype=dtype)
+    if _colable(x_meta, cfg, Cin, Cout, KH, KW) == "in":
+        return None
+    pk = _packable(x_meta, cfg, Cin, Cout, KH, KW)
+    p = cfg.pad
+    if pk == "out":
+        return (p, p, H + 2 * p, W + 2 * p, _rows64(N * (H + 2 * p) * (W + 2 * p)), cfg.pad_mode == PAD_REFLECT, 1, Cin) if p else None
+    if pk is not None or _thin(x_meta, Cin, Cout) is not None:
+        return None
+    if cfg.transposed:
+        passes, _ = convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)
+    else:
+        if cfg.pad_mode == PAD_REFLECT and (p >= H or p >= W):
+            return None
+        if cfg.stride == 1 and _window_ok(dtype, Cin, Cout, KH, KW, H + 2 * p, W + 2 * p, False):
+            return (p, p, H + 2 * p, W + 2 * p, _rows64(N * (H + 2 * p) * (W + 2 * p)), cfg.pad_mode == PAD_REFLECT, 1, Cin) if p else None
+        passes = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
+    if not passes:
+        return None
+    pl = _plan_window_passes(passes, dtype)
+    return _planes_key(pl, N, Cin) if pl is not None else None
+
+
+def _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux=None, xin=None, stats=None):
+    """nn.Conv2d (+ nn.ReflectionPad2d) / nn.ConvTranspose2d forward, NHWC (networks.py:145-154, 190-207, 223-246, 340-361).
+    xin: (key, planes) -- the input already laid out as this layer's padded planes (plan_input_layout) by its producer;
+    stats: [N,Cout,2] fp32 buffer for InstanceNorm's sums taken in the conv epilogue.  Returns (y, stats_taken)."""
     N, H, W, Cx = x.shape
     wphys, Cout, Cin, KH, KW = _phys(weight, cfg)
     assert Cx == Cin, (Cx, Cin)
     wq = _weight_for(x, wphys, w16)
     Jout = Cout
+    if xin is not None and xin[0] != plan_input_layout(x.shape, x.dtype, weight, cfg):
+        xin = None
+    if xin is None:
+        x = x.contiguous()
     if _colable(x, cfg, Cin, Cout, KH, KW) == "in":
-        return _col_in_forward(x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux)
+        return _col_in_forward(x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux, stats)
     pk = _packable(x, cfg, Cin, Cout, KH, KW)
     if pk is not None:
-        return _packed_forward(pk, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux)
+        return _packed_forward(pk, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux, xin), False
     thin = _thin(x, Cin, Cout)
     if thin is not None and thin[0] != Cin:             # the forward pass only needs the gathered side padded
         x, wq, Cin = _pad_last(x, thin[0]), _pad_weight(wq, Cout, thin[0]), thin[0]
@@ -758,22 +835,30 @@ def _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux=None):
                 reflect = cfg.pad_mode == PAD_REFLECT
                 Hp, Wp = H + 2 * p, W + 2 * p
                 rows = (N * Hp * Wp + 63) // 64 * 64
-                xp = torch.empty((rows, Cin), dtype=x.dtype, device=x.device)
-                _lib.check(_lib.lib().p2p_pad_planes(_p(x), _p(xp), N, H, W, Cin, p, p, Hp, Wp, 1, rows, int(reflect),
-                                                     _DT[x.dtype], _stream()))
+                key = (p, p, Hp, Wp, rows, reflect, 1, Cin)
+                if xin is not None:
+                    xp = xin[1].view(rows, Cin)
+                else:
+                    xp = torch.empty((rows, Cin), dtype=x.dtype, device=x.device)
+                    _lib.check(_lib.lib().p2p_pad_planes(_p(x), _p(xp), N, H, W, Cin, p, p, Hp, Wp, 1, rows, int(reflect),
+                                                         _DT[x.dtype], _stream()))
                 if aux is not None:
-                    aux.append(((p, p, Hp, Wp, rows, reflect, 1, Cin), xp))
+                    aux.append((key, xp))
             else:
                 xp, Hp, Wp = x, H, W
-            return conv_window(xp, wq, bias, out_dtype, KH, KW, Jout, False, Cout * Cin, 1, Cin, "fwd", (N, Hp, Wp, Cin))
+            if stats is not None:
+                return conv_window(xp, wq, bias, out_dtype, KH, KW, Jout, False, Cout * Cin, 1, Cin, "fwd", (N, Hp, Wp, Cin), stats)
+            return conv_window(xp, wq, bias, out_dtype, KH, KW, Jout, False, Cout * Cin, 1, Cin, "fwd", (N, Hp, Wp, Cin)), False
         passes = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
         OH, OW = passes[0].OH, passes[0].OW
     y = torch.empty((N, OH, OW, Jout), dtype=out_dtype, device=x.device)
-    if _window_passes(passes, x, wq, bias, y, KH * KW, "fwd"):
-        return y
+    r = _window_passes(passes, x, wq, bias, y, KH * KW, "fwd", aux if thin is None else None, xin, stats)
+    if r:
+        return y, r == "stats"
+    x = x.contiguous()
     for P in passes:
         _run_pass(P, x, wq, bias, y)
-    return y
+    return y, False
 
 
 def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None, xpad=None):
@@ -861,6 +946,7 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
         else:
             wpasses = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
         if not _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None, fresh, dy_shared):
+            x = x.contiguous()
             for P in wpasses:
                 _run_wgrad(P, x, dy, dwp)
         if direct:
@@ -888,16 +974,19 @@ def _alg_ratio(x, weight, cfg):
     return (Cin * Cout) / float(_ceil16(Cin) * _ceil16(Cout))
 
 
-def conv_forward(x, weight, bias, w16, cfg, out_dtype, aux=None):
-    """aux: optional list; the stride-1 window path appends (key, padded planes) for conv_backward(xpad=...) to reuse"""
+def conv_forward(x, weight, bias, w16, cfg, out_dtype, aux=None, xin=None, stats=None):
+    """aux: optional list; the window paths append (key, padded planes) for conv_backward(xpad=...) to reuse.
+    xin / stats: see _conv_forward; with `stats` the result is (y, stats_taken), else y alone."""
     global _FLOP_RATIO
     if _TIMING is None:
-        return _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux)
-    _FLOP_RATIO = _alg_ratio(x, weight, cfg)
-    try:
-        return _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux)
-    finally:
-        _FLOP_RATIO = 1.0
+        y, took = _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux, xin, stats)
+    else:
+        _FLOP_RATIO = _alg_ratio(x, weight, cfg)
+        try:
+            y, took = _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux, xin, stats)
+        finally:
+            _FLOP_RATIO = 1.0
+    return (y, took) if stats is not None else y
 
 
 def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None, xpad=None):
@@ -921,6 +1010,54 @@ def norm_act_forward(y, res, norm, act, slope, eps, out_dtype):
     _lib.check(_lib.lib().p2p_instnorm_act_fwd(_p(y), _p(res), _p(z), _p(stats), N, H * W, C, int(norm), act, slope, eps,
                                                _DT[y.dtype], _DT[out_dtype], _stream()))
     return z, stats
+
+
+def planes_apply_ok(y, out_dtype):
+    """the fused normalise + activate + pad kernel (csrc/in_fused.cu) covers this tensor"""
+    return (out_dtype == torch.bfloat16 and y.dtype in (torch.float32, torch.bfloat16) and y.shape[3] % 8 == 0
+            and y.shape[3] <= 2048 and y.shape[0] < 65535)
+
+
+def norm_act_forward_planes(y, bias, raw, res, norm, act, slope, eps, key, want_plain):
+    """z = act(InstanceNorm2d(y)) [+ res] (bf16) written DIRECTLY as the padded planes `key` of the layer that consumes it
+    (plan_input_layout; None: plain NHWC only).  raw: the conv epilogue's [N,C,2] sums of (y - bias), or None (a separate
+    reduction runs).  -> (z, layout or None, stats): z is the plain tensor when want_plain or the consumer is strided, else a
+    strided view of the planes' interior; layout = (key, planes) for conv_forward(xin=...); stats = (mean, rstd) [N,C,2]."""
+    N, H, W, C = y.shape
+    lib = _lib.lib()
+    plain_only = key is None
+    if plain_only:
+        key = (0, 0, H, W, N * H * W, False, 1, C)
+    pt, pl, Hh, Wh, rows, reflect, s, Ck = key
+    assert Ck == C
+    planes = torch.empty((s * s, rows, C), dtype=torch.bfloat16, device=y.device)
+    dual = (not plain_only) and (want_plain or s != 1)
+    z_plain = torch.empty((N, H, W, C), dtype=torch.bfloat16, device=y.device) if dual else None
+    stats = stats_in = stats_out = None
+    raw_mode = 0
+    if norm:
+        stats = torch.empty((N, C, 2), dtype=torch.float32, device=y.device)
+        if raw is None:
+            _lib.check(lib.p2p_instnorm_stats(_p(y), _p(stats), N, H * W, C, eps, _DT[y.dtype], _stream()))
+            stats_in = stats
+        else:
+            raw_mode, stats_in, stats_out = 1, raw, stats
+    rs = (0, 0, 0)
+    if res is not None:
+        assert res.shape == y.shape and res.dtype == torch.bfloat16
+        if res.stride(3) != 1 or any(st % 8 for st in res.stride()[:3]) or res.data_ptr() % 16:
+            res = res.contiguous()
+        rs = res.stride()[:3]
+    _lib.check(lib.p2p_instnorm_act_planes(_p(y), _p(bias) if raw_mode else None, _p(stats_in), raw_mode, _p(stats_out), _p(res),
+                                           rs[0], rs[1], rs[2], _p(planes), _p(z_plain), N, H, W, C, pt, pl, Hh, Wh, s, rows,
+                                           int(reflect), int(norm), act, slope, eps, _DT[y.dtype], _stream()))
+    if plain_only:
+        return planes.view(N, H, W, C), None, stats
+    if dual:
+        z = z_plain
+    else:
+        z = planes[0, :N * Hh * Wh].view(N, Hh, Wh, C)[:, pt:pt + H, pl:pl + W, :]
+    return z, (key, planes), stats
 
 
 def norm_act_backward(y, stats, dz, norm, act, slope):
@@ -960,19 +1097,40 @@ class GradSink:
 class ConvBlockFn(torch.autograd.Function):
     """[ReflectionPad2d] Conv2d | ConvTranspose2d  ->  [InstanceNorm2d]  ->  [ReLU | LeakyReLU]  [+ residual]
     as ONE differentiable op.  In bf16 mode the pre-normalisation conv output stays fp32 inside the op (see
-    include/p2p_b200.h), so only O(1)-scaled tensors are ever rounded to bf16."""
+    include/p2p_b200.h), so only O(1)-scaled tensors are ever rounded to bf16.
+
+    Round 2: the InstanceNorm sums come out of the conv epilogue, and the normalise / activate / residual pass writes its
+    result directly as the padded planes of the NEXT convolution (`out_plan(shape, dtype)` -> that layer's
+    plan_input_layout; `xin` = the (key, planes) this layer's producer wrote).  Returns (z, layout or None)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, w16, res, cfg, norm, act, slope, eps, gphys=None):
+    def forward(ctx, x, weight, bias, w16, res, cfg, norm, act, slope, eps, gphys=None, xin=None, out_plan=None,
+                want_plain=False):
         _need_cuda(x, weight)
-        x = x.contiguous()
         plain = (not norm) and act == ACT_NONE and res is None
         aux = [] if ctx.needs_input_grad[1] else None
-        y = conv_forward(x, weight, bias, w16, cfg, torch.float32 if norm else x.dtype, aux)
+        y_dtype = torch.float32 if norm else x.dtype
+        Cout = weight.shape[1] if cfg.transposed else weight.shape[0]
+        fused = (not plain) and FUSE_NORM_PAD and x.dtype == torch.bfloat16 and Cout % 8 == 0 and Cout <= 2048 and x.shape[0] < 65535
+        raw = None
+        if fused and norm:
+            raw = torch.empty((x.shape[0], Cout, 2), dtype=torch.float32, device=x.device)
+            y, took = conv_forward(x, weight, bias, w16, cfg, y_dtype, aux, xin, raw)
+            if not took:
+                raw = None
+        else:
+            y = conv_forward(x, weight, bias, w16, cfg, y_dtype, aux, xin)
         ctx.xpad = aux[0] if aux else None
+        layout = None
         if plain:
             z, stats, ysave = y, None, None
+        elif fused and planes_apply_ok(y, x.dtype):
+            key = out_plan(tuple(y.shape), x.dtype) if out_plan is not None else None
+            z, layout, stats = norm_act_forward_planes(y, bias, raw, res, norm, act, slope, eps, key, want_plain)
+            ysave = y
         else:
+            if norm and raw is not None:
+                raise RuntimeError("epilogue statistics without the fused apply kernel")
             if res is not None:
                 res = res.contiguous()
             z, stats = norm_act_forward(y, res, norm, act, slope, eps, x.dtype)
@@ -981,10 +1139,10 @@ class ConvBlockFn(torch.autograd.Function):
         ctx.cfg = (cfg, norm, act, slope, bias is not None, res is not None, plain)
         ctx.gphys = gphys
         ctx.bias_n = bias.numel() if bias is not None else 0
-        return z
+        return z, layout
 
     @staticmethod
-    def backward(ctx, dz):
+    def backward(ctx, dz, _unused=None):
         x, weight, w16, y, stats = ctx.saved_tensors
         cfg, norm, act, slope, has_bias, has_res, plain = ctx.cfg
         dz = dz.contiguous()
@@ -996,7 +1154,10 @@ class ConvBlockFn(torch.autograd.Function):
                                    need_db, ctx.gphys, ctx.xpad)
         if has_bias and ctx.needs_input_grad[2] and not need_db and ctx.gphys is None:
             db = torch.zeros(ctx.bias_n, dtype=torch.float32, device=x.device)    # no flat gradient buffer behind .grad: give autograd the zero
-        return dx, dw, db, None, (dz if has_res else None), None, None, None, None, None, None
+        return dx, dw, db, None, (dz if has_res else None), None, None, None, None, None, None, None, None, None
+
+
+FUSE_NORM_PAD = os.environ.get("P2P_FUSE_NORM_PAD", "1") == "1"
 
 
 class InstNormActFn(torch.autograd.Function):

@@ -233,11 +233,11 @@ def test_bf16_layers_within_tolerance(layer):
         w = torch.nn.Parameter(wl.permute(*perm).contiguous().permute(*inv))
         w16 = w.detach().permute(*perm).contiguous().bfloat16()
         xi = x.detach().to(dt).clone().requires_grad_(True)
-        z = ops.ConvBlockFn.apply(xi, w, b, w16, None, cfg, norm, act, 0.2, 1e-5)
+        z, _ = ops.ConvBlockFn.apply(xi, w, b, w16, None, cfg, norm, act, 0.2, 1e-5)
         r = None
         if has_res:
             r = torch.randn(z.shape, device="cuda").to(dt)
-            z = ops.ConvBlockFn.apply(xi, w, b, w16, r, cfg, norm, act, 0.2, 1e-5)
+            z, _ = ops.ConvBlockFn.apply(xi, w, b, w16, r, cfg, norm, act, 0.2, 1e-5)
         torch.manual_seed(7)
         g = torch.randn(z.shape, device="cuda").bfloat16()
         z.backward(g.to(dt))
