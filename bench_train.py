@@ -151,7 +151,7 @@ def run_train(args):
     from bench import ClockSampler, tensor_peak
     from pix2pixhdaudiosr_b200 import _lib, ops, options
     from pix2pixhdaudiosr_b200.models.models import create_model
-    from pix2pixhdaudiosr_b200.train import GradSync, GraphedTrainStep, broadcast_parameters, train_step
+    from pix2pixhdaudiosr_b200.train import GradSync, GraphedTrainStep, broadcast_parameters, replica_drift, train_step
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -179,7 +179,9 @@ def run_train(args):
             extra.update(transform="mdct2", n_fft=512, hop_length=256, win_length=512, segment_length=t_seg)
         model = create_model(options.g3l2_opt(gpu_ids=[local], batchSize=B, precision=args.precision, **extra))
     broadcast_parameters(model)
-    sync = GradSync()
+    # bf16: sharded data parallelism (reduce-scatter, Adam on 1/world of the parameters per rank, all-gather of the bf16 shadow);
+    # P2P_DP_SHARD=0 keeps one all-reduce of the fp32 gradients per network (round 1)
+    sync = GradSync(shard=args.precision == "bf16" and os.environ.get("P2P_DP_SHARD", "1") == "1")
     if os.environ.get("P2P_EARLY_SYNC", "0") == "1":      # measured slower at 8 GPUs (12.7 vs 12.1 ms/step): off by default
         sync.attach_early(model.optimizer_G)
     lr_host, hr_host = synth_audio(B, 1000 + rank, t_seg)
@@ -240,12 +242,37 @@ def run_train(args):
     # ---- one extra, un-timed step with CUDA events around every convolution launch: the roofline leg
     n0 = lib.p2p_kernel_launches()
     torch.cuda.synchronize(dev)
-    torch.cuda._sleep(int(0.035 * 1.9e9))     # ~35 ms of device spin: the host enqueues the eager step behind it, so the
-    ops.start_conv_timing()                   # event pairs bracket kernels that run back to back (no launch-latency gaps)
-    train_step(model, lr_d, hr_d, sync=sync)
+    if args.no_graph:
+        torch.cuda._sleep(int(0.035 * 1.9e9))     # ~35 ms of device spin: the host enqueues the eager step behind it
+        ops.start_conv_timing()
+        train_step(model, lr_d, hr_d, sync=sync)
+    else:
+        # the profiled step is itself captured in a CUDA graph with the event pairs as record nodes and replayed once: every
+        # kernel runs back to back exactly as in the timed region (an eager step outruns the host's launch rate, and the launch
+        # queue holds only ~1000 of its ~1300 launches, so event pairs late in an eager step include host gaps)
+        pg = torch.cuda.CUDAGraph()
+        ops.start_conv_timing(external=True)
+        with torch.cuda.graph(pg):
+            train_step(model, lr_d, hr_d, sync=sync)
+        ops.pause_conv_timing()
+        pg.replay()
+        torch.cuda.synchronize(dev)
+        # a second profiled replay with an event pair around EVERY C-ABI entry point: the step's breakdown
+        pg2 = torch.cuda.CUDAGraph()
+        _lib.start_call_profile(external=True)
+        with torch.cuda.graph(pg2):
+            train_step(model, lr_d, hr_d, sync=sync)
+        _lib.pause_call_profile()
+        pg2.replay()
+        _lib.resume_call_profile()
+        calls = _lib.stop_call_profile()
+        del pg2
     rec = ops.stop_conv_timing()
     launches = (lib.p2p_kernel_launches() - n0) * K       # kernels of ours per step (counted eagerly) x timed steps
+    if args.no_graph:
+        calls = {}
 
+    drift = replica_drift(model)          # 0 = every rank holds bit-identical bf16 weights after all the steps above
     times = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
@@ -272,7 +299,8 @@ def run_train(args):
             "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
             "config": {"workload": workload_name(args),
                        "transform": getattr(args, "transform", "mdct4") + (" (n_fft 512, hop 256, 32512-sample segments)" if t_seg != T_SEG else ""),
-                       "global_batch": B * world, "parallelism": f"dp{world}",
+                       "global_batch": B * world, "parallelism": f"dp{world}" + (" (reduce-scatter + sharded Adam + all-gather)" if sync.shard else ""),
+                       "replica_drift": drift,
                        "launch": "eager" if args.no_graph else "one CUDA graph replay per step",
                        "l2": "per-step working set (0.31 GB bf16 weights + 0.65 GB fp32 master + activations) exceeds the 126 MB L2; no flush",
                        "weights": "random init N(0,0.02), seed 1234; mask_mode mode2; Adam lr 2e-4 beta1 0.5",
@@ -285,12 +313,18 @@ def run_train(args):
                          "all_tcgen05": {"launches_per_step": um_n, "achieved": round(ach, 1), "frac": round(ach / peak, 4),
                                          "ms_per_step_in_kernels": round(um_ms, 3), "share_of_step": round(um_ms / step_ms, 3)},
                          "note": "algorithmic conv FLOPs (2*MACs) of the kernel's launches in one step / their summed "
-                                 "CUDA-event durations, measured in an extra profiled (eager) step after the timed region"},
+                                 "CUDA-event durations, measured in one extra profiled step after the timed region "
+                                 "(a CUDA graph replay with the event pairs as graph nodes; eager with --no-graph)"},
             "step_tensor_utilisation": round(all_flops / (step_ms * 1e-3) / 1e12 / peak, 4),
             "conv_flops_per_step": round(all_flops),
             "kernels": {k: {"launches": v[0], "GFLOP": round(v[1] / 1e9, 1), "ms": round(v[2], 3),
                             "TFLOPs": round(v[1] / (v[2] * 1e-3) / 1e12, 1) if v[2] > 0 else None}
                         for k, v in sorted(classes.items())},
+            "entry_points": {"note": "one profiled graph replay: device ms per step inside each C-ABI entry point (event pairs as graph "
+                                     "nodes); `other` = step time not inside any of them (ATen kernels, NCCL, graph launch gaps)",
+                             "ms": {k: round(v[1], 3) for k, v in sorted(calls.items(), key=lambda kv: -kv[1][1])},
+                             "calls": {k: v[0] for k, v in sorted(calls.items(), key=lambda kv: -kv[1][1])},
+                             "other_ms": round(step_ms - sum(v[1] for v in calls.values()), 3)},
             "e2e": {"value": round(B * world * K / (e2e_ms * 1e-3), 2), "unit": "samples/s",
                     "h2d_bytes_per_step": 2 * B * t_seg * 4 * world, "d2h_bytes_per_step": 4 * len(names) * world,
                     "ms_per_step": round(e2e_ms / K, 3)},
@@ -316,12 +350,17 @@ def run_train(args):
                                        "seconds_per_step": round(sec, 2)}
         print(json.dumps(out), flush=True)
     if world > 1:
-        # A CUDA graph that captured NCCL kernels keeps the communicator busy: destroy_process_group() was seen to hang
-        # after the result was printed.  Drop the graph, line the ranks up, and leave without the collective teardown.
-        step = None
+        # CUDA graphs that captured NCCL kernels keep the communicator busy: drop every graph, drain the device, line the ranks
+        # up, then tear the group down.  A watchdog ends the process if the teardown still does not return (seen in round 1).
+        import gc
+        import sys
+        import threading
+        step = pg = pg2 = None
+        gc.collect()
         torch.cuda.synchronize()
         dist.barrier()
-        import sys
         sys.stdout.flush()
         sys.stderr.flush()
+        threading.Timer(20.0, lambda: os._exit(0)).start()
+        dist.destroy_process_group()
         os._exit(0)

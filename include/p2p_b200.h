@@ -223,6 +223,11 @@ int p2p_instnorm_act_fwd(const void* y, const void* res, void* z, float* stats, 
  * work: fp32 scratch [N,C,2] (ignored when norm == 0). */
 int p2p_instnorm_act_bwd(const void* y, const float* stats, const void* dz, void* dy, float* work, int N,
                          long long HW, int C, int norm, int act, float slope, int y_dtype, int dtype, void* stream);
+/* Caller-owned, ZEROED device scratch (ws_floats >= 2*N*C floats, cnt_words >= N*ceil(C/128) 32-bit words, for the largest
+ * tensor) that lets the InstanceNorm reductions of p2p_instnorm_act_fwd / _bwd / p2p_instnorm_stats run as ONE launch each
+ * (partial sums meet in ws, the last CTA finalises and re-zeroes it) instead of memset + reduction + finalise.  The calls
+ * that use it must be ordered on one stream; NULL pointers unregister it. */
+int p2p_instnorm_workspace(float* ws, long long ws_floats, unsigned* cnt, long long cnt_words);
 /* stats [N,C,2] = (mean, rstd) of y [N,HW,C] alone: the reduction half of p2p_instnorm_act_fwd, for p2p_instnorm_act_planes. */
 int p2p_instnorm_stats(const void* y, float* stats, int N, long long HW, int C, float eps, int y_dtype, void* stream);
 

@@ -69,6 +69,7 @@ _SIGS.update({
     "p2p_instnorm_act_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _f, _f, _i, _i, _vp]),
     "p2p_instnorm_act_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _f, _i, _i, _vp]),
     "p2p_instnorm_stats": (_i, [_vp, _vp, _i, _ll, _i, _f, _i, _vp]),
+    "p2p_instnorm_workspace": (_i, [_vp, _ll, _vp, _ll]),
     "p2p_avgpool3s2_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "p2p_avgpool3s2_bwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "p2p_tanh_fwd": (_i, [_vp, _vp, _ll, _i, _vp]),
@@ -110,7 +111,69 @@ def lib():
             fn = getattr(h, name)
             fn.restype, fn.argtypes = res, args
         _lib = h
-    return _lib
+    return _profile if _profile is not None else _lib
+
+
+class _ProfiledLib:
+    """proxy used by start_call_profile(): brackets every C-ABI call that takes a stream with a CUDA event pair"""
+
+    def __init__(self, h, records, external):
+        self._h, self._records, self._external = h, records, external
+
+    def __getattr__(self, name):
+        fn = getattr(self._h, name)
+        sig = _SIGS.get(name)
+        if sig is None or not sig[1] or sig[1][-1] is not _vp or name in ("p2p_mdct4_fill_tables", "p2p_mdct2_fill_tables", "p2p_conv_window_debug_buffer"):
+            return fn
+        import torch
+
+        def call(*a):
+            e0 = torch.cuda.Event(enable_timing=True, external=self._external)
+            e1 = torch.cuda.Event(enable_timing=True, external=self._external)
+            e0.record()
+            rc = fn(*a)
+            e1.record()
+            self._records.append((name, e0, e1))
+            return rc
+        return call
+
+
+_profile = None
+
+
+def start_call_profile(external=False):
+    """from now on lib() hands out a proxy that times every kernel-launching entry point (bench.py's per-entry-point
+    breakdown of one step; external=True while the step is being captured into a CUDA graph)"""
+    global _profile
+    lib()
+    _profile = _ProfiledLib(_lib, [], external)
+
+
+def stop_call_profile():
+    """-> {entry point: (calls, milliseconds)} since start_call_profile(); call after the work has completed"""
+    global _profile
+    import torch
+    recs, _profile = (_profile._records if _profile is not None else []), None
+    torch.cuda.synchronize()
+    out = {}
+    for name, e0, e1 in recs:
+        c, ms = out.get(name, (0, 0.0))
+        out[name] = (c + 1, ms + e0.elapsed_time(e1))
+    return out
+
+
+def pause_call_profile():
+    """stop handing out the proxy but keep the records (graph capture finished; replay, then stop_call_profile())"""
+    global _profile, _held
+    _held, _profile = _profile, None
+
+
+def resume_call_profile():
+    global _profile, _held
+    _profile, _held = _held, None
+
+
+_held = None
 
 
 def exported_symbols():

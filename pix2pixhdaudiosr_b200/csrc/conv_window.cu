@@ -54,7 +54,7 @@ struct WindowArgs {
     int pbeg[4][5];          // sub-pass u: taps [pbeg[u][p], pbeg[u][p+1]) read plane p
     int win_rows, rows_per_box, nboxes;
     int BN, n_tiles, m_tiles, cpb;
-    int out_bf16, b_mn_major;
+    int out_bf16, b_mn_major, out_bf16_hint;
     int base_off_mode;
     int tps, b_tap_bytes;          // taps per ring stage (amortises the issuing thread's per-stage overhead), bytes of one tap tile
     int b_stages, b_stage_bytes;   // weight ring: stages of tps tap tiles, as many as fit WRING_BYTES
@@ -63,6 +63,7 @@ struct WindowArgs {
     int mrep;                      // 128-row MMAs per weight tile (1 or 2): a work item covers 128*mrep padded pixels
     int win_bytes;                 // bytes of one window buffer (multiple of 1024); the ring gets WDATA_BYTES - 2*win_bytes
     int acc_slots, half_cols;      // TMEM: accumulator slots of 256 (or 512) columns, column stride between the two row halves
+    int resident;                  // the weight ring holds ALL (chunk, tap) tiles of a work item: loaded once, re-used by every item
     int nsplit, ci_per_split;      // split of the (channel chunk, plane) loop across CTAs; > 1 => fp32 red.add epilogue   // weight-tile ring: as many stages as fit 128 KB (TMA latency needs bytes in flight)
     short shift[P2P_MAX_TAPS];       // dh*Wp + dw
     unsigned char wtap[P2P_MAX_TAPS];
@@ -80,13 +81,18 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+    // bounded: a protocol error traps (an error the host sees) instead of hanging the GPU.  One try_wait suspends the thread
+    // for up to the hardware's time limit, so 2^22 failed attempts are seconds, far beyond any legitimate wait here.
+    uint32_t tries = 0;
+    for (;;) {
+        uint32_t ok;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (ok) return;
+        if (++tries > (1u << 22)) __trap();
+    }
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, int c0, int c1, uint32_t bar) {
     asm volatile(
@@ -124,17 +130,15 @@ __device__ __forceinline__ uint32_t mapa_rank(uint32_t saddr, uint32_t rank) {  
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void mbar_expect_tx_cluster(uint32_t cbar, uint32_t bytes) {     // cbar: shared::cluster address
-    asm volatile("mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [%0], %1;" ::"r"(cbar), "r"(bytes) : "memory");
-}
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cbar) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cbar) : "memory");
 }
-// TMA load into this CTA's shared memory whose completion is signalled on the LEADER CTA's barrier (cbar: shared::cluster address)
-__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* tm, int c0, int c1, uint32_t cbar) {
+// TMA load issued by the pair's leader into the shared memory (same offset `dst`) of the CTAs in `mask`; completion is
+// signalled on the leader's barrier `bar` (.cta_group::2: the barrier address selects the CTA of the pair that receives it)
+__device__ __forceinline__ void tma_load_2d_to(uint32_t dst, const CUtensorMap* tm, int c0, int c1, uint32_t bar, uint16_t mask) {
     asm volatile(
-        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
-        "l"(tm), "r"(c0), "r"(c1), "r"(cbar) : "memory");
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%2, %3}], [%4], %5;"
+        ::"r"(dst), "l"(tm), "r"(c0), "r"(c1), "r"(bar), "h"(mask) : "memory");
 }
 __device__ __forceinline__ void umma2_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -143,15 +147,15 @@ __device__ __forceinline__ void umma2_bf16(uint32_t d_tmem, uint64_t adesc, uint
         "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc),
         "r"(accumulate) : "memory");
 }
-__device__ __forceinline__ void umma2_commit(uint32_t bar) {        // arrives on `bar` (same offset) in BOTH CTAs of the pair
+__device__ __forceinline__ void umma2_commit(uint32_t bar, uint16_t mask) {     // arrives on `bar` (same offset) in the CTAs of `mask`
     asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
-                 "h"((uint16_t)3) : "memory");
+                 "h"(mask) : "memory");
 }
 template <int CG> __device__ __forceinline__ void umma_cg(uint32_t d, uint64_t ad, uint64_t bd, uint32_t idesc, uint32_t acc) {
     if constexpr (CG == 2) umma2_bf16(d, ad, bd, idesc, acc); else umma_bf16(d, ad, bd, idesc, acc);
 }
-template <int CG> __device__ __forceinline__ void commit_cg(uint32_t bar) {
-    if constexpr (CG == 2) umma2_commit(bar); else umma_commit(bar);
+template <int CG> __device__ __forceinline__ void commit_cg(uint32_t bar, uint16_t mask) {
+    if constexpr (CG == 2) umma2_commit(bar, mask); else umma_commit(bar);
 }
 
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
@@ -299,8 +303,9 @@ __device__ __forceinline__ void issue_stage(uint32_t d_tmem, uint32_t half_cols,
     }
 }
 
-// CG = 2: the CTAs of a pair (cluster of 2) each own 128*mrep window rows and half of every weight tile; the leader's MMA warp
-// issues tcgen05.mma.cta_group::2 (M = 256) for both.  Measured (profiles/r02_mma_rate_cg2.txt): 46-50 cycles per MMA for
+// CG = 2: the CTAs of a pair (cluster of 2) each own 128*mrep window rows and half of every weight tile; the LEADER's TMA warp
+// fills both CTAs' shared memory (multicast-addressed loads, one destination each) and its MMA warp issues
+// tcgen05.mma.cta_group::2 (M = 256) for both, so the refill loop never crosses the pair; the other CTA only drains its TMEM.  Measured (profiles/r02_mma_rate_cg2.txt): 46-50 cycles per MMA for
 // N <= 96 against 93 for cta_group::1 -- the per-instruction floor that capped the 96-channel layers at half the tensor peak.
 template <int CG>
 __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __grid_constant__ WindowArgs a) {
@@ -338,10 +343,10 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
 
     if (warp == 1) {
         if (lane == 0) {
-            // full barriers live in the leader: one arrive.expect_tx per CTA of the pair; empty / tfull barriers are local and
-            // receive the (multicast) commit; tempty collects one arrive per epilogue warp of every CTA
-            for (int i = 0; i < 2; ++i) { mbar_init(afull(i), CG); mbar_init(aempty(i), 1); mbar_init(tfull(i), 1); mbar_init(tempty(i), 8 * CG); }
-            for (int s = 0; s < kBStages; ++s) { mbar_init(bfull(s), CG); mbar_init(bempty(s), 1); }
+            // full / empty barriers are used in the leader only; tfull receives the multicast commit in both CTAs; the leader's
+            // tempty collects one arrive per epilogue warp of every CTA
+            for (int i = 0; i < 2; ++i) { mbar_init(afull(i), 1); mbar_init(aempty(i), 1); mbar_init(tfull(i), 1); mbar_init(tempty(i), 8 * CG); }
+            for (int s = 0; s < kBStages; ++s) { mbar_init(bfull(s), 1); mbar_init(bempty(s), 1); }
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
         __syncwarp();
@@ -367,7 +372,7 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
         // Besides the loads, the producer writes one 32-byte record per weight-ring stage (A/B descriptor low words, tap and
         // k16 counts, tile/chunk boundary flags) so that the MMA warp's loop is flat: wait, read the record, issue.  Measured
         // with -DP2P_WINDOW_TIMING: the nested schedule walk in the issuing warp cost as many cycles as the MMAs themselves.
-        if (lane == 0) {
+        if (lane == 0 && rank == 0) {
             asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_x) : "memory");
             asm volatile("prefetch.tensormap [%0];" ::"l"(&a.tm_w) : "memory");
             const uint32_t a_lo = (uint32_t)make_desc(0, 16, 1024, 0);
@@ -379,8 +384,8 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
                 const uint32_t nt = w % n_tiles, wr = w / n_tiles;
                 const uint32_t sp = wr % nsplit, mtu = wr / nsplit;
                 const int u = (int)(mtu / (uint32_t)a.m_tiles);
-                const int q0 = (int)((mtu - (uint32_t)u * (uint32_t)a.m_tiles) * CG + rank) * (WBM * a.mrep);
-                const int j0 = (int)nt * BN + (int)rank * BNL;
+                const int q0 = (int)((mtu - (uint32_t)u * (uint32_t)a.m_tiles) * CG) * (WBM * a.mrep);      // CTA r of a pair: + r * 128 * mrep
+                const int j0 = (int)nt * BN;                                                                  // CTA r of a pair: + r * BNL
                 const int ci0 = (int)sp * a.ci_per_split, ci1 = min(a.cpb * a.nplanes, ((int)sp + 1) * a.ci_per_split);
                 const uint32_t f_last_tile = (w + ncl >= nwork) ? REC_LAST : 0u;
                 for (int ci = ci0; ci < ci1; ++ci, ++ia) {
@@ -391,10 +396,11 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
                     const uint32_t win = base + ab * win_bytes;
                     if (ia >= 2) mbar_wait(aempty(ab), (uint32_t)(((ia >> 1) - 1) & 1));
                     if constexpr (CG == 2) {
-                        const uint32_t fb = lead(afull(ab));
-                        mbar_expect_tx_cluster(fb, a_bytes);
-                        for (int bx = 0; bx < a.nboxes; ++bx)
-                            tma_load_2d_pair(win + bx * a.rows_per_box * 128, &a.tm_x, c0, pl * (int)a.Qp + q0 + bx * a.rows_per_box, fb);
+                        mbar_expect_tx(afull(ab), 2 * a_bytes);
+                        for (int r = 0; r < 2; ++r)
+                            for (int bx = 0; bx < a.nboxes; ++bx)
+                                tma_load_2d_to(win + bx * a.rows_per_box * 128, &a.tm_x, c0,
+                                               pl * (int)a.Qp + q0 + r * (WBM * a.mrep) + bx * a.rows_per_box, afull(ab), (uint16_t)(1u << r));
                     } else {
                         mbar_expect_tx(afull(ab), a_bytes);
                         for (int bx = 0; bx < a.nboxes; ++bx)
@@ -417,17 +423,22 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
                         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(recs + 32u * s), "r"(alo[0]), "r"(alo[1]), "r"(alo[2]),
                                      "r"(alo[3]) : "memory");
                         asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(recs + 32u * s + 16u), "r"(meta), "r"(b_lo | (stage_base >> 4)) : "memory");
+                        if (a.resident && w != cid) {       // weights already in place (first work item): publish the record only
+                            mbar_arrive(bfull(s));
+                        } else
                         if constexpr (CG == 2) {
-                            const uint32_t fb = lead(bfull(s));
-                            mbar_expect_tx_cluster(fb, b_bytes * (uint32_t)nt_s);       // release: the leader's record is visible to the waiter
+                            mbar_expect_tx(bfull(s), 2 * b_bytes * (uint32_t)nt_s);     // release: the record is visible to the waiter
                             for (int k = 0; k < nt_s; ++k) {
                                 const int t = t0 + k;
                                 const uint32_t dst = stage_base + (uint32_t)k * TAP_STRIDE;
-                                if (!a.b_mn_major) {
-                                    tma_load_2d_pair(dst, &a.tm_w, c0, (int)a.wtap[t] * J + j0, fb);
-                                } else {
-                                    for (int jb = 0; jb * 64 < BNL; ++jb)
-                                        tma_load_2d_pair(dst + jb * 8192, &a.tm_w, j0 + jb * 64, (int)a.wtap[t] * C + c0, fb);
+                                for (int r = 0; r < 2; ++r) {
+                                    if (!a.b_mn_major) {
+                                        tma_load_2d_to(dst, &a.tm_w, c0, (int)a.wtap[t] * J + j0 + r * BNL, bfull(s), (uint16_t)(1u << r));
+                                    } else {
+                                        for (int jb = 0; jb * 64 < BNL; ++jb)
+                                            tma_load_2d_to(dst + jb * 8192, &a.tm_w, j0 + r * BNL + jb * 64, (int)a.wtap[t] * C + c0, bfull(s),
+                                                           (uint16_t)(1u << r));
+                                    }
                                 }
                             }
                         } else {
@@ -500,9 +511,9 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
                 if (elect_one()) {
                     if (a.mrep == 2) issue_stage<2, CG>(d_tmem, half_cols, a_hi, b_hi, al0, al1, al2, al3, bl, b_k16, b_tap, idesc, meta, accumulate);
                     else issue_stage<1, CG>(d_tmem, half_cols, a_hi, b_hi, al0, al1, al2, al3, bl, b_k16, b_tap, idesc, meta, accumulate);
-                    commit_cg<CG>(bempty(s));
-                    if (meta & REC_CHUNK_LAST) commit_cg<CG>(aempty(ia & 1));
-                    if (meta & REC_TILE_LAST) commit_cg<CG>(tfull((uint32_t)li & slot_mask));
+                    commit_cg<CG>(bempty(s), 1);                                            // the leader refills
+                    if (meta & REC_CHUNK_LAST) commit_cg<CG>(aempty(ia & 1), 1);
+                    if (meta & REC_TILE_LAST) commit_cg<CG>(tfull((uint32_t)li & slot_mask), 3);    // both CTAs drain their rows
                 }
                 __syncwarp();
                 accumulate = 1;
@@ -1350,9 +1361,11 @@ extern "C" int p2p_conv_window_run_stats(const p2p_conv_window_desc* d, const vo
         a.BN = swap ? 128 : (bn < 16 ? 16 : bn);
     }
     a.n_tiles = (J + a.BN - 1) / a.BN;
-    // CTA pairs (tcgen05 cta_group::2, see conv_window_kernel): on by default; P2P_CONV_CG=1 keeps single CTAs (A/B measurements)
+    // CTA pairs (tcgen05 cta_group::2, see conv_window_kernel): opt-in with P2P_CONV_CG=2.  Measured on B200 (profiles/README.md,
+    // round 2): the pair form issues MMAs at the same ~78 cycles each as single CTAs in this kernel (the operand reads out of
+    // shared memory, not the instruction floor of the microbenchmark, pace it) and loses to them on every G3L2 layer.
     static int cg_env = -1;
-    if (cg_env < 0) { const char* e = getenv("P2P_CONV_CG"); cg_env = (e && e[0] == '1') ? 1 : 2; }
+    if (cg_env < 0) { const char* e = getenv("P2P_CONV_CG"); cg_env = (e && e[0] == '2') ? 2 : 1; }
     const int CG = (!swap && cg_env == 2 && sms % 2 == 0) ? 2 : 1;
     const int slots = sms / CG;                 // CTAs (CG = 1) or CTA pairs (CG = 2) resident at once
     // Two 128-row MMAs per weight tile (mrep = 2) halve the weight bytes TMA writes into shared memory per pixel.  The kernel
@@ -1361,6 +1374,7 @@ extern "C" int p2p_conv_window_run_stats(const p2p_conv_window_desc* d, const vo
     static int mrep_env = -1;
     if (mrep_env < 0) { const char* e = getenv("P2P_CONV_MREP"); mrep_env = (e && e[0] == '1') ? 1 : 2; }
     a.mrep = 1;
+    a.out_bf16_hint = out_dtype == P2P_BF16;
     if (!swap && mrep_env == 2) {
         const long long w1 = ((a.Q + 128 * CG - 1) / (128 * CG)) * a.n_tiles * d->nsub, w2 = ((a.Q + 256 * CG - 1) / (256 * CG)) * a.n_tiles * d->nsub;
         const long long r1 = (w1 + slots - 1) / slots, r2 = (w2 + slots - 1) / slots;
@@ -1370,7 +1384,34 @@ extern "C" int p2p_conv_window_run_stats(const p2p_conv_window_desc* d, const vo
         const int tap_bytes_k = ((bnl * 128 + 1023) / 1024) * 1024, tap_bytes_mn = ((bnl + 63) / 64) * 8192;
         const int tap_max = tap_bytes_k > tap_bytes_mn ? tap_bytes_k : tap_bytes_mn;
         if (w1 * 2 > slots && r2 * 16 < r1 * 10 && WDATA_BYTES - 2 * rows2 >= 3 * tap_max) a.mrep = 2;
+        // few-tile layers (channel loop split across CTAs below): these are bound by the weight bytes TMA pulls out of L2, and
+        // the split fills the chip either way -- take the longer tiles whenever at least two of them exist
+        const int cpb_ = (C + 63) / 64 * nplanes;
+        if (w1 * 2 <= slots && !a.out_bf16_hint && cpb_ >= 4 && a.Q > 256 * CG && w2 * (cpb_ / 2) >= slots / 2 &&
+            WDATA_BYTES - 2 * rows2 >= 3 * tap_max && !deterministic()) a.mrep = 2;
     }
+    // pairs: a layer whose (half) weight set fits next to 128-row windows but not next to 256-row ones keeps the short tiles
+    // and its weights resident (see `resident` below)
+    auto win_bytes_for = [&](int mrep) {
+        const int rows = WBM * mrep + halo, nb = (rows + 255) / 256, rpb = ((rows + nb - 1) / nb + 7) / 8 * 8;
+        const int wb = (rows * 128 + 1023) / 1024 * 1024, bb = (nb * rpb * 128 + 1023) / 1024 * 1024;
+        return wb > bb ? wb : bb;
+    };
+    auto resident_fits = [&](int mrep) {
+        if (swap || (J + a.BN - 1) / a.BN != 1 || d->nsub != 1) return false;
+        const int bnl = a.BN / CG;
+        const bool mn = !(d->w_k == 1);
+        const int tapb = mn ? ((bnl + 63) / 64) * 8192 : ((bnl * 128 + 1023) / 1024) * 1024;
+        const int ring = WDATA_BYTES - 2 * win_bytes_for(mrep);
+        for (int tps = 4; tps >= 1; --tps) {
+            int stages = 0;
+            for (int p = 0; p < nplanes; ++p) stages += (a.pbeg[0][p + 1] - a.pbeg[0][p] + tps - 1) / tps;
+            stages *= (C + 63) / 64;
+            if (stages >= 2 && stages <= kBStagesMax && (long long)stages * tps * tapb <= ring) return true;
+        }
+        return false;
+    };
+    if (CG == 2 && a.mrep == 2 && !resident_fits(2) && resident_fits(1)) a.mrep = 1;
     const int TR = swap ? SBM : WBM * a.mrep, rows_max = swap ? kSwapRowsMax : (WDATA_BYTES / 2) / 128;
     a.win_rows = TR + halo;
     if (a.win_rows > rows_max || (!swap && a.mrep == 1 && a.win_rows > kWinRowsMax))
@@ -1403,13 +1444,31 @@ extern "C" int p2p_conv_window_run_stats(const p2p_conv_window_desc* d, const vo
     if (CG == 2 && (a.BN % 16 != 0)) return fail(P2P_ENOTSUP, "CTA pairs need a column tile that is a multiple of 16");
     a.b_tap_bytes = a.b_mn_major ? ((BNL + 63) / 64) * 8192 : ((BNL * 128 + 1023) / 1024) * 1024;
     const int ring_bytes = swap ? WRING_BYTES : WDATA_BYTES - 2 * a.win_bytes;
-    a.tps = ring_bytes / (3 * a.b_tap_bytes);          // keep >= 3 stages in flight
-    if (a.tps > 4) a.tps = 4;
+    a.tps = ring_bytes / ((CG == 2 ? 6 : 3) * a.b_tap_bytes);          // keep >= 3 (pairs: 6) stages in flight: the refill of a
+    if (a.tps > 4) a.tps = 4;                                           // stage waits for its MMAs to COMPLETE and for TMA's latency
     if (a.tps < 1) a.tps = 1;
     a.b_stage_bytes = a.tps * a.b_tap_bytes;
     a.b_stages = ring_bytes / a.b_stage_bytes;
     if (a.b_stages > kBStagesMax) a.b_stages = kBStagesMax;
     if (a.b_stages < 2) return fail(P2P_ENOTSUP, "weight ring too small for this window");
+    // Resident weights: a layer whose whole weight set (this CTA's half of it) fits the ring keeps it there -- every work item
+    // after the first re-uses the tiles, so only the windows stream from L2 (the 96-channel layers would otherwise pull
+    // ~40 B/clk/SM of weights at the cta_group::2 MMA rate, the L2's whole bandwidth)
+    a.resident = 0;
+    static int res_env = -1;
+    if (res_env < 0) { const char* e = getenv("P2P_CONV_RESIDENT"); res_env = (e && e[0] == '0') ? 0 : 1; }
+    const long long nwork0 = ((a.Q + (long long)TR * CG - 1) / ((long long)TR * CG)) * a.n_tiles * d->nsub;
+    const bool will_split = !swap && out_dtype != P2P_BF16 && nwork0 * 2 <= slots && ((C + 63) / 64) * nplanes >= 4 && !deterministic();
+    if (!swap && res_env && !will_split && nwork0 > slots && (J + a.BN - 1) / a.BN == 1 && d->nsub == 1) {
+        for (int tps = 4; tps >= 1 && !a.resident; --tps) {
+            int stages = 0;
+            for (int p = 0; p < nplanes; ++p) stages += (a.pbeg[0][p + 1] - a.pbeg[0][p] + tps - 1) / tps;
+            stages *= (C + 63) / 64;
+            if (stages >= 2 && stages <= kBStagesMax && (long long)stages * tps * a.b_tap_bytes <= ring_bytes) {
+                a.resident = 1; a.tps = tps; a.b_stage_bytes = tps * a.b_tap_bytes; a.b_stages = stages;
+            }
+        }
+    }
     const long long mt = swap ? (a.Q + TR - 1) / TR : (a.Q + (long long)TR * CG - 1) / ((long long)TR * CG);      // row tiles per CTA (pair)
     if (mt * a.nsub > 2000000000LL / a.n_tiles) return fail(P2P_ENOTSUP, "too many tiles");
     if ((long long)nplanes * a.Qp + halo + (long long)TR * CG > 2000000000LL) return fail(P2P_ENOTSUP, "too many rows for 32-bit row indices");
@@ -1427,6 +1486,7 @@ extern "C" int p2p_conv_window_run_stats(const p2p_conv_window_desc* d, const vo
         if (ns > a.cpb * nplanes / 2) ns = a.cpb * nplanes / 2;
         a.ci_per_split = (a.cpb * nplanes + ns - 1) / ns;
         a.nsplit = (a.cpb * nplanes + a.ci_per_split - 1) / a.ci_per_split;
+        if (a.nsplit > 1 && a.resident) return fail(P2P_ENOTSUP, "internal: resident weights with a split channel loop");
         if (a.nsplit > 1) {
             const size_t bytes = (size_t)d->N * d->OHf * d->OWf * J * sizeof(float);
             if (cudaMemsetAsync(out, 0, bytes, (cudaStream_t)stream) != cudaSuccess) return check_launch("cudaMemsetAsync(split output)");

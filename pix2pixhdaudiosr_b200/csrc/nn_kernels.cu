@@ -164,6 +164,130 @@ __global__ void __launch_bounds__(256) in_stats_v4_kernel(const T* __restrict__ 
     }
 }
 
+// Single-launch statistics (round 2): the CTAs of one (image, 128-channel block) add their partial sums into a zeroed
+// workspace; the LAST of them to finish (self-resetting atomicInc counter) turns the sums into (mean, rstd) -- or, for the
+// backward pass, copies them out -- and zeroes the workspace again.  Replaces memset + reduction + finalize (3 graph nodes).
+// ws: [N][C][2] floats, cnt: [N][gridDim.x] counters, both zero between calls (one stream: calls are ordered).
+__device__ __forceinline__ bool last_cta_of_group(unsigned* cnt, unsigned S) {
+    __shared__ unsigned s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0 && threadIdx.y == 0) s_last = atomicInc(cnt, S - 1) == S - 1;
+    __syncthreads();
+    return s_last != 0;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) in_stats_fused_v4_kernel(const T* __restrict__ y, float* __restrict__ stats, float* __restrict__ ws,
+                                                                unsigned* __restrict__ cnt, int HW, int C, int chunk, float eps) {
+    __shared__ float sm[8][32][9];
+    const int cg = blockIdx.x * 32 + threadIdx.x, n = blockIdx.y, C4 = C >> 2;
+    const int r0 = blockIdx.z * chunk, r1 = min(HW, r0 + chunk);
+    float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f};
+    if (cg < C4) {
+        const T* base = y + (long long)n * HW * C + cg * 4;
+        float shift[4];
+        ld4(base, shift);
+        int r = r0 + threadIdx.y;
+        for (; r + 24 < r1; r += 32) {           // four rows in flight per thread
+            float v[4][4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) ld4(base + (long long)(r + 8 * u) * C, v[u]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { const float d = v[u][i] - shift[i]; a[i] += d; b[i] += d * d; }
+        }
+        for (; r < r1; r += 8) {
+            float v[4];
+            ld4(base + (long long)r * C, v);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { const float d = v[i] - shift[i]; a[i] += d; b[i] += d * d; }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { sm[threadIdx.y][threadIdx.x][i] = a[i]; sm[threadIdx.y][threadIdx.x][4 + i] = b[i]; }
+    __syncthreads();
+    const int t = threadIdx.y * 32 + threadIdx.x, g = t >> 3, k = t & 7, cgo = blockIdx.x * 32 + g;
+    const long long wi = ((long long)n * C + cgo * 4 + (k & 3)) * 2 + (k >> 2);
+    if (cgo < C4) {
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s += sm[i][g][k];
+        if (gridDim.z > 1) atomicAdd(ws + wi, s); else ws[wi] = s;
+    }
+    if (!last_cta_of_group(cnt + (long long)n * gridDim.x + blockIdx.x, gridDim.z)) return;
+    // finalize this (image, channel block): thread t owns (channel group g, component k); pair lanes k and k + 4 of a channel
+    float tot = 0.f;
+    if (cgo < C4) { tot = __ldcg(ws + wi); ws[wi] = 0.f; }
+    const float other = __shfl_xor_sync(0xffffffffu, tot, 4);            // sum <-> sum of squares of the same channel
+    if (cgo < C4 && k < 4) {
+        const int c = cgo * 4 + k;
+        const float shift = ldf(y + (long long)n * HW * C + c);
+        const float m = tot / (float)HW;
+        const float var = fmaxf(other / (float)HW - m * m, 0.f);          // biased variance (PyTorch instance_norm)
+        *reinterpret_cast<float2*>(stats + ((long long)n * C + c) * 2) = make_float2(m + shift, rsqrtf(var + eps));
+    }
+}
+
+template <typename TY, typename T>
+__global__ void __launch_bounds__(256) in_bwd_stats_fused_v4_kernel(const TY* __restrict__ y, const float* __restrict__ stats,
+                                                                    const T* __restrict__ dz, float* __restrict__ work,
+                                                                    float* __restrict__ ws, unsigned* __restrict__ cnt, int HW, int C,
+                                                                    int chunk, int act, float slope) {
+    __shared__ float sm[8][32][9];
+    const int cg = blockIdx.x * 32 + threadIdx.x, n = blockIdx.y, C4 = C >> 2;
+    const int r0 = blockIdx.z * chunk, r1 = min(HW, r0 + chunk);
+    float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f};
+    if (cg < C4) {
+        const long long off = (long long)n * HW * C + cg * 4;
+        const float4* sp = reinterpret_cast<const float4*>(stats + ((long long)n * C + cg * 4) * 2);
+        const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
+        const float mean[4] = {s0.x, s0.z, s1.x, s1.z}, rstd[4] = {s0.y, s0.w, s1.y, s1.w};
+        int r = r0 + threadIdx.y;
+        for (; r + 24 < r1; r += 32) {           // four rows in flight per thread
+            float v[4][4], g[4][4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                ld4(y + off + (long long)(r + 8 * u) * C, v[u]);
+                ld4(dz + off + (long long)(r + 8 * u) * C, g[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float xh = (v[u][i] - mean[i]) * rstd[i];
+                    const float gg = g[u][i] * act_grad(xh, act, slope);
+                    a[i] += gg; b[i] += gg * xh;
+                }
+        }
+        for (; r < r1; r += 8) {
+            float v[4], g[4];
+            ld4(y + off + (long long)r * C, v);
+            ld4(dz + off + (long long)r * C, g);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float xh = (v[i] - mean[i]) * rstd[i];
+                const float gg = g[i] * act_grad(xh, act, slope);
+                a[i] += gg; b[i] += gg * xh;
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { sm[threadIdx.y][threadIdx.x][i] = a[i]; sm[threadIdx.y][threadIdx.x][4 + i] = b[i]; }
+    __syncthreads();
+    const int t = threadIdx.y * 32 + threadIdx.x, g = t >> 3, k = t & 7, cgo = blockIdx.x * 32 + g;
+    const long long wi = ((long long)n * C + cgo * 4 + (k & 3)) * 2 + (k >> 2);
+    if (cgo < C4) {
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s += sm[i][g][k];
+        if (gridDim.z > 1) atomicAdd(ws + wi, s); else ws[wi] = s;
+    }
+    if (!last_cta_of_group(cnt + (long long)n * gridDim.x + blockIdx.x, gridDim.z)) return;
+    if (cgo < C4) { work[wi] = __ldcg(ws + wi); ws[wi] = 0.f; }
+}
+
 template <typename TY, typename T>
 __global__ void __launch_bounds__(256) in_apply_v4_kernel(const TY* __restrict__ y, const T* __restrict__ res, T* __restrict__ z,
                                                           const float* __restrict__ stats, unsigned HWC4, unsigned C4,
@@ -467,7 +591,7 @@ __global__ void adam_dev_kernel(float* __restrict__ w, const float* __restrict__
     }
 }
 
-__global__ void __launch_bounds__(256) adam_dev_v4_kernel(float4* __restrict__ w, const float4* __restrict__ g, float4* __restrict__ m,
+__global__ void __launch_bounds__(128) adam_dev_v4_kernel(float4* __restrict__ w, const float4* __restrict__ g, float4* __restrict__ m,
                                                           float4* __restrict__ v, uint2* __restrict__ wb, long long n4,
                                                           const float* __restrict__ scratch, float beta1, float beta2, float eps,
                                                           float gscale) {
@@ -516,6 +640,31 @@ inline int split_for(long long rows, int base_ctas) {      // chunks of the row 
 
 using namespace p2p;
 
+namespace p2p {
+float* g_stats_ws = nullptr;        // [>= N*C*2] floats, zero between calls (p2p_instnorm_workspace)
+unsigned* g_stats_cnt = nullptr;    // [>= N * ceil(C/128)] counters, zero between calls
+long long g_stats_ws_floats = 0, g_stats_cnt_words = 0;
+int g_stats_ws_device = -1;
+inline bool ws_fits(int N, int C) {
+    if (!g_stats_ws || (long long)N * C * 2 > g_stats_ws_floats || (long long)N * ((C / 4 + 31) / 32) > g_stats_cnt_words) return false;
+    int dev = -1;
+    cudaGetDevice(&dev);
+    return dev == g_stats_ws_device;
+}
+}  // namespace p2p
+
+// Caller-owned, ZEROED device scratch for the single-launch InstanceNorm reductions (the kernels leave it zeroed): ws_floats
+// floats at ws, cnt_words 32-bit words at cnt.  Without it (or when a tensor does not fit) the three-node form runs.
+// One workspace serves every layer: the calls of a step are ordered on one stream.
+extern "C" int p2p_instnorm_workspace(float* ws, long long ws_floats, unsigned* cnt, long long cnt_words) {
+    g_stats_ws = ws; g_stats_ws_floats = ws ? ws_floats : 0;
+    g_stats_cnt = cnt; g_stats_cnt_words = cnt ? cnt_words : 0;
+    g_stats_ws_device = -1;
+    if (ws && cnt) cudaGetDevice(&g_stats_ws_device);       // the workspace serves the device that is current now
+    return P2P_OK;
+}
+
+
 extern "C" int p2p_instnorm_act_fwd(const void* y, const void* res, void* z, float* stats, int N, long long HW, int C,
                                     int norm, int act, float slope, float eps, int y_dtype, int dtype, void* stream) {
     if (N < 0 || HW < 0 || C < 0) return fail(P2P_EINVAL, "negative size");
@@ -527,7 +676,11 @@ extern "C" int p2p_instnorm_act_fwd(const void* y, const void* res, void* z, flo
     const bool v4 = C % 4 == 0 && total / 4 < 2000000000LL && HW < 2000000000LL;
     P2P_DISPATCH_DTYPE2(y_dtype, TY, dtype, T, {
         const bool vec = v4 && vec4_ok(y, sizeof(TY)) && vec4_ok(res, sizeof(T)) && vec4_ok(z, sizeof(T)) && vec4_ok(stats, 4);
-        if (norm) {
+        if (norm && vec && ws_fits(N, C)) {
+            const int cb = (C / 4 + 31) / 32, S = split_for(HW, cb * N);
+            const int chunk = (int)((HW + S - 1) / S);
+            in_stats_fused_v4_kernel<TY><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, g_stats_ws, g_stats_cnt, (int)HW, C, chunk, eps);
+        } else if (norm) {
             if (cudaMemsetAsync(stats, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
             if (vec) {
                 const int cb = (C / 4 + 31) / 32, S = split_for(HW, cb * N);
@@ -557,6 +710,13 @@ extern "C" int p2p_instnorm_stats(const void* y, float* stats, int N, long long 
     if (!y || !stats) return fail(P2P_EINVAL, "null pointer argument");
     if (N > 65535) return fail(P2P_ENOTSUP, "N=%d too large", N);
     cudaStream_t st = (cudaStream_t)stream;
+    if (C % 4 == 0 && HW < 2000000000LL && vec4_ok(y, y_dtype == P2P_BF16 ? 2 : 4) && vec4_ok(stats, 4) && ws_fits(N, C)) {
+        const int cb = (C / 4 + 31) / 32, S = split_for(HW, cb * N);
+        const int chunk = (int)((HW + S - 1) / S);
+        P2P_DISPATCH_DTYPE(y_dtype, TY, in_stats_fused_v4_kernel<TY><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>(
+            (const TY*)y, stats, g_stats_ws, g_stats_cnt, (int)HW, C, chunk, eps));
+        return check_launch("instnorm_stats (single launch)");
+    }
     if (cudaMemsetAsync(stats, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
     P2P_DISPATCH_DTYPE(y_dtype, TY, {
         if (C % 4 == 0 && HW < 2000000000LL && vec4_ok(y, sizeof(TY)) && vec4_ok(stats, 4)) {
@@ -584,7 +744,12 @@ extern "C" int p2p_instnorm_act_bwd(const void* y, const float* stats, const voi
     const bool v4 = C % 4 == 0 && total / 4 < 2000000000LL && HW < 2000000000LL;
     P2P_DISPATCH_DTYPE2(y_dtype, TY, dtype, T, {
         const bool vec = v4 && vec4_ok(y, sizeof(TY)) && vec4_ok(dz, sizeof(T)) && vec4_ok(dy, sizeof(T)) && vec4_ok(stats, 4) && vec4_ok(work, 4);
-        if (norm) {
+        if (norm && vec && ws_fits(N, C)) {
+            const int cb = (C / 4 + 31) / 32, S = split_for(HW, cb * N);
+            const int chunk = (int)((HW + S - 1) / S);
+            in_bwd_stats_fused_v4_kernel<TY, T><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, (const T*)dz, work, g_stats_ws,
+                                                                                         g_stats_cnt, (int)HW, C, chunk, act, slope);
+        } else if (norm) {
             if (cudaMemsetAsync(work, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
             if (vec) {
                 const int cb = (C / 4 + 31) / 32, S = split_for(HW, cb * N);
@@ -688,7 +853,9 @@ extern "C" int p2p_adam_step_dev(float* w, const float* g, float* m, float* v, v
     if (!w || !g || !m || !v || !lr_dev || !step_dev || !scratch2) return fail(P2P_EINVAL, "null pointer argument");
     adam_prepare_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_dev, lr_dev, beta1, beta2, scratch2);
     if (n % 4 == 0 && vec4_ok(w, 4) && vec4_ok(g, 4) && vec4_ok(m, 4) && vec4_ok(v, 4) && vec4_ok(w_bf16, 2))
-        adam_dev_v4_kernel<<<ew_grid(n / 4), kEw, 0, (cudaStream_t)stream>>>((float4*)w, (const float4*)g, (float4*)m, (float4*)v,
+        // 128-thread blocks: small enough (registers) to share an SM with a resident conv_window_kernel CTA -- train_step runs
+        // the generator's Adam on a side stream during the discriminator's backward pass
+        adam_dev_v4_kernel<<<(unsigned)((n / 4 + 127) / 128 < 148 * 12 ? (n / 4 + 127) / 128 : 148 * 12), 128, 0, (cudaStream_t)stream>>>((float4*)w, (const float4*)g, (float4*)m, (float4*)v,
                                                                             (uint2*)w_bf16, n / 4, scratch2, beta1, beta2, eps, grad_scale);
     else
         adam_dev_kernel<<<ew_grid(n), kEw, 0, (cudaStream_t)stream>>>(w, g, m, v, (__nv_bfloat16*)w_bf16, n, scratch2, beta1, beta2,

@@ -119,14 +119,31 @@ _TIMING = None
 _FLOP_RATIO = 1.0     # algorithmic / launched FLOPs of the launches being recorded (channel-padded or packed thin layers)
 
 
-def start_conv_timing():
-    global _TIMING
+_EVENT_EXTERNAL = False
+
+
+def start_conv_timing(external=False):
+    """external=True: the events become record nodes of a CUDA graph being captured (timed after the graph's replay: the
+    kernels then run back to back, with no host launch gaps inside the event pairs)"""
+    global _TIMING, _EVENT_EXTERNAL
     _TIMING = []
+    _EVENT_EXTERNAL = bool(external)
+
+
+def pause_conv_timing():
+    """stop recording (keeps what was recorded for stop_conv_timing)"""
+    global _TIMING, _TIMING_HELD
+    _TIMING_HELD, _TIMING = _TIMING, None
+
+
+_TIMING_HELD = None
 
 
 def stop_conv_timing():
     """-> list of (kind, tensor_core?, flops, milliseconds) for every convolution pass since start_conv_timing()"""
-    global _TIMING
+    global _TIMING, _TIMING_HELD
+    if _TIMING is None and _TIMING_HELD is not None:
+        _TIMING, _TIMING_HELD = _TIMING_HELD, None
     rec, _TIMING = _TIMING, None
     torch.cuda.synchronize()
     return [(kind, umma, flops, e0.elapsed_time(e1), shape) for kind, umma, flops, e0, e1, shape in rec]
@@ -137,7 +154,8 @@ def _timed(kind, P, launch, umma=None):
         launch()
         return
     lib = _lib.lib()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0 = torch.cuda.Event(enable_timing=True, external=_EVENT_EXTERNAL)
+    e1 = torch.cuda.Event(enable_timing=True, external=_EVENT_EXTERNAL)
     n0 = lib.p2p_conv_umma_launches()
     e0.record()
     launch()
@@ -1000,9 +1018,30 @@ def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None
         _FLOP_RATIO = 1.0
 
 
+_STATS_WS = {}
+
+
+def _ensure_stats_workspace(device):
+    """zeroed scratch that lets the InstanceNorm reductions run as one launch each (p2p_instnorm_workspace); one per process
+    (one process per GPU), created on first use and kept alive here"""
+    if not USE_STATS_WS:
+        return
+    key = torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()
+    if _STATS_WS.get("device") == key:
+        return
+    ws = torch.zeros(1 << 20, dtype=torch.float32, device=device)
+    cnt = torch.zeros(1 << 16, dtype=torch.int32, device=device)
+    _STATS_WS.update(device=key, ws=ws, cnt=cnt)
+    _lib.check(_lib.lib().p2p_instnorm_workspace(_p(ws), ws.numel(), _p(cnt), cnt.numel()))
+
+
+USE_STATS_WS = os.environ.get("P2P_STATS_WS", "1") == "1"
+
+
 def norm_act_forward(y, res, norm, act, slope, eps, out_dtype):
     """z = act(InstanceNorm2d(affine=False)(y)) [+ res]; returns (z, stats)"""
     N, H, W, C = y.shape
+    _ensure_stats_workspace(y.device)
     z = torch.empty(y.shape, dtype=out_dtype, device=y.device)
     stats = torch.empty((N, C, 2), dtype=torch.float32, device=y.device) if norm else None
     if res is not None:
@@ -1025,6 +1064,7 @@ def norm_act_forward_planes(y, bias, raw, res, norm, act, slope, eps, key, want_
     strided view of the planes' interior; layout = (key, planes) for conv_forward(xin=...); stats = (mean, rstd) [N,C,2]."""
     N, H, W, C = y.shape
     lib = _lib.lib()
+    _ensure_stats_workspace(y.device)
     plain_only = key is None
     if plain_only:
         key = (0, 0, H, W, N * H * W, False, 1, C)
@@ -1062,6 +1102,7 @@ def norm_act_forward_planes(y, bias, raw, res, norm, act, slope, eps, key, want_
 
 def norm_act_backward(y, stats, dz, norm, act, slope):
     N, H, W, C = y.shape
+    _ensure_stats_workspace(y.device)
     dy = torch.empty(y.shape, dtype=dz.dtype, device=y.device)
     work = torch.empty((N, C, 2), dtype=torch.float32, device=y.device) if norm else None
     _lib.check(_lib.lib().p2p_instnorm_act_bwd(_p(y), _p(stats), _p(dz), _p(dy), _p(work), N, H * W, C, int(norm), act,
@@ -1109,17 +1150,22 @@ class ConvBlockFn(torch.autograd.Function):
         _need_cuda(x, weight)
         plain = (not norm) and act == ACT_NONE and res is None
         aux = [] if ctx.needs_input_grad[1] else None
-        y_dtype = torch.float32 if norm else x.dtype
         Cout = weight.shape[1] if cfg.transposed else weight.shape[0]
         fused = (not plain) and FUSE_NORM_PAD and x.dtype == torch.bfloat16 and Cout % 8 == 0 and Cout <= 2048 and x.shape[0] < 65535
+        # bf16 mode, fused path: the pre-normalisation output is stored in bf16 WITHOUT the conv bias (InstanceNorm2d(affine=False)
+        # removes any per-channel constant, so the bias only cost mantissa bits before the mean subtraction); the statistics are
+        # taken of the stored values, as torch.autocast does for the reference.  P2P_BF16_PRENORM=0 keeps fp32 (round-1 behaviour).
+        y16 = fused and norm and BF16_PRENORM and not (EPI_STATS and not deterministic())
+        y_dtype = (x.dtype if y16 else torch.float32) if norm else x.dtype
+        cbias = None if y16 else bias
         raw = None
-        if fused and norm:
+        if fused and norm and EPI_STATS and not y16:
             raw = torch.empty((x.shape[0], Cout, 2), dtype=torch.float32, device=x.device)
-            y, took = conv_forward(x, weight, bias, w16, cfg, y_dtype, aux, xin, raw)
+            y, took = conv_forward(x, weight, cbias, w16, cfg, y_dtype, aux, xin, raw)
             if not took:
                 raw = None
         else:
-            y = conv_forward(x, weight, bias, w16, cfg, y_dtype, aux, xin)
+            y = conv_forward(x, weight, cbias, w16, cfg, y_dtype, aux, xin)
         ctx.xpad = aux[0] if aux else None
         layout = None
         if plain:
@@ -1158,6 +1204,13 @@ class ConvBlockFn(torch.autograd.Function):
 
 
 FUSE_NORM_PAD = os.environ.get("P2P_FUSE_NORM_PAD", "1") == "1"
+# measured (round 2): storing the pre-normalisation output in bf16 moves the G3L2 step by 0.4 % (these passes are launch- and
+# latency-bound, not byte-bound) and costs four per-layer 2e-2 tolerance checks: fp32 stays the default
+BF16_PRENORM = os.environ.get("P2P_BF16_PRENORM", "0") == "1"
+# InstanceNorm sums from the conv epilogue instead of a separate reduction pass.  Measured on B200 (round 2, G3L2 step): the
+# window kernel's forward launches get 0.74 ms slower per step (column sums + red.add in the epilogue warps) while the
+# reduction kernels they replace cost 0.4 ms -- a net loss, so the separate pass stays the default (P2P_EPI_STATS=1 opts in).
+EPI_STATS = os.environ.get("P2P_EPI_STATS", "0") == "1"
 
 
 class InstNormActFn(torch.autograd.Function):

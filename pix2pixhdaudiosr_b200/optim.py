@@ -10,6 +10,7 @@ import torch
 from . import ops
 
 _ALIGN = 8      # elements: keeps every bf16 slice 16-byte aligned for the vector / tensor-core loads
+_SHARD_ALIGN = 128   # the flat buffers are a multiple of this: equal, 16-byte aligned shards for up to 16 data-parallel ranks
 
 
 class FusedAdam:
@@ -22,7 +23,9 @@ class FusedAdam:
             raise RuntimeError("FusedAdam needs CUDA parameters (no CPU fallback): move the networks to the GPU first")
         self.param_groups = [{"params": params, "lr": lr, "betas": tuple(betas), "eps": eps}]
         sizes = [(p.numel() + _ALIGN - 1) // _ALIGN * _ALIGN for p in params]
-        total = sum(sizes)
+        total = (sum(sizes) + _SHARD_ALIGN - 1) // _SHARD_ALIGN * _SHARD_ALIGN
+        self.shard = None                                                  # (rank, world): train.GradSync's sharded mode
+        self.grad_shard = None
         self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
         self.flat_grad = torch.zeros(total, dtype=torch.float32, device=dev)
         self.exp_avg = torch.zeros(total, dtype=torch.float32, device=dev)
@@ -80,8 +83,38 @@ class FusedAdam:
         if not torch.cuda.is_current_stream_capturing():
             self.sync_lr()
         self.step_count += 1
+        if self.shard is not None:
+            # sharded data parallelism (train.GradSync(shard=True)): this rank owns 1/world of the flat buffers -- its
+            # gradients arrived by reduce-scatter in grad_shard, it updates its slice of the master weights, the moments and the
+            # bf16 shadow; the shadow slices are all-gathered afterwards.  Adam's HBM traffic per rank drops by the world size.
+            lo, hi = self.shard_range()
+            ops.adam_step_dev(self.flat[lo:hi], self.grad_shard, self.exp_avg[lo:hi], self.exp_avg_sq[lo:hi], self.flat_bf16[lo:hi],
+                              self.lr_dev, g["betas"][0], g["betas"][1], g["eps"], self.grad_scale, self.step_dev, self._scratch)
+            return
         ops.adam_step_dev(self.flat, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.flat_bf16, self.lr_dev,
                           g["betas"][0], g["betas"][1], g["eps"], self.grad_scale, self.step_dev, self._scratch)
+
+    def shard_range(self):
+        rank, world = self.shard
+        n = self.flat.numel() // world
+        return rank * n, (rank + 1) * n
+
+    def set_shard(self, rank, world):
+        if self.flat.numel() % (world * 4) != 0:
+            raise ValueError("flat buffers do not split into %d aligned shards" % world)
+        self.shard = (rank, world)
+        if self.grad_shard is None or self.grad_shard.numel() != self.flat.numel() // world:
+            self.grad_shard = torch.zeros(self.flat.numel() // world, dtype=torch.float32, device=self.flat.device)
+
+    def gather_state(self, group=None):
+        """sharded mode: bring the master weights and both moments of every shard to every rank (before a checkpoint is
+        written; between steps only the bf16 shadow is complete everywhere)"""
+        if self.shard is None:
+            return
+        import torch.distributed as dist
+        lo, hi = self.shard_range()
+        for buf in (self.flat, self.exp_avg, self.exp_avg_sq):
+            dist.all_gather_into_tensor(buf, buf[lo:hi].clone(), group=group)
 
     def state_dict(self):
         return {"step": int(self.step_dev.item()), "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq,

@@ -9,6 +9,8 @@ average of the flat gradient buffers (one NCCL all-reduce per network over NVLin
 issued asynchronously right after loss_G.backward() and overlaps loss_D.backward(): the discriminator's backward
 touches neither G's weights nor G's gradients, so applying optimizer_G.step() after it is arithmetically the
 reference's order."""
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -33,10 +35,16 @@ class GradSync:
 
     EARLY_MIN = 1 << 20            # elements; smaller gradients travel with the final all-reduce
 
-    def __init__(self, group=None):
+    def __init__(self, group=None, shard=False):
+        """shard=True (bf16 training): reduce-scatter the gradients, let every rank run Adam on its 1/world slice only and
+        all-gather the bf16 weight shadow the kernels read -- the same bytes over NVLink as the all-reduce would move in fp32
+        minus a quarter, and Adam's 30 bytes per parameter of HBM traffic divided by the world size.  Between steps the fp32
+        master weights and the moments are complete only per shard (FusedAdam.gather_state before a checkpoint)."""
         self.enabled = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
         self.group = group
         self.world = dist.get_world_size(group) if self.enabled else 1
+        self.rank = dist.get_rank(group) if self.enabled else 0
+        self.shard = bool(shard) and self.enabled
         self._early = {}           # optimizer id -> {"handles": [...], "ranges": [(offset, n), ...]}
 
     def attach_early(self, optimizer):
@@ -54,6 +62,17 @@ class GradSync:
     def start(self, optimizer):
         if not self.enabled:
             return None
+        if self.shard:
+            if optimizer.shard is None:
+                optimizer.set_shard(self.rank, self.world)
+            if dist.get_backend(self.group) == "gloo":      # CPU tests: gloo has no reduce-scatter -- all-reduce, keep the own slice
+                h = dist.all_reduce(optimizer.flat_grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                h.wait()
+                lo, hi = optimizer.shard_range()
+                optimizer.grad_shard.copy_(optimizer.flat_grad[lo:hi])
+                return []
+            return [dist.reduce_scatter_tensor(optimizer.grad_shard, optimizer.flat_grad, op=dist.ReduceOp.SUM, group=self.group,
+                                               async_op=True)]
         st = self._early.get(id(optimizer))
         if st is None or not st["ranges"]:
             return [dist.all_reduce(optimizer.flat_grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True)]
@@ -73,6 +92,60 @@ class GradSync:
         optimizer.grad_scale = 1.0 / self.world     # the averaging is folded into the Adam kernel's gradient read
 
 
+    def after_step(self, optimizer):
+        """sharded mode: all-gather the bf16 shadow slices the ranks just updated (asynchronous; finish_gather waits)"""
+        if not self.shard:
+            return None
+        lo, hi = optimizer.shard_range()
+        return dist.all_gather_into_tensor(optimizer.flat_bf16, optimizer.flat_bf16[lo:hi].clone(), group=self.group, async_op=True)
+
+    def finish_gather(self, handle):
+        if handle is not None:
+            handle.wait()
+
+    def gather_state(self, model):
+        """sharded mode: complete master weights / moments on every rank (call before saving a checkpoint)"""
+        if self.shard:
+            for opt in (model.optimizer_G, model.optimizer_D):
+                opt.gather_state(self.group)
+
+
+class _NoSync:
+    """single process: every exchange is a no-op"""
+    enabled = shard = False
+
+    def start(self, optimizer):
+        return None
+
+    def finish(self, optimizer, handles):
+        pass
+
+    def after_step(self, optimizer):
+        return None
+
+    def finish_gather(self, handle):
+        pass
+
+
+_NOSYNC = _NoSync()
+
+
+def replica_drift(model, group=None):
+    """max - min over the ranks of a checksum of every bf16 weight the kernels read (0 = the replicas are bit-identical)"""
+    if not (dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1):
+        return 0
+    out = 0
+    for opt in (model.optimizer_G, model.optimizer_D):
+        v = opt.flat_bf16.view(torch.int16).to(torch.int64)
+        idx = torch.arange(v.numel(), device=v.device, dtype=torch.int64) % 8191 + 1
+        c = (v * idx).sum().reshape(1)
+        hi, lo = c.clone(), c.clone()
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
+        out = max(out, int((hi - lo).item()))
+    return out
+
+
 def broadcast_parameters(model, src=0, group=None):
     """identical replicas at start (the reference's DataParallel re-broadcasts every step)"""
     if not (dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1):
@@ -82,23 +155,58 @@ def broadcast_parameters(model, src=0, group=None):
         opt.flat_bf16.copy_(opt.flat)
 
 
+OVERLAP_G_STEP = os.environ.get("P2P_OVERLAP_GSTEP", "1") == "1"
+_SIDE = {}
+
+
+def _side_stream(device):
+    key = torch.device(device)
+    if key not in _SIDE:
+        _SIDE[key] = torch.cuda.Stream(device=key)
+    return _SIDE[key]
+
+
 def train_step(model, lr_audio, hr_audio, inst=None, feat=None, infer=False, sync=None):
-    """returns (loss_dict, generated-or-None); loss values stay on the device (no host sync in the step)"""
+    """returns (loss_dict, generated-or-None); loss values stay on the device (no host sync in the step).
+
+    The generator's update -- gradient exchange, Adam (156 M parameters, HBM-bound), all-gather of the bf16 shadow -- runs on
+    a side stream WHILE the main stream computes the discriminator's backward pass: loss_D.backward() reads neither G's
+    weights nor G's gradients, so this is arithmetically the reference's order (train.py:164-184), and the bandwidth-bound
+    optimiser kernels share the SMs with the tensor-core-bound convolutions instead of running after them."""
     losses, generated = model(lr_audio, inst, hr_audio, feat, infer)
     loss_dict, loss_G, loss_D = assemble_losses(model, losses)
     opt_G, opt_D = model.optimizer_G, model.optimizer_D
     opt_G.zero_grad()
     loss_G.backward()
-    h_G = sync.start(opt_G) if sync is not None else None
+    if sync is None:
+        sync = _NOSYNC
+
+    def update(opt):
+        h = sync.start(opt)
+        sync.finish(opt, h)
+        opt.step()
+        sync.finish_gather(sync.after_step(opt))
+
+    overlap = OVERLAP_G_STEP and opt_G.flat.is_cuda
+    if overlap:
+        main = torch.cuda.current_stream(opt_G.flat.device)
+        side = _side_stream(opt_G.flat.device)
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            update(opt_G)
+    else:
+        h_G = sync.start(opt_G)
     opt_D.zero_grad()
     loss_D.backward()
-    h_D = sync.start(opt_D) if sync is not None else None
-    if sync is not None:
+    if not overlap:
         sync.finish(opt_G, h_G)
-    opt_G.step()
-    if sync is not None:
-        sync.finish(opt_D, h_D)
-    opt_D.step()
+        opt_G.step()
+        g_G = sync.after_step(opt_G)
+        update(opt_D)
+        sync.finish_gather(g_G)
+    else:
+        update(opt_D)
+        main.wait_stream(side)
     return {k: (v.detach() if torch.is_tensor(v) else v) for k, v in loss_dict.items()}, generated
 
 

@@ -106,7 +106,9 @@ def run(opt, model, make_dataset, dataset_size, max_steps=None, print_freq=100, 
     start_epoch, epoch_iter = read_iter(iter_path, opt.continue_train)
     if opt.continue_train:
         load_optimizers(model)
-    sync = GradSync()
+    # bf16 training shards the optimiser step over the ranks (train.GradSync); the exact fp32 path reads the fp32 master weights
+    # in its kernels, so it keeps the plain all-reduce
+    sync = GradSync(shard=model.act_dtype == torch.bfloat16)
     broadcast_parameters(model)
     if rank == 0:
         os.makedirs(save_dir, exist_ok=True)
@@ -117,6 +119,7 @@ def run(opt, model, make_dataset, dataset_size, max_steps=None, print_freq=100, 
     steps, iter_start_time = 0, time.time()
 
     def save(epoch, epoch_iter_next, also_epoch=False):
+        sync.gather_state(model)          # sharded mode: a collective every rank takes part in (complete masters / moments)
         if rank != 0:
             return
         model.save('latest')

@@ -63,3 +63,56 @@ def test_single_process_sync_is_a_no_op():
     s = GradSync()
     assert not s.enabled and s.start(None) is None
     s.finish(None, None)
+
+
+def _shard_worker(rank, world, port, out):
+    """sharded mode on stand-in buffers: every rank steps only its slice (a plain SGD stand-in for the fused Adam kernel) and the
+    bf16 shadow must come back complete and identical on all ranks"""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from pix2pixhdaudiosr_b200.train import GradSync, replica_drift
+
+    class Opt:
+        def __init__(self, n):
+            g = torch.Generator().manual_seed(5)
+            self.flat = torch.randn(n, generator=g)
+            self.flat_bf16 = self.flat.to(torch.bfloat16)
+            torch.manual_seed(100 + rank)
+            self.flat_grad = torch.randn(n)
+            self.grad_scale, self.shard, self.grad_shard = 1.0, None, None
+
+        def set_shard(self, r, w):
+            self.shard = (r, w)
+            self.grad_shard = torch.zeros(self.flat.numel() // w)
+
+        def shard_range(self):
+            r, w = self.shard
+            n = self.flat.numel() // w
+            return r * n, (r + 1) * n
+
+        def step(self):
+            lo, hi = self.shard_range()
+            self.flat[lo:hi] -= 0.1 * self.grad_scale * self.grad_shard
+            self.flat_bf16[lo:hi] = self.flat[lo:hi].to(torch.bfloat16)
+
+    opt = Opt(256)
+    local = opt.flat_grad.clone()
+    sync = GradSync(shard=True)
+    assert sync.shard and sync.rank == rank
+    h = sync.start(opt)
+    sync.finish(opt, h)
+    opt.step()
+    sync.finish_gather(sync.after_step(opt))
+    model = types.SimpleNamespace(optimizer_G=opt, optimizer_D=opt)
+    out[rank] = dict(w16=opt.flat_bf16.clone(), local=local, drift=replica_drift(model), w0=torch.randn(256, generator=torch.Generator().manual_seed(5)))
+    dist.destroy_process_group()
+
+
+def test_two_rank_sharded_step_and_gather():
+    world = 2
+    out = mp.Manager().dict()
+    mp.spawn(_shard_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    a, b = out[0], out[1]
+    want = (a["w0"] - 0.1 * (a["local"] + b["local"]) / world).to(torch.bfloat16)
+    assert torch.equal(a["w16"], b["w16"]) and a["drift"] == 0 and b["drift"] == 0
+    assert torch.allclose(a["w16"].float(), want.float(), atol=1e-2)
