@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- the driver's measurement contract for the hot path (see DESIGN.md "Measurement").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload train|train_time|mdct]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload train|train_time|mdct|global_g]
 
 One JSON line on stdout (rank 0).
 Workload "train" (default; BASELINE.json configs[2]): one step = one full G3L2-ngf48 optimisation step
@@ -10,6 +10,8 @@ Workload "train" (default; BASELINE.json configs[2]): one step = one full G3L2-n
 fp32 accumulation; ranks are data-parallel replicas exchanging only the gradient all-reduce.  `value` = samples/s with
 the audio resident in HBM; `e2e` = the same step fed from pinned HOST audio with the losses read back every step.
 The line also carries "mdct4": the MDCT4 / IMDCT4 kernels' GB/s against the HBM peak (second half of the metric).
+Workload "global_g" (BASELINE.json configs[1]): one step = one forward of define_G(1,1,64,'global',4,9) on [8,1,512,256]
+(bench_global.py).
 Workload "mdct": one step = MDCT4.forward + IMDCT4.forward over a batch of B synthetic 48 kHz segments (n_fft 1024,
 hop 512, KBD window, center), inputs larger than L2 so no flush is needed.
 """
@@ -35,7 +37,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="train", choices=["train", "train_time", "mdct"])
+    ap.add_argument("--workload", default="train", choices=["train", "train_time", "mdct", "global_g"])
     ap.add_argument("--transform", default="mdct4", choices=["mdct4", "mdct2"],
                     help="train workloads: the lapped transform in front of the networks (mdct2 = the shipped wiring)")
     ap.add_argument("--batch", type=int, default=None, help="segments per GPU per step (train: 8, mdct: 512)")
@@ -60,6 +62,23 @@ def tensor_peak():
         d = json.load(open(p))
         return float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "measured (sustained)"
     return 1400.0, "fallback"
+
+
+def tensor_peak_burst():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["bf16_tflops"])
+    return 1590.0
+
+
+def kept_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the ncu capture kept under profiles/
+    (profiles/r02_dram_traffic.json, written by profiles/dram_traffic.py from an ncu pass over one step), or None"""
+    p = os.path.join(ROOT, "profiles", "r02_dram_traffic.json")
+    try:
+        return json.load(open(p)).get(kernel)
+    except (OSError, ValueError):
+        return None
 
 
 def mdct_bytes(B, T, F, M, T_out):
@@ -305,8 +324,11 @@ def main():
     sys.stdout = os.fdopen(os.dup(1), "w", buffering=1)
     os.dup2(2, 1)
     if args.batch is None:
-        args.batch = 8 if args.workload.startswith("train") else 512
-    if args.workload.startswith("train"):
+        args.batch = 8 if args.workload.startswith("train") or args.workload == "global_g" else 512
+    if args.workload == "global_g":
+        from bench_global import run_global, run_global_reference
+        (run_global_reference if args.impl == "reference" else run_global)(args)
+    elif args.workload.startswith("train"):
         from bench_train import run_train, run_train_reference
         (run_train_reference if args.impl == "reference" else run_train)(args)
     elif args.impl == "reference":

@@ -148,7 +148,7 @@ def run_train_reference(args):
 def run_train(args):
     import torch
     import torch.distributed as dist
-    from bench import ClockSampler, tensor_peak
+    from bench import ClockSampler, kept_traffic, tensor_peak, tensor_peak_burst
     from pix2pixhdaudiosr_b200 import _lib, ops, options
     from pix2pixhdaudiosr_b200.models.models import create_model
     from pix2pixhdaudiosr_b200.train import GradSync, GraphedTrainStep, broadcast_parameters, replica_drift, train_step
@@ -278,6 +278,13 @@ def run_train(args):
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
     total_ms, e2e_ms = times.tolist()
     if rank == 0:
+        dump = os.environ.get("P2P_BENCH_DUMP_LAUNCHES")
+        if dump:        # per-launch table of the profiled step: kind, GEMM shape, algorithmic GFLOP, ms, TFLOP/s
+            with open(dump, "w") as f:
+                for kind, umma, flops, ms, shape in rec:
+                    f.write("%-14s %s M=%-7d J=%-5d K=%-5d taps=%-3d HxW=%dx%d  %8.2f GF %8.4f ms %7.1f TF\n" % (
+                        kind, "tc" if umma else "cc", shape["M"], shape["J"], shape["K"], shape["taps"], shape["H"], shape["W"],
+                        flops / 1e9, ms, flops / max(ms, 1e-9) / 1e9))
         peak, peak_src = tensor_peak()
         step_ms = total_ms / K
         classes = {}
@@ -307,7 +314,10 @@ def run_train(args):
                        "final_losses": final_losses},
             "roofline": {"bound": "tensor", "kernel": "conv_window_kernel (TMA-fed tcgen05 shifted-window implicit GEMM: forward + input-gradient passes)",
                          "achieved": round(dom_ach, 1), "peak": peak, "unit": "TFLOP/s", "frac": round(dom_ach / peak, 4),
-                         "peak_source": peak_src, "traffic": None, "launches_per_step": dom_n,
+                         "peak_source": peak_src + ": bf16_tflops_sustained of MEASURED_PEAKS.json (cuBLAS, seconds-long loop); the kernel was "
+                                        "timed inside the step at the SM clock in `clocks`",
+                         "frac_of_burst_peak": round(dom_ach / tensor_peak_burst(), 4),
+                         "traffic": kept_traffic("conv_window_kernel"), "launches_per_step": dom_n,
                          "flops_per_launch": round(dom_flops / max(dom_n, 1)), "ms_per_launch": round(dom_ms / max(dom_n, 1), 5),
                          "ms_per_step_in_kernel": round(dom_ms, 3), "share_of_step": round(dom_ms / step_ms, 3),
                          "all_tcgen05": {"launches_per_step": um_n, "achieved": round(ach, 1), "frac": round(ach / peak, 4),

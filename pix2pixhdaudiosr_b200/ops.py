@@ -427,7 +427,7 @@ def _dgrad_wrap(dy_shared, wq, dtype, N, H, W, p, KH, KW, Cout, Cin, reflect):
     few = _few_tiles(N * Hh * Wh, Cin, 1, (Cout + 63) // 64)
     out = torch.empty((N, gy, gx, Cin), dtype=torch.float32 if few else dtype, device=buf.device)
     planes = buf[off:]
-    _timed("dgrad", _Shape(N, gy, gx, Cin, KH * KW, Cout, Hh, Wh),
+    _timed("dgrad", _Shape(N, H, W, Cin, KH * KW, Cout, Hh, Wh),          # algorithmic FLOPs: the unpadded H x W, not the padded grid
            lambda: _lib.check(_lib.lib().p2p_conv_window_run(ctypes.byref(d), _p(planes), _p(wq), None, _p(out), _DT[out.dtype],
                                                             _stream())), umma=True)
     return out if out.dtype == dtype else out.to(dtype)

@@ -217,7 +217,12 @@ class GraphedTrainStep:
     static device buffers; the loss values of the last replay are in `self.losses` (device tensors)."""
 
     def __init__(self, model, lr_audio, hr_audio, sync=None, warmup=3):
+        """NOTE: the `warmup` eager steps before the capture are REAL optimisation steps (they move the weights and Adam's
+        state, like any other step).  The learning rate lives on the device: __call__ pushes param_groups['lr'] changes
+        (update_learning_rate) before every replay.  After model.update_fixed_params() (a new optimizer_G with new flat
+        buffers) the captured graph is stale: build a new GraphedTrainStep -- __call__ refuses to replay a stale graph."""
         self.model, self.sync = model, sync
+        self._opt_ids = (id(model.optimizer_G), id(model.optimizer_D))
         dev = torch.device(model.device)
         self.lr_static = lr_audio.to(dev).clone()
         self.hr_static = hr_audio.to(dev).clone()
@@ -235,6 +240,11 @@ class GraphedTrainStep:
             self.losses, _ = train_step(model, self.lr_static, self.hr_static, sync=sync)
 
     def __call__(self, lr_audio, hr_audio):
+        if (id(self.model.optimizer_G), id(self.model.optimizer_D)) != self._opt_ids:
+            raise RuntimeError("the model's optimizers were replaced after the step was captured (update_fixed_params): "
+                               "build a new GraphedTrainStep")
+        for opt in (self.model.optimizer_G, self.model.optimizer_D):
+            opt.sync_lr()
         if lr_audio.data_ptr() != self.lr_static.data_ptr():
             self.lr_static.copy_(lr_audio, non_blocking=True)
         if hr_audio.data_ptr() != self.hr_static.data_ptr():

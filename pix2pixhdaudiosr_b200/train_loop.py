@@ -54,9 +54,22 @@ def format_errors(epoch, i, errors, t):
     return message
 
 
-def _optim_state(opt_):
-    """step + moments per parameter, in the logical (reference) layout and order of param_groups[0]['params']"""
-    out = {'step': int(opt_.step_dev.item()), 'lr': float(opt_.param_groups[0]['lr']), 'exp_avg': [], 'exp_avg_sq': []}
+def _param_names(model, opt_):
+    """'G.model.1.weight'-style names of the optimiser's parameters, in its order (None when a parameter is not found)"""
+    ids = {}
+    for tag in ('netG', 'netD', 'time_D'):
+        net = getattr(model, tag, None)
+        if net is not None:
+            for k, p in net.named_parameters():
+                ids[id(p)] = '%s.%s' % (tag, k)
+    return [ids.get(id(p)) for p, _ in opt_._views]
+
+
+def _optim_state(opt_, names=None):
+    """step + moments per parameter, in the logical (reference) layout and order of param_groups[0]['params']; `names` (one per
+    parameter) lets a later load match the moments by name instead of by position"""
+    out = {'step': int(opt_.step_dev.item()), 'lr': float(opt_.param_groups[0]['lr']), 'exp_avg': [], 'exp_avg_sq': [],
+           'names': list(names) if names is not None else None}
     for p, g in opt_._views:
         o, n = g.storage_offset(), p.numel()
         for name, flat in (('exp_avg', opt_.exp_avg), ('exp_avg_sq', opt_.exp_avg_sq)):
@@ -66,12 +79,32 @@ def _optim_state(opt_):
     return out
 
 
-def _load_optim_state(opt_, sd):
+def _load_optim_state(opt_, sd, names=None):
+    """moments are matched BY NAME and shape when both sides carry names (a checkpoint written after update_fixed_params holds
+    all of netG's parameters, a rebuilt optimizer_G with niter_fix_global > 0 only the local enhancer's): what is missing is
+    left at zero with a warning; without names the lists must agree in length and every shape must match"""
     opt_.step_count = int(sd['step'])
     opt_.step_dev.fill_(opt_.step_count)
     opt_.param_groups[0]['lr'] = float(sd['lr'])
     opt_.sync_lr()
-    for (p, g), m, v in zip(opt_._views, sd['exp_avg'], sd['exp_avg_sq']):
+    saved_names = sd.get('names')
+    if names is not None and saved_names is not None and None not in names and None not in saved_names:
+        by_name = {k: (m, v) for k, m, v in zip(saved_names, sd['exp_avg'], sd['exp_avg_sq'])}
+        pairs = [by_name.get(k) for k in names]
+        missing = [k for k, pr in zip(names, pairs) if pr is None]
+        if missing:
+            print('optimizer state: no saved moments for %d parameter(s) (e.g. %s): they restart from zero' % (len(missing), missing[0]))
+    else:
+        if len(sd['exp_avg']) != len(opt_._views):
+            raise ValueError('optimizer state holds %d parameters, the optimizer %d (and no names to match them by)'
+                             % (len(sd['exp_avg']), len(opt_._views)))
+        pairs = list(zip(sd['exp_avg'], sd['exp_avg_sq']))
+    for (p, g), pr in zip(opt_._views, pairs):
+        if pr is None:
+            continue
+        m, v = pr
+        if tuple(m.shape) != tuple(g.size()):
+            raise ValueError('optimizer state: moment of shape %s for a parameter of shape %s' % (tuple(m.shape), tuple(g.size())))
         o = g.storage_offset()
         torch.as_strided(opt_.exp_avg, g.size(), g.stride(), o).copy_(m)
         torch.as_strided(opt_.exp_avg_sq, g.size(), g.stride(), o).copy_(v)
@@ -79,7 +112,8 @@ def _load_optim_state(opt_, sd):
 
 def save_optimizers(model, label='latest'):
     os.makedirs(model.save_dir, exist_ok=True)
-    torch.save({'G': _optim_state(model.optimizer_G), 'D': _optim_state(model.optimizer_D), 'old_lr': model.old_lr},
+    torch.save({'G': _optim_state(model.optimizer_G, _param_names(model, model.optimizer_G)),
+                'D': _optim_state(model.optimizer_D, _param_names(model, model.optimizer_D)), 'old_lr': model.old_lr},
                os.path.join(model.save_dir, '%s_optim.pth' % label))
 
 
@@ -89,8 +123,8 @@ def load_optimizers(model, label='latest'):
         print('%s not exists yet! (Adam restarts from zero moments, as the reference does)' % path)
         return False
     sd = torch.load(path, map_location='cpu')
-    _load_optim_state(model.optimizer_G, sd['G'])
-    _load_optim_state(model.optimizer_D, sd['D'])
+    _load_optim_state(model.optimizer_G, sd['G'], _param_names(model, model.optimizer_G))
+    _load_optim_state(model.optimizer_D, sd['D'], _param_names(model, model.optimizer_D))
     model.old_lr = sd['old_lr']
     return True
 

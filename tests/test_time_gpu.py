@@ -189,6 +189,40 @@ def test_first_step_with_time_D_matches_reference(ref):
             assert np.abs(v.cpu().numpy() - ref[f"{tag}1/{k}"]).max() <= 2.0 * 2e-4 + 1e-7, (tag, k)
 
 
+def test_first_step_is_bit_reproducible_in_deterministic_mode(ref):
+    """P2P_DETERMINISTIC (p2p_set_deterministic): no split-K / split-pixel red.add between CTAs, single-chunk statistics and
+    loss sums -- two runs of the config-4 first step from the same state must give BIT-IDENTICAL losses and gradients (fp32 and
+    bf16 paths), and the fp32 losses must sit within 2e-3 of the reference's (2e-2 is what atomics reordering needed)"""
+    from pix2pixhdaudiosr_b200 import _lib
+    old = _lib.lib().p2p_set_deterministic(1)
+    try:
+        for precision in ("fp32", "bf16"):
+            runs = []
+            for _ in range(2):
+                model = create_model(time_opt(ref, precision=precision))
+                _load(model, ref)
+                lr, hr = batch(0)
+                losses, _ = model(lr, None, hr, None, infer=False)
+                vals = torch.stack([x.detach().float().reshape(()) for x in losses]).cpu()
+                _, loss_G, loss_D = assemble_losses(model, losses)
+                model.optimizer_G.zero_grad()
+                loss_G.backward()
+                model.optimizer_D.zero_grad()
+                loss_D.backward()
+                runs.append((vals, model.optimizer_G.flat_grad.clone(), model.optimizer_D.flat_grad.clone()))
+                del model
+            assert torch.equal(runs[0][0], runs[1][0]), (precision, runs[0][0], runs[1][0])
+            assert torch.equal(runs[0][1], runs[1][1]) and torch.equal(runs[0][2], runs[1][2]), precision
+            if precision == "fp32":
+                got, want = runs[0][0].numpy().astype(np.float64), ref["curve"][0]
+                mat = NAMES.index('G_mat')
+                err = np.abs(got - want) / np.abs(want)
+                print("deterministic fp32 first-step loss errors", err)
+                assert np.delete(err, mat).max() < 2e-3, err
+    finally:
+        _lib.lib().p2p_set_deterministic(old)
+
+
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])
 def test_time_D_loss_curve(ref, precision):
     """40 optimisation steps with --use_time_D --use_match_loss from the reference's seeded weights"""
