@@ -37,6 +37,33 @@ inline bool deterministic() {
     return f != 0;
 }
 
+// ---- programmatic dependent launch (PDL) -----------------------------------------------------------------------------------
+// A kernel launched through launch_k() may be scheduled while its predecessor on the stream is still draining (the
+// predecessor announces that with pdl_trigger()); it must execute pdl_wait() before its first access to global memory, which
+// blocks until the predecessor grid has completed and its writes are visible.  Inside a CUDA graph the attribute becomes a
+// programmatic edge: launch latency, the prologue (barrier init, TMEM allocation, table loads) and the CTA ramp-up of kernel
+// n+1 overlap the tail of kernel n.  Only kernels that call pdl_wait() may be launched this way.  P2P_PDL=0 turns it off.
+inline bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("P2P_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v != 0;
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <typename... KA, typename... A>
+inline cudaError_t launch_k(void (*kern)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KA>(args)...);
+}
+#endif
+
 inline bool is_pow2(long long v) { return v > 0 && (v & (v - 1)) == 0; }
 
 }  // namespace p2p

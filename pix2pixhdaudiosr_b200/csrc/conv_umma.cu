@@ -194,6 +194,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_umma_kernel(const __grid_con
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    pdl_trigger();
+    pdl_wait();
 
     if (warp < 4) {
         // ================================ producers: im2col gather with cp.async ================================
@@ -452,14 +454,16 @@ int sm_count() {
 
 template <int MODE>
 int launch(const UmmaArgs& a, cudaStream_t st, const char* what) {
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[64] = {};            // per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
         if (cudaFuncSetAttribute(conv_umma_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess)
             return check_launch("cudaFuncSetAttribute(conv_umma_kernel)");
-        configured = true;
+        configured[dev] = true;
     }
     const long long grid = a.nwork < sm_count() ? a.nwork : sm_count();
-    conv_umma_kernel<MODE><<<(unsigned)grid, kThreads, SMEM_BYTES, st>>>(a);
+    launch_k(conv_umma_kernel<MODE>, dim3((unsigned)grid), dim3(kThreads), SMEM_BYTES, st, a);
     ++g_launches;
     return check_launch(what);
 }

@@ -364,6 +364,8 @@ __global__ void __launch_bounds__(kWinThreads, 1) conv_window_kernel(const __gri
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    pdl_trigger();          // the next kernel on the stream may start its prologue while this one runs ...
+    pdl_wait();             // ... and this one touches global memory only after its predecessor has completed (common.cuh)
     // barrier addresses as seen from this CTA for arrivals that must land in the leader
     auto lead = [&](uint32_t bar) { return CG == 2 ? mapa_rank(bar, 0) : bar; };
 
@@ -729,6 +731,8 @@ __global__ void pad_nhwc_kernel(const T* __restrict__ x, T* __restrict__ xp, int
     // C8 = 16-byte vectors per pixel; every plane occupies plane_rows >= N*Hp*Wp pixel rows (the tail is zero-filled)
     const long long plane = plane_rows * C8, used = (long long)N * Hp * Wp * C8;
     const long long total = plane * s * s;
+    pdl_trigger();
+    pdl_wait();
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int pq = (int)(i / plane);
         long long p = i - pq * plane;
@@ -1040,6 +1044,8 @@ __global__ void __launch_bounds__(kWThreads, 1) conv_wgrad_window_kernel(const _
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    pdl_trigger();
+    pdl_wait();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -1261,7 +1267,7 @@ extern "C" int p2p_pad_nhwc(const void* x, void* xp, int N, int H, int W, int C,
     const long long total = (long long)N * Hp * Wp * C8;
     long long blocks = (total + 255) / 256;
     if (blocks > 148LL * 32) blocks = 148LL * 32;
-    pad_nhwc_kernel<uint4><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)xp, N, H, W, C8, pt, pl, Hp, Wp, reflect, 1, (long long)N * Hp * Wp);
+    launch_k(pad_nhwc_kernel<uint4>, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream, (const uint4*)x, (uint4*)xp, N, H, W, C8, pt, pl, Hp, Wp, reflect, 1, (long long)N * Hp * Wp);
     return check_launch("pad_nhwc_kernel");
 }
 
@@ -1279,7 +1285,7 @@ extern "C" int p2p_pad_planes(const void* x, void* planes, int N, int H, int W, 
     const long long total = plane_rows * C8 * s * s;
     long long blocks = (total + 255) / 256;
     if (blocks > 148LL * 32) blocks = 148LL * 32;
-    pad_nhwc_kernel<uint4><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)planes, N, H, W, C8, pt, pl, Hh, Wh, reflect, s, plane_rows);
+    launch_k(pad_nhwc_kernel<uint4>, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream, (const uint4*)x, (uint4*)planes, N, H, W, C8, pt, pl, Hh, Wh, reflect, s, plane_rows);
     return check_launch("pad_planes_kernel");
 }
 
@@ -1527,14 +1533,16 @@ extern "C" int p2p_conv_window_run_stats(const p2p_conv_window_desc* d, const vo
         cfg.blockDim = dim3(kWinThreads);
         cfg.dynamicSmemBytes = WSMEM;
         cfg.stream = (cudaStream_t)stream;
-        cudaLaunchAttribute attr[1];
+        cudaLaunchAttribute attr[2];
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[1].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr;
-        cfg.numAttrs = 1;
+        cfg.numAttrs = pdl_enabled() ? 2 : 1;
         if (cudaLaunchKernelEx(&cfg, conv_window_kernel<2>, a) != cudaSuccess) return check_launch("conv_window_kernel<2> (cluster launch)");
     } else {
-        conv_window_kernel<1><<<(unsigned)grid, kWinThreads, WSMEM, (cudaStream_t)stream>>>(a);
+        launch_k(conv_window_kernel<1>, dim3((unsigned)grid), dim3(kWinThreads), WSMEM, (cudaStream_t)stream, a);
     }
     note_umma_launch();
     return check_launch("conv_window_kernel");
@@ -1650,14 +1658,14 @@ extern "C" int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const v
     a.nwork = items * a.nsplit;
     if (int rc = encode_2d(&a.tm_a, aplanes, (unsigned long long)J, (unsigned long long)n_aplanes * plane_rows, 64, 64)) return rc;
     if (int rc = encode_2d(&a.tm_b, bplanes, (unsigned long long)C, (unsigned long long)n_bplanes * plane_rows, 64, (unsigned)a.b_rows_per_box)) return rc;
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[64] = {};            // the attribute is per device
+    if (dev >= 0 && dev < 64 && !configured[dev]) {
         if (cudaFuncSetAttribute(conv_wgrad_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GSMEM) != cudaSuccess)
             return check_launch("cudaFuncSetAttribute(conv_wgrad_window_kernel)");
-        configured = true;
+        configured[dev] = true;
     }
     const long long grid = a.nwork < sms ? a.nwork : sms;
-    conv_wgrad_window_kernel<<<(unsigned)grid, kWThreads, GSMEM, (cudaStream_t)stream>>>(a);
+    launch_k(conv_wgrad_window_kernel, dim3((unsigned)grid), dim3(kWThreads), GSMEM, (cudaStream_t)stream, a);
     note_umma_launch();
     return check_launch("conv_wgrad_window_kernel");
 }

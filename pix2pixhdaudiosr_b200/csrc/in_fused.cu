@@ -60,6 +60,8 @@ __global__ void __launch_bounds__(256) in_apply_planes_kernel(const TY* __restri
                                                               const PlanesGeom g, int norm, int act, float slope, float eps) {
     const int C8 = g.C8, tid = threadIdx.x;
     const int c8 = tid % C8, lane_r = tid / C8;
+    pdl_trigger();
+    pdl_wait();
     const int n = blockIdx.y;
     const int per_plane = g.Hh * g.Wh, npos = g.s * g.s * per_plane;
     uint4* dst = reinterpret_cast<uint4*>(planes);
@@ -183,11 +185,11 @@ extern "C" int p2p_instnorm_act_planes(const void* y, const float* bias, const f
     const int threads = g.C8 * g.R;
     cudaStream_t st = (cudaStream_t)stream;
     if (y_dtype == P2P_F32)
-        in_apply_planes_kernel<float><<<grid, threads, 0, st>>>((const float*)y, bias, stats_in, raw_mode, stats_out,
+        launch_k(in_apply_planes_kernel<float>, grid, dim3(threads), 0, st, (const float*)y, bias, stats_in, raw_mode, stats_out,
                                                                 (const __nv_bfloat16*)res, res_sn, res_sh, res_sw,
                                                                 (__nv_bfloat16*)planes, (__nv_bfloat16*)z_out, g, norm, act, slope, eps);
     else if (y_dtype == P2P_BF16)
-        in_apply_planes_kernel<__nv_bfloat16><<<grid, threads, 0, st>>>((const __nv_bfloat16*)y, bias, stats_in, raw_mode, stats_out,
+        launch_k(in_apply_planes_kernel<__nv_bfloat16>, grid, dim3(threads), 0, st, (const __nv_bfloat16*)y, bias, stats_in, raw_mode, stats_out,
                                                                         (const __nv_bfloat16*)res, res_sn, res_sh, res_sw,
                                                                         (__nv_bfloat16*)planes, (__nv_bfloat16*)z_out, g, norm, act, slope, eps);
     else

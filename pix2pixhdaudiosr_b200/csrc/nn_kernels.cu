@@ -180,6 +180,8 @@ __device__ __forceinline__ bool last_cta_of_group(unsigned* cnt, unsigned S) {
 template <typename T>
 __global__ void __launch_bounds__(256) in_stats_fused_v4_kernel(const T* __restrict__ y, float* __restrict__ stats, float* __restrict__ ws,
                                                                 unsigned* __restrict__ cnt, int HW, int C, int chunk, float eps) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ float sm[8][32][9];
     const int cg = blockIdx.x * 32 + threadIdx.x, n = blockIdx.y, C4 = C >> 2;
     const int r0 = blockIdx.z * chunk, r1 = min(HW, r0 + chunk);
@@ -235,6 +237,8 @@ __global__ void __launch_bounds__(256) in_bwd_stats_fused_v4_kernel(const TY* __
                                                                     const T* __restrict__ dz, float* __restrict__ work,
                                                                     float* __restrict__ ws, unsigned* __restrict__ cnt, int HW, int C,
                                                                     int chunk, int act, float slope) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ float sm[8][32][9];
     const int cg = blockIdx.x * 32 + threadIdx.x, n = blockIdx.y, C4 = C >> 2;
     const int r0 = blockIdx.z * chunk, r1 = min(HW, r0 + chunk);
@@ -292,6 +296,8 @@ template <typename TY, typename T>
 __global__ void __launch_bounds__(256) in_apply_v4_kernel(const TY* __restrict__ y, const T* __restrict__ res, T* __restrict__ z,
                                                           const float* __restrict__ stats, unsigned HWC4, unsigned C4,
                                                           unsigned total4, int norm, int act, float slope) {
+    pdl_trigger();
+    pdl_wait();
 #pragma unroll 2
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
         float v[4];
@@ -374,6 +380,8 @@ __global__ void __launch_bounds__(256) in_bwd_apply_v4_kernel(const TY* __restri
                                                               const T* __restrict__ dz, const float* __restrict__ work,
                                                               T* __restrict__ dy, unsigned HWC4, unsigned C4, unsigned total4,
                                                               float inv, int norm, int act, float slope) {
+    pdl_trigger();
+    pdl_wait();
 #pragma unroll 2
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
         float v[4], g[4], o[4];
@@ -404,6 +412,8 @@ __global__ void __launch_bounds__(256) in_bwd_apply_v4_kernel(const TY* __restri
 template <typename T>
 __global__ void __launch_bounds__(256) reflect_fold_v4_kernel(const T* __restrict__ dxp, T* __restrict__ dx, int H, int W, int C4,
                                                               int p, unsigned total4) {
+    pdl_trigger();
+    pdl_wait();
     const int HP = H + 2 * p, WP = W + 2 * p;
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
         const unsigned c4 = i % C4;
@@ -434,6 +444,8 @@ __global__ void __launch_bounds__(256) reflect_fold_v4_kernel(const T* __restric
 template <typename T>
 __global__ void avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int H, int W, int C, int OH, int OW,
                                    long long total) {
+    pdl_trigger();
+    pdl_wait();
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int c = (int)(i % C);
         long long r = i / C;
@@ -451,6 +463,8 @@ __global__ void avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, i
 template <typename T>
 __global__ void avgpool_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int H, int W, int C, int OH, int OW,
                                    long long total) {
+    pdl_trigger();
+    pdl_wait();
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int c = (int)(i % C);
         long long r = i / C;
@@ -473,11 +487,15 @@ __global__ void avgpool_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx,
 // ---- elementwise ------------------------------------------------------------------------------------------
 template <typename T>
 __global__ void tanh_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long long n) {
+    pdl_trigger();
+    pdl_wait();
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         stf(y + i, tanhf(ldf(x + i)));
 }
 template <typename T>
 __global__ void tanh_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, long long n) {
+    pdl_trigger();
+    pdl_wait();
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         const float t = ldf(y + i);
         stf(dx + i, ldf(dy + i) * (1.f - t * t));
@@ -511,6 +529,8 @@ __global__ void reflect_fold_kernel(const T* __restrict__ dxp, T* __restrict__ d
 // dbias[j] += column sums; grid (ceil(J/32), S), block (32, 8)
 template <typename T>
 __global__ void bias_grad_kernel(const T* __restrict__ dout, float* __restrict__ dbias, long long rows, int J, long long chunk) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ float s1[8][33];
     const int j = blockIdx.x * 32 + threadIdx.x;
     const long long r0 = (long long)blockIdx.y * chunk, r1 = min(rows, r0 + chunk);
@@ -530,6 +550,8 @@ __global__ void bias_grad_kernel(const T* __restrict__ dout, float* __restrict__
 template <typename T>
 __global__ void mse_const_kernel(const T* __restrict__ x, float target, float wgt, float* __restrict__ loss,
                                  T* __restrict__ dx, float gcoef, const float* __restrict__ gdev, long long n) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ float scratch[33];
     float acc = 0.f;
     if (gdev) gcoef *= __ldg(gdev);
@@ -544,6 +566,8 @@ __global__ void mse_const_kernel(const T* __restrict__ x, float target, float wg
 template <typename T>
 __global__ void l1_kernel(const T* __restrict__ a, const T* __restrict__ b, float wgt, float* __restrict__ loss,
                           T* __restrict__ da, float gcoef, const float* __restrict__ gdev, long long n) {
+    pdl_trigger();
+    pdl_wait();
     __shared__ float scratch[33];
     float acc = 0.f;
     if (gdev) gcoef *= __ldg(gdev);
@@ -679,7 +703,7 @@ extern "C" int p2p_instnorm_act_fwd(const void* y, const void* res, void* z, flo
         if (norm && vec && ws_fits(N, C)) {
             const int cb = (C / 4 + 31) / 32, S = split_for(HW, cb * N);
             const int chunk = (int)((HW + S - 1) / S);
-            in_stats_fused_v4_kernel<TY><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, g_stats_ws, g_stats_cnt, (int)HW, C, chunk, eps);
+            launch_k(in_stats_fused_v4_kernel<TY>, dim3(cb, N, S), dim3(32, 8), 0, st, (const TY*)y, stats, g_stats_ws, g_stats_cnt, (int)HW, C, chunk, eps);
         } else if (norm) {
             if (cudaMemsetAsync(stats, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
             if (vec) {
@@ -694,7 +718,7 @@ extern "C" int p2p_instnorm_act_fwd(const void* y, const void* res, void* z, flo
             in_finalize_kernel<TY><<<(N * C + 255) / 256, 256, 0, st>>>((const TY*)y, stats, HW, C, N * C, eps);
         }
         if (vec)
-            in_apply_v4_kernel<TY, T><<<ew_grid(total / 4), kEw, 0, st>>>((const TY*)y, (const T*)res, (T*)z, stats, (unsigned)(HW * (C / 4)),
+            launch_k(in_apply_v4_kernel<TY, T>, dim3((unsigned)(ew_grid(total / 4))), dim3(kEw), 0, st, (const TY*)y, (const T*)res, (T*)z, stats, (unsigned)(HW * (C / 4)),
                                                                           (unsigned)(C / 4), (unsigned)(total / 4), norm, act, slope);
         else
             in_apply_kernel<TY, T><<<ew_grid(total), kEw, 0, st>>>((const TY*)y, (const T*)res, (T*)z, stats, HW, C, total, norm, act, slope);
@@ -713,7 +737,7 @@ extern "C" int p2p_instnorm_stats(const void* y, float* stats, int N, long long 
     if (C % 4 == 0 && HW < 2000000000LL && vec4_ok(y, y_dtype == P2P_BF16 ? 2 : 4) && vec4_ok(stats, 4) && ws_fits(N, C)) {
         const int cb = (C / 4 + 31) / 32, S = split_for(HW, cb * N);
         const int chunk = (int)((HW + S - 1) / S);
-        P2P_DISPATCH_DTYPE(y_dtype, TY, in_stats_fused_v4_kernel<TY><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>(
+        P2P_DISPATCH_DTYPE(y_dtype, TY, launch_k(in_stats_fused_v4_kernel<TY>, dim3(cb, N, S), dim3(32, 8), 0, st, 
             (const TY*)y, stats, g_stats_ws, g_stats_cnt, (int)HW, C, chunk, eps));
         return check_launch("instnorm_stats (single launch)");
     }
@@ -747,7 +771,7 @@ extern "C" int p2p_instnorm_act_bwd(const void* y, const float* stats, const voi
         if (norm && vec && ws_fits(N, C)) {
             const int cb = (C / 4 + 31) / 32, S = split_for(HW, cb * N);
             const int chunk = (int)((HW + S - 1) / S);
-            in_bwd_stats_fused_v4_kernel<TY, T><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, (const T*)dz, work, g_stats_ws,
+            launch_k(in_bwd_stats_fused_v4_kernel<TY, T>, dim3(cb, N, S), dim3(32, 8), 0, st, (const TY*)y, stats, (const T*)dz, work, g_stats_ws,
                                                                                          g_stats_cnt, (int)HW, C, chunk, act, slope);
         } else if (norm) {
             if (cudaMemsetAsync(work, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
@@ -762,7 +786,7 @@ extern "C" int p2p_instnorm_act_bwd(const void* y, const float* stats, const voi
             }
         }
         if (vec)
-            in_bwd_apply_v4_kernel<TY, T><<<ew_grid(total / 4), kEw, 0, st>>>((const TY*)y, stats, (const T*)dz, work, (T*)dy, (unsigned)(HW * (C / 4)),
+            launch_k(in_bwd_apply_v4_kernel<TY, T>, dim3((unsigned)(ew_grid(total / 4))), dim3(kEw), 0, st, (const TY*)y, stats, (const T*)dz, work, (T*)dy, (unsigned)(HW * (C / 4)),
                                                                               (unsigned)(C / 4), (unsigned)(total / 4), 1.f / (float)HW, norm, act, slope);
         else
             in_bwd_apply_kernel<TY, T><<<ew_grid(total), kEw, 0, st>>>((const TY*)y, stats, (const T*)dz, work, (T*)dy, HW, C, total, norm, act, slope);
@@ -776,7 +800,7 @@ extern "C" int p2p_avgpool3s2_fwd(const void* x, void* y, int N, int H, int W, i
     const long long total = (long long)N * OH * OW * C;
     if (total == 0) return P2P_OK;
     if (!x || !y) return fail(P2P_EINVAL, "null pointer argument");
-    P2P_DISPATCH_DTYPE(dtype, T, avgpool_fwd_kernel<T><<<ew_grid(total), kEw, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, H, W, C, OH, OW, total));
+    P2P_DISPATCH_DTYPE(dtype, T, launch_k(avgpool_fwd_kernel<T>, dim3((unsigned)(ew_grid(total))), dim3(kEw), 0, (cudaStream_t)stream, (const T*)x, (T*)y, H, W, C, OH, OW, total));
     return check_launch("avgpool3s2_fwd");
 }
 
@@ -786,18 +810,18 @@ extern "C" int p2p_avgpool3s2_bwd(const void* dy, void* dx, int N, int H, int W,
     const long long total = (long long)N * H * W * C;
     if (total == 0) return P2P_OK;
     if (!dx || !dy) return fail(P2P_EINVAL, "null pointer argument");
-    P2P_DISPATCH_DTYPE(dtype, T, avgpool_bwd_kernel<T><<<ew_grid(total), kEw, 0, (cudaStream_t)stream>>>((const T*)dy, (T*)dx, H, W, C, OH, OW, total));
+    P2P_DISPATCH_DTYPE(dtype, T, launch_k(avgpool_bwd_kernel<T>, dim3((unsigned)(ew_grid(total))), dim3(kEw), 0, (cudaStream_t)stream, (const T*)dy, (T*)dx, H, W, C, OH, OW, total));
     return check_launch("avgpool3s2_bwd");
 }
 
 extern "C" int p2p_tanh_fwd(const void* x, void* y, long long n, int dtype, void* stream) {
     if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
-    P2P_DISPATCH_DTYPE(dtype, T, tanh_fwd_kernel<T><<<ew_grid(n), kEw, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, n));
+    P2P_DISPATCH_DTYPE(dtype, T, launch_k(tanh_fwd_kernel<T>, dim3((unsigned)(ew_grid(n))), dim3(kEw), 0, (cudaStream_t)stream, (const T*)x, (T*)y, n));
     return check_launch("tanh_fwd");
 }
 extern "C" int p2p_tanh_bwd(const void* y, const void* dy, void* dx, long long n, int dtype, void* stream) {
     if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
-    P2P_DISPATCH_DTYPE(dtype, T, tanh_bwd_kernel<T><<<ew_grid(n), kEw, 0, (cudaStream_t)stream>>>((const T*)y, (const T*)dy, (T*)dx, n));
+    P2P_DISPATCH_DTYPE(dtype, T, launch_k(tanh_bwd_kernel<T>, dim3((unsigned)(ew_grid(n))), dim3(kEw), 0, (cudaStream_t)stream, (const T*)y, (const T*)dy, (T*)dx, n));
     return check_launch("tanh_bwd");
 }
 
@@ -809,7 +833,7 @@ extern "C" int p2p_reflect_pad_fold(const void* dxp, void* dx, int N, int H, int
     const bool v4 = C % 4 == 0 && total / 4 < 2000000000LL;
     P2P_DISPATCH_DTYPE(dtype, T, {
         if (v4 && vec4_ok(dxp, sizeof(T)) && vec4_ok(dx, sizeof(T)))
-            reflect_fold_v4_kernel<T><<<ew_grid(total / 4), kEw, 0, (cudaStream_t)stream>>>((const T*)dxp, (T*)dx, H, W, C / 4, p, (unsigned)(total / 4));
+            launch_k(reflect_fold_v4_kernel<T>, dim3((unsigned)(ew_grid(total / 4))), dim3(kEw), 0, (cudaStream_t)stream, (const T*)dxp, (T*)dx, H, W, C / 4, p, (unsigned)(total / 4));
         else
             reflect_fold_kernel<T><<<ew_grid(total), kEw, 0, (cudaStream_t)stream>>>((const T*)dxp, (T*)dx, H, W, C, p, total);
     });
@@ -824,7 +848,7 @@ extern "C" int p2p_bias_grad(const void* dout, float* dbias, long long rows, int
     if (rows == 0) return P2P_OK;
     const int jb = (J + 31) / 32, S = split_for(rows, jb);
     const long long chunk = (rows + S - 1) / S;
-    P2P_DISPATCH_DTYPE(dtype, T, bias_grad_kernel<T><<<dim3(jb, S), dim3(32, 8), 0, st>>>((const T*)dout, dbias, rows, J, chunk));
+    P2P_DISPATCH_DTYPE(dtype, T, launch_k(bias_grad_kernel<T>, dim3(jb, S), dim3(32, 8), 0, st, (const T*)dout, dbias, rows, J, chunk));
     return check_launch("bias_grad");
 }
 
@@ -833,7 +857,7 @@ extern "C" int p2p_loss_mse_const(const void* x, float target, float weight, flo
     if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
     const float gcoef = gscale * weight * 2.f / (float)n;
     const int grid = (loss && deterministic()) ? 1 : (ew_grid(n) > 592 ? 592 : ew_grid(n));
-    P2P_DISPATCH_DTYPE(dtype, T, mse_const_kernel<T><<<grid, kEw, 0, (cudaStream_t)stream>>>((const T*)x, target, weight, loss, (T*)dx, gcoef, gscale_dev, n));
+    P2P_DISPATCH_DTYPE(dtype, T, launch_k(mse_const_kernel<T>, dim3((unsigned)(grid)), dim3(kEw), 0, (cudaStream_t)stream, (const T*)x, target, weight, loss, (T*)dx, gcoef, gscale_dev, n));
     return check_launch("loss_mse_const");
 }
 
@@ -842,7 +866,7 @@ extern "C" int p2p_loss_l1(const void* a, const void* b, float weight, float* lo
     if (n <= 0) return n == 0 ? P2P_OK : fail(P2P_EINVAL, "negative size");
     const float gcoef = gscale * weight / (float)n;
     const int grid = (loss && deterministic()) ? 1 : (ew_grid(n) > 592 ? 592 : ew_grid(n));
-    P2P_DISPATCH_DTYPE(dtype, T, l1_kernel<T><<<grid, kEw, 0, (cudaStream_t)stream>>>((const T*)a, (const T*)b, weight, loss, (T*)da, gcoef, gscale_dev, n));
+    P2P_DISPATCH_DTYPE(dtype, T, launch_k(l1_kernel<T>, dim3((unsigned)(grid)), dim3(kEw), 0, (cudaStream_t)stream, (const T*)a, (const T*)b, weight, loss, (T*)da, gcoef, gscale_dev, n));
     return check_launch("loss_l1");
 }
 

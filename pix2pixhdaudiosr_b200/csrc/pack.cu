@@ -16,6 +16,8 @@ __device__ __forceinline__ int reflect_idx(int i, int n) {
 template <typename T>
 __global__ void __launch_bounds__(256) pack_in_kernel(const T* __restrict__ x, T* __restrict__ xpk, int N, int H, int W, int C,
                                                       int KW, int s, int p, int reflect, int OW, unsigned total) {
+    pdl_trigger();
+    pdl_wait();
     const int Hp = H + 2 * p;
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int ox = (int)(i % OW);
@@ -46,6 +48,8 @@ __global__ void __launch_bounds__(256) pack_in_kernel(const T* __restrict__ x, T
 template <typename T>
 __global__ void __launch_bounds__(256) fold_out_kernel(const float* __restrict__ ypk, const float* __restrict__ bias, T* __restrict__ y,
                                                        int OH, int Wp, int OW, int KW, int Cout, unsigned total) {
+    pdl_trigger();
+    pdl_wait();
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int co = (int)(i % Cout);
         unsigned r = i / Cout;
@@ -62,6 +66,8 @@ __global__ void __launch_bounds__(256) fold_out_kernel(const float* __restrict__
 template <typename T>
 __global__ void __launch_bounds__(256) pack_dy_kernel(const T* __restrict__ dy, T* __restrict__ dypk, int OW, int Cout, int KW, int Wp,
                                                       unsigned total) {
+    pdl_trigger();
+    pdl_wait();
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int xp = (int)(i % Wp);
         const unsigned r = i / Wp;     // = n * OH + y
@@ -87,6 +93,8 @@ __global__ void __launch_bounds__(256) pack_dy_kernel(const T* __restrict__ dy, 
 __global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ xcol, int N, int H,
                                                      int W, int C, int KH, int KW, int s, int p, int reflect, int OH, int OW, int Kc,
                                                      long long rows, unsigned total) {
+    pdl_trigger();
+    pdl_wait();
     const int G = Kc >> 3, KWC = KW * C, KK = KH * KWC;
     __shared__ int tab[128];            // k -> kh << 16 | kw << 8 | c
     for (int k = threadIdx.x; k < 128; k += blockDim.x) {
@@ -124,6 +132,8 @@ __global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __rest
 // adjoint of im2col with zero padding: dx[n, y, x, c] = sum over (kh, kw) with (y + p - kh, x + p - kw) = s * (oy, ox)
 __global__ void __launch_bounds__(256) col2im_kernel(const __nv_bfloat16* __restrict__ dxcol, __nv_bfloat16* __restrict__ dx, int H, int W,
                                                      int C, int KH, int KW, int s, int p, int OH, int OW, int Kc, unsigned total) {
+    pdl_trigger();
+    pdl_wait();
     for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int c = (int)(i % C);
         unsigned r = i / C;
@@ -148,6 +158,8 @@ __global__ void __launch_bounds__(256) col2im_kernel(const __nv_bfloat16* __rest
 __global__ void __launch_bounds__(256) pack_dy_full_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ out, int OH,
                                                            int OW, int Cout, int KH, int KW, int Hp, int Wp, int Kc, long long rows,
                                                            unsigned total) {
+    pdl_trigger();
+    pdl_wait();
     const int G = Kc >> 3, KWC = KW * Cout, KK = KH * KWC;
     __shared__ int tab[128];            // k -> kh << 16 | kw << 8 | co
     for (int k = threadIdx.x; k < 128; k += blockDim.x) {
@@ -198,7 +210,7 @@ extern "C" int p2p_pack_in(const void* x, void* xpk, int N, int H, int W, int C,
     if ((OW - 1) * stride + KW > W + 2 * pad) return fail(P2P_EINVAL, "OW reaches past the padded row");
     const long long total = (long long)N * (H + 2 * pad) * OW;
     if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
-    P2P_DISPATCH_DTYPE(dtype, T, pack_in_kernel<T><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+    P2P_DISPATCH_DTYPE(dtype, T, launch_k(pack_in_kernel<T>, dim3((unsigned)(grid_for(total))), dim3(256), 0, (cudaStream_t)stream, 
         (const T*)x, (T*)xpk, N, H, W, C, KW, stride, pad, reflect, OW, (unsigned)total));
     return check_launch("pack_in");
 }
@@ -210,7 +222,7 @@ extern "C" int p2p_fold_out(const float* ypk, const float* bias, void* y, int N,
         return fail(P2P_EINVAL, "bad folding geometry (KW*Cout must be <= 16)");
     const long long total = (long long)N * OH * OW * Cout;
     if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
-    P2P_DISPATCH_DTYPE(out_dtype, T, fold_out_kernel<T><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+    P2P_DISPATCH_DTYPE(out_dtype, T, launch_k(fold_out_kernel<T>, dim3((unsigned)(grid_for(total))), dim3(256), 0, (cudaStream_t)stream, 
         ypk, bias, (T*)y, OH, Wp, OW, KW, Cout, (unsigned)total));
     return check_launch("fold_out");
 }
@@ -221,7 +233,7 @@ extern "C" int p2p_pack_dy(const void* dy, void* dypk, int N, int OH, int OW, in
         return fail(P2P_EINVAL, "bad packing geometry (KW*Cout must be <= 16)");
     const long long total = (long long)N * OH * Wp;
     if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
-    P2P_DISPATCH_DTYPE(dtype, T, pack_dy_kernel<T><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(
+    P2P_DISPATCH_DTYPE(dtype, T, launch_k(pack_dy_kernel<T>, dim3((unsigned)(grid_for(total))), dim3(256), 0, (cudaStream_t)stream, 
         (const T*)dy, (T*)dypk, OW, Cout, KW, Wp, (unsigned)total));
     return check_launch("pack_dy");
 }
@@ -238,7 +250,7 @@ extern "C" int p2p_im2col(const void* x, void* xcol, int N, int H, int W, int C,
     if (rows_alloc < rows) return fail(P2P_EINVAL, "rows_alloc smaller than N*OH*OW");
     const long long total = rows_alloc * (Kc / 8);
     if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
-    im2col_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)xcol, N, H, W, C, KH, KW,
+    launch_k(im2col_kernel, dim3((unsigned)(grid_for(total))), dim3(256), 0, (cudaStream_t)stream, (const __nv_bfloat16*)x, (__nv_bfloat16*)xcol, N, H, W, C, KH, KW,
                                                                      stride, pad, reflect, OH, OW, Kc, rows, (unsigned)total);
     return check_launch("im2col");
 }
@@ -250,7 +262,7 @@ extern "C" int p2p_col2im(const void* dxcol, void* dx, int N, int H, int W, int 
         return fail(P2P_EINVAL, "bad col2im geometry");
     const long long total = (long long)N * H * W * C;
     if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
-    col2im_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dxcol, (__nv_bfloat16*)dx, H, W, C, KH, KW,
+    launch_k(col2im_kernel, dim3((unsigned)(grid_for(total))), dim3(256), 0, (cudaStream_t)stream, (const __nv_bfloat16*)dxcol, (__nv_bfloat16*)dx, H, W, C, KH, KW,
                                                                      stride, pad, OH, OW, Kc, (unsigned)total);
     return check_launch("col2im");
 }
@@ -265,7 +277,7 @@ extern "C" int p2p_pack_dy_full(const void* dy, void* out, int N, int OH, int OW
     if (rows_alloc < rows) return fail(P2P_EINVAL, "rows_alloc smaller than the padded grid");
     const long long total = rows_alloc * (Kc / 8);
     if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
-    pack_dy_full_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dy, (__nv_bfloat16*)out, OH, OW, Cout,
+    launch_k(pack_dy_full_kernel, dim3((unsigned)(grid_for(total))), dim3(256), 0, (cudaStream_t)stream, (const __nv_bfloat16*)dy, (__nv_bfloat16*)out, OH, OW, Cout,
                                                                            KH, KW, Hp, Wp, Kc, rows, (unsigned)total);
     return check_launch("pack_dy_full");
 }

@@ -114,11 +114,11 @@ class Conv2d(_ConvBase):
             return ops.ConvCfg(False, self.stride, reflect_pad, ops.PAD_REFLECT, tswap=self.tswap)
         return ops.ConvCfg(False, self.stride, self.padding, ops.PAD_ZERO, tswap=self.tswap)
 
-    def run(self, x, reflect_pad=0, needs_wgrad=True, norm=None, act_mod=None, res=None, consumer=None, want_plain=False):
+    def run(self, x, reflect_pad=0, needs_wgrad=True, norm=None, act_mod=None, res=None, consumer=None, want_plain=False, gated=False):
         """conv [+ InstanceNorm] [+ activation] [+ residual] as one fused op; `consumer` = (conv module, ConvCfg) of the layer
         that reads the result (its padded input planes are then written directly), want_plain: the result must be a plain
         contiguous NHWC tensor (it is also handed out as a feature map)"""
-        return _conv_block(self, x, self.cfg_for(reflect_pad), needs_wgrad, norm, act_mod, res, consumer, want_plain)
+        return _conv_block(self, x, self.cfg_for(reflect_pad), needs_wgrad, norm, act_mod, res, consumer, want_plain, gated)
 
     def extra_repr(self):
         return f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, stride={self.stride}, padding={self.padding}"
@@ -154,7 +154,7 @@ def _act_code(act_mod):
     return ops.ACT_NONE, 0.0
 
 
-def _conv_block(conv, x, cfg, needs_wgrad, norm, act_mod, res, consumer=None, want_plain=False):
+def _conv_block(conv, x, cfg, needs_wgrad, norm, act_mod, res, consumer=None, want_plain=False, gated=False):
     w = conv.weight if needs_wgrad else conv.weight.detach()
     b = conv.bias if needs_wgrad else conv.bias.detach()
     if x.dtype == torch.bfloat16 and (conv.w16 is None or conv.w16.device != x.device):
@@ -166,7 +166,7 @@ def _conv_block(conv, x, cfg, needs_wgrad, norm, act_mod, res, consumer=None, wa
         out_plan = lambda shape, dtype: ops.plan_input_layout(shape, dtype, cmod.weight, ccfg)      # noqa: E731
     z, layout = ops.ConvBlockFn.apply(x, w, b, conv.w16, res, cfg, norm is not None, act, slope,
                                       norm.eps if norm is not None else 0.0, conv.gphys if needs_wgrad else None,
-                                      getattr(x, "_p2p_layout", None), out_plan, want_plain)
+                                      getattr(x, "_p2p_layout", None), out_plan, want_plain, gated)
     if layout is not None:
         z._p2p_layout = layout          # (key, planes): this tensor already exists as its consumer's padded input
     return z
@@ -229,7 +229,7 @@ def _take_norm_act(mods, i):
     return norm, act, i
 
 
-def run_layers(mods, x, needs_wgrad=True, res_last=None, next_consumer=None, want_plain=False):
+def run_layers(mods, x, needs_wgrad=True, res_last=None, next_consumer=None, want_plain=False, gated=False):
     """Execute a reference-shaped module list.  Conv [+IN] [+act] runs as one fused op; `res_last` is added in
     the last conv block of the list (LocalEnhancer's `model_downsample(input_i) + output_prev`).  `next_consumer`: the
     module(s) that will read this list's result (lets the last block write its consumer's padded input directly);
@@ -240,10 +240,10 @@ def run_layers(mods, x, needs_wgrad=True, res_last=None, next_consumer=None, wan
         m = mods[i]
         if isinstance(m, nn.Sequential):
             x = run_layers(m, x, needs_wgrad, next_consumer=mods[i + 1:] if i + 1 < len(mods) else next_consumer,
-                           want_plain=want_plain and i + 1 == len(mods))
+                           want_plain=want_plain and i + 1 == len(mods), gated=gated and i == 0)
             i += 1
         elif isinstance(m, (ReflectionPad2d, Conv2d, ConvTranspose2d)):
-            pad = 0
+            pad, first = 0, i == 0
             if isinstance(m, ReflectionPad2d):
                 pad, m = m.padding, mods[i + 1]
                 assert isinstance(m, Conv2d), "ReflectionPad2d must be followed by Conv2d"
@@ -255,7 +255,7 @@ def run_layers(mods, x, needs_wgrad=True, res_last=None, next_consumer=None, wan
             plain = want_plain and last
             if isinstance(m, Conv2d):
                 x = m.run(x, reflect_pad=pad, needs_wgrad=needs_wgrad, norm=norm, act_mod=act, res=res, consumer=consumer,
-                          want_plain=plain)
+                          want_plain=plain, gated=gated and first)
             else:
                 x = m.run(x, needs_wgrad=needs_wgrad, norm=norm, act_mod=act, res=res, consumer=consumer, want_plain=plain)
             if res is not None:
@@ -492,16 +492,17 @@ class MultiscaleDiscriminator(nn.Module):
         y = _to_nchw(x)
         return y.transpose(2, 3) if self.transposed_image else y
 
-    def singleD_forward(self, model, x, needs_wgrad=True):
+    def singleD_forward(self, model, x, needs_wgrad=True, gated=False):
         if self.getIntermFeat:
             result = []
             for i in range(len(model)):
-                x = run_layers(model[i], x, needs_wgrad, next_consumer=model[i + 1] if i + 1 < len(model) else None, want_plain=True)
+                x = run_layers(model[i], x, needs_wgrad, next_consumer=model[i + 1] if i + 1 < len(model) else None, want_plain=True,
+                               gated=gated and i == 0)
                 result.append(self._out(x))
             return result
-        return [self._out(run_layers(model, x, needs_wgrad))]
+        return [self._out(run_layers(model, x, needs_wgrad, gated=gated))]
 
-    def forward(self, input, needs_wgrad=True):
+    def forward(self, input, needs_wgrad=True, gated=False):
         """needs_wgrad=False runs with detached weights: the generator's pass through D, whose weight gradients
         the reference computes and then discards (train.py:164-176)."""
         num_D = self.num_D
@@ -512,9 +513,9 @@ class MultiscaleDiscriminator(nn.Module):
                 model = [getattr(self, 'scale' + str(num_D - 1 - i) + '_layer' + str(j)) for j in range(self.n_layers + 2)]
             else:
                 model = getattr(self, 'layer' + str(num_D - 1 - i))
-            result.append(self.singleD_forward(model, x, needs_wgrad))
+            result.append(self.singleD_forward(model, x, needs_wgrad, gated))
             if i != (num_D - 1):
-                x = ops.AvgPool3s2Fn.apply(x)
+                x = ops.AvgPool3s2Fn.apply(x, gated)
         return result
 
 

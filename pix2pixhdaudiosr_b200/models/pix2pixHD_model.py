@@ -298,13 +298,25 @@ class Pix2PixHDModel(BaseModel):
         lr_spectro, lr_pha, hr_spectro, hr_pha, _, _, hr_norm_param, lr_norm_param = self.encode_input(lr_audio, inst, hr_audio, feat)
         sr_result = self.netG.forward(lr_spectro)
 
-        pred_fake_pool = self.discriminate_F(lr_spectro, sr_result, use_pool=True)
-        loss_D_fake = self.criterionGAN(pred_fake_pool, False)
-        pred_real = self.discriminate_F(lr_spectro, hr_spectro)
-        loss_D_real = self.criterionGAN(pred_real, True)
-        # the generator's pass: gradients flow to G through D's activations; D's own weight gradients are not formed
-        pred_fake = self.netD.forward(torch.cat((lr_spectro, sr_result.float()), dim=1), needs_wgrad=False)
-        loss_G_GAN = self.criterionGAN(pred_fake, True)
+        if getattr(self, '_share_fake_pass', False):
+            # train.train_step: D's forward on (label, fake) runs ONCE and serves both losses -- the reference's first and third
+            # D passes (:351-361) compute the same numbers (pool_size 0).  The gate in front of D is closed while loss_D is
+            # back-propagated (the reference detaches the fake image there), and D's weight gradients are not formed while
+            # loss_G is (ops.set_backward_phase).  The caller must back-propagate loss_G with retain_graph=True.
+            fake_in = ops.GradGateFn.apply(torch.cat((lr_spectro, sr_result.float()), dim=1))
+            pred_fake = self.netD.forward(fake_in, gated=True)
+            loss_D_fake = self.criterionGAN(pred_fake, False)
+            pred_real = self.discriminate_F(lr_spectro, hr_spectro)
+            loss_D_real = self.criterionGAN(pred_real, True)
+            loss_G_GAN = self.criterionGAN(pred_fake, True)
+        else:
+            pred_fake_pool = self.discriminate_F(lr_spectro, sr_result, use_pool=True)
+            loss_D_fake = self.criterionGAN(pred_fake_pool, False)
+            pred_real = self.discriminate_F(lr_spectro, hr_spectro)
+            loss_D_real = self.criterionGAN(pred_real, True)
+            # the generator's pass: gradients flow to G through D's activations; D's own weight gradients are not formed
+            pred_fake = self.netD.forward(torch.cat((lr_spectro, sr_result.float()), dim=1), needs_wgrad=False)
+            loss_G_GAN = self.criterionGAN(pred_fake, True)
 
         # time-domain GAN on frames (:375-387)
         loss_G_GAN_time = loss_D_real_time = loss_D_fake_time = 0

@@ -1135,6 +1135,40 @@ class GradSink:
             hook(self)
 
 
+# ---- backward-pass phases (train.train_step with a SHARED discriminator forward on the generated image) -------------------------
+# The reference runs D three times per step (pix2pixHD_model.py:351-361): on (label, fake.detach()) for the discriminator's
+# loss, on (label, real), and once more on (label, fake) for the generator's loss -- the first and the third forward compute
+# the same numbers.  train_step runs that forward ONCE and walks its graph twice:
+#   phase G (loss_G.backward): gradients flow through D's activations to G; D's weight gradients are not formed
+#                              (BACKWARD_OWNERS = {optimizer_G}); the gate in front of D is open;
+#   phase D (loss_D.backward): D's weight gradients are formed, the gate is closed (the reference detaches the fake image).
+BACKWARD_OWNERS = None      # ids of the optimizers whose parameters receive gradients in the running backward pass (None: all)
+GATE_OPEN = True
+
+
+def set_backward_phase(owners=None, gate_open=True):
+    global BACKWARD_OWNERS, GATE_OPEN
+    BACKWARD_OWNERS = None if owners is None else {id(o) for o in owners}
+    GATE_OPEN = bool(gate_open)
+
+
+def _owner_active(gphys):
+    return BACKWARD_OWNERS is None or gphys is None or id(gphys.owner) in BACKWARD_OWNERS
+
+
+class GradGateFn(torch.autograd.Function):
+    """identity whose gradient passes only while the gate is open (set_backward_phase)"""
+
+    @staticmethod
+    def forward(ctx, x):
+        ctx.set_materialize_grads(False)
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g if GATE_OPEN else None
+
+
 class ConvBlockFn(torch.autograd.Function):
     """[ReflectionPad2d] Conv2d | ConvTranspose2d  ->  [InstanceNorm2d]  ->  [ReLU | LeakyReLU]  [+ residual]
     as ONE differentiable op.  In bf16 mode the pre-normalisation conv output stays fp32 inside the op (see
@@ -1146,8 +1180,10 @@ class ConvBlockFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, weight, bias, w16, res, cfg, norm, act, slope, eps, gphys=None, xin=None, out_plan=None,
-                want_plain=False):
+                want_plain=False, gated=False):
         _need_cuda(x, weight)
+        ctx.gated = bool(gated)         # x sits right behind a GradGateFn: no input gradient while the gate is closed
+        ctx.set_materialize_grads(False)    # an undefined upstream gradient (closed gate) must not run this layer's backward on zeros
         plain = (not norm) and act == ACT_NONE and res is None
         aux = [] if ctx.needs_input_grad[1] else None
         Cout = weight.shape[1] if cfg.transposed else weight.shape[0]
@@ -1189,18 +1225,22 @@ class ConvBlockFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dz, _unused=None):
+        if dz is None:
+            return (None,) * 15
         x, weight, w16, y, stats = ctx.saved_tensors
         cfg, norm, act, slope, has_bias, has_res, plain = ctx.cfg
         dz = dz.contiguous()
         dy = dz if plain else norm_act_backward(y, stats, dz, norm, act, slope)
         # a bias in front of InstanceNorm2d(affine=False) has an exactly zero gradient (the mean subtraction removes it; the
         # reference's autograd returns rounding noise of ~1e-7 relative size): not computed unless P2P_NORM_BIAS_GRAD=1
-        need_db = has_bias and ctx.needs_input_grad[2] and (not norm or NORM_BIAS_GRAD)
-        dx, dw, db = conv_backward(x, weight, w16, dy, cfg, ctx.needs_input_grad[0], ctx.needs_input_grad[1],
+        active = _owner_active(ctx.gphys)       # this layer's parameters take gradients in the running backward phase
+        need_db = has_bias and ctx.needs_input_grad[2] and (not norm or NORM_BIAS_GRAD) and active
+        need_dx = ctx.needs_input_grad[0] and not (ctx.gated and not GATE_OPEN)
+        dx, dw, db = conv_backward(x, weight, w16, dy, cfg, need_dx, ctx.needs_input_grad[1] and active,
                                    need_db, ctx.gphys, ctx.xpad)
-        if has_bias and ctx.needs_input_grad[2] and not need_db and ctx.gphys is None:
+        if has_bias and ctx.needs_input_grad[2] and not need_db and ctx.gphys is None and active:
             db = torch.zeros(ctx.bias_n, dtype=torch.float32, device=x.device)    # no flat gradient buffer behind .grad: give autograd the zero
-        return dx, dw, db, None, (dz if has_res else None), None, None, None, None, None, None, None, None, None
+        return dx, dw, db, None, (dz if has_res else None), None, None, None, None, None, None, None, None, None, None
 
 
 FUSE_NORM_PAD = os.environ.get("P2P_FUSE_NORM_PAD", "1") == "1"
@@ -1219,6 +1259,7 @@ class InstNormActFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, y, res, norm, act, slope, eps):
         _need_cuda(y)
+        ctx.set_materialize_grads(False)
         y = y.contiguous()
         if res is not None:
             res = res.contiguous()
@@ -1229,6 +1270,8 @@ class InstNormActFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dz):
+        if dz is None:
+            return (None,) * 6
         y, stats = ctx.saved_tensors
         norm, act, slope, has_res = ctx.cfg
         dz = dz.contiguous()
@@ -1239,8 +1282,10 @@ class AvgPool3s2Fn(torch.autograd.Function):
     """nn.AvgPool2d(3, stride=2, padding=[1,1], count_include_pad=False), networks.py:166, 309."""
 
     @staticmethod
-    def forward(ctx, x):
+    def forward(ctx, x, gated=False):
         _need_cuda(x)
+        ctx.gated = bool(gated)
+        ctx.set_materialize_grads(False)
         x = x.contiguous()
         N, H, W, C = x.shape
         y = torch.empty((N, (H - 1) // 2 + 1, (W - 1) // 2 + 1, C), dtype=x.dtype, device=x.device)
@@ -1250,17 +1295,20 @@ class AvgPool3s2Fn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
+        if dy is None or (ctx.gated and not GATE_OPEN):
+            return None, None
         N, H, W, C = ctx.shape
         dy = dy.contiguous()
         dx = torch.empty((N, H, W, C), dtype=dy.dtype, device=dy.device)
         _lib.check(_lib.lib().p2p_avgpool3s2_bwd(_p(dy), _p(dx), N, H, W, C, _DT[dy.dtype], _stream()))
-        return dx
+        return dx, None
 
 
 class TanhFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x):
         _need_cuda(x)
+        ctx.set_materialize_grads(False)
         x = x.contiguous()
         y = torch.empty_like(x)
         _lib.check(_lib.lib().p2p_tanh_fwd(_p(x), _p(y), x.numel(), _DT[x.dtype], _stream()))
@@ -1269,6 +1317,8 @@ class TanhFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
+        if dy is None:
+            return None
         (y,) = ctx.saved_tensors
         dy = dy.contiguous()
         dx = torch.empty_like(y)

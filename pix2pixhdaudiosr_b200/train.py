@@ -156,6 +156,7 @@ def broadcast_parameters(model, src=0, group=None):
 
 
 OVERLAP_G_STEP = os.environ.get("P2P_OVERLAP_GSTEP", "1") == "1"
+SHARE_FAKE_PASS = os.environ.get("P2P_SHARE_FAKE_PASS", "1") == "1"
 _SIDE = {}
 
 
@@ -173,11 +174,22 @@ def train_step(model, lr_audio, hr_audio, inst=None, feat=None, infer=False, syn
     a side stream WHILE the main stream computes the discriminator's backward pass: loss_D.backward() reads neither G's
     weights nor G's gradients, so this is arithmetically the reference's order (train.py:164-184), and the bandwidth-bound
     optimiser kernels share the SMs with the tensor-core-bound convolutions instead of running after them."""
-    losses, generated = model(lr_audio, inst, hr_audio, feat, infer)
+    shared = SHARE_FAKE_PASS and hasattr(model, 'netD') and getattr(model.opt, 'pool_size', 0) == 0
+    model._share_fake_pass = shared          # one D forward on the generated image serves both losses (see Pix2PixHDModel.forward)
+    try:
+        losses, generated = model(lr_audio, inst, hr_audio, feat, infer)
+    finally:
+        model._share_fake_pass = False
     loss_dict, loss_G, loss_D = assemble_losses(model, losses)
     opt_G, opt_D = model.optimizer_G, model.optimizer_D
+    from . import ops
     opt_G.zero_grad()
-    loss_G.backward()
+    try:
+        if shared:
+            ops.set_backward_phase(owners=[opt_G], gate_open=True)
+        loss_G.backward(retain_graph=shared)
+    finally:
+        ops.set_backward_phase(None, True)
     if sync is None:
         sync = _NOSYNC
 
@@ -197,7 +209,12 @@ def train_step(model, lr_audio, hr_audio, inst=None, feat=None, infer=False, syn
     else:
         h_G = sync.start(opt_G)
     opt_D.zero_grad()
-    loss_D.backward()
+    try:
+        if shared:
+            ops.set_backward_phase(owners=[opt_D], gate_open=False)
+        loss_D.backward()
+    finally:
+        ops.set_backward_phase(None, True)
     if not overlap:
         sync.finish(opt_G, h_G)
         opt_G.step()

@@ -165,3 +165,32 @@ def test_inference_and_to_audio_match_reference(ref):
     audio = model.to_audio(torch.from_numpy(ref["inf_sr"]).cuda(), npar, pha)
     assert tuple(audio.shape) == ref["inf_audio"].shape
     assert relerr(audio.cpu().numpy(), ref["inf_audio"]) < 2e-3
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_shared_fake_pass_equals_three_pass_step(ref, precision):
+    """train_step's single discriminator forward on the generated image (phased backward, gate in front of D) must give
+    EXACTLY what the reference's three-pass order gives: in deterministic mode the flat gradients of G and D, the losses and
+    the updated weights of one optimisation step are bit-identical between the two"""
+    from pix2pixhdaudiosr_b200 import _lib, train
+    old = _lib.lib().p2p_set_deterministic(1)
+    share0, overlap0 = train.SHARE_FAKE_PASS, train.OVERLAP_G_STEP
+    out = {}
+    try:
+        for share in (True, False):
+            train.SHARE_FAKE_PASS = share
+            train.OVERLAP_G_STEP = share            # the three-pass run also keeps the reference's stream order
+            torch.manual_seed(99)                   # the LR mask noise is drawn per step
+            model = create_model(tiny_opt(precision=precision, mask=True, mask_mode='mode2'))
+            _load(model, ref)
+            lr, hr = batch(0)
+            loss_dict, _ = train_step(model, lr.cuda(), hr.cuda())
+            torch.cuda.synchronize()
+            out[share] = (torch.stack([loss_dict[k].float() for k in sorted(loss_dict)]).cpu(), model.optimizer_G.flat_grad.clone(),
+                          model.optimizer_D.flat_grad.clone(), model.optimizer_G.flat.clone(), model.optimizer_D.flat.clone())
+            del model
+    finally:
+        train.SHARE_FAKE_PASS, train.OVERLAP_G_STEP = share0, overlap0
+        _lib.lib().p2p_set_deterministic(old)
+    for a, b, what in zip(out[True], out[False], ("losses", "G gradients", "D gradients", "G weights", "D weights")):
+        assert torch.equal(a, b), (precision, what, float((a.double() - b.double()).abs().max()))

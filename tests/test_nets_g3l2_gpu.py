@@ -128,8 +128,8 @@ def test_bf16_layers_at_ngf48_with_fp32_activations_injected(fix):
     records = []
     orig = N._conv_block
 
-    def recording(conv, x, cfg, needs_wgrad, norm, act_mod, res, consumer=None, want_plain=False):
-        z = orig(conv, x, cfg, needs_wgrad, norm, act_mod, res, consumer, want_plain)
+    def recording(conv, x, cfg, needs_wgrad, norm, act_mod, res, *rest):
+        z = orig(conv, x, cfg, needs_wgrad, norm, act_mod, res, *rest)
         records.append((conv, x.detach(), cfg, norm, act_mod, None if res is None else res.detach(), z.detach()))
         return z
 
