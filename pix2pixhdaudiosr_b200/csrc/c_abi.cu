@@ -1,5 +1,8 @@
 // Error slot + version for libp2p_b200.so (include/p2p_b200.h).
 #include "common.cuh"
+#include <mutex>
+#include <set>
+#include <utility>
 
 namespace p2p {
 char* error_slot() {
@@ -9,6 +12,15 @@ char* error_slot() {
 long long& launch_counter() {
     static long long n = 0;
     return n;
+}
+void note_kernel_for_carveout(const void* fn) {
+    static std::mutex mu;
+    static std::set<std::pair<const void*, int>> seen;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (seen.insert({fn, dev}).second)
+        cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
 }
 int& deterministic_flag() {
     static int f = -1;

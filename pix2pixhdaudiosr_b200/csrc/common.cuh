@@ -51,8 +51,19 @@ inline bool pdl_enabled() {
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// Kernels without dynamic shared memory ask for the SAME (maximum shared memory) L1 carve-out as the 227 KB convolution
+// kernels they alternate with (P2P_CARVEOUT=0 keeps the driver's default): streaming element-wise kernels gain nothing from
+// a large L1, and a carve-out change between two launches costs an SM reconfiguration.
+inline bool carveout_enabled() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("P2P_CARVEOUT"); v = (e && e[0] == '1') ? 1 : 0; }
+    return v != 0;
+}
+void note_kernel_for_carveout(const void* fn);      // c_abi.cu: cudaFuncSetAttribute once per (function, device)
+
 template <typename... KA, typename... A>
 inline cudaError_t launch_k(void (*kern)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A&&... args) {
+    if (smem == 0 && carveout_enabled()) note_kernel_for_carveout((const void*)kern);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute attr[1];

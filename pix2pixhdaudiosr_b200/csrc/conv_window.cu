@@ -1632,6 +1632,25 @@ extern "C" int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const v
     const int nct = (Cr + bn_cap - 1) / bn_cap;
     int bn = ((Cr + nct - 1) / nct + 15) / 16 * 16;
     if (bn > bn_cap) bn = bn_cap;
+    // Channel-tile width by a two-term cost model (round 2, measured constants): per 64-pixel step a work item pulls the dout
+    // tile (16 KB) plus BN/64 window chunks through TMA (~24 B/clk/SM) and issues set_taps x 4 MMAs of max(93, BN/2) cycles;
+    // the TMEM holds set_taps x BN = 512 accumulator columns.  A wide tile halves the MMA count but doubles the window bytes
+    // per accumulated column -- the wide-channel layers (1536-channel bottleneck, D's 256 -> 512) are TMA-bound at BN = 256.
+    static int bn_model = -1;
+    if (bn_model < 0) { const char* e = getenv("P2P_WGRAD_BN_MODEL"); bn_model = (e && e[0] == '0') ? 0 : 1; }
+    if (bn_model && C >= 256) {                 // (measured: the 192-channel layers lose with narrower tiles)
+        double best = 1e30;
+        int best_bn = bn;
+        for (int cand = 64; cand <= bn_cap && cand <= Cr; cand += 64) {
+            if (C % cand != 0 && cand != bn) continue;                   // whole tiles only (ragged tiles keep the balanced width)
+            const int tmax_c = 512 / cand, nsets_c = (ntaps + tmax_c - 1) / tmax_c, set_c = (ntaps + nsets_c - 1) / nsets_c;
+            const double mma = set_c * 4.0 * (cand / 2 > 93 ? cand / 2 : 93);
+            const double tma = (GA_BYTES + (double)((cand + 63) / 64) * a.chunk_bytes) / 24.0;
+            const double cost = (mma > tma ? mma : tma) * nsets_c / ((double)ntaps * cand);      // cycles per accumulated (tap, column)
+            if (cost < best * 0.97) { best = cost; best_bn = cand; }
+        }
+        bn = best_bn;
+    }
     a.BN = bn;
     a.nchunks = (bn + 63) / 64;
     a.j_tiles = (J + 127) / 128;
