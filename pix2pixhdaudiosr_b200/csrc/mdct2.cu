@@ -13,10 +13,12 @@
 //     synthesis(scale, c0): out  = scale * crop(OLA_hop(w[n] * 2 sum_k c0_k X[k] cos(.)))     c0_0 = c0, c0_k = 1 (k > 0)
 //   MDCT2 = analysis(1, 1); IMDCT2 = synthesis(1/2, 1/2); d MDCT2 / dx = synthesis(1/N, 1); d IMDCT2 / dX = analysis(N/2, 1/2).
 // Layout: signal [B,T] fp32, coefficients [B,F,N] fp32 (bins fastest).  Bound: HBM (4 B in + 8 B out per sample at
-// hop = N/2).  Two real frames share one complex FFT (real / imaginary lanes); next: the register FFT + TMA prefetch
-// structure of mdct4_fast.cuh.
+// hop = N/2).  Two real frames share one complex FFT (real / imaginary lanes).  The canonical geometry (win == n_fft,
+// hop == n_fft/2, n_fft 64..1024) runs the register-FFT + TMA-prefetch kernels of mdct2_fast.cuh; the kernels in this
+// file are the general path (any hop / win, n_fft up to 4096).
 #include "common.cuh"
 #include "smem_fft.cuh"
+#include "mdct2_fast.cuh"
 #include <cmath>
 #include <cstdint>
 
@@ -220,6 +222,60 @@ int ensure_smem2(K kernel, size_t bytes) {
     return P2P_OK;
 }
 
+int sm_count_and_blocks2(const void* kernel, size_t smem, int* blocks_per_sm) {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, kernel, fast2::kThreads, smem) != cudaSuccess) return -1;
+    return sms;
+}
+
+template <class C>
+int launch_analysis2_fast(const float* x, float* spec, const float* window, const void* tables, int B, long long T, int F,
+                          long long offset, float scale, float c0, cudaStream_t stream) {
+    auto kernel = fast2::mdct2_analysis_fast<C>;
+    const size_t smem = C::A_SMEM;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail(P2P_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    int bps = 0;
+    const int sms = sm_count_and_blocks2((const void*)kernel, smem, &bps);
+    if (sms <= 0 || bps <= 0) { cudaGetLastError(); return fail(P2P_ECUDA, "occupancy query failed (smem %zu)", smem); }
+    const int tiles_per_row = (F + C::FPT - 1) / C::FPT;
+    const long long total = (long long)tiles_per_row * B;
+    const long long grid = total < (long long)sms * bps ? total : (long long)sms * bps;
+    const int aligned = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && (T % 4 == 0) && (offset % 4 == 0);
+    kernel<<<(unsigned)grid, fast2::kThreads, smem, stream>>>(x, spec, window, tables, T, F, offset, scale, c0, tiles_per_row,
+                                                              total, aligned);
+    return check_launch("mdct2_analysis_fast");
+}
+
+template <class C>
+int launch_synthesis2_fast(const float* spec, float* out, const float* window, const void* tables, int B, int F,
+                           long long T_out, long long crop_left, float scale, float c0, cudaStream_t stream) {
+    auto kernel = fast2::mdct2_synthesis_fast<C>;
+    const size_t smem = C::S_SMEM;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return fail(P2P_ECUDA, "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    int bps = 0;
+    const int sms = sm_count_and_blocks2((const void*)kernel, smem, &bps);
+    if (sms <= 0 || bps <= 0) { cudaGetLastError(); return fail(P2P_ECUDA, "occupancy query failed (smem %zu)", smem); }
+    const long long hf = crop_left / C::M, hl = (crop_left + T_out - 1) / C::M;
+    if (hl > 2147483000LL) return fail(P2P_ENOTSUP, "T_out too large");
+    const int tiles_per_row = (int)((hl - hf + 1 + C::FPT - 2) / (C::FPT - 1));
+    const long long total = (long long)tiles_per_row * B;
+    const long long grid = total < (long long)sms * bps ? total : (long long)sms * bps;
+    const int aligned_in = (reinterpret_cast<uintptr_t>(spec) & 15) == 0;
+    const int vec_out = ((reinterpret_cast<uintptr_t>(out) & 15) == 0) && (T_out % 4 == 0) && (crop_left % 4 == 0);
+    kernel<<<(unsigned)grid, fast2::kThreads, smem, stream>>>(spec, out, window, tables, F, T_out, crop_left, scale, c0,
+                                                              (int)hf, (int)hl, tiles_per_row, total, aligned_in, vec_out);
+    return check_launch("mdct2_synthesis_fast");
+}
+
+bool fast2_enabled() {
+    static const bool on = [] { const char* e = getenv("P2P_MDCT2_FAST"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
 }  // namespace
 }  // namespace p2p
 
@@ -256,6 +312,16 @@ extern "C" int p2p_mdct2_analysis(const float* x, float* spec, const float* wind
     if (B == 0 || F == 0) return P2P_OK;
     if (!spec || !window || !tables || (!x && T > 0)) return fail(P2P_EINVAL, "null pointer argument");
     if (B > 65535) return fail(P2P_ENOTSUP, "B=%d exceeds 65535 rows per launch", B);
+    if (fast2_enabled() && win == n_fft && hop * 2 == n_fft && x) {
+        cudaStream_t st = (cudaStream_t)stream;
+        switch (n_fft) {
+            case 64: return launch_analysis2_fast<fast2::Cfg2<8, 8, 2>>(x, spec, window, tables, B, T, F, offset, scale, c0, st);
+            case 128: return launch_analysis2_fast<fast2::Cfg2<16, 8, 2>>(x, spec, window, tables, B, T, F, offset, scale, c0, st);
+            case 256: return launch_analysis2_fast<fast2::Cfg2<16, 16, 2>>(x, spec, window, tables, B, T, F, offset, scale, c0, st);
+            case 512: return launch_analysis2_fast<fast2::Cfg2<32, 16, 1>>(x, spec, window, tables, B, T, F, offset, scale, c0, st);
+            case 1024: return launch_analysis2_fast<fast2::Cfg2<32, 32, 2>>(x, spec, window, tables, B, T, F, offset, scale, c0, st);
+        }
+    }
     int fpb = 8192 / n_fft; if (fpb < 2) fpb = 2; if (fpb > 32) fpb = 32;      // even: frames are transformed in pairs
     const int span_max = (fpb - 1) * hop + win;
     const size_t smem = 4ull * (((span_max + 3) & ~3) + ((win + 3) & ~3) + 2 * (fpb / 2) * n_fft);
@@ -276,6 +342,16 @@ extern "C" int p2p_mdct2_synthesis(const float* spec, float* out, const float* w
     if (B == 0 || T_out == 0) return P2P_OK;
     if (!out || !window || !tables || (!spec && F > 0)) return fail(P2P_EINVAL, "null pointer argument");
     if (B > 65535) return fail(P2P_ENOTSUP, "B=%d exceeds 65535 rows per launch", B);
+    if (fast2_enabled() && win == n_fft && hop * 2 == n_fft && F > 0) {
+        cudaStream_t st = (cudaStream_t)stream;
+        switch (n_fft) {
+            case 64: return launch_synthesis2_fast<fast2::Cfg2<8, 8, 2>>(spec, out, window, tables, B, F, T_out, crop_left, scale, c0, st);
+            case 128: return launch_synthesis2_fast<fast2::Cfg2<16, 8, 2>>(spec, out, window, tables, B, F, T_out, crop_left, scale, c0, st);
+            case 256: return launch_synthesis2_fast<fast2::Cfg2<16, 16, 2>>(spec, out, window, tables, B, F, T_out, crop_left, scale, c0, st);
+            case 512: return launch_synthesis2_fast<fast2::Cfg2<32, 16, 1>>(spec, out, window, tables, B, F, T_out, crop_left, scale, c0, st);
+            case 1024: return launch_synthesis2_fast<fast2::Cfg2<32, 32, 2>>(spec, out, window, tables, B, F, T_out, crop_left, scale, c0, st);
+        }
+    }
     const int overlap = (win + hop - 1) / hop;            // frames covering one sample
     int nf_target = 8192 / n_fft; if (nf_target < 2) nf_target = 2;
     int hpb = nf_target - overlap; if (hpb < 1) hpb = 1;
