@@ -311,7 +311,10 @@ int p2p_spectro_decode_bwd(const void* x, long long sb, long long sc, long long 
  * c0 1/2); their autograd adjoints are synthesis(1/n_fft, 1) and analysis(n_fft/2, 1/2).  x_pad is x shifted right by
  * `offset` zeros and zero-extended.  x [B,T], spec [B,F,n_fft], window [win], all fp32 device pointers; tables: device
  * copy of p2p_mdct2_fill_tables(n_fft) (p2p_mdct2_table_words(n_fft) 4-byte words, computed in double on the host).
- * n_fft: power of two in [4, 4096]; 1 <= hop <= win <= n_fft. */
+ * n_fft: power of two in [4, 4096]; 1 <= hop <= win <= n_fft.  win == n_fft, hop == n_fft/2, n_fft in 64..1024 runs the
+ * register-FFT kernels (two frames per complex FFT, TMA-prefetched spans); p2p_mdct2_force_general(1) (a testing knob,
+ * returns the old value) forces the general shared-memory kernels there too. */
+int p2p_mdct2_force_general(int on);
 int p2p_mdct2_table_words(int n_fft);
 int p2p_mdct2_fill_tables(int n_fft, void* host_tables);
 int p2p_mdct2_analysis(const float* x, float* spec, const float* window, const void* tables, int B, int64_t T, int F,

@@ -13,6 +13,7 @@ _SIGS = {
     "p2p_kernel_launches": (_c.c_longlong, []),
     "p2p_set_deterministic": (_c.c_int, [_c.c_int]),
     "p2p_mdct4_force_general": (_c.c_int, [_c.c_int]),
+    "p2p_mdct2_force_general": (_c.c_int, [_c.c_int]),
     "p2p_mdct4_table_words": (_c.c_int, [_c.c_int]),
     "p2p_mdct4_fill_tables": (_c.c_int, [_c.c_int, _c.c_void_p]),
     "p2p_mdct4_analysis": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_int, _c.c_int64,

@@ -271,13 +271,22 @@ int launch_synthesis2_fast(const float* spec, float* out, const float* window, c
     return check_launch("mdct2_synthesis_fast");
 }
 
+// n_fft 512 synthesis: one coefficient buffer and two CTAs per SM (default) or two buffers and one CTA (P2P_MDCT2_NBUF=2)
+int synthesis_nbuf_512() {
+    static const int n = [] { const char* e = getenv("P2P_MDCT2_NBUF"); return (e && e[0] == '2') ? 2 : 1; }();
+    return n;
+}
+
+int g_force_general2 = 0;
 bool fast2_enabled() {
     static const bool on = [] { const char* e = getenv("P2P_MDCT2_FAST"); return !(e && e[0] == '0'); }();
-    return on;
+    return on && !g_force_general2;
 }
 
 }  // namespace
 }  // namespace p2p
+
+extern "C" int p2p_mdct2_force_general(int on) { const int old = p2p::g_force_general2; p2p::g_force_general2 = on; return old; }
 
 extern "C" int p2p_mdct2_table_words(int n_fft) {
     if (!p2p::is_pow2(n_fft) || n_fft < 4 || n_fft > 4096)
@@ -348,7 +357,10 @@ extern "C" int p2p_mdct2_synthesis(const float* spec, float* out, const float* w
             case 64: return launch_synthesis2_fast<fast2::Cfg2<8, 8, 2>>(spec, out, window, tables, B, F, T_out, crop_left, scale, c0, st);
             case 128: return launch_synthesis2_fast<fast2::Cfg2<16, 8, 2>>(spec, out, window, tables, B, F, T_out, crop_left, scale, c0, st);
             case 256: return launch_synthesis2_fast<fast2::Cfg2<16, 16, 2>>(spec, out, window, tables, B, F, T_out, crop_left, scale, c0, st);
-            case 512: return launch_synthesis2_fast<fast2::Cfg2<32, 16, 1>>(spec, out, window, tables, B, F, T_out, crop_left, scale, c0, st);
+            case 512:
+                if (synthesis_nbuf_512() == 2)
+                    return launch_synthesis2_fast<fast2::Cfg2<32, 16, 2>>(spec, out, window, tables, B, F, T_out, crop_left, scale, c0, st);
+                return launch_synthesis2_fast<fast2::Cfg2<32, 16, 1>>(spec, out, window, tables, B, F, T_out, crop_left, scale, c0, st);
             case 1024: return launch_synthesis2_fast<fast2::Cfg2<32, 32, 2>>(spec, out, window, tables, B, F, T_out, crop_left, scale, c0, st);
         }
     }

@@ -38,6 +38,11 @@ struct Cfg2 {
     static constexpr int XW = 2 * P * (P + 1);            // words of one pair's exchange region (P rows of P+1 float2)
     static constexpr bool XTW_IN_REGS = (V <= 16);
     static constexpr int XV = XTW_IN_REGS ? V : 1;
+    // V = 32: the exchange twiddles w_N^(j k1) come from a [k1][j] table in shared memory (conflict-free, immediate
+    // offsets) - a gather from roots[] touches up to 16 cache lines per load.  The (-1)^k1 of flipped lanes is part of
+    // the table when P = 32 (one lane per column); for P < 32 a whole pair is flipped and the sign moves to the output.
+    static constexpr int XT = XTW_IN_REGS ? 0 : 2 * N;    // words
+    static constexpr bool SIGN_AT_OUTPUT = !XTW_IN_REGS && P < 32;
     static_assert(Q == 1 || Q == 2, "V must be P or 2P");
     static constexpr int MINB = (N <= 512) ? 2 : 1;       // CTAs per SM the register allocation must allow
     // analysis: sig[2][ASIG] | ws[N + APAD] | exch[PAIRS][XW] | tw[2N] | mbar
@@ -47,7 +52,8 @@ struct Cfg2 {
     static constexpr int A_OFF_WS = 2 * ASIG;
     static constexpr int A_OFF_X = A_OFF_WS + N + APAD;
     static constexpr int A_OFF_TW = A_OFF_X + PAIRS * XW;
-    static constexpr int A_OFF_BAR = A_OFF_TW + 2 * N;
+    static constexpr int A_OFF_XT = A_OFF_TW + 2 * N;
+    static constexpr int A_OFF_BAR = A_OFF_XT + XT;
     static constexpr size_t A_SMEM = 4ull * A_OFF_BAR + 16;
     // synthesis: buf[NBUF][SBUF] | exch | tw | mbar
     static constexpr int NBUF = NBUF_S_;
@@ -56,7 +62,8 @@ struct Cfg2 {
     static constexpr int SBUF = FPT * SROW + 4;           // + slack: row[N - 0] of the last row is read (and discarded)
     static constexpr int S_OFF_X = NBUF * SBUF;
     static constexpr int S_OFF_TW = S_OFF_X + PAIRS * XW;
-    static constexpr int S_OFF_BAR = S_OFF_TW + 2 * N;
+    static constexpr int S_OFF_XT = S_OFF_TW + 2 * N;
+    static constexpr int S_OFF_BAR = S_OFF_XT + XT;
     static constexpr size_t S_SMEM = 4ull * S_OFF_BAR + 16;
     static constexpr int G4 = M / 4;                      // float4 groups per hop slot (overlap-add pass)
     static constexpr int NQ = G4 > kThreads ? G4 / kThreads : 1;
@@ -74,8 +81,8 @@ __device__ __forceinline__ int xtw_index(int j, int k1, bool flip) {
 // z: V points of column j (slot i holds n1 = i, or (i + V/2) % V on a flipped lane)  ->  X[h][k2] = FFT_N bin K1(h) + V k2,
 // K1(0) = j, K1(1) = (j == 0 ? P : V - j).
 template <class C>
-__device__ __forceinline__ void fft_core2(float2 (&z)[C::V], float2* __restrict__ ex, const float2* __restrict__ roots,
-                                          const float2 (&xr)[C::XV], int j, bool flip, float2 (&X)[C::Q][C::P]) {
+__device__ __forceinline__ void fft_core2(float2 (&z)[C::V], float2* __restrict__ ex, const float2* __restrict__ xt_lane,
+                                          const float2 (&xr)[C::XV], int j, float2 (&X)[C::Q][C::P]) {
     constexpr int V = C::V, P = C::P;
     fft_reg<V>(z);
 #pragma unroll
@@ -86,7 +93,7 @@ __device__ __forceinline__ void fft_core2(float2 (&z)[C::V], float2* __restrict_
             float2 v = z[brev<V>(k1)];
             if (k1 > 0) {
                 if constexpr (C::XTW_IN_REGS) v = cmulf(v, xr[k1]);
-                else v = cmulf(v, __ldg(roots + xtw_index<C>(j, k1, flip)));
+                else v = cmulf(v, xt_lane[k1 * P]);
             }
             ex[r * (P + 1) + j] = v;
         }
@@ -99,6 +106,17 @@ __device__ __forceinline__ void fft_core2(float2 (&z)[C::V], float2* __restrict_
         fft_reg<P>(b);
 #pragma unroll
         for (int k2 = 0; k2 < P; ++k2) X[h][k2] = b[brev<P>(k2)];
+    }
+}
+
+// fills the shared-memory table (V = 32); `signed_cols`: columns j >= 16 carry the (-1)^k1 of flipped lanes (analysis, P = 32)
+template <class C>
+__device__ __forceinline__ void fill_xt(float2* xt, const float2* roots, bool signed_cols) {
+    if constexpr (!C::XTW_IN_REGS) {
+        for (int i = threadIdx.x; i < C::N; i += kThreads) {
+            const int k1 = i / C::P, j = i % C::P;
+            xt[i] = __ldg(roots + xtw_index<C>(j, k1, signed_cols && C::P == 32 && j >= 16));
+        }
     }
 }
 
@@ -171,7 +189,7 @@ __device__ __forceinline__ void split_pair(float2 Zk, float2 Zm, float2 t, float
 template <class C>
 __device__ __forceinline__ void analysis2_warp(const float* __restrict__ sig, const float* __restrict__ ws,
                                                float* __restrict__ ex_warp, const float2* __restrict__ tw,
-                                               const float2* __restrict__ roots, const float2 (&xr)[C::XV],
+                                               const float2* __restrict__ xt, const float2 (&xr)[C::XV],
                                                float* __restrict__ spec_tile, int nfr, int warp, int lane, float c0) {
     constexpr int V = C::V, P = C::P, N = C::N, H = V / 2;
     const int j = lane % P, g = lane / P;
@@ -196,26 +214,33 @@ __device__ __forceinline__ void analysis2_warp(const float* __restrict__ sig, co
         z[i] = make_float2(vA ? w * a : 0.f, vB ? w * b : 0.f);
     }
     float2 X[C::Q][P];
-    fft_core2<C>(z, reinterpret_cast<float2*>(ex_warp + g * C::XW), roots, xr, j, flip, X);
+    fft_core2<C>(z, reinterpret_cast<float2*>(ex_warp + g * C::XW), xt + j, xr, j, X);
 
     float* rowA = spec_tile + (long long)(2 * pr) * N;
-    float* rowB = rowA + N;
     if constexpr (C::Q == 2) {
         const int k1b = (j == 0) ? P : V - j;
+        // all bins of a flipped pair's odd columns come out negated (rows j and V - j have the parity of j)
+        const float sg = (C::SIGN_AT_OUTPUT && flip && (j & 1)) ? -1.f : 1.f;
+        float* pA = rowA + j;                              // bins j + V k2
+        float* qA = rowA + k1b;                            // bins k1b + V k2
+        const float2* tp = tw + j;
+        const float2* tq = tw + k1b;
 #pragma unroll
         for (int k2 = 0; k2 < P; ++k2) {
             const float2 Zp = X[0][k2], Zs = X[1][P - 1 - k2];
             const float2 mp = (j == 0) ? X[0][(P - k2) % P] : Zs;
             const float2 ms = (j == 0) ? X[1][k2] : Zp;
-            const int kp = j + V * k2, ks = k1b + V * (P - 1 - k2);
+            float2 t1 = tp[V * k2], t2 = tq[V * (P - 1 - k2)];
+            if constexpr (C::SIGN_AT_OUTPUT) { t1.x *= sg; t1.y *= sg; t2.x *= sg; t2.y *= sg; }
             float ap, bp, as, bs;
-            split_pair(Zp, mp, tw[kp], ap, bp);
-            split_pair(Zs, ms, tw[ks], as, bs);
+            split_pair(Zp, mp, t1, ap, bp);
+            split_pair(Zs, ms, t2, as, bs);
             if (k2 == 0 && j == 0) { ap *= c0; bp *= c0; }
-            if (vA) { rowA[kp] = ap; rowA[ks] = as; }
-            if (vB) { rowB[kp] = bp; rowB[ks] = bs; }
+            if (vA) { pA[V * k2] = ap; qA[V * (P - 1 - k2)] = as; }
+            if (vB) { pA[N + V * k2] = bp; qA[N + V * (P - 1 - k2)] = bs; }
         }
     } else {
+        float* rowB = rowA + N;
         const int src = (lane & ~(P - 1)) | ((P - j) & (P - 1));
 #pragma unroll
         for (int k2 = 0; k2 < P; ++k2) {
@@ -257,6 +282,8 @@ mdct2_analysis_fast(const float* __restrict__ x, float* __restrict__ spec, const
     }
     float2 xr[C::XV];
     load_xtw<C>(xr, roots, lane % C::P, (lane >> 4) & 1);
+    float2* xt = reinterpret_cast<float2*>(smem + C::A_OFF_XT);
+    fill_xt<C>(xt, roots, true);
     __syncthreads();
 
     long long w = blockIdx.x;
@@ -272,7 +299,7 @@ mdct2_analysis_fast(const float* __restrict__ x, float* __restrict__ spec, const
         mbar_wait(&bars[buf], phase[buf]);
         phase[buf] ^= 1;
         if (warp * C::G * 2 < tc.nfr)
-            analysis2_warp<C>(sig0 + buf * C::ASIG, ws, exch + warp * C::G * C::XW, tw, roots, xr,
+            analysis2_warp<C>(sig0 + buf * C::ASIG, ws, exch + warp * C::G * C::XW, tw, xt, xr,
                               spec + ((long long)tc.row * F + tc.f0) * N, tc.nfr, warp, lane, c0);
         __syncthreads();
         buf ^= 1;
@@ -302,6 +329,12 @@ __device__ __forceinline__ void fetch_rows2(float* buf, uint64_t* bar, const flo
             for (int i = threadIdx.x; i < C::N; i += kThreads)
                 buf[r * C::SROW + i] = __ldg(spec_row + (long long)(fA + r) * C::N + i);
     }
+    // rows of frames outside [0, F) (first / last tile of a batch row) are zero coefficients
+#pragma unroll 1
+    for (int r = 0; r < C::FPT; ++r) {
+        if (r >= r_lo && r < r_hi) { r = r_hi - 1; continue; }
+        for (int i = threadIdx.x; i < C::N; i += kThreads) buf[r * C::SROW + i] = 0.f;
+    }
 }
 
 // One warp: the coefficient rows of its G pairs -> y = 2 sum_k c_k X[k] cos(pi (2n+1) k / (2N)) written back IN PLACE.
@@ -309,13 +342,13 @@ __device__ __forceinline__ void fetch_rows2(float* buf, uint64_t* bar, const flo
 // FFT_N(hA + j hB) carries frame A on the real and frame B on the imaginary lane:  v[n] -> y[2n] (n < N/2), y[2(N-1-n)+1].
 template <class C>
 __device__ __forceinline__ void synthesis2_warp(float* __restrict__ buf, float* __restrict__ ex_warp,
-                                                const float2* __restrict__ tw, const float2* __restrict__ roots,
+                                                const float2* __restrict__ tw, const float2* __restrict__ xt,
                                                 const float2 (&xr)[C::XV], int fA, int F, int warp, int lane, float c0x2) {
     constexpr int V = C::V, P = C::P, N = C::N;
     const int j = lane % P, g = lane / P;
     const int pr = warp * C::G + g;
     float* rA = buf + (2 * pr) * C::SROW;
-    float* rB = rA + C::SROW;
+    const float* rB = rA + C::SROW;
     const int fa = fA + 2 * pr;
     const bool vA = fa >= 0 && fa < F, vB = fa + 1 >= 0 && fa + 1 < F;
 
@@ -328,21 +361,31 @@ __device__ __forceinline__ void synthesis2_warp(float* __restrict__ buf, float* 
         float2 hA = make_float2(t.x * ak - t.y * am, t.x * am + t.y * ak);
         float2 hB = make_float2(t.x * bk - t.y * bm, t.x * bm + t.y * bk);
         if (i == 0 && j == 0) { hA = make_float2(c0x2 * ak, 0.f); hB = make_float2(c0x2 * bk, 0.f); }
-        if (!vA) hA = make_float2(0.f, 0.f);
-        if (!vB) hB = make_float2(0.f, 0.f);
-        z[i] = make_float2(hA.x - hB.y, hA.y + hB.x);
+        z[i] = make_float2(hA.x - hB.y, hA.y + hB.x);      // rows of frames outside [0, F) hold zeros (fetch_rows2)
     }
     float2 X[C::Q][P];
-    fft_core2<C>(z, reinterpret_cast<float2*>(ex_warp + g * C::XW), roots, xr, j, false, X);
+    fft_core2<C>(z, reinterpret_cast<float2*>(ex_warp + g * C::XW), xt + j, xr, j, X);
 
+    const bool all_valid = __all_sync(0xffffffffu, vA && vB);
 #pragma unroll
     for (int h = 0; h < C::Q; ++h) {
         const int k1 = h == 0 ? j : (j == 0 ? P : V - j);
+        float* lo = rA + 2 * k1;                           // y[2n], n = k1 + V k2 < N/2
+        float* hi = rA + 2 * N - 1 - 2 * k1;               // y[2(N-1-n)+1] otherwise
+        if (all_valid) {
 #pragma unroll
-        for (int k2 = 0; k2 < P; ++k2) {
-            const int yi = k2 < P / 2 ? 2 * k1 + 2 * V * k2 : 2 * N - 1 - 2 * k1 - 2 * V * k2;
-            rA[yi] = vA ? X[h][k2].x : 0.f;
-            rB[yi] = vB ? X[h][k2].y : 0.f;
+            for (int k2 = 0; k2 < P; ++k2) {
+                float* d = k2 < P / 2 ? lo + 2 * V * k2 : hi - 2 * V * k2;
+                d[0] = X[h][k2].x;
+                d[C::SROW] = X[h][k2].y;
+            }
+        } else {                                           // a zero row must stay exactly zero: its partner's rounding noise
+#pragma unroll
+            for (int k2 = 0; k2 < P; ++k2) {
+                float* d = k2 < P / 2 ? lo + 2 * V * k2 : hi - 2 * V * k2;
+                d[0] = vA ? X[h][k2].x : 0.f;
+                d[C::SROW] = vB ? X[h][k2].y : 0.f;
+            }
         }
     }
 }
@@ -366,6 +409,8 @@ mdct2_synthesis_fast(const float* __restrict__ spec, float* __restrict__ out, co
     for (int p = threadIdx.x; p < N; p += kThreads) tw[p] = __ldg(gtw + p);
     float2 xr[C::XV];
     load_xtw<C>(xr, roots, lane % C::P, false);
+    float2* xt = reinterpret_cast<float2*>(smem + C::S_OFF_XT);
+    fill_xt<C>(xt, roots, false);
     // overlap-add role of this thread: float4 group(s) q of every SS-th hop slot; window * scale stays in registers
     const int q0 = threadIdx.x % C::G4;
     const int sl0 = (C::G4 < kThreads) ? threadIdx.x / C::G4 : 0;
@@ -406,7 +451,7 @@ mdct2_synthesis_fast(const float* __restrict__ spec, float* __restrict__ out, co
         phase[b] ^= 1;
         float* buf = buf0 + b * C::SBUF;
         if (warp * C::G * 2 <= ns)       // frames fA .. fA+ns are needed (ns+1 rows)
-            synthesis2_warp<C>(buf, exch + warp * C::G * C::XW, tw, roots, xr, h0 - 1, F, warp, lane, 2.f * c0);
+            synthesis2_warp<C>(buf, exch + warp * C::G * C::XW, tw, xt, xr, h0 - 1, F, warp, lane, 2.f * c0);
         __syncthreads();
 
         float* orow = out + (long long)row * T_out;

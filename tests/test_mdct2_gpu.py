@@ -123,3 +123,43 @@ def test_error_behaviour():
         im(torch.zeros(3, 256).cuda())                                    # 3-D only (mdct.py:433)
     with pytest.raises((NotImplementedError, ValueError, RuntimeError)):
         MDCT2(384, 192, 384, None, device="cuda")(torch.zeros(2, 4000).cuda())   # not a power of two
+
+
+@pytest.mark.parametrize("n_fft", [64, 128, 256, 512, 1024])
+@pytest.mark.parametrize("B,T", [(1, 0), (3, 20003), (2, 65536), (5, 33 * 512 + 4)])
+def test_register_fft_path_matches_oracle_and_general_kernels(n_fft, B, T):
+    """canonical geometry (win = n_fft, hop = n_fft/2): the register-FFT kernels (frame pairs, ragged last tiles, odd frame
+    counts, unaligned lengths, signals shorter than one tile) against the float64 oracle and the general kernels, forward
+    and both autograd adjoints"""
+    from pix2pixhdaudiosr_b200 import _lib
+    T = T or 2 * n_fft + 6
+    torch.manual_seed(n_fft + T)
+    hop = n_fft // 2
+    x = 0.1 * torch.randn(B, T)
+    w = kbdwin(n_fft).float()
+    m = MDCT2(n_fft, hop, n_fft, w, True, device="cuda")
+    im = IMDCT2(n_fft, hop, n_fft, w, True, device="cuda")
+
+    def run():
+        xc = x.cuda().requires_grad_(True)
+        spec = m(xc)
+        g = torch.randn(spec.shape, generator=torch.Generator().manual_seed(7)).cuda()
+        (gx,) = torch.autograd.grad(spec, xc, g)
+        sc = spec.detach().clone().requires_grad_(True)
+        y = im(sc)
+        gy = torch.randn(y.shape, generator=torch.Generator().manual_seed(8)).cuda()
+        (gs,) = torch.autograd.grad(y, sc, gy)
+        return [t.detach().cpu().numpy() for t in (spec, gx, y, gs)]
+
+    fast = run()
+    old = _lib.lib().p2p_mdct2_force_general(1)
+    try:
+        general = run()
+    finally:
+        _lib.lib().p2p_mdct2_force_general(old)
+    want = O2.mdct2_forward(x.numpy(), w.numpy(), n_fft, hop, True)
+    assert fast[0].shape == want.shape
+    assert relerr(fast[0], want) < TOL
+    assert relerr(fast[2], O2.imdct2_forward(fast[0].astype(np.float64), w.numpy(), n_fft, hop, True)) < TOL
+    for a, b in zip(fast, general):
+        assert a.shape == b.shape and relerr(a, b) < TOL
