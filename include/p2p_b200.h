@@ -230,6 +230,16 @@ int p2p_instnorm_act_bwd(const void* y, const float* stats, const void* dz, void
 int p2p_instnorm_workspace(float* ws, long long ws_floats, unsigned* cnt, long long cnt_words);
 /* stats [N,C,2] = (mean, rstd) of y [N,HW,C] alone: the reduction half of p2p_instnorm_act_fwd, for p2p_instnorm_act_planes. */
 int p2p_instnorm_stats(const void* y, float* stats, int N, long long HW, int C, float eps, int y_dtype, void* stream);
+/* Allocation-free variant of p2p_instnorm_stats.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments and result; the single-launch reduction's scratch (partial sums + group
+ * counters) is a file-scope device array inside the library (520 KB on every GPU that loads it, held until exit) whose
+ * device address is looked up once per device with cudaGetSymbolAddress.  The call makes no cudaMalloc / cudaFree /
+ * allocating library call.  Limits: N*C <= 65536, N*ceil(C/128) <= 2048, C % 4 == 0, HW < 2e9, y and stats 16-byte
+ * aligned; anything beyond returns P2P_ENOTSUP with a message (use p2p_instnorm_stats there).  All calls on a device share
+ * the array: the used region is cleared on `stream` before each launch, and calls that OVERLAP on the GPU (different
+ * streams, concurrent graph branches) race on it - order them on one stream. */
+int p2p_instnorm_stats_static(const void* y, float* stats, int N, long long HW, int C, float eps, int y_dtype, void* stream);
 
 /* AvgPool2d(3, stride 2, padding 1, count_include_pad=False), NHWC. OH=(H-1)/2+1, OW=(W-1)/2+1. */
 int p2p_avgpool3s2_fwd(const void* x, void* y, int N, int H, int W, int C, int dtype, void* stream);

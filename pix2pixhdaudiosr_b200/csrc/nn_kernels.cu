@@ -3,6 +3,7 @@
 // Reference call sites: models/networks.py:18-25 (InstanceNorm2d affine=False), :166,309 (AvgPool2d
 // count_include_pad=False), :68-110 (GANLoss), pix2pixHD_model.py:390-398 (feature matching), train.py:164-184.
 #include "dtype.cuh"
+#include <mutex>
 
 namespace p2p {
 namespace {
@@ -755,6 +756,63 @@ extern "C" int p2p_instnorm_stats(const void* y, float* stats, int N, long long 
         in_finalize_kernel<TY><<<(N * C + 255) / 256, 256, 0, st>>>((const TY*)y, stats, HW, C, N * C, eps);
     });
     return check_launch("instnorm_stats");
+}
+
+// ---- allocation-free variant of p2p_instnorm_stats (no counterpart in the reference; added
+// for callers that cannot allocate: graph capture, serving loops) ------------------------------------------------
+// The partial-sum workspace and the group counters of the single-launch reduction live in ONE file-scope device array
+// instead of caller-allocated memory: kStaticSums floats of sums, then kStaticCnt 32-bit counters (520 KB per GPU that loads
+// the library, held until exit).  Every call shares it; the region a call uses is cleared on the caller's stream first.
+namespace p2p {
+namespace {
+constexpr long long kStaticSums = 131072;      // floats: 2 * N * C  -> N * C <= 65536
+constexpr long long kStaticCnt = 2048;         // words:  N * ceil(C / 128)
+static __device__ __align__(256) float g_static_stats_scratch[kStaticSums + kStaticCnt];
+
+// device address of the array on the CURRENT device (the symbol's name is only a host-side handle), looked up once per device
+float* static_scratch_ptr() {
+    static float* ptr[64] = {};
+    static std::mutex mu;
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { fail(P2P_ECUDA, "cudaGetDevice failed"); return nullptr; }
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_stats_scratch);
+        if (e != cudaSuccess || !p) { fail(P2P_ECUDA, "cudaGetSymbolAddress: %s", cudaGetErrorString(e)); return nullptr; }
+        ptr[dev] = static_cast<float*>(p);
+    }
+    return ptr[dev];
+}
+}  // namespace
+}  // namespace p2p
+
+extern "C" int p2p_instnorm_stats_static(const void* y, float* stats, int N, long long HW, int C, float eps, int y_dtype,
+                                         void* stream) {
+    if (N < 0 || HW < 0 || C < 0) return fail(P2P_EINVAL, "negative size");
+    if ((long long)N * HW * C == 0) return P2P_OK;
+    if (!y || !stats) return fail(P2P_EINVAL, "null pointer argument");
+    if (y_dtype != P2P_F32 && y_dtype != P2P_BF16) return fail(P2P_EINVAL, "y_dtype must be P2P_F32 or P2P_BF16");
+    const int cb = (C / 4 + 31) / 32;
+    if (C % 4 != 0 || HW >= 2000000000LL || N > 65535 || !vec4_ok(y, y_dtype == P2P_BF16 ? 2 : 4) || !vec4_ok(stats, 4))
+        return fail(P2P_ENOTSUP, "p2p_instnorm_stats_static needs C %% 4 == 0, HW < 2e9, N <= 65535 and 16-byte aligned y / stats "
+                                 "(C=%d HW=%lld N=%d)", C, HW, N);
+    if (2LL * N * C > kStaticSums || (long long)N * cb > kStaticCnt)
+        return fail(P2P_ENOTSUP, "p2p_instnorm_stats_static: N*C=%lld exceeds the built-in scratch (N*C <= %lld and N*ceil(C/128) <= %lld); "
+                                 "use p2p_instnorm_stats", (long long)N * C, kStaticSums / 2, kStaticCnt);
+    float* ws = static_scratch_ptr();
+    if (!ws) return P2P_ECUDA;
+    unsigned* cnt = reinterpret_cast<unsigned*>(ws + kStaticSums);
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array keeps whatever the last call (possibly an aborted or overlapping one) left: clear what must start at zero
+    if (cudaMemsetAsync(ws, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess ||
+        cudaMemsetAsync(cnt, 0, sizeof(unsigned) * N * cb, st) != cudaSuccess)
+        return fail(P2P_ECUDA, "memset of the built-in scratch failed");
+    const int S = split_for(HW, cb * N);
+    const int chunk = (int)((HW + S - 1) / S);
+    P2P_DISPATCH_DTYPE(y_dtype, TY, (in_stats_fused_v4_kernel<TY><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>(
+        (const TY*)y, stats, ws, cnt, (int)HW, C, chunk, eps)));
+    return check_launch("instnorm_stats_static");
 }
 
 extern "C" int p2p_instnorm_act_bwd(const void* y, const float* stats, const void* dz, void* dy, float* work, int N,
