@@ -223,6 +223,13 @@ int p2p_instnorm_act_fwd(const void* y, const void* res, void* z, float* stats, 
  * work: fp32 scratch [N,C,2] (ignored when norm == 0). */
 int p2p_instnorm_act_bwd(const void* y, const float* stats, const void* dz, void* dy, float* work, int N,
                          long long HW, int C, int norm, int act, float slope, int y_dtype, int dtype, void* stream);
+/* p2p_instnorm_act_bwd that writes dy directly in the layout the stride-1 gradient kernels of the conv in front of the
+ * normalisation read (the adjoint of ReflectionPad2d / zero padding of models/networks.py:196-204 folded into the producer):
+ * grid [rows, C], image n at pixel row n*Hh*Wh, dy[n,h,w,:] at + h*Wh + w, zeros everywhere else (Hh >= H, Wh >= W,
+ * rows >= N*Hh*Wh).  C % 4 == 0 and 16-byte aligned pointers, else P2P_ENOTSUP. */
+int p2p_instnorm_act_bwd_wrap(const void* y, const float* stats, const void* dz, void* grid, float* work, int N, int H,
+                              int W, int C, int Hh, int Wh, long long rows, int norm, int act, float slope, int y_dtype,
+                              int dtype, void* stream);
 /* Caller-owned, ZEROED device scratch (ws_floats >= 2*N*C floats, cnt_words >= N*ceil(C/128) 32-bit words, for the largest
  * tensor) that lets the InstanceNorm reductions of p2p_instnorm_act_fwd / _bwd / p2p_instnorm_stats run as ONE launch each
  * (partial sums meet in ws, the last CTA finalises and re-zeroes it) instead of memset + reduction + finalise.  The calls

@@ -409,6 +409,48 @@ __global__ void __launch_bounds__(256) in_bwd_apply_v4_kernel(const TY* __restri
     }
 }
 
+// in_bwd_apply_v4_kernel writing dy straight into the layout the stride-1 gradient kernels read (ops._dy_wrap): a grid of
+// `rows` pixel rows at the pitch of the PADDED input, image n at row n*Hh*Wh, dy[n,h,w] at +h*Wh+w, zeros everywhere else.
+template <typename TY, typename T>
+__global__ void __launch_bounds__(256) in_bwd_apply_wrap_v4_kernel(const TY* __restrict__ y, const float* __restrict__ stats,
+                                                                   const T* __restrict__ dz, const float* __restrict__ work,
+                                                                   T* __restrict__ grid, int N, int H, int W, unsigned C4, int Hh, int Wh,
+                                                                   unsigned total4, float inv, int norm, int act, float slope) {
+    pdl_trigger();
+    pdl_wait();
+    const unsigned plane = (unsigned)(Hh * Wh);
+#pragma unroll 2
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
+        const unsigned c4 = i % C4, r = i / C4;
+        const unsigned n = r / plane, rem = r - n * plane;
+        const unsigned h = rem / (unsigned)Wh, w = rem - h * (unsigned)Wh;
+        float o[4] = {0.f, 0.f, 0.f, 0.f};
+        if (n < (unsigned)N && h < (unsigned)H && w < (unsigned)W) {
+            const long long src = ((((long long)n * H + h) * W + w) * C4 + c4) * 4;
+            float v[4], g[4];
+            ld4(y + src, v);
+            ld4(dz + src, g);
+            if (!norm) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) o[k] = g[k] * act_grad(v[k], act, slope);
+            } else {
+                const long long so = ((long long)n * C4 + c4) * 8;
+                const float4 s0 = __ldg(reinterpret_cast<const float4*>(stats + so)), s1 = __ldg(reinterpret_cast<const float4*>(stats + so) + 1);
+                const float4 w0 = __ldg(reinterpret_cast<const float4*>(work + so)), w1 = __ldg(reinterpret_cast<const float4*>(work + so) + 1);
+                const float mean[4] = {s0.x, s0.z, s1.x, s1.z}, rstd[4] = {s0.y, s0.w, s1.y, s1.w};
+                const float wa[4] = {w0.x, w0.z, w1.x, w1.z}, wb[4] = {w0.y, w0.w, w1.y, w1.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float xh = (v[k] - mean[k]) * rstd[k];
+                    const float gg = g[k] * act_grad(xh, act, slope);
+                    o[k] = rstd[k] * (gg - wa[k] * inv - xh * wb[k] * inv);
+                }
+            }
+        }
+        st4(grid + 4ll * i, o);
+    }
+}
+
 // adjoint of ReflectionPad2d, four channels per thread
 template <typename T>
 __global__ void __launch_bounds__(256) reflect_fold_v4_kernel(const T* __restrict__ dxp, T* __restrict__ dx, int H, int W, int C4,
@@ -850,6 +892,34 @@ extern "C" int p2p_instnorm_act_bwd(const void* y, const float* stats, const voi
             in_bwd_apply_kernel<TY, T><<<ew_grid(total), kEw, 0, st>>>((const TY*)y, stats, (const T*)dz, work, (T*)dy, HW, C, total, norm, act, slope);
     });
     return check_launch("instnorm_act_bwd");
+}
+
+// p2p_instnorm_act_bwd with dy written at the pitch of the padded input (see in_bwd_apply_wrap_v4_kernel): grid [rows, C],
+// rows >= N*Hh*Wh, Hh >= H, Wh >= W.  Vector shapes only (C % 4 == 0, 16-byte aligned pointers); P2P_ENOTSUP otherwise.
+extern "C" int p2p_instnorm_act_bwd_wrap(const void* y, const float* stats, const void* dz, void* grid, float* work, int N, int H,
+                                         int W, int C, int Hh, int Wh, long long rows, int norm, int act, float slope, int y_dtype,
+                                         int dtype, void* stream) {
+    if (N < 1 || H < 1 || W < 1 || C < 1 || Hh < H || Wh < W || rows < (long long)N * Hh * Wh) return fail(P2P_EINVAL, "bad size");
+    if (!y || !dz || !grid || (norm && (!stats || !work))) return fail(P2P_EINVAL, "null pointer argument");
+    const long long HW = (long long)H * W, total = rows * C;
+    if (N > 65535 || C % 4 != 0 || total / 4 >= 2000000000LL) return fail(P2P_ENOTSUP, "instnorm_act_bwd_wrap: shape not covered (C=%d)", C);
+    cudaStream_t st = (cudaStream_t)stream;
+    P2P_DISPATCH_DTYPE2(y_dtype, TY, dtype, T, {
+        if (!(vec4_ok(y, sizeof(TY)) && vec4_ok(dz, sizeof(T)) && vec4_ok(grid, sizeof(T)) && vec4_ok(stats, 4) && vec4_ok(work, 4)))
+            return fail(P2P_ENOTSUP, "instnorm_act_bwd_wrap: pointers must be 16-byte aligned");
+        const int cb = (C / 4 + 31) / 32, S = split_for(HW, cb * N);
+        const int chunk = (int)((HW + S - 1) / S);
+        if (norm && ws_fits(N, C)) {
+            launch_k(in_bwd_stats_fused_v4_kernel<TY, T>, dim3(cb, N, S), dim3(32, 8), 0, st, (const TY*)y, stats, (const T*)dz, work, g_stats_ws,
+                     g_stats_cnt, (int)HW, C, chunk, act, slope);
+        } else if (norm) {
+            if (cudaMemsetAsync(work, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
+            in_bwd_stats_v4_kernel<TY, T><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, (const T*)dz, work, (int)HW, C, chunk, act, slope);
+        }
+        launch_k(in_bwd_apply_wrap_v4_kernel<TY, T>, dim3((unsigned)(ew_grid(total / 4))), dim3(kEw), 0, st, (const TY*)y, stats, (const T*)dz,
+                 (const float*)work, (T*)grid, N, H, W, (unsigned)(C / 4), Hh, Wh, (unsigned)(total / 4), 1.f / (float)HW, norm, act, slope);
+    });
+    return check_launch("instnorm_act_bwd_wrap");
 }
 
 extern "C" int p2p_avgpool3s2_fwd(const void* x, void* y, int N, int H, int W, int C, int dtype, void* stream) {

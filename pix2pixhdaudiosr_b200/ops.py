@@ -385,23 +385,51 @@ def deterministic():
 _WRAP_BUFFERS = {}
 
 
-def _dy_wrap(dy, Hh, Wh, KH, KW):
-    """dy [N,OH,OW,J] laid out at the pitch of the padded input ([N,Hh,Wh] grid, dy at its top-left, zeros elsewhere) in a
-    buffer of P64 + rows64 + P64 rows whose first and last P64 >= (KH-1)*Wh + KW-1 rows are zero -> (key, buffer, P64)"""
-    N, OH, OW, J = dy.shape
+def _wrap_buffer(device, dtype, N, Hh, Wh, KH, KW, J):
+    """the shared gradient-grid buffer of one geometry: P64 zero rows | rows64(N*Hh*Wh) grid rows | P64 zero rows, P64 >=
+    (KH-1)*Wh + KW-1 -> (buffer, P64, rows)"""
     rows = _rows64(N * Hh * Wh)
     P64 = _rows64((KH - 1) * Wh + KW - 1)
-    key = (dy.device, dy.dtype, P64, rows, J)
+    key = (device, dtype, P64, rows, J)
     buf = _WRAP_BUFFERS.get(key)
     if buf is None or torch.cuda.is_current_stream_capturing() != _WRAP_BUFFERS.get(("capturing", key), False):
         # zero prefix | dy grid | zero suffix; the margins are written once, the grid (and its zero tail) by every call.
         # The buffer is reused by later calls of the same geometry: the two gradient passes that read it are enqueued on the
         # same stream before the next layer overwrites it.  (One buffer per capture state: a CUDA graph keeps its own.)
-        buf = torch.zeros((P64 + rows + P64, J), dtype=dy.dtype, device=dy.device)
+        buf = torch.zeros((P64 + rows + P64, J), dtype=dtype, device=device)
         _WRAP_BUFFERS[key] = buf
         _WRAP_BUFFERS[("capturing", key)] = torch.cuda.is_current_stream_capturing()
+    return buf, P64, rows
+
+
+def _dy_wrap(dy, Hh, Wh, KH, KW):
+    """dy [N,OH,OW,J] laid out at the pitch of the padded input ([N,Hh,Wh] grid, dy at its top-left, zeros elsewhere) in a
+    buffer of P64 + rows64 + P64 rows whose first and last P64 >= (KH-1)*Wh + KW-1 rows are zero -> (key, buffer, P64)"""
+    N, OH, OW, J = dy.shape
+    buf, P64, rows = _wrap_buffer(dy.device, dy.dtype, N, Hh, Wh, KH, KW, J)
     _lib.check(_lib.lib().p2p_pad_planes(_p(dy), _p(buf[P64:]), N, OH, OW, J, 0, 0, Hh, Wh, 1, rows, 0, _DT[dy.dtype], _stream()))
     return (Hh, Wh, rows, J), buf, P64
+
+
+def _dy_wrap_plan(x, weight, cfg, need_dx, need_dw, need_db):
+    """(Hh, Wh, KH, KW, Cout) when _conv_backward will take its shared-dy branch for this layer call (stride-1 window input
+    gradient + window weight gradient from ONE copy of dy at the padded input's pitch), else None.  The producer of dy
+    (norm_act_backward_wrap) then writes that copy itself."""
+    if not (FUSE_BWD_WRAP and need_dx and need_dw) or need_db or cfg.transposed or cfg.stride != 1 or not USE_WINDOW:
+        return None
+    if x.dtype != torch.bfloat16:
+        return None
+    _, Cout, Cin, KH, KW = _phys(weight, cfg)
+    if _colable(x, cfg, Cin, Cout, KH, KW) is not None or _packable(x, cfg, Cin, Cout, KH, KW) is not None:
+        return None
+    if _thin(x, Cin, Cout) is not None or Cout % 4 != 0:
+        return None
+    N, H, W, _ = x.shape
+    p = cfg.pad
+    q = (KH - 1) if cfg.pad_mode == PAD_REFLECT else (KH - 1 - p)
+    if not (KH == KW and q >= 0 and p > 0 and _window_ok(x.dtype, Cout, Cin, KH, KW, H + 2 * p, W + 2 * p, True)):
+        return None
+    return H + 2 * p, W + 2 * p, KH, KW, Cout
 
 
 def _dgrad_wrap(dy_shared, wq, dtype, N, H, W, p, KH, KW, Cout, Cin, reflect):
@@ -483,6 +511,7 @@ def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None, fresh=False, dy_sh
         aplanes = dy_shared[1][dy_shared[2]: dy_shared[2] + rows]       # the copy the input-gradient pass already made
     else:
         aplanes = torch.empty((s_out * s_out, rows, J), dtype=dy.dtype, device=dy.device)
+        dy = dy.contiguous()
         _lib.check(lib.p2p_pad_planes(_p(dy), _p(aplanes), N, dy.shape[1], dy.shape[2], J, 0, 0, Hh, Wh, s_out, rows, 0, _DT[dy.dtype], _stream()))
     IntArr = ctypes.c_int * len(taps)
     ta, tb, th, tw, twt = (IntArr(*[q[i] for q in taps]) for i in range(5))
@@ -879,13 +908,15 @@ def _conv_forward(x, weight, bias, w16, cfg, out_dtype, aux=None, xin=None, stat
     return y, False
 
 
-def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None, xpad=None):
+def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None, xpad=None, dy_pre=None):
     """gradients of conv_forward; dy has x's dtype.  Returns (dx, dw_logical, db).  With `gphys` (FusedAdam's view of
     this weight's slice of the flat gradient buffer, physical layout) the wgrad kernels accumulate straight into it
     and dw comes back None -- no zero-fill, no AccumulateGrad add."""
     N, H, W, _ = x.shape
     wphys, Cout, Cin, KH, KW = _phys(weight, cfg)
-    assert dy.dtype == x.dtype and dy.is_contiguous()
+    assert dy.dtype == x.dtype and (dy.is_contiguous() or dy_pre is not None)
+    if dy_pre is not None and _dy_wrap_plan(x, weight, cfg, need_dx, need_dw, need_db) is None:
+        raise RuntimeError("a pre-wrapped output gradient was passed to a layer that does not take the shared-dy path")
     dx = dw = db = None
     dy_shared = None
     if need_db:
@@ -931,7 +962,7 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
                     and _window_ok(x.dtype, Cout, Cin, KH, KW, H + 2 * p, W + 2 * p, True)):
                 # ONE copy of dy serves both gradients: dy at the pitch of the padded input (what the wgrad kernel wants)
                 # behind a zero prefix; the flipped-tap window reads wrap into the zero margins of the previous row / image
-                dy_shared = _dy_wrap(dy, H + 2 * p, W + 2 * p, KH, KW)
+                dy_shared = dy_pre if dy_pre is not None else _dy_wrap(dy, H + 2 * p, W + 2 * p, KH, KW)
                 buf = _dgrad_wrap(dy_shared, wq, x.dtype, N, H, W, p, KH, KW, Cout, Cin, cfg.pad_mode == PAD_REFLECT)
                 passes = []
             elif (cfg.stride == 1 and KH == KW and q >= 0
@@ -964,7 +995,7 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
         else:
             wpasses = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
         if not _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None, fresh, dy_shared):
-            x = x.contiguous()
+            x, dy = x.contiguous(), dy.contiguous()
             for P in wpasses:
                 _run_wgrad(P, x, dy, dwp)
         if direct:
@@ -1007,13 +1038,13 @@ def conv_forward(x, weight, bias, w16, cfg, out_dtype, aux=None, xin=None, stats
     return (y, took) if stats is not None else y
 
 
-def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None, xpad=None):
+def conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=None, xpad=None, dy_pre=None):
     global _FLOP_RATIO
     if _TIMING is None:
-        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys, xpad)
+        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys, xpad, dy_pre)
     _FLOP_RATIO = _alg_ratio(x, weight, cfg)
     try:
-        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys, xpad)
+        return _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys, xpad, dy_pre)
     finally:
         _FLOP_RATIO = 1.0
 
@@ -1108,6 +1139,25 @@ def norm_act_backward(y, stats, dz, norm, act, slope):
     _lib.check(_lib.lib().p2p_instnorm_act_bwd(_p(y), _p(stats), _p(dz), _p(dy), _p(work), N, H * W, C, int(norm), act,
                                                slope, _DT[y.dtype], _DT[dz.dtype], _stream()))
     return dy
+
+
+# The InstanceNorm backward writes dy directly as the zero-margined grid the stride-1 gradient kernels of the convolution in
+# front of it read (p2p_instnorm_act_bwd_wrap): one pass less over dy per 3x3 / 4x4 stride-1 layer.  P2P_FUSE_BWD_WRAP=0: off.
+FUSE_BWD_WRAP = os.environ.get("P2P_FUSE_BWD_WRAP", "1") == "1"
+
+
+def norm_act_backward_wrap(y, stats, dz, norm, act, slope, plan):
+    """norm_act_backward whose result lands in the shared gradient grid of `plan` (_dy_wrap_plan) -> (strided view of dy
+    inside the grid, the dy_shared triple _conv_backward takes as dy_pre)"""
+    N, H, W, C = y.shape
+    Hh, Wh, KH, KW, _ = plan
+    _ensure_stats_workspace(y.device)
+    buf, P64, rows = _wrap_buffer(y.device, dz.dtype, N, Hh, Wh, KH, KW, C)
+    work = torch.empty((N, C, 2), dtype=torch.float32, device=y.device) if norm else None
+    _lib.check(_lib.lib().p2p_instnorm_act_bwd_wrap(_p(y), _p(stats), _p(dz), _p(buf[P64:]), _p(work), N, H, W, C, Hh, Wh, rows,
+                                                    int(norm), act, slope, _DT[y.dtype], _DT[dz.dtype], _stream()))
+    view = buf[P64:P64 + N * Hh * Wh].view(N, Hh, Wh, C)[:, :H, :W, :]
+    return view, ((Hh, Wh, rows, C), buf, P64)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -1230,14 +1280,21 @@ class ConvBlockFn(torch.autograd.Function):
         x, weight, w16, y, stats = ctx.saved_tensors
         cfg, norm, act, slope, has_bias, has_res, plain = ctx.cfg
         dz = dz.contiguous()
-        dy = dz if plain else norm_act_backward(y, stats, dz, norm, act, slope)
         # a bias in front of InstanceNorm2d(affine=False) has an exactly zero gradient (the mean subtraction removes it; the
         # reference's autograd returns rounding noise of ~1e-7 relative size): not computed unless P2P_NORM_BIAS_GRAD=1
         active = _owner_active(ctx.gphys)       # this layer's parameters take gradients in the running backward phase
         need_db = has_bias and ctx.needs_input_grad[2] and (not norm or NORM_BIAS_GRAD) and active
         need_dx = ctx.needs_input_grad[0] and not (ctx.gated and not GATE_OPEN)
-        dx, dw, db = conv_backward(x, weight, w16, dy, cfg, need_dx, ctx.needs_input_grad[1] and active,
-                                   need_db, ctx.gphys, ctx.xpad)
+        need_dw = ctx.needs_input_grad[1] and active
+        dy_pre = None
+        plan = None if plain or y.shape[0] >= 65535 else _dy_wrap_plan(x, weight, cfg, need_dx, need_dw, need_db)
+        if plain:
+            dy = dz
+        elif plan is not None:
+            dy, dy_pre = norm_act_backward_wrap(y, stats, dz, norm, act, slope, plan)
+        else:
+            dy = norm_act_backward(y, stats, dz, norm, act, slope)
+        dx, dw, db = conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, ctx.gphys, ctx.xpad, dy_pre)
         if has_bias and ctx.needs_input_grad[2] and not need_db and ctx.gphys is None and active:
             db = torch.zeros(ctx.bias_n, dtype=torch.float32, device=x.device)    # no flat gradient buffer behind .grad: give autograd the zero
         return dx, dw, db, None, (dz if has_res else None), None, None, None, None, None, None, None, None, None, None
