@@ -415,7 +415,7 @@ def _dy_wrap_plan(x, weight, cfg, need_dx, need_dw, need_db):
     """(Hh, Wh, KH, KW, Cout) when _conv_backward will take its shared-dy branch for this layer call (stride-1 window input
     gradient + window weight gradient from ONE copy of dy at the padded input's pitch), else None.  The producer of dy
     (norm_act_backward_wrap) then writes that copy itself."""
-    if not (FUSE_BWD_WRAP and need_dx and need_dw) or need_db or cfg.transposed or cfg.stride != 1 or not USE_WINDOW:
+    if not (FUSE_BWD_WRAP and need_dx) or need_db or cfg.transposed or cfg.stride != 1 or not USE_WINDOW:
         return None
     if x.dtype != torch.bfloat16:
         return None
@@ -461,7 +461,7 @@ def _dgrad_wrap(dy_shared, wq, dtype, N, H, W, p, KH, KW, Cout, Cin, reflect):
     return out if out.dtype == dtype else out.to(dtype)
 
 
-def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None, fresh=False, dy_shared=None):
+def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None, fresh=False, dy_shared=None, dy_planes=None):
     """weight gradient of a layer call (its forward-type passes) as ONE launch of the window wgrad kernel:
     dW_t = sum over the padded grid of dout (laid out at the input's pitch) x shifted input window.  False if it does not fit."""
     if not USE_WINDOW or not passes or x.dtype != torch.bfloat16 or _lib.lib().p2p_conv_force_simple(-1) == 1:
@@ -509,6 +509,8 @@ def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None, fresh=False, dy_sh
         _lib.check(lib.p2p_pad_planes(_p(x), _p(bplanes), N, H, W, C, pt, pl, Hh, Wh, s_in, rows, int(reflect), _DT[x.dtype], _stream()))
     if dy_shared is not None and s_out == 1 and dy_shared[0] == (Hh, Wh, rows, J):
         aplanes = dy_shared[1][dy_shared[2]: dy_shared[2] + rows]       # the copy the input-gradient pass already made
+    elif dy_planes is not None and dy_planes[0] == (0, 0, Hh, Wh, rows, False, s_out, J):
+        aplanes = dy_planes[1]              # stride-2 layers: the planes the input-gradient window pass padded dy into
     else:
         aplanes = torch.empty((s_out * s_out, rows, J), dtype=dy.dtype, device=dy.device)
         dy = dy.contiguous()
@@ -919,6 +921,7 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
         raise RuntimeError("a pre-wrapped output gradient was passed to a layer that does not take the shared-dy path")
     dx = dw = db = None
     dy_shared = None
+    dy_aux = []             # (key, planes) of dy as the input-gradient window pass laid it out: reused by the weight gradient
     if need_db:
         db = _bias_grad(dy, Cout)
     col = _colable(x, cfg, Cin, Cout, KH, KW)
@@ -958,7 +961,7 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
             q = (KH - 1) if cfg.pad_mode == PAD_REFLECT else (KH - 1 - cfg.pad)      # zero margin around dy
             OHd, OWd = dy.shape[1], dy.shape[2]
             p = cfg.pad
-            if (cfg.stride == 1 and KH == KW and q >= 0 and p > 0 and need_dw and thin is None and USE_WINDOW
+            if (cfg.stride == 1 and KH == KW and q >= 0 and p > 0 and thin is None and USE_WINDOW
                     and _window_ok(x.dtype, Cout, Cin, KH, KW, H + 2 * p, W + 2 * p, True)):
                 # ONE copy of dy serves both gradients: dy at the pitch of the padded input (what the wgrad kernel wants)
                 # behind a zero prefix; the flipped-tap window reads wrap into the zero margins of the previous row / image
@@ -975,7 +978,7 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
                 if passes is None:
                     raise NotImplementedError("input gradient of a convolution whose stride skips whole parity classes")
                 buf = torch.empty((N, DH, DW, Cin), dtype=x.dtype, device=x.device)
-                if _window_passes(passes, dy, wq, None, buf, KH * KW, "dgrad"):
+                if _window_passes(passes, dy, wq, None, buf, KH * KW, "dgrad", dy_aux):
                     passes = []
             for P in passes:
                 _run_pass(P, dy, wq, None, buf, "dgrad")
@@ -994,7 +997,8 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
             wpasses = convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0]
         else:
             wpasses = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
-        if not _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None, fresh, dy_shared):
+        if not _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None, fresh, dy_shared,
+                             dy_aux[0] if dy_aux else None):
             x, dy = x.contiguous(), dy.contiguous()
             for P in wpasses:
                 _run_wgrad(P, x, dy, dwp)
