@@ -159,7 +159,10 @@ int p2p_pad_planes(const void* x, void* planes, int N, int H, int W, int C, int 
  * over the padded pixel grid: aplanes = the output gradient laid out at the pitch of the padded input (zero where no output
  * exists), bplanes = the padded input (or its parity planes).  plane_rows % 64 == 0; taps grouped by (tap_a, tap_b); <= 32 taps.
  * dw_is_zero != 0 promises that dW holds zeros (first gradient after zero_grad): tiles with a single writer are then stored
- * instead of red.add-ed. */
+ * instead of red.add-ed.  dw_is_zero == 2: dW holds STALE values and must be overwritten (the caller skipped its memset,
+ * optimizer.zero_grad of train.py:164-184): one writer per tile is forced.  p2p_conv_wgrad_window_stored() tells whether the
+ * calling thread's last call stored (1) or accumulated (0). */
+int p2p_conv_wgrad_window_stored(void);
 int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const void* bplanes, int n_bplanes, long long plane_rows, int Wp,
                           int J, int C, float* dw, int wtaps_total, int ntaps, const int* tap_a, const int* tap_b,
                           const int* tap_dh, const int* tap_dw, const int* tap_w, int dw_is_zero, void* stream);

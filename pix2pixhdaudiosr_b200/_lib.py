@@ -54,6 +54,7 @@ _SIGS.update({
     "p2p_conv_window": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _vp]),
     "p2p_pad_planes": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _ll, _i, _i, _vp]),
     "p2p_conv_wgrad_window": (_i, [_vp, _i, _vp, _i, _ll, _i, _i, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
+    "p2p_conv_wgrad_window_stored": (_i, []),
     "p2p_conv_window_debug_buffer": (_i, [_vp]),
     "p2p_conv_window_run": (_i, [_c.POINTER(WindowDesc), _vp, _vp, _vp, _vp, _i, _vp]),
     "p2p_conv_window_stats": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _ll, _ll, _ll, _i, _vp, _vp]),

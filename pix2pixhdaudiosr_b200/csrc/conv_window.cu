@@ -1585,6 +1585,10 @@ extern "C" int p2p_conv_window_stats(const void* xp, const void* weight, const f
 //   aplanes[tap_a[t]][q][j] * bplanes[tap_b[t]][q + tap_dh[t]*Wp + tap_dw[t]][c];
 // planes are [plane_rows][channels] bf16 with plane_rows a multiple of 64 (p2p_pad_planes zero-fills the tail);
 // taps must be grouped by (tap_a, tap_b).  ntaps * BN <= 512 TMEM columns: ntaps <= 32.
+static thread_local int g_last_wgrad_stored = 0;
+// 1 when this thread's last p2p_conv_wgrad_window call STORED dW (one writer per tile), 0 when it accumulated with red.add
+extern "C" int p2p_conv_wgrad_window_stored(void) { return g_last_wgrad_stored; }
+
 extern "C" int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const void* bplanes, int n_bplanes, long long plane_rows,
                                      int Wp, int J, int C, float* dw, int wtaps_total, int ntaps, const int* tap_a,
                                      const int* tap_b, const int* tap_dh, const int* tap_dw, const int* tap_w, int dw_is_zero,
@@ -1669,11 +1673,12 @@ extern "C" int p2p_conv_wgrad_window(const void* aplanes, int n_aplanes, const v
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int nsplit = (int)(sms / items);                       // at most one wave: every extra split is another pass of atomics over dW
     if (nsplit > a.total_kb / 2) nsplit = a.total_kb / 2;
-    if (nsplit < 1 || deterministic()) nsplit = 1;
+    if (nsplit < 1 || deterministic() || dw_is_zero == 2) nsplit = 1;     // 2: dW holds stale values and MUST be overwritten
     a.kb_per_split = (a.total_kb + nsplit - 1) / nsplit;
     a.nsplit = (a.total_kb + a.kb_per_split - 1) / a.kb_per_split;
     a.fast_epi = C % 4 == 0 && (((uintptr_t)dw) & 15) == 0;
     a.atomic = !(dw_is_zero && a.nsplit == 1);    // dW += with red.add unless the buffer is known zero and the tile has one writer
+    g_last_wgrad_stored = a.atomic ? 0 : 1;
     a.nwork = items * a.nsplit;
     if (int rc = encode_2d(&a.tm_a, aplanes, (unsigned long long)J, (unsigned long long)n_aplanes * plane_rows, 64, 64)) return rc;
     if (int rc = encode_2d(&a.tm_b, bplanes, (unsigned long long)C, (unsigned long long)n_bplanes * plane_rows, 64, (unsigned)a.b_rows_per_box)) return rc;

@@ -997,8 +997,15 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
             wpasses = convT_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.out_pad)[0]
         else:
             wpasses = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
-        if not _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None, fresh, dy_shared,
-                             dy_aux[0] if dy_aux else None):
+        # 2: zero_grad left this slice alone (FusedAdam lazy zeroing), the kernel must overwrite it
+        must_store = direct and fresh and gphys.unzeroed_epoch == gphys.owner.grad_epoch
+        if _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None, 2 if must_store else fresh, dy_shared,
+                         dy_aux[0] if dy_aux else None):
+            if direct and fresh and _lib.lib().p2p_conv_wgrad_window_stored() == 1:
+                gphys.stored_epoch = gphys.owner.grad_epoch
+        else:
+            if must_store:
+                dwp.zero_()                 # zero_grad skipped this slice expecting a store: the fallback kernels accumulate
             x, dy = x.contiguous(), dy.contiguous()
             for P in wpasses:
                 _run_wgrad(P, x, dy, dwp)
@@ -1176,6 +1183,8 @@ class GradSink:
 
     def __init__(self, view, owner, offset=0):
         self.view, self.owner, self.epoch, self.offset = view, owner, -1, offset
+        self.stored_epoch = -1      # epoch whose first write was a STORE by the window wgrad kernel (FusedAdam.zero_grad)
+        self.unzeroed_epoch = -1    # epoch for which zero_grad left this slice alone
 
     def first_write(self):
         fresh = self.epoch != self.owner.grad_epoch

@@ -5,9 +5,17 @@ All parameters handed to the optimiser are re-homed into ONE fp32 master buffer 
 tap-major layout), with matching flat gradient / moment buffers and a flat bf16 shadow that the tcgen05 kernels
 read.  `step()` is a single `p2p_adam_step` launch that also refreshes the bf16 shadow; `zero_grad()` is one
 memset; the data-parallel gradient exchange is one all-reduce of `flat_grad` (train.py of this package)."""
+import os
+
 import torch
 
 from . import ops
+
+# zero_grad() skips the slices of the flat gradient buffer that the weight-gradient kernels STORE into (first write of an
+# epoch, ops.GradSink) when they are large: on G3L2-ngf48 the six 1536x1536x3x3 bottleneck weights are 127 M of the 156 M
+# gradient words, a 0.5 GB memset per step.  P2P_LAZY_ZERO_GRAD=0 restores the single full memset.
+LAZY_ZERO_GRAD = os.environ.get("P2P_LAZY_ZERO_GRAD", "1") == "1"
+_LAZY_MIN = 1 << 20      # elements: smaller slices are not worth a separate memset range
 
 _ALIGN = 8      # elements: keeps every bf16 slice 16-byte aligned for the vector / tensor-core loads
 _SHARD_ALIGN = 128   # the flat buffers are a multiple of this: equal, 16-byte aligned shards for up to 16 data-parallel ranks
@@ -40,6 +48,9 @@ class FusedAdam:
         self._scratch = torch.zeros(2, dtype=torch.float32, device=dev)
         self.grad_scale = 1.0                                              # 1 / world size under data parallelism
         self._views = []
+        self._sinks = []
+        self._skipped = []                                                 # sinks left un-zeroed by the last zero_grad
+        self._seg_key, self._segs = None, None
         o = 0
         for p, sz in zip(params, sizes):
             n = p.numel()
@@ -54,6 +65,7 @@ class FusedAdam:
                 gview = self.flat_grad[o:o + n].view(phys.shape).permute(*inv)
                 conv.w16 = self.flat_bf16[o:o + n].view(phys.shape)
                 conv.gphys = ops.GradSink(self.flat_grad[o:o + n].view(phys.shape), self, o)   # wgrad kernels write here directly
+                self._sinks.append(conv.gphys)
             else:
                 self.flat[o:o + n].copy_(p.data.reshape(-1))
                 p.data = self.flat[o:o + n].view(p.shape)
@@ -64,8 +76,30 @@ class FusedAdam:
         self.flat_bf16.copy_(self.flat)
 
     def zero_grad(self, set_to_none=False):
-        self.flat_grad.zero_()
+        # slices whose first write of the epoch that just ended was a STORE by the window weight-gradient kernel are left
+        # alone (the same layer call stores again); ops._conv_backward zeroes such a slice itself if it ever has to
+        # accumulate into it, and step() zeroes the ones that received no gradient at all
+        skip = [k for k in self._sinks if k.stored_epoch == self.grad_epoch and k.view.numel() >= _LAZY_MIN] \
+            if LAZY_ZERO_GRAD and self.grad_epoch > 0 else []
+        if not skip:
+            self.flat_grad.zero_()
+        else:
+            key = tuple(k.offset for k in skip)
+            if key != self._seg_key:
+                segs, lo = [], 0
+                for k in sorted(skip, key=lambda q: q.offset):
+                    if k.offset > lo:
+                        segs.append((lo, k.offset))
+                    lo = k.offset + k.view.numel()
+                if lo < self.flat_grad.numel():
+                    segs.append((lo, self.flat_grad.numel()))
+                self._seg_key, self._segs = key, segs
+            for lo, hi in self._segs:
+                self.flat_grad[lo:hi].zero_()
+        self._skipped = skip
         self.grad_epoch += 1
+        for k in skip:
+            k.unzeroed_epoch = self.grad_epoch
         for p, g in self._views:
             if p.grad is not g:
                 p.grad = g
@@ -82,6 +116,10 @@ class FusedAdam:
         g = self.param_groups[0]
         if not torch.cuda.is_current_stream_capturing():
             self.sync_lr()
+        for k in self._skipped:                 # left un-zeroed and not written this epoch: its gradient is zero, not last step's
+            if k.epoch != self.grad_epoch:
+                k.view.zero_()
+        self._skipped = []
         self.step_count += 1
         if self.shard is not None:
             # sharded data parallelism (train.GradSync(shard=True)): this rank owns 1/world of the flat buffers -- its

@@ -194,3 +194,36 @@ def test_shared_fake_pass_equals_three_pass_step(ref, precision):
         _lib.lib().p2p_set_deterministic(old)
     for a, b, what in zip(out[True], out[False], ("losses", "G gradients", "D gradients", "G weights", "D weights")):
         assert torch.equal(a, b), (precision, what, float((a.double() - b.double()).abs().max()))
+
+
+def test_lazy_zero_grad_equals_full_memset(ref):
+    """FusedAdam.zero_grad leaves alone the slices that the window weight-gradient kernel overwrites (first write of an epoch is
+    a store): three optimisation steps give bit-identical gradients and weights with and without it (deterministic mode; the
+    size threshold is lowered so that the miniature network's slices qualify)"""
+    from pix2pixhdaudiosr_b200 import _lib, optim
+    old = _lib.lib().p2p_set_deterministic(1)
+    lazy0, min0 = optim.LAZY_ZERO_GRAD, optim._LAZY_MIN
+    out, skipped = {}, 0
+    try:
+        for lazy in (True, False):
+            optim.LAZY_ZERO_GRAD, optim._LAZY_MIN = lazy, 1
+            torch.manual_seed(99)
+            model = create_model(tiny_opt(precision="bf16", mask=True, mask_mode='mode2'))
+            _load(model, ref)
+            snaps = []
+            for it in range(3):
+                lr, hr = batch(it % 2)
+                train_step(model, lr.cuda(), hr.cuda())
+                torch.cuda.synchronize()
+                snaps += [model.optimizer_G.flat_grad.clone(), model.optimizer_D.flat_grad.clone(), model.optimizer_G.flat.clone(),
+                          model.optimizer_D.flat.clone()]
+            if lazy:
+                skipped = len(model.optimizer_G._seg_key or ()) + len(model.optimizer_D._seg_key or ())
+            out[lazy] = snaps
+            del model
+    finally:
+        optim.LAZY_ZERO_GRAD, optim._LAZY_MIN = lazy0, min0
+        _lib.lib().p2p_set_deterministic(old)
+    assert skipped > 0, "no gradient slice was left to the store path: the test does not exercise lazy zeroing"
+    for i, (a, b) in enumerate(zip(out[True], out[False])):
+        assert torch.equal(a, b), (i, float((a.double() - b.double()).abs().max()))
