@@ -203,6 +203,10 @@ int p2p_pack_in(const void* x, void* xpk, int N, int H, int W, int C, int KW, in
                 int dtype, void* stream);
 int p2p_fold_out(const float* ypk, const float* bias, void* y, int N, int OH, int Wp, int OW, int KW, int Cout, int out_dtype,
                  void* stream);
+/* the same with the kernel ROWS packed into the channels (taps shift along a pixel row, so the shifted-window kernel runs it):
+ *   fold_out_rows: y[n, oh, ow, co] = bias[co] + sum_dh ypk[n, oh + dh, ow, dh*Cout + co]   ypk: fp32 [N][Hp][Wy][16], KH*Cout <= 16 */
+int p2p_fold_out_rows(const float* ypk, const float* bias, void* y, int N, int Hp, int Wy, int OH, int OW, int KH, int Cout,
+                      int out_dtype, void* stream);
 int p2p_pack_dy(const void* dy, void* dypk, int N, int OH, int OW, int Cout, int KW, int Wp, int dtype, void* stream);
 /* Full-patch forms (bf16 only; KH*KW*C <= Kc <= 128, Kc % 8 == 0): the thin side's whole patch becomes one channel vector,
  * so the layer is a 1x1 convolution for the window kernels.  Buffers have rows_alloc rows (a multiple of 64 for the

@@ -64,6 +64,7 @@ _SIGS.update({
     "p2p_reflect_pad_fold": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_pack_in": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_fold_out": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "p2p_fold_out_rows": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_pack_dy": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_im2col": (_i, [_vp, _vp] + [_i] * 12 + [_ll, _vp]),
     "p2p_col2im": (_i, [_vp, _vp] + [_i] * 11 + [_vp]),

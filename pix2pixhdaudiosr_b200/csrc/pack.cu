@@ -62,6 +62,26 @@ __global__ void __launch_bounds__(256) fold_out_kernel(const float* __restrict__
     }
 }
 
+// row-packed form: y[n, oh, ow, co] = bias[co] + sum_dh ypk[n, oh + dh, ow, dh*Cout + co]     ypk: fp32 [N][Hp][Wy][16]
+template <typename T>
+__global__ void __launch_bounds__(256) fold_rows_kernel(const float* __restrict__ ypk, const float* __restrict__ bias, T* __restrict__ y,
+                                                        int Hp, int Wy, int OH, int OW, int KH, int Cout, unsigned total) {
+    pdl_trigger();
+    pdl_wait();
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int co = (int)(i % Cout);
+        unsigned r = i / Cout;
+        const int ow = (int)(r % OW);
+        r /= OW;
+        const int oh = (int)(r % OH);
+        const unsigned n = r / OH;
+        const float* src = ypk + (((long long)n * Hp + oh) * Wy + ow) * 16 + co;
+        float s = bias ? bias[co] : 0.f;
+        for (int dh = 0; dh < KH; ++dh) s += src[(long long)dh * Wy * 16 + dh * Cout];
+        stf(y + i, s);
+    }
+}
+
 // dypk[n, y, x', dw*Cout + co] = dy[n, y, x' - dw, co] (zero outside), 16 channels per pixel
 template <typename T>
 __global__ void __launch_bounds__(256) pack_dy_kernel(const T* __restrict__ dy, T* __restrict__ dypk, int OW, int Cout, int KW, int Wp,
@@ -225,6 +245,18 @@ extern "C" int p2p_fold_out(const float* ypk, const float* bias, void* y, int N,
     P2P_DISPATCH_DTYPE(out_dtype, T, launch_k(fold_out_kernel<T>, dim3((unsigned)(grid_for(total))), dim3(256), 0, (cudaStream_t)stream, 
         ypk, bias, (T*)y, OH, Wp, OW, KW, Cout, (unsigned)total));
     return check_launch("fold_out");
+}
+
+extern "C" int p2p_fold_out_rows(const float* ypk, const float* bias, void* y, int N, int Hp, int Wy, int OH, int OW, int KH, int Cout,
+                                 int out_dtype, void* stream) {
+    if (!ypk || !y) return fail(P2P_EINVAL, "null pointer argument");
+    if (N < 1 || OH < 1 || OW < 1 || KH < 1 || Cout < 1 || KH * Cout > 16 || Wy < OW || Hp < OH + KH - 1)
+        return fail(P2P_EINVAL, "bad packing geometry (KH*Cout must be <= 16)");
+    const long long total = (long long)N * OH * OW * Cout;
+    if (total > 4000000000LL) return fail(P2P_ENOTSUP, "tensor too large");
+    P2P_DISPATCH_DTYPE(out_dtype, T, launch_k(fold_rows_kernel<T>, dim3((unsigned)(grid_for(total))), dim3(256), 0, (cudaStream_t)stream,
+        ypk, bias, (T*)y, Hp, Wy, OH, OW, KH, Cout, (unsigned)total));
+    return check_launch("fold_out_rows");
 }
 
 extern "C" int p2p_pack_dy(const void* dy, void* dypk, int N, int OH, int OW, int Cout, int KW, int Wp, int dtype, void* stream) {

@@ -621,6 +621,9 @@ def _pack_dy(dy, KW, Cout, Wp):
     return out
 
 
+ROW_PACKED = os.environ.get("P2P_ROW_PACKED", "1") == "1"
+
+
 def _packed_forward(kind, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux=None, xin=None):
     if kind == "in":
         xpk, wpk, P, (OH, OW) = _packed_in_operands(x, wq, cfg, Cin, Cout, KH, KW)
@@ -638,6 +641,16 @@ def _packed_forward(kind, x, wq, bias, cfg, Cin, Cout, KH, KW, out_dtype, aux=No
             _pad_hw(x, cfg.pad, cfg.pad_mode == PAD_REFLECT)
     if aux is not None:
         aux.append(("packed_out", xp))
+    if (ROW_PACKED and KH * Cout <= 16 and (Cin * x.element_size()) % 16 == 0
+            and _window_ok(x.dtype, Cin, 16, 1, KW, Hp, Wp, False)):
+        # kernel ROWS packed into the 16 output channels instead of its columns: the KW taps then shift along a pixel row
+        # (halo KW-1 rows instead of (KH-1)*Wp), which the TMA-fed window kernel runs; the gather-form kernel below took
+        # 168 us for G's last 7x7 layer (29 TFLOP/s)
+        wr = _pad_rows(wq.permute(1, 0, 2, 3).reshape(KW, KH * Cout, Cin), 16)
+        yr = conv_window(xp, wr, None, torch.float32, 1, KW, 16, False, 16 * Cin, 1, Cin, "fwd", (N, Hp, Wp, Cin))
+        y = torch.empty((N, OH, OW, Cout), dtype=out_dtype, device=x.device)
+        _lib.check(_lib.lib().p2p_fold_out_rows(_p(yr), _p(bias), _p(y), N, Hp, OW, OH, OW, KH, Cout, _DT[out_dtype], _stream()))
+        return y
     ypk = torch.empty((N, OH, Wp, 16), dtype=torch.float32, device=x.device)
     _run_pass(P, xp, _pack_out_weight(wq, KH, KW, Cout, Cin), None, ypk)
     y = torch.empty((N, OH, OW, Cout), dtype=out_dtype, device=x.device)
