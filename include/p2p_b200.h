@@ -193,6 +193,8 @@ int p2p_instnorm_act_planes(const void* y, const float* bias, const float* stats
 /* Adjoint of reflection padding: dx[n,h,w,c] = sum of dxp over the padded positions that mirror onto (h,w).
  * dxp is [N, H+2p, W+2p, C], dx is [N,H,W,C]. */
 int p2p_reflect_pad_fold(const void* dxp, void* dx, int N, int H, int W, int C, int p, int dtype, void* stream);
+/* the same reading an fp32 padded gradient (what the split-K input-gradient pass accumulates) and writing `dtype` */
+int p2p_reflect_pad_fold_f32(const float* dxp, void* dx, int N, int H, int W, int C, int p, int dtype, void* stream);
 
 /* Operand packing for the thin layers (networks.py:145-154 G's 7x7 2->ngf / ngf->2 convolutions, :340-361 D's 4->ndf and
  * ->1 logit convolutions): KW*C <= 16 kernel-column x channel pairs become the 16 tensor-core channels of a KHx1 convolution.

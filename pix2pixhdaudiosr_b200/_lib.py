@@ -62,6 +62,7 @@ _SIGS.update({
     "p2p_instnorm_act_planes": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _ll, _ll, _ll, _vp, _vp] + [_i] * 9 + [_ll, _i, _i, _i, _f, _f, _i, _vp]),
     "p2p_bias_grad": (_i, [_vp, _vp, _ll, _i, _i, _vp]),
     "p2p_reflect_pad_fold": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "p2p_reflect_pad_fold_f32": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_pack_in": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_fold_out": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "p2p_fold_out_rows": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),

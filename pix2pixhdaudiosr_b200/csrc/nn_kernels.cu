@@ -452,8 +452,8 @@ __global__ void __launch_bounds__(256) in_bwd_apply_wrap_v4_kernel(const TY* __r
 }
 
 // adjoint of ReflectionPad2d, four channels per thread
-template <typename T>
-__global__ void __launch_bounds__(256) reflect_fold_v4_kernel(const T* __restrict__ dxp, T* __restrict__ dx, int H, int W, int C4,
+template <typename TI, typename T>
+__global__ void __launch_bounds__(256) reflect_fold_v4_kernel(const TI* __restrict__ dxp, T* __restrict__ dx, int H, int W, int C4,
                                                               int p, unsigned total4) {
     pdl_trigger();
     pdl_wait();
@@ -545,8 +545,8 @@ __global__ void tanh_bwd_kernel(const T* __restrict__ y, const T* __restrict__ d
     }
 }
 
-template <typename T>
-__global__ void reflect_fold_kernel(const T* __restrict__ dxp, T* __restrict__ dx, int H, int W, int C, int p,
+template <typename TI, typename T>
+__global__ void reflect_fold_kernel(const TI* __restrict__ dxp, T* __restrict__ dx, int H, int W, int C, int p,
                                     long long total) {
     const int HP = H + 2 * p, WP = W + 2 * p;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -961,11 +961,28 @@ extern "C" int p2p_reflect_pad_fold(const void* dxp, void* dx, int N, int H, int
     const bool v4 = C % 4 == 0 && total / 4 < 2000000000LL;
     P2P_DISPATCH_DTYPE(dtype, T, {
         if (v4 && vec4_ok(dxp, sizeof(T)) && vec4_ok(dx, sizeof(T)))
-            launch_k(reflect_fold_v4_kernel<T>, dim3((unsigned)(ew_grid(total / 4))), dim3(kEw), 0, (cudaStream_t)stream, (const T*)dxp, (T*)dx, H, W, C / 4, p, (unsigned)(total / 4));
+            launch_k(reflect_fold_v4_kernel<T, T>, dim3((unsigned)(ew_grid(total / 4))), dim3(kEw), 0, (cudaStream_t)stream, (const T*)dxp, (T*)dx, H, W, C / 4, p, (unsigned)(total / 4));
         else
-            reflect_fold_kernel<T><<<ew_grid(total), kEw, 0, (cudaStream_t)stream>>>((const T*)dxp, (T*)dx, H, W, C, p, total);
+            reflect_fold_kernel<T, T><<<ew_grid(total), kEw, 0, (cudaStream_t)stream>>>((const T*)dxp, (T*)dx, H, W, C, p, total);
     });
     return check_launch("reflect_pad_fold");
+}
+
+// the same with an fp32 padded gradient (the split-K window pass's red.add output) folded into a tensor of `dtype`
+extern "C" int p2p_reflect_pad_fold_f32(const float* dxp, void* dx, int N, int H, int W, int C, int p, int dtype, void* stream) {
+    if (N < 0 || H < 1 || W < 1 || C < 0 || p < 0) return fail(P2P_EINVAL, "bad size");
+    if (p >= H || p >= W) return fail(P2P_EINVAL, "reflection pad %d must be smaller than H=%d, W=%d", p, H, W);
+    const long long total = (long long)N * H * W * C;
+    if (total == 0) return P2P_OK;
+    if (!dxp || !dx) return fail(P2P_EINVAL, "null pointer argument");
+    const bool v4 = C % 4 == 0 && total / 4 < 2000000000LL;
+    P2P_DISPATCH_DTYPE(dtype, T, {
+        if (v4 && vec4_ok(dxp, 4) && vec4_ok(dx, sizeof(T)))
+            launch_k(reflect_fold_v4_kernel<float, T>, dim3((unsigned)(ew_grid(total / 4))), dim3(kEw), 0, (cudaStream_t)stream, dxp, (T*)dx, H, W, C / 4, p, (unsigned)(total / 4));
+        else
+            reflect_fold_kernel<float, T><<<ew_grid(total), kEw, 0, (cudaStream_t)stream>>>(dxp, (T*)dx, H, W, C, p, total);
+    });
+    return check_launch("reflect_pad_fold_f32");
 }
 
 extern "C" int p2p_bias_grad(const void* dout, float* dbias, long long rows, int J, int dtype, void* stream) {

@@ -552,10 +552,9 @@ class GANLoss(nn.Module):
 
     def __call__(self, input, target_is_real):
         if isinstance(input[0], list):
-            loss = 0
-            for input_i in input:
-                loss = loss + self._one(input_i[-1], target_is_real)
-            return loss
+            # one scalar for all scales: the loss kernels accumulate into it (no per-scale zero-fill / add kernels)
+            return ops.MseConstSumFn.apply(self.real_label if target_is_real else self.fake_label, 1.0,
+                                           *[_nhwc_view(input_i[-1]) for input_i in input])
         return self._one(input[-1], target_is_real)
 
 
@@ -563,9 +562,8 @@ def feature_matching_loss(pred_fake, pred_real, num_D, n_layers_D, lambda_feat):
     """pix2pixHD_model.py:390-398: sum_i sum_{j<len-1} D_weights * feat_weights * L1(fake_ij, real_ij.detach()) * lambda_feat"""
     feat_weights = 4.0 / (n_layers_D + 1)
     D_weights = 1.0 / num_D
-    loss = 0
-    for i in range(num_D):
-        for j in range(len(pred_fake[i]) - 1):
-            loss = loss + ops.L1Fn.apply(_nhwc_view(pred_fake[i][j]), _nhwc_view(pred_real[i][j]).detach(),
-                                         D_weights * feat_weights * lambda_feat)
-    return loss
+    fakes = [_nhwc_view(pred_fake[i][j]) for i in range(num_D) for j in range(len(pred_fake[i]) - 1)]
+    reals = [_nhwc_view(pred_real[i][j]).detach() for i in range(num_D) for j in range(len(pred_fake[i]) - 1)]
+    if not fakes:
+        return 0
+    return ops.L1SumFn.apply(D_weights * feat_weights * lambda_feat, *fakes, *reals)     # one accumulator for every term

@@ -458,7 +458,8 @@ def _dgrad_wrap(dy_shared, wq, dtype, N, H, W, p, KH, KW, Cout, Cin, reflect):
     _timed("dgrad", _Shape(N, H, W, Cin, KH * KW, Cout, Hh, Wh),          # algorithmic FLOPs: the unpadded H x W, not the padded grid
            lambda: _lib.check(_lib.lib().p2p_conv_window_run(ctypes.byref(d), _p(planes), _p(wq), None, _p(out), _DT[out.dtype],
                                                             _stream())), umma=True)
-    return out if out.dtype == dtype else out.to(dtype)
+    # reflection: the caller's fold kernel reads the fp32 split-K result directly (no conversion pass)
+    return out if (out.dtype == dtype or reflect) else out.to(dtype)
 
 
 def _window_wgrad(passes, x, dy, dwp, wtaps_total, xpad=None, fresh=False, dy_shared=None, dy_planes=None):
@@ -997,7 +998,9 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
                 _run_pass(P, dy, wq, None, buf, "dgrad")
             if cfg.pad_mode == PAD_REFLECT and cfg.pad > 0:
                 dx = torch.empty_like(x)
-                _lib.check(_lib.lib().p2p_reflect_pad_fold(_p(buf), _p(dx), N, H, W, Cin, cfg.pad, _DT[x.dtype], _stream()))
+                fold = _lib.lib().p2p_reflect_pad_fold_f32 if buf.dtype == torch.float32 and x.dtype != torch.float32 \
+                    else _lib.lib().p2p_reflect_pad_fold
+                _lib.check(fold(_p(buf), _p(dx), N, H, W, Cin, cfg.pad, _DT[x.dtype], _stream()))
             else:
                 dx = buf
         if Cin != Cin0:
@@ -1453,6 +1456,69 @@ class L1Fn(torch.autograd.Function):
         g = g.to(torch.float32).contiguous()
         _lib.check(_lib.lib().p2p_loss_l1(_p(a), _p(b), ctx.weight, None, _p(da), 1.0, _p(g), a.numel(), _DT[a.dtype], _stream()))
         return da, None, None
+
+
+class MseConstSumFn(torch.autograd.Function):
+    """sum_i weight * mean((x_i - target)^2) over several tensors as ONE 0-dim fp32 tensor: the loss kernels accumulate into
+    the same scalar (GANLoss over the discriminator's scales, networks.py:98-106) -- one zero-fill and no add kernels"""
+
+    @staticmethod
+    def forward(ctx, target, weight, *xs):
+        _need_cuda(*xs)
+        xs = tuple(x.contiguous() for x in xs)
+        loss = torch.zeros((), dtype=torch.float32, device=xs[0].device)
+        for x in xs:
+            _lib.check(_lib.lib().p2p_loss_mse_const(_p(x), target, weight, _p(loss), None, 0.0, None, x.numel(), _DT[x.dtype], _stream()))
+        ctx.save_for_backward(*xs)
+        ctx.cfg = (target, weight)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        target, weight = ctx.cfg
+        g = g.to(torch.float32).contiguous()
+        out = []
+        for i, x in enumerate(ctx.saved_tensors):
+            if not ctx.needs_input_grad[2 + i]:
+                out.append(None)
+                continue
+            dx = torch.empty_like(x)
+            _lib.check(_lib.lib().p2p_loss_mse_const(_p(x), target, weight, None, _p(dx), 1.0, _p(g), x.numel(), _DT[x.dtype], _stream()))
+            out.append(dx)
+        return (None, None) + tuple(out)
+
+
+class L1SumFn(torch.autograd.Function):
+    """sum_i weight * mean(|a_i - b_i|) as ONE 0-dim fp32 tensor, gradients to the a_i only (the feature-matching sum of
+    pix2pixHD_model.py:390-398); arguments: weight, a_0 .. a_{n-1}, b_0 .. b_{n-1}"""
+
+    @staticmethod
+    def forward(ctx, weight, *ts):
+        n = len(ts) // 2
+        _need_cuda(*ts)
+        ts = tuple(t.contiguous() for t in ts)
+        loss = torch.zeros((), dtype=torch.float32, device=ts[0].device)
+        for a, b in zip(ts[:n], ts[n:]):
+            assert a.shape == b.shape and a.dtype == b.dtype
+            _lib.check(_lib.lib().p2p_loss_l1(_p(a), _p(b), weight, _p(loss), None, 0.0, None, a.numel(), _DT[a.dtype], _stream()))
+        ctx.save_for_backward(*ts)
+        ctx.weight = weight
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        ts = ctx.saved_tensors
+        n = len(ts) // 2
+        g = g.to(torch.float32).contiguous()
+        out = []
+        for i, (a, b) in enumerate(zip(ts[:n], ts[n:])):
+            if not ctx.needs_input_grad[1 + i]:
+                out.append(None)
+                continue
+            da = torch.empty_like(a)
+            _lib.check(_lib.lib().p2p_loss_l1(_p(a), _p(b), ctx.weight, None, _p(da), 1.0, _p(g), a.numel(), _DT[a.dtype], _stream()))
+            out.append(da)
+        return (None,) + tuple(out) + (None,) * n
 
 
 class FramesDbFn(torch.autograd.Function):

@@ -17,11 +17,17 @@ import torch.distributed as dist
 
 def assemble_losses(model, losses):
     """train.py:155-160"""
-    losses = [torch.mean(x) if not isinstance(x, int) else x for x in losses]
+    # (the mean of a 0-dim loss and the "+ 0" of an absent term are identities: not launched as kernels)
+    losses = [x if isinstance(x, int) or x.dim() == 0 else torch.mean(x) for x in losses]
     loss_dict = dict(zip(model.loss_names, losses))
-    loss_D = (loss_dict['D_fake'] + loss_dict['D_real']) * 0.5 + (loss_dict.get('D_fake_t', 0) + loss_dict.get('D_real_t', 0)) * 0.5
-    loss_G = (loss_dict['G_GAN'] + loss_dict.get('G_mat', 0) + loss_dict.get('G_GAN_Feat', 0) + loss_dict.get('G_VGG', 0)
-              + loss_dict.get('G_GAN_t', 0))
+
+    def total(*names):
+        terms = [loss_dict[k] for k in names if k in loss_dict and not isinstance(loss_dict[k], int)]
+        return sum(terms[1:], terms[0]) if terms else 0
+    loss_D = total('D_fake', 'D_real') * 0.5
+    if 'D_fake_t' in loss_dict or 'D_real_t' in loss_dict:
+        loss_D = loss_D + total('D_fake_t', 'D_real_t') * 0.5
+    loss_G = total('G_GAN', 'G_mat', 'G_GAN_Feat', 'G_VGG', 'G_GAN_t')
     return loss_dict, loss_G, loss_D
 
 
