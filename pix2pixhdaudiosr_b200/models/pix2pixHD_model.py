@@ -298,7 +298,26 @@ class Pix2PixHDModel(BaseModel):
         lr_spectro, lr_pha, hr_spectro, hr_pha, _, _, hr_norm_param, lr_norm_param = self.encode_input(lr_audio, inst, hr_audio, feat)
         sr_result = self.netG.forward(lr_spectro)
 
-        if getattr(self, '_share_fake_pass', False):
+        if getattr(self, '_share_fake_pass', False) and getattr(self, '_batch_D', False):
+            # train.train_step with train.BATCH_D: the shared pass below AND the pass on the real image run as ONE discriminator
+            # forward over cat(real, fake) along the batch (InstanceNorm2d is per image: each image sees the arithmetic of
+            # its own pass); the features are split back into their halves.  loss_G's backward walks the fake half only
+            # (ops.set_backward_phase(fake_half_only=True)), loss_D's the whole batch.
+            B = lr_spectro.shape[0]
+            real_in = torch.cat((lr_spectro, hr_spectro.detach().float()), dim=1)
+            fake_in = ops.GradGateFn.apply(torch.cat((lr_spectro, sr_result.float()), dim=1))
+            old = ops.set_batch_halves(B)
+            try:
+                both = self.netD.forward(torch.cat((real_in, fake_in), dim=0), gated=True)
+            finally:
+                ops.set_batch_halves(old)
+            split = [[ops.BatchHalvesFn.apply(f, B) for f in scale] for scale in both]
+            pred_real = [[rf[0] for rf in scale] for scale in split]
+            pred_fake = [[rf[1] for rf in scale] for scale in split]
+            loss_D_fake = self.criterionGAN(pred_fake, False)
+            loss_D_real = self.criterionGAN(pred_real, True)
+            loss_G_GAN = self.criterionGAN(pred_fake, True)
+        elif getattr(self, '_share_fake_pass', False):
             # train.train_step: D's forward on (label, fake) runs ONCE and serves both losses -- the reference's first and third
             # D passes (:351-361) compute the same numbers (pool_size 0).  The gate in front of D is closed while loss_D is
             # back-propagated (the reference detaches the fake image there), and D's weight gradients are not formed while

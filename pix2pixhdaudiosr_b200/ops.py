@@ -1223,16 +1223,57 @@ class GradSink:
 #   phase D (loss_D.backward): D's weight gradients are formed, the gate is closed (the reference detaches the fake image).
 BACKWARD_OWNERS = None      # ids of the optimizers whose parameters receive gradients in the running backward pass (None: all)
 GATE_OPEN = True
+# Batched discriminator pass (train.BATCH_D): D runs ONCE on cat(real, fake) along the batch -- InstanceNorm is per image, so
+# every image sees exactly the arithmetic of a separate pass.  Forward: BATCH_HALVES = B marks the layers of that pass.
+# Phase G back-propagates through the FAKE half only (FAKE_HALF_ONLY): those layers slice their saved tensors to [B:], and
+# the real half of every gradient tensor that travels between them is never written nor read.
+BATCH_HALVES = 0
+FAKE_HALF_ONLY = False
 
 
-def set_backward_phase(owners=None, gate_open=True):
-    global BACKWARD_OWNERS, GATE_OPEN
+def set_backward_phase(owners=None, gate_open=True, fake_half_only=False):
+    global BACKWARD_OWNERS, GATE_OPEN, FAKE_HALF_ONLY
     BACKWARD_OWNERS = None if owners is None else {id(o) for o in owners}
     GATE_OPEN = bool(gate_open)
+    FAKE_HALF_ONLY = bool(fake_half_only)
+
+
+def set_batch_halves(B):
+    """forward-time marker: the layers run until the next call belong to a pass over cat(real[B], fake[B])"""
+    global BATCH_HALVES
+    old, BATCH_HALVES = BATCH_HALVES, int(B)
+    return old
 
 
 def _owner_active(gphys):
     return BACKWARD_OWNERS is None or gphys is None or id(gphys.owner) in BACKWARD_OWNERS
+
+
+class BatchHalvesFn(torch.autograd.Function):
+    """x [2B, ...] -> (x[:B], x[B:]) (views).  Backward: in phase G only the fake half carries a gradient and only that half
+    of the result is written; otherwise missing halves are zeros."""
+
+    @staticmethod
+    def forward(ctx, x, B):
+        ctx.set_materialize_grads(False)
+        ctx.meta = (int(B), tuple(x.shape), tuple(x.stride()), x.dtype, x.device)
+        return x[:B], x[B:]
+
+    @staticmethod
+    def backward(ctx, d_real, d_fake):
+        if d_real is None and d_fake is None:
+            return None, None
+        B, shape, stride, dtype, device = ctx.meta
+        out = torch.empty_strided(shape, stride, dtype=dtype, device=device)
+        if d_real is None and FAKE_HALF_ONLY:
+            out[B:].copy_(d_fake)               # the real half is never read in this phase
+            return out, None
+        for half, d in ((out[:B], d_real), (out[B:], d_fake)):
+            if d is None:
+                half.zero_()
+            else:
+                half.copy_(d)
+        return out, None
 
 
 class GradGateFn(torch.autograd.Function):
@@ -1262,6 +1303,7 @@ class ConvBlockFn(torch.autograd.Function):
                 want_plain=False, gated=False):
         _need_cuda(x, weight)
         ctx.gated = bool(gated)         # x sits right behind a GradGateFn: no input gradient while the gate is closed
+        ctx.halves = BATCH_HALVES       # > 0: this call is part of a batched (real, fake) discriminator pass
         ctx.set_materialize_grads(False)    # an undefined upstream gradient (closed gate) must not run this layer's backward on zeros
         plain = (not norm) and act == ACT_NONE and res is None
         aux = [] if ctx.needs_input_grad[1] else None
@@ -1309,6 +1351,13 @@ class ConvBlockFn(torch.autograd.Function):
         x, weight, w16, y, stats = ctx.saved_tensors
         cfg, norm, act, slope, has_bias, has_res, plain = ctx.cfg
         dz = dz.contiguous()
+        xpad = ctx.xpad
+        half = ctx.halves if (ctx.halves and FAKE_HALF_ONLY and not has_res) else 0
+        if half:                        # phase G of a batched discriminator pass: the fake images only
+            assert x.shape[0] == 2 * half and dz.shape[0] == 2 * half
+            dz, x, xpad = dz[half:], x[half:], None
+            y = y[half:] if y is not None else None
+            stats = stats[half:] if stats is not None else None
         # a bias in front of InstanceNorm2d(affine=False) has an exactly zero gradient (the mean subtraction removes it; the
         # reference's autograd returns rounding noise of ~1e-7 relative size): not computed unless P2P_NORM_BIAS_GRAD=1
         active = _owner_active(ctx.gphys)       # this layer's parameters take gradients in the running backward phase
@@ -1323,7 +1372,14 @@ class ConvBlockFn(torch.autograd.Function):
             dy, dy_pre = norm_act_backward_wrap(y, stats, dz, norm, act, slope, plan)
         else:
             dy = norm_act_backward(y, stats, dz, norm, act, slope)
-        dx, dw, db = conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, ctx.gphys, ctx.xpad, dy_pre)
+        dx, dw, db = conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, ctx.gphys, xpad, dy_pre)
+        if half:
+            if need_dw or need_db:
+                raise RuntimeError("the fake-half backward phase must not form parameter gradients of the batched pass")
+            if dx is not None:          # autograd wants the full batch's shape; the real half stays unwritten (never read)
+                full = torch.empty((2 * half,) + tuple(dx.shape[1:]), dtype=dx.dtype, device=dx.device)
+                full[half:].copy_(dx)
+                dx = full
         if has_bias and ctx.needs_input_grad[2] and not need_db and ctx.gphys is None and active:
             db = torch.zeros(ctx.bias_n, dtype=torch.float32, device=x.device)    # no flat gradient buffer behind .grad: give autograd the zero
         return dx, dw, db, None, (dz if has_res else None), None, None, None, None, None, None, None, None, None, None

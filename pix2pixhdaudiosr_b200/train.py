@@ -163,6 +163,9 @@ def broadcast_parameters(model, src=0, group=None):
 
 OVERLAP_G_STEP = os.environ.get("P2P_OVERLAP_GSTEP", "1") == "1"
 SHARE_FAKE_PASS = os.environ.get("P2P_SHARE_FAKE_PASS", "1") == "1"
+# with the shared pass: the discriminator's forward on the real image joins it -- ONE forward over cat(real, fake), ONE
+# full-batch backward for loss_D, a fake-half backward for loss_G (Pix2PixHDModel.forward, ops.BatchHalvesFn)
+BATCH_D = os.environ.get("P2P_BATCH_D", "1") == "1"
 _SIDE = {}
 
 
@@ -182,17 +185,20 @@ def train_step(model, lr_audio, hr_audio, inst=None, feat=None, infer=False, syn
     optimiser kernels share the SMs with the tensor-core-bound convolutions instead of running after them."""
     shared = SHARE_FAKE_PASS and hasattr(model, 'netD') and getattr(model.opt, 'pool_size', 0) == 0
     model._share_fake_pass = shared          # one D forward on the generated image serves both losses (see Pix2PixHDModel.forward)
+    batched = shared and BATCH_D
+    model._batch_D = batched
     try:
         losses, generated = model(lr_audio, inst, hr_audio, feat, infer)
     finally:
         model._share_fake_pass = False
+        model._batch_D = False
     loss_dict, loss_G, loss_D = assemble_losses(model, losses)
     opt_G, opt_D = model.optimizer_G, model.optimizer_D
     from . import ops
     opt_G.zero_grad()
     try:
         if shared:
-            ops.set_backward_phase(owners=[opt_G], gate_open=True)
+            ops.set_backward_phase(owners=[opt_G], gate_open=True, fake_half_only=batched)
         loss_G.backward(retain_graph=shared)
     finally:
         ops.set_backward_phase(None, True)

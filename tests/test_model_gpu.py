@@ -174,9 +174,10 @@ def test_shared_fake_pass_equals_three_pass_step(ref, precision):
     the updated weights of one optimisation step are bit-identical between the two"""
     from pix2pixhdaudiosr_b200 import _lib, train
     old = _lib.lib().p2p_set_deterministic(1)
-    share0, overlap0 = train.SHARE_FAKE_PASS, train.OVERLAP_G_STEP
+    share0, overlap0, batch0 = train.SHARE_FAKE_PASS, train.OVERLAP_G_STEP, train.BATCH_D
     out = {}
     try:
+        train.BATCH_D = False                       # (the batched pass sums D's weight gradients in another order: next test)
         for share in (True, False):
             train.SHARE_FAKE_PASS = share
             train.OVERLAP_G_STEP = share            # the three-pass run also keeps the reference's stream order
@@ -190,10 +191,41 @@ def test_shared_fake_pass_equals_three_pass_step(ref, precision):
                           model.optimizer_D.flat_grad.clone(), model.optimizer_G.flat.clone(), model.optimizer_D.flat.clone())
             del model
     finally:
-        train.SHARE_FAKE_PASS, train.OVERLAP_G_STEP = share0, overlap0
+        train.SHARE_FAKE_PASS, train.OVERLAP_G_STEP, train.BATCH_D = share0, overlap0, batch0
         _lib.lib().p2p_set_deterministic(old)
     for a, b, what in zip(out[True], out[False], ("losses", "G gradients", "D gradients", "G weights", "D weights")):
         assert torch.equal(a, b), (precision, what, float((a.double() - b.double()).abs().max()))
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_batched_discriminator_pass_equals_separate_passes(ref, precision):
+    """train.BATCH_D: the discriminator's forward on the real image joins the shared pass on the generated one (one forward over
+    cat(real, fake), InstanceNorm per image).  In deterministic mode the losses and G's gradients -- which see exactly the
+    per-image arithmetic of separate passes -- are bit-identical over three steps' first step; D's weight gradients are sums
+    over 2B images taken in one launch instead of two, equal to rounding (1e-5 of the largest gradient; fp32 sums)."""
+    from pix2pixhdaudiosr_b200 import _lib, train
+    old = _lib.lib().p2p_set_deterministic(1)
+    batch0 = train.BATCH_D
+    out = {}
+    try:
+        for batched in (True, False):
+            train.BATCH_D = batched
+            torch.manual_seed(99)
+            model = create_model(tiny_opt(precision=precision, mask=True, mask_mode='mode2'))
+            _load(model, ref)
+            lr, hr = batch(0)
+            loss_dict, _ = train_step(model, lr.cuda(), hr.cuda())
+            torch.cuda.synchronize()
+            out[batched] = (torch.stack([loss_dict[k].float() for k in sorted(loss_dict)]).cpu(), model.optimizer_G.flat_grad.clone(),
+                            model.optimizer_G.flat.clone(), model.optimizer_D.flat_grad.clone())
+            del model
+    finally:
+        train.BATCH_D = batch0
+        _lib.lib().p2p_set_deterministic(old)
+    for a, b, what in zip(out[True][:3], out[False][:3], ("losses", "G gradients", "G weights")):
+        assert torch.equal(a, b), (precision, what, float((a.double() - b.double()).abs().max()))
+    gd, gd0 = out[True][3].double(), out[False][3].double()
+    assert float((gd - gd0).abs().max()) <= 1e-5 * float(gd0.abs().max()), float((gd - gd0).abs().max() / gd0.abs().max())
 
 
 def test_lazy_zero_grad_equals_full_memset(ref):
