@@ -250,10 +250,17 @@ def run_train(args):
         # the profiled step is itself captured in a CUDA graph with the event pairs as record nodes and replayed once: every
         # kernel runs back to back exactly as in the timed region (an eager step outruns the host's launch rate, and the launch
         # queue holds only ~1000 of its ~1300 launches, so event pairs late in an eager step include host gaps)
+        # (with the weight gradients IN the main stream: in the timed step they run on a side stream next to the memory-bound
+        # kernels, which speeds the step up but makes an event pair measure two kernels sharing the SMs -- the roofline leg
+        # wants each kernel's own duration)
         pg = torch.cuda.CUDAGraph()
+        overlap0, ops.WGRAD_OVERLAP = ops.WGRAD_OVERLAP, False
         ops.start_conv_timing(external=True)
-        with torch.cuda.graph(pg):
-            train_step(model, lr_d, hr_d, sync=sync)
+        try:
+            with torch.cuda.graph(pg):
+                train_step(model, lr_d, hr_d, sync=sync)
+        finally:
+            ops.WGRAD_OVERLAP = overlap0
         ops.pause_conv_timing()
         pg.replay()
         torch.cuda.synchronize(dev)
@@ -324,7 +331,10 @@ def run_train(args):
                                          "ms_per_step_in_kernels": round(um_ms, 3), "share_of_step": round(um_ms / step_ms, 3)},
                          "note": "algorithmic conv FLOPs (2*MACs) of the kernel's launches in one step / their summed "
                                  "CUDA-event durations, measured in one extra profiled step after the timed region "
-                                 "(a CUDA graph replay with the event pairs as graph nodes; eager with --no-graph)"},
+                                 "(a CUDA graph replay with the event pairs as graph nodes and the weight-gradient kernels in the "
+                                 "main stream -- the timed step runs them on a side stream next to memory-bound kernels, where an "
+                                 "event pair would time two kernels sharing the SMs; eager with --no-graph); share_of_step therefore "
+                                 "compares un-overlapped kernel time with the overlapped step"},
             "step_tensor_utilisation": round(all_flops / (step_ms * 1e-3) / 1e12 / peak, 4),
             "conv_flops_per_step": round(all_flops),
             "kernels": {k: {"launches": v[0], "GFLOP": round(v[1] / 1e9, 1), "ms": round(v[2], 3),

@@ -384,31 +384,124 @@ def deterministic():
 
 _WRAP_BUFFERS = {}
 
+# ---- weight gradients on a side stream -----------------------------------------------------------------------------------------
+# Within one layer's backward the input gradient feeds the next layer down, the weight gradient feeds nothing until the
+# optimiser runs.  train.train_step therefore lets the window weight-gradient kernels (tensor-core bound) run on a side
+# stream while the main stream goes on with the next layer's InstanceNorm backward (memory bound) and input gradient:
+#   wgrad_overlap_begin() ... loss.backward() ... wgrad_overlap_join()
+# Everything a side-stream launch reads is kept alive until the join (the caching allocator must not hand the memory to a
+# main-stream tensor while the side stream still reads it -- also at graph-capture time), and the shared gradient-grid
+# buffers become a ring whose entries are re-used only after the weight-gradient pass that read them (event).
+WGRAD_OVERLAP = os.environ.get("P2P_WGRAD_OVERLAP", "1") == "1"
+
+
+class _SideWgrad:
+    active = False
+    streams = {}
+    used = set()        # devices whose side stream took work since wgrad_overlap_begin()
+    keep = []
+
+
+def wgrad_overlap_begin():
+    _SideWgrad.active = WGRAD_OVERLAP
+    _SideWgrad.used = set()
+    # nothing is in flight on the side stream here (the last join made the main stream wait for it), and an event of an earlier
+    # CUDA-graph capture must not be waited on inside another one: forget the ring's events
+    for key, ring in _WRAP_BUFFERS.items():
+        if isinstance(key, tuple) and key and key[0] == "ring":
+            for slot in ring["slots"]:
+                slot[1] = None
+
+
+def wgrad_overlap_join():
+    if _SideWgrad.active:
+        for dev in _SideWgrad.used:       # (a side stream that took no work is not part of a running capture: do not touch it)
+            torch.cuda.current_stream(dev).wait_stream(_SideWgrad.streams[dev])
+    _SideWgrad.active = False
+    _SideWgrad.used = set()
+    _SideWgrad.keep = []
+
+
+def _flat_tensors(objs):
+    for o in objs:
+        if torch.is_tensor(o):
+            yield o
+        elif isinstance(o, (tuple, list)):
+            yield from _flat_tensors(o)
+
+
+class _wgrad_side:
+    """context: launches inside go to the weight-gradient side stream (after everything already enqueued on the current
+    stream); `reads` are kept alive until wgrad_overlap_join(); `ring` entries get the event that frees them for re-use"""
+
+    def __init__(self, enable, reads=(), ring=None):
+        self.on = bool(enable) and _SideWgrad.active
+        self.reads, self.ring, self.ctx = reads, ring, None
+
+    def __enter__(self):
+        if not self.on:
+            return self
+        dev = torch.cuda.current_device()
+        side = _SideWgrad.streams.get(dev)
+        if side is None:
+            side = _SideWgrad.streams[dev] = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        _SideWgrad.used.add(dev)
+        _SideWgrad.keep.extend(_flat_tensors(self.reads))
+        self.side = side
+        self.ctx = torch.cuda.stream(side)
+        self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self.on:
+            if self.ring is not None:
+                ev = torch.cuda.Event()
+                ev.record(self.side)
+                self.ring[1] = ev
+            self.ctx.__exit__(*exc)
+        return False
+
+
 
 def _wrap_buffer(device, dtype, N, Hh, Wh, KH, KW, J):
     """the shared gradient-grid buffer of one geometry: P64 zero rows | rows64(N*Hh*Wh) grid rows | P64 zero rows, P64 >=
-    (KH-1)*Wh + KW-1 -> (buffer, P64, rows)"""
+    (KH-1)*Wh + KW-1 -> (buffer, P64, rows, ring entry or None)"""
     rows = _rows64(N * Hh * Wh)
     P64 = _rows64((KH - 1) * Wh + KW - 1)
+    capturing = torch.cuda.is_current_stream_capturing()
+    if _SideWgrad.active:
+        # three buffers per geometry, used in turn; an entry is re-used only after the side-stream pass that read it
+        key = ("ring", device, dtype, P64, rows, J, capturing)
+        ring = _WRAP_BUFFERS.get(key)
+        if ring is None:
+            ring = _WRAP_BUFFERS[key] = {"next": 0, "slots": [[torch.zeros((P64 + rows + P64, J), dtype=dtype, device=device), None]
+                                                              for _ in range(3)]}
+        slot = ring["slots"][ring["next"]]
+        ring["next"] = (ring["next"] + 1) % len(ring["slots"])
+        if slot[1] is not None:
+            torch.cuda.current_stream().wait_event(slot[1])
+            slot[1] = None
+        return slot[0], P64, rows, slot
     key = (device, dtype, P64, rows, J)
     buf = _WRAP_BUFFERS.get(key)
-    if buf is None or torch.cuda.is_current_stream_capturing() != _WRAP_BUFFERS.get(("capturing", key), False):
+    if buf is None or capturing != _WRAP_BUFFERS.get(("capturing", key), False):
         # zero prefix | dy grid | zero suffix; the margins are written once, the grid (and its zero tail) by every call.
         # The buffer is reused by later calls of the same geometry: the two gradient passes that read it are enqueued on the
         # same stream before the next layer overwrites it.  (One buffer per capture state: a CUDA graph keeps its own.)
         buf = torch.zeros((P64 + rows + P64, J), dtype=dtype, device=device)
         _WRAP_BUFFERS[key] = buf
-        _WRAP_BUFFERS[("capturing", key)] = torch.cuda.is_current_stream_capturing()
-    return buf, P64, rows
+        _WRAP_BUFFERS[("capturing", key)] = capturing
+    return buf, P64, rows, None
 
 
 def _dy_wrap(dy, Hh, Wh, KH, KW):
     """dy [N,OH,OW,J] laid out at the pitch of the padded input ([N,Hh,Wh] grid, dy at its top-left, zeros elsewhere) in a
     buffer of P64 + rows64 + P64 rows whose first and last P64 >= (KH-1)*Wh + KW-1 rows are zero -> (key, buffer, P64)"""
     N, OH, OW, J = dy.shape
-    buf, P64, rows = _wrap_buffer(dy.device, dy.dtype, N, Hh, Wh, KH, KW, J)
+    buf, P64, rows, slot = _wrap_buffer(dy.device, dy.dtype, N, Hh, Wh, KH, KW, J)
     _lib.check(_lib.lib().p2p_pad_planes(_p(dy), _p(buf[P64:]), N, OH, OW, J, 0, 0, Hh, Wh, 1, rows, 0, _DT[dy.dtype], _stream()))
-    return (Hh, Wh, rows, J), buf, P64
+    return (Hh, Wh, rows, J), buf, P64, slot
 
 
 def _dy_wrap_plan(x, weight, cfg, need_dx, need_dw, need_db):
@@ -435,7 +528,7 @@ def _dy_wrap_plan(x, weight, cfg, need_dx, need_dw, need_db):
 def _dgrad_wrap(dy_shared, wq, dtype, N, H, W, p, KH, KW, Cout, Cin, reflect):
     """input gradient of a stride-1 convolution from the shared dy copy: output on the padded grid (reflection: folded by the
     caller) or directly [N,H,W,Cin] (zero padding)"""
-    (Hh, Wh, rows, J), buf, P64 = dy_shared
+    (Hh, Wh, rows, J), buf, P64 = dy_shared[:3]
     P = (KH - 1) * Wh + (KW - 1)
     off = P64 - P + (0 if reflect else p * Wh + p)
     d = _lib.WindowDesc()
@@ -1015,16 +1108,19 @@ def _conv_backward(x, weight, w16, dy, cfg, need_dx, need_dw, need_db, gphys=Non
             wpasses = conv_fwd_passes(N, H, W, Cin, Cout, KH, KW, cfg.stride, cfg.pad, cfg.pad_mode)
         # 2: zero_grad left this slice alone (FusedAdam lazy zeroing), the kernel must overwrite it
         must_store = direct and fresh and gphys.unzeroed_epoch == gphys.owner.grad_epoch
-        if _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None, 2 if must_store else fresh, dy_shared,
-                         dy_aux[0] if dy_aux else None):
-            if direct and fresh and _lib.lib().p2p_conv_wgrad_window_stored() == 1:
-                gphys.stored_epoch = gphys.owner.grad_epoch
-        else:
-            if must_store:
-                dwp.zero_()                 # zero_grad skipped this slice expecting a store: the fallback kernels accumulate
-            x, dy = x.contiguous(), dy.contiguous()
-            for P in wpasses:
-                _run_wgrad(P, x, dy, dwp)
+        # direct gradients feed nothing until the optimiser runs: their kernels go to the side stream (see _SideWgrad)
+        ring = dy_shared[3] if dy_shared is not None and len(dy_shared) > 3 else None
+        with _wgrad_side(direct, (x, dy, xpad, dy_shared[:3] if dy_shared is not None else None, dy_aux), ring):
+            if _window_wgrad(wpasses, x, dy, dwp, KH * KW, xpad if thin is None else None, 2 if must_store else fresh, dy_shared,
+                             dy_aux[0] if dy_aux else None):
+                if direct and fresh and _lib.lib().p2p_conv_wgrad_window_stored() == 1:
+                    gphys.stored_epoch = gphys.owner.grad_epoch
+            else:
+                if must_store:
+                    dwp.zero_()             # zero_grad skipped this slice expecting a store: the fallback kernels accumulate
+                x, dy = x.contiguous(), dy.contiguous()
+                for P in wpasses:
+                    _run_wgrad(P, x, dy, dwp)
         if direct:
             gphys.written()
             return dx, None, db
@@ -1179,12 +1275,12 @@ def norm_act_backward_wrap(y, stats, dz, norm, act, slope, plan):
     N, H, W, C = y.shape
     Hh, Wh, KH, KW, _ = plan
     _ensure_stats_workspace(y.device)
-    buf, P64, rows = _wrap_buffer(y.device, dz.dtype, N, Hh, Wh, KH, KW, C)
+    buf, P64, rows, slot = _wrap_buffer(y.device, dz.dtype, N, Hh, Wh, KH, KW, C)
     work = torch.empty((N, C, 2), dtype=torch.float32, device=y.device) if norm else None
     _lib.check(_lib.lib().p2p_instnorm_act_bwd_wrap(_p(y), _p(stats), _p(dz), _p(buf[P64:]), _p(work), N, H, W, C, Hh, Wh, rows,
                                                     int(norm), act, slope, _DT[y.dtype], _DT[dz.dtype], _stream()))
     view = buf[P64:P64 + N * Hh * Wh].view(N, Hh, Wh, C)[:, :H, :W, :]
-    return view, ((Hh, Wh, rows, C), buf, P64)
+    return view, ((Hh, Wh, rows, C), buf, P64, slot)
 
 
 # ---------------------------------------------------------------------------------------------------

@@ -199,8 +199,10 @@ def train_step(model, lr_audio, hr_audio, inst=None, feat=None, infer=False, syn
     try:
         if shared:
             ops.set_backward_phase(owners=[opt_G], gate_open=True, fake_half_only=batched)
+        ops.wgrad_overlap_begin()           # window weight gradients on a side stream (ops._SideWgrad), joined below
         loss_G.backward(retain_graph=shared)
     finally:
+        ops.wgrad_overlap_join()
         ops.set_backward_phase(None, True)
     if sync is None:
         sync = _NOSYNC
@@ -224,8 +226,10 @@ def train_step(model, lr_audio, hr_audio, inst=None, feat=None, infer=False, syn
     try:
         if shared:
             ops.set_backward_phase(owners=[opt_D], gate_open=False)
+        ops.wgrad_overlap_begin()
         loss_D.backward()
     finally:
+        ops.wgrad_overlap_join()
         ops.set_backward_phase(None, True)
     if not overlap:
         sync.finish(opt_G, h_G)

@@ -259,3 +259,53 @@ def test_lazy_zero_grad_equals_full_memset(ref):
     assert skipped > 0, "no gradient slice was left to the store path: the test does not exercise lazy zeroing"
     for i, (a, b) in enumerate(zip(out[True], out[False])):
         assert torch.equal(a, b), (i, float((a.double() - b.double()).abs().max()))
+
+
+@pytest.mark.parametrize("graphed", [False, True])
+def test_side_stream_weight_gradients_equal_in_stream_ones(graphed):
+    """train_step runs the window weight-gradient kernels on a side stream (ops._SideWgrad: keep-alive list, ring of gradient
+    grids, joined before the optimiser): in deterministic mode three optimisation steps -- eager, and as CUDA-graph replays --
+    give bit-identical gradients and weights with and without it.  (16-channel nets: the miniature ones of the other tests
+    have no layer the tensor-core weight-gradient kernel takes.)"""
+    from pix2pixhdaudiosr_b200 import _lib, ops
+    from pix2pixhdaudiosr_b200.train import GraphedTrainStep
+    old = _lib.lib().p2p_set_deterministic(1)
+    ov0 = ops.WGRAD_OVERLAP
+    out, on_side = {}, 0
+    try:
+        for overlap in (True, False):
+            ops.WGRAD_OVERLAP = overlap
+            torch.manual_seed(7)
+            model = create_model(tiny_opt(precision="bf16", ngf=16, ndf=16, mask=True, mask_mode='mode2'))
+            lr, hr = batch(0)
+            lr, hr = lr.cuda(), hr.cuda()
+            calls = {"n": 0}
+            enter = ops._wgrad_side.__enter__
+
+            def counting(self, _enter=enter, _calls=calls):
+                _calls["n"] += int(self.on)
+                return _enter(self)
+            ops._wgrad_side.__enter__ = counting
+            try:
+                if graphed:
+                    step = GraphedTrainStep(model, lr, hr)
+                    for _ in range(3):
+                        step(step.lr_static, step.hr_static)
+                else:
+                    for _ in range(3):
+                        train_step(model, lr, hr)
+            finally:
+                ops._wgrad_side.__enter__ = enter
+            torch.cuda.synchronize()
+            if overlap:
+                on_side = calls["n"]
+            out[overlap] = [model.optimizer_G.flat_grad.clone(), model.optimizer_D.flat_grad.clone(), model.optimizer_G.flat.clone(),
+                            model.optimizer_D.flat.clone()]
+            del model
+    finally:
+        ops.WGRAD_OVERLAP = ov0
+        _lib.lib().p2p_set_deterministic(old)
+    assert on_side > 0, "no weight gradient went to the side stream: the test does not exercise the overlap"
+    for i, (a, b) in enumerate(zip(out[True], out[False])):
+        assert torch.isfinite(a).all()
+        assert torch.equal(a, b), (graphed, i, float((a.double() - b.double()).abs().max()))
