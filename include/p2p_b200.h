@@ -244,6 +244,9 @@ int p2p_instnorm_act_bwd_wrap(const void* y, const float* stats, const void* dz,
  * (partial sums meet in ws, the last CTA finalises and re-zeroes it) instead of memset + reduction + finalise.  The calls
  * that use it must be ordered on one stream; NULL pointers unregister it. */
 int p2p_instnorm_workspace(float* ws, long long ws_floats, unsigned* cnt, long long cnt_words);
+/* Bytes of those two regions for tensors of up to N images x C channels (the library's only held workspace; every other
+ * entry point takes caller-allocated scratch as explicit arguments). */
+int p2p_workspace_bytes(int N, int C, long long* ws_bytes, long long* cnt_bytes);
 /* stats [N,C,2] = (mean, rstd) of y [N,HW,C] alone: the reduction half of p2p_instnorm_act_fwd, for p2p_instnorm_act_planes. */
 int p2p_instnorm_stats(const void* y, float* stats, int N, long long HW, int C, float eps, int y_dtype, void* stream);
 /* Allocation-free variant of p2p_instnorm_stats.  It has NO counterpart in the reference: it was added

@@ -74,6 +74,7 @@ _SIGS.update({
     "p2p_instnorm_act_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _ll, _i, _i, _i, _f, _i, _i, _vp]),
     "p2p_instnorm_act_bwd_wrap": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _ll, _i, _i, _f, _i, _i, _vp]),
     "p2p_instnorm_stats": (_i, [_vp, _vp, _i, _ll, _i, _f, _i, _vp]),
+    "p2p_workspace_bytes": (_i, [_i, _i, _vp, _vp]),
     "p2p_instnorm_stats_static": (_i, [_vp, _vp, _i, _ll, _i, _f, _i, _vp]),
     "p2p_instnorm_workspace": (_i, [_vp, _ll, _vp, _ll]),
     "p2p_avgpool3s2_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),

@@ -723,6 +723,16 @@ inline bool ws_fits(int N, int C) {
 // Caller-owned, ZEROED device scratch for the single-launch InstanceNorm reductions (the kernels leave it zeroed): ws_floats
 // floats at ws, cnt_words 32-bit words at cnt.  Without it (or when a tensor does not fit) the three-node form runs.
 // One workspace serves every layer: the calls of a step are ordered on one stream.
+// Scratch query: bytes of the two regions p2p_instnorm_workspace wants for tensors of up to N images x C channels
+// (*ws_bytes: fp32 partial sums, *cnt_bytes: 32-bit group counters).  Every other entry point takes its scratch as explicit
+// arguments sized by the formulas in this header; this is the only library-held workspace.
+extern "C" int p2p_workspace_bytes(int N, int C, long long* ws_bytes, long long* cnt_bytes) {
+    if (N < 0 || C < 0 || !ws_bytes || !cnt_bytes) return fail(P2P_EINVAL, "bad argument");
+    *ws_bytes = 2LL * N * C * (long long)sizeof(float);
+    *cnt_bytes = (long long)N * ((C / 4 + 31) / 32) * (long long)sizeof(unsigned);
+    return P2P_OK;
+}
+
 extern "C" int p2p_instnorm_workspace(float* ws, long long ws_floats, unsigned* cnt, long long cnt_words) {
     g_stats_ws = ws; g_stats_ws_floats = ws ? ws_floats : 0;
     g_stats_cnt = cnt; g_stats_cnt_words = cnt ? cnt_words : 0;

@@ -121,3 +121,13 @@ def test_no_cpu_fallback():
     m = MDCT4(256, 128, 256, kbdwin, device="cpu")
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         m(torch.zeros(2, 1024))
+
+
+def test_workspace_query():
+    """p2p_workspace_bytes: sizes of the InstanceNorm workspace for N images x C channels; no GPU needed"""
+    import ctypes
+    from pix2pixhdaudiosr_b200 import _lib
+    ws, cnt = ctypes.c_longlong(), ctypes.c_longlong()
+    assert _lib.lib().p2p_workspace_bytes(16, 1536, ctypes.byref(ws), ctypes.byref(cnt)) == 0
+    assert ws.value == 2 * 16 * 1536 * 4 and cnt.value == 16 * 12 * 4
+    assert _lib.lib().p2p_workspace_bytes(-1, 8, ctypes.byref(ws), ctypes.byref(cnt)) == -1
