@@ -146,14 +146,16 @@ __device__ __forceinline__ int pi_rev(int n1, int c) { return (c - n1 + 2 * C::V
 
 // stages 1b..2 shared by analysis and synthesis: z (V registers, lane order as above) -> Y[k1 + V k2] * post
 // returns re_[m][k2] = Re, nim[m][k2] = -Im for k = j + P m + V k2.
-template <class C>
+// SWZ: the exchange region is V rows of exactly P float2 (no padding column), element (row r, column c) at
+// r*P + (c ^ (r % P)) -- conflict-free like the padded form, and 2*V*P floats = one frame row, so the synthesis kernel can
+// lay it over the frame's own (already consumed) coefficient row; `xstride` = floats between the regions of a warp's frames.
+template <class C, bool SWZ = false>
 __device__ __forceinline__ void fft_core(float2 (&z)[C::V], float* __restrict__ ex_warp, const float2* post,
                                          const float2* roots, const float2 (&xr)[C::XV], const LaneRole<C>& ln, int c,
-                                         float (&re_)[C::Q][C::P], float (&nim)[C::Q][C::P]) {
-    constexpr int V = C::V, P = C::P;
+                                         float (&re_)[C::Q][C::P], float (&nim)[C::Q][C::P], int xstride = C::XREG) {
+    constexpr int V = C::V, P = C::P, PS = SWZ ? P : P + 1;
     fft_reg<V>(z);
-    float2* ex = reinterpret_cast<float2*>(ex_warp + ln.g * C::XREG);
-    float2* exw = ex + ln.j;
+    float2* ex = reinterpret_cast<float2*>(ex_warp + ln.g * xstride);
 #pragma unroll
     for (int k1 = 0; k1 < V; ++k1) {
         float2 v = z[brev<V>(k1)];
@@ -161,20 +163,22 @@ __device__ __forceinline__ void fft_core(float2 (&z)[C::V], float* __restrict__ 
             if constexpr (C::XTW_IN_REGS) v = cmulf(v, xr[k1]);
             else v = cmulf(v, __ldg(roots + ln.xtw_index(k1, c)));
         }
-        exw[k1 * (P + 1)] = v;          // flipped lanes: physical row k1 holds logical row (V-k1)%V
+        ex[k1 * PS + (SWZ ? (ln.j ^ (k1 % P)) : ln.j)] = v;          // flipped lanes: physical row k1 holds logical row (V-k1)%V
     }
     __syncwarp();
 #pragma unroll
     for (int m = 0; m < C::Q; ++m) {
         float2 b[P];
         const int k1 = ln.j + P * m;
-        const float2* rowN = ex + k1 * (P + 1);
-        const float2* rowF = ex + ((V - k1) % V) * (P + 1);
+        const int rN = k1, rF = (V - k1) % V;
+        const float2* rowN = ex + rN * PS;
+        const float2* rowF = ex + rF * PS;
+        const int rL = ln.flip ? rF : rN;
         const float2* rowL = ln.flip ? rowF : rowN;
 #pragma unroll
         for (int n2 = 0; n2 < P; ++n2) {
-            if constexpr (P == 32) b[n2] = (n2 >= 16 ? rowF : rowN)[n2];   // columns 16.. were written by flipped lanes
-            else b[n2] = rowL[n2];
+            if constexpr (P == 32) b[n2] = (n2 >= 16 ? rowF : rowN)[SWZ ? (n2 ^ ((n2 >= 16 ? rF : rN) % P)) : n2];   // columns 16.. were written by flipped lanes
+            else b[n2] = rowL[SWZ ? (n2 ^ (rL % P)) : n2];
         }
         fft_reg<P>(b);
         const float2* pk = post + k1;
@@ -321,8 +325,12 @@ template <class C>
 struct SynCfg {
     static constexpr int ROWS = C::FPT;
     static constexpr int BUF = ROWS * C::ROW;                       // floats per coefficient buffer
+    // (16,16), n_fft 1024: the exchange region of a frame is laid over the frame's own coefficient row (swizzled form,
+    // 2*V*P floats = M = the row), which brings the CTA from 106 KB to 72 KB of shared memory: three CTAs per SM
+    static constexpr bool ALIAS = (C::V == 16 && C::P == 16 && C::ROWPAD == 0);
+    static constexpr int MINB = ALIAS ? 3 : 0;                      // 0: no occupancy request (as before)
     static constexpr int OFF_X = 2 * BUF;
-    static constexpr int OFF_TB = OFF_X + kWarps * C::G * C::XREG;
+    static constexpr int OFF_TB = OFF_X + (ALIAS ? 0 : kWarps * C::G * C::XREG);
     static constexpr int OFF_BAR = OFF_TB + C::TBF;
     static constexpr size_t SMEM_BYTES = 4ull * OFF_BAR + 16;
     static constexpr int G4 = C::M / 4;                             // float4 groups per hop slot
@@ -375,7 +383,12 @@ __device__ __forceinline__ void synthesis_warp(float* __restrict__ buf, float* _
         z[n1] = cmulf(make_float2(ln.flip ? b : a, ln.flip ? a : b), tw);
     }
     float re_[C::Q][P], nim[C::Q][P];
-    fft_core<C>(z, ex_warp, post, roots, xr, ln, CREV, re_, nim);
+    if constexpr (SynCfg<C>::ALIAS) {
+        __syncwarp();                       // every lane of the frame holds its coefficients: the row becomes the exchange region
+        fft_core<C, true>(z, buf + warp * C::G * C::ROW, post, roots, xr, ln, CREV, re_, nim, C::ROW);
+    } else {
+        fft_core<C>(z, ex_warp, post, roots, xr, ln, CREV, re_, nim);
+    }
 
     float* tp = row + 2 * ln.j;
 #pragma unroll
@@ -390,7 +403,7 @@ __device__ __forceinline__ void synthesis_warp(float* __restrict__ buf, float* _
 }
 
 template <class C>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, SynCfg<C>::MINB)
 mdct4_synthesis_fast(const float* __restrict__ spec, float* __restrict__ out, const float* __restrict__ window,
                      const void* __restrict__ tables, int F, long long T_out, long long crop_left, float scale,
                      int h_first, int h_last, int tiles_per_row, long long total_tiles, int aligned_in, int vec_out) {
