@@ -503,17 +503,17 @@ __global__ void avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, i
     }
 }
 
-template <typename T>
+template <typename T, typename I>        // I: index type (unsigned when the tensor has < 2^31 elements: 64-bit divisions are slow)
 __global__ void avgpool_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int H, int W, int C, int OH, int OW,
                                    long long total) {
     pdl_trigger();
     pdl_wait();
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int c = (int)(i % C);
-        long long r = i / C;
-        const int w = (int)(r % W); r /= W;
-        const int h = (int)(r % H);
-        const long long n = r / H;
+    for (I i = (I)blockIdx.x * blockDim.x + threadIdx.x; i < (I)total; i += (I)gridDim.x * blockDim.x) {
+        const int c = (int)(i % (I)C);
+        I r = i / (I)C;
+        const int w = (int)(r % (I)W); r /= (I)W;
+        const int h = (int)(r % (I)H);
+        const long long n = (long long)(r / (I)H);
         // outputs whose window [2o-1, 2o+1] contains h: o in [ceil((h-1)/2), floor((h+1)/2)]
         float s = 0.f;
         for (int oh = h / 2; oh <= min((h + 1) / 2, OH - 1); ++oh) {
@@ -948,7 +948,10 @@ extern "C" int p2p_avgpool3s2_bwd(const void* dy, void* dx, int N, int H, int W,
     const long long total = (long long)N * H * W * C;
     if (total == 0) return P2P_OK;
     if (!dx || !dy) return fail(P2P_EINVAL, "null pointer argument");
-    P2P_DISPATCH_DTYPE(dtype, T, launch_k(avgpool_bwd_kernel<T>, dim3((unsigned)(ew_grid(total))), dim3(kEw), 0, (cudaStream_t)stream, (const T*)dy, (T*)dx, H, W, C, OH, OW, total));
+    if (total < 2000000000LL)
+        P2P_DISPATCH_DTYPE(dtype, T, launch_k(avgpool_bwd_kernel<T, unsigned>, dim3((unsigned)(ew_grid(total))), dim3(kEw), 0, (cudaStream_t)stream, (const T*)dy, (T*)dx, H, W, C, OH, OW, total));
+    else
+        P2P_DISPATCH_DTYPE(dtype, T, launch_k(avgpool_bwd_kernel<T, long long>, dim3((unsigned)(ew_grid(total))), dim3(kEw), 0, (cudaStream_t)stream, (const T*)dy, (T*)dx, H, W, C, OH, OW, total));
     return check_launch("avgpool3s2_bwd");
 }
 

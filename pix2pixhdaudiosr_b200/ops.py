@@ -1523,6 +1523,7 @@ class AvgPool3s2Fn(torch.autograd.Function):
     def forward(ctx, x, gated=False):
         _need_cuda(x)
         ctx.gated = bool(gated)
+        ctx.halves = BATCH_HALVES
         ctx.set_materialize_grads(False)
         x = x.contiguous()
         N, H, W, C = x.shape
@@ -1538,7 +1539,11 @@ class AvgPool3s2Fn(torch.autograd.Function):
         N, H, W, C = ctx.shape
         dy = dy.contiguous()
         dx = torch.empty((N, H, W, C), dtype=dy.dtype, device=dy.device)
-        _lib.check(_lib.lib().p2p_avgpool3s2_bwd(_p(dy), _p(dx), N, H, W, C, _DT[dy.dtype], _stream()))
+        if ctx.halves and FAKE_HALF_ONLY and N == 2 * ctx.halves:       # batched discriminator pass, phase G: the fake images only
+            B = ctx.halves
+            _lib.check(_lib.lib().p2p_avgpool3s2_bwd(_p(dy[B:]), _p(dx[B:]), B, H, W, C, _DT[dy.dtype], _stream()))
+        else:
+            _lib.check(_lib.lib().p2p_avgpool3s2_bwd(_p(dy), _p(dx), N, H, W, C, _DT[dy.dtype], _stream()))
         return dx, None
 
 
