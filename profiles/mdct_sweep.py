@@ -38,7 +38,10 @@ def main():
         hop = n_fft // 2
         m = (pm.MDCT2 if mdct2 else pm.MDCT4)(n_fft, hop, n_fft, kbdwin, True, device=dev)
         im = (pm.IMDCT2 if mdct2 else pm.IMDCT4)(n_fft, hop, n_fft, kbdwin, True, device=dev)
-        for B_total in ((1, 16, 256, 1024) if mdct2 else (1, 4, 16, 64, 256, 1024)):
+        sizes = (1, 16, 256, 1024) if mdct2 else (1, 4, 16, 64, 256, 1024)
+        if world > 1:
+            sizes = sizes + (1024 * world,)          # the per-GPU plateau size on every rank
+        for B_total in sizes:
             B = max(1, B_total // world)            # per rank (B_total < world: every rank runs one segment)
             x = 0.1 * torch.randn(B, T, device=dev)
             sp, ep = m.pads(B)
