@@ -451,6 +451,77 @@ __global__ void __launch_bounds__(256) in_bwd_apply_wrap_v4_kernel(const TY* __r
     }
 }
 
+// Round 2 (second half): the same arithmetic with one (image, channel group) per THREAD.  grid (gx, N), 256 threads, 256*gx a
+// multiple of C4: thread t = blockIdx.x*256 + threadIdx.x keeps channel group t % C4 for its whole life and walks the rows
+// t / C4, + 256*gx/C4, ...; the four (mean, rstd) and (sum g, sum g*xhat) pairs are loaded once instead of per element, and the
+// per-element divisions are gone.  WRAP: rows are those of the zero-margined grid at the padded input's pitch (see
+// in_bwd_apply_wrap_v4_kernel), margin rows are written as zeros; the slice blockIdx.y == N zeroes the tail of the grid.
+template <typename TY, typename T, bool WRAP>
+__global__ void __launch_bounds__(256) in_bwd_apply_rows_v4_kernel(const TY* __restrict__ y, const float* __restrict__ stats,
+                                                                   const T* __restrict__ dz, const float* __restrict__ work,
+                                                                   T* __restrict__ out, int N, int H, int W, unsigned C4, int Hh, int Wh,
+                                                                   long long grid_rows, float inv, int norm, int act, float slope) {
+    pdl_trigger();
+    pdl_wait();
+    const unsigned t = blockIdx.x * 256u + threadIdx.x, c4 = t % C4, row0 = t / C4, rstep = gridDim.x * 256u / C4;
+    const unsigned n = blockIdx.y;
+    const float zero4[4] = {0.f, 0.f, 0.f, 0.f};
+    if (WRAP && n == (unsigned)N) {                      // tail of the grid beyond the last image
+        for (long long q = (long long)N * Hh * Wh + row0; q < grid_rows; q += rstep) st4(out + (q * C4 + c4) * 4, zero4);
+        return;
+    }
+    float mean[4] = {0.f, 0.f, 0.f, 0.f}, rstd[4] = {1.f, 1.f, 1.f, 1.f}, wa[4] = {0.f, 0.f, 0.f, 0.f}, wb[4] = {0.f, 0.f, 0.f, 0.f};
+    if (norm) {
+        const long long so = ((long long)n * C4 + c4) * 8;
+        const float4 s0 = __ldg(reinterpret_cast<const float4*>(stats + so)), s1 = __ldg(reinterpret_cast<const float4*>(stats + so) + 1);
+        const float4 w0 = __ldg(reinterpret_cast<const float4*>(work + so)), w1 = __ldg(reinterpret_cast<const float4*>(work + so) + 1);
+        mean[0] = s0.x; mean[1] = s0.z; mean[2] = s1.x; mean[3] = s1.z;
+        rstd[0] = s0.y; rstd[1] = s0.w; rstd[2] = s1.y; rstd[3] = s1.w;
+        wa[0] = w0.x; wa[1] = w0.z; wa[2] = w1.x; wa[3] = w1.z;
+        wb[0] = w0.y; wb[1] = w0.w; wb[2] = w1.y; wb[3] = w1.w;
+    }
+    const unsigned HW = (unsigned)(H * W), rows = WRAP ? (unsigned)(Hh * Wh) : HW;
+    const TY* yb = y + ((long long)n * HW * C4 + c4) * 4;
+    const T* zb = dz + ((long long)n * HW * C4 + c4) * 4;
+    T* ob = out + ((long long)n * rows * C4 + c4) * 4;
+#pragma unroll 2
+    for (unsigned q = row0; q < rows; q += rstep) {
+        unsigned r = q;
+        if (WRAP) {
+            const unsigned h = q / (unsigned)Wh, w = q - h * (unsigned)Wh;
+            if (h >= (unsigned)H || w >= (unsigned)W) { st4(ob + (long long)q * C4 * 4, zero4); continue; }
+            r = h * (unsigned)W + w;
+        }
+        float v[4], g[4], o[4];
+        ld4(yb + (long long)r * C4 * 4, v);
+        ld4(zb + (long long)r * C4 * 4, g);
+        if (!norm) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) o[k] = g[k] * act_grad(v[k], act, slope);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float xh = (v[k] - mean[k]) * rstd[k];
+                const float gg = g[k] * act_grad(xh, act, slope);
+                o[k] = rstd[k] * (gg - wa[k] * inv - xh * wb[k] * inv);
+            }
+        }
+        st4(ob + (long long)q * C4 * 4, o);
+    }
+}
+
+// grid.x for the kernel above: ~16 CTAs per SM in total, a multiple of C4 / gcd(C4, 256), no more threads than (row, group) pairs
+inline unsigned rows_grid_x(unsigned C4, long long rows, int slices) {
+    unsigned a = C4, b = 256;
+    while (b) { const unsigned r = a % b; a = b; b = r; }
+    const unsigned m = C4 / a;                                       // 256 * gx % C4 == 0  <=>  gx % m == 0
+    long long want = (148LL * 16 + slices - 1) / slices;
+    const long long cap = (rows * C4 + 255) / 256;
+    if (want > cap) want = cap;
+    if (want < 1) want = 1;
+    return (unsigned)((want + m - 1) / m * m);
+}
+
 // adjoint of ReflectionPad2d, four channels per thread
 template <typename TI, typename T>
 __global__ void __launch_bounds__(256) reflect_fold_v4_kernel(const TI* __restrict__ dxp, T* __restrict__ dx, int H, int W, int C4,
@@ -692,6 +763,10 @@ inline int ew_grid(long long n) {
     const long long cap = 148LL * 16;
     return (int)(b < 1 ? 1 : (b > cap ? cap : b));
 }
+inline bool bwd_rows_form() {          // P2P_IN_BWD_ROWS=0: the per-element kernels of round 1
+    static const bool on = [] { const char* e = getenv("P2P_IN_BWD_ROWS"); return !(e && e[0] == '0'); }();
+    return on;
+}
 inline int split_for(long long rows, int base_ctas) {      // chunks of the row dimension so that ~4 CTAs/SM exist
     if (deterministic()) return 1;                         // one writer per statistic
     long long s = (148LL * 4 + base_ctas - 1) / base_ctas;
@@ -895,7 +970,10 @@ extern "C" int p2p_instnorm_act_bwd(const void* y, const float* stats, const voi
                 in_bwd_stats_kernel<TY, T><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, (const T*)dz, work, HW, C, chunk, act, slope);
             }
         }
-        if (vec)
+        if (vec && bwd_rows_form() && HW * (C / 4) < 2000000000LL)
+            launch_k(in_bwd_apply_rows_v4_kernel<TY, T, false>, dim3(rows_grid_x((unsigned)(C / 4), HW, N), N), dim3(256), 0, st, (const TY*)y, stats,
+                     (const T*)dz, (const float*)work, (T*)dy, N, (int)HW, 1, (unsigned)(C / 4), (int)HW, 1, 0LL, 1.f / (float)HW, norm, act, slope);
+        else if (vec)
             launch_k(in_bwd_apply_v4_kernel<TY, T>, dim3((unsigned)(ew_grid(total / 4))), dim3(kEw), 0, st, (const TY*)y, stats, (const T*)dz, work, (T*)dy, (unsigned)(HW * (C / 4)),
                                                                               (unsigned)(C / 4), (unsigned)(total / 4), 1.f / (float)HW, norm, act, slope);
         else
@@ -926,8 +1004,12 @@ extern "C" int p2p_instnorm_act_bwd_wrap(const void* y, const float* stats, cons
             if (cudaMemsetAsync(work, 0, sizeof(float) * 2 * N * C, st) != cudaSuccess) return fail(P2P_ECUDA, "memset failed");
             in_bwd_stats_v4_kernel<TY, T><<<dim3(cb, N, S), dim3(32, 8), 0, st>>>((const TY*)y, stats, (const T*)dz, work, (int)HW, C, chunk, act, slope);
         }
-        launch_k(in_bwd_apply_wrap_v4_kernel<TY, T>, dim3((unsigned)(ew_grid(total / 4))), dim3(kEw), 0, st, (const TY*)y, stats, (const T*)dz,
-                 (const float*)work, (T*)grid, N, H, W, (unsigned)(C / 4), Hh, Wh, (unsigned)(total / 4), 1.f / (float)HW, norm, act, slope);
+        if (bwd_rows_form() && (long long)Hh * Wh * (C / 4) < 2000000000LL)
+            launch_k(in_bwd_apply_rows_v4_kernel<TY, T, true>, dim3(rows_grid_x((unsigned)(C / 4), (long long)Hh * Wh, N + 1), N + 1), dim3(256), 0, st,
+                     (const TY*)y, stats, (const T*)dz, (const float*)work, (T*)grid, N, H, W, (unsigned)(C / 4), Hh, Wh, rows, 1.f / (float)HW, norm, act, slope);
+        else
+            launch_k(in_bwd_apply_wrap_v4_kernel<TY, T>, dim3((unsigned)(ew_grid(total / 4))), dim3(kEw), 0, st, (const TY*)y, stats, (const T*)dz,
+                     (const float*)work, (T*)grid, N, H, W, (unsigned)(C / 4), Hh, Wh, (unsigned)(total / 4), 1.f / (float)HW, norm, act, slope);
     });
     return check_launch("instnorm_act_bwd_wrap");
 }
