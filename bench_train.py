@@ -254,13 +254,16 @@ def run_train(args):
         # kernels, which speeds the step up but makes an event pair measure two kernels sharing the SMs -- the roofline leg
         # wants each kernel's own duration)
         pg = torch.cuda.CUDAGraph()
+        from pix2pixhdaudiosr_b200 import train as _train
         overlap0, ops.WGRAD_OVERLAP = ops.WGRAD_OVERLAP, False
+        gstep0, _train.OVERLAP_G_STEP = _train.OVERLAP_G_STEP, False      # (likewise the generator's Adam next to D's backward)
         ops.start_conv_timing(external=True)
         try:
             with torch.cuda.graph(pg):
                 train_step(model, lr_d, hr_d, sync=sync)
         finally:
             ops.WGRAD_OVERLAP = overlap0
+            _train.OVERLAP_G_STEP = gstep0
         ops.pause_conv_timing()
         pg.replay()
         torch.cuda.synchronize(dev)
@@ -331,9 +334,9 @@ def run_train(args):
                                          "ms_per_step_in_kernels": round(um_ms, 3), "share_of_step": round(um_ms / step_ms, 3)},
                          "note": "algorithmic conv FLOPs (2*MACs) of the kernel's launches in one step / their summed "
                                  "CUDA-event durations, measured in one extra profiled step after the timed region "
-                                 "(a CUDA graph replay with the event pairs as graph nodes and the weight-gradient kernels in the "
-                                 "main stream -- the timed step runs them on a side stream next to memory-bound kernels, where an "
-                                 "event pair would time two kernels sharing the SMs; eager with --no-graph); share_of_step therefore "
+                                 "(a CUDA graph replay with the event pairs as graph nodes and the weight-gradient kernels and the "
+                                 "generator's optimiser update in the main stream -- the timed step runs them on side streams next to "
+                                 "other kernels, where an event pair would time two kernels sharing the SMs; eager with --no-graph); share_of_step therefore "
                                  "compares un-overlapped kernel time with the overlapped step"},
             "step_tensor_utilisation": round(all_flops / (step_ms * 1e-3) / 1e12 / peak, 4),
             "conv_flops_per_step": round(all_flops),
