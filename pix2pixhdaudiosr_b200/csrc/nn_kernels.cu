@@ -183,25 +183,30 @@ __global__ void __launch_bounds__(256) in_stats_fused_v4_kernel(const T* __restr
                                                                 unsigned* __restrict__ cnt, int HW, int C, int chunk, float eps) {
     pdl_trigger();
     pdl_wait();
-    __shared__ float sm[8][32][9];
-    const int cg = blockIdx.x * 32 + threadIdx.x, n = blockIdx.y, C4 = C >> 2;
+    // LX channel groups x RY rows of threads: 32 x 8 on a full channel block; a block with fewer than 32 groups (C < 128, or
+    // the last block of C % 128 != 0) spreads its 256 threads over more rows instead of leaving lanes idle
+    __shared__ float sm[256 * 9];
+    const int n = blockIdx.y, C4 = C >> 2;
+    const int t = threadIdx.y * 32 + threadIdx.x;
+    const int LX = min(32, C4 - (int)blockIdx.x * 32), RY = 256 / LX;
+    const int cx = t % LX, ry = t / LX, cg = blockIdx.x * 32 + cx;
     const int r0 = blockIdx.z * chunk, r1 = min(HW, r0 + chunk);
     float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f};
-    if (cg < C4) {
+    if (ry < RY) {
         const T* base = y + (long long)n * HW * C + cg * 4;
         float shift[4];
         ld4(base, shift);
-        int r = r0 + threadIdx.y;
-        for (; r + 24 < r1; r += 32) {           // four rows in flight per thread
+        int r = r0 + ry;
+        for (; r + 3 * RY < r1; r += 4 * RY) {           // four rows in flight per thread
             float v[4][4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) ld4(base + (long long)(r + 8 * u) * C, v[u]);
+            for (int u = 0; u < 4; ++u) ld4(base + (long long)(r + RY * u) * C, v[u]);
 #pragma unroll
             for (int u = 0; u < 4; ++u)
 #pragma unroll
                 for (int i = 0; i < 4; ++i) { const float d = v[u][i] - shift[i]; a[i] += d; b[i] += d * d; }
         }
-        for (; r < r1; r += 8) {
+        for (; r < r1; r += RY) {
             float v[4];
             ld4(base + (long long)r * C, v);
 #pragma unroll
@@ -209,14 +214,13 @@ __global__ void __launch_bounds__(256) in_stats_fused_v4_kernel(const T* __restr
         }
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { sm[threadIdx.y][threadIdx.x][i] = a[i]; sm[threadIdx.y][threadIdx.x][4 + i] = b[i]; }
+    for (int i = 0; i < 4; ++i) { sm[t * 9 + i] = a[i]; sm[t * 9 + 4 + i] = b[i]; }
     __syncthreads();
-    const int t = threadIdx.y * 32 + threadIdx.x, g = t >> 3, k = t & 7, cgo = blockIdx.x * 32 + g;
+    const int g = t >> 3, k = t & 7, cgo = blockIdx.x * 32 + g;
     const long long wi = ((long long)n * C + cgo * 4 + (k & 3)) * 2 + (k >> 2);
-    if (cgo < C4) {
+    if (g < LX) {
         float s = 0.f;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) s += sm[i][g][k];
+        for (int i = 0; i < RY; ++i) s += sm[(i * LX + g) * 9 + k];
         if (gridDim.z > 1) atomicAdd(ws + wi, s); else ws[wi] = s;
     }
     if (!last_cta_of_group(cnt + (long long)n * gridDim.x + blockIdx.x, gridDim.z)) return;
@@ -240,22 +244,25 @@ __global__ void __launch_bounds__(256) in_bwd_stats_fused_v4_kernel(const TY* __
                                                                     int chunk, int act, float slope) {
     pdl_trigger();
     pdl_wait();
-    __shared__ float sm[8][32][9];
-    const int cg = blockIdx.x * 32 + threadIdx.x, n = blockIdx.y, C4 = C >> 2;
+    __shared__ float sm[256 * 9];                // thread layout: see in_stats_fused_v4_kernel
+    const int n = blockIdx.y, C4 = C >> 2;
+    const int t = threadIdx.y * 32 + threadIdx.x;
+    const int LX = min(32, C4 - (int)blockIdx.x * 32), RY = 256 / LX;
+    const int cx = t % LX, ry = t / LX, cg = blockIdx.x * 32 + cx;
     const int r0 = blockIdx.z * chunk, r1 = min(HW, r0 + chunk);
     float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f};
-    if (cg < C4) {
+    if (ry < RY) {
         const long long off = (long long)n * HW * C + cg * 4;
         const float4* sp = reinterpret_cast<const float4*>(stats + ((long long)n * C + cg * 4) * 2);
         const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
         const float mean[4] = {s0.x, s0.z, s1.x, s1.z}, rstd[4] = {s0.y, s0.w, s1.y, s1.w};
-        int r = r0 + threadIdx.y;
-        for (; r + 24 < r1; r += 32) {           // four rows in flight per thread
+        int r = r0 + ry;
+        for (; r + 3 * RY < r1; r += 4 * RY) {           // four rows in flight per thread
             float v[4][4], g[4][4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                ld4(y + off + (long long)(r + 8 * u) * C, v[u]);
-                ld4(dz + off + (long long)(r + 8 * u) * C, g[u]);
+                ld4(y + off + (long long)(r + RY * u) * C, v[u]);
+                ld4(dz + off + (long long)(r + RY * u) * C, g[u]);
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u)
@@ -266,7 +273,7 @@ __global__ void __launch_bounds__(256) in_bwd_stats_fused_v4_kernel(const TY* __
                     a[i] += gg; b[i] += gg * xh;
                 }
         }
-        for (; r < r1; r += 8) {
+        for (; r < r1; r += RY) {
             float v[4], g[4];
             ld4(y + off + (long long)r * C, v);
             ld4(dz + off + (long long)r * C, g);
@@ -279,18 +286,17 @@ __global__ void __launch_bounds__(256) in_bwd_stats_fused_v4_kernel(const TY* __
         }
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { sm[threadIdx.y][threadIdx.x][i] = a[i]; sm[threadIdx.y][threadIdx.x][4 + i] = b[i]; }
+    for (int i = 0; i < 4; ++i) { sm[t * 9 + i] = a[i]; sm[t * 9 + 4 + i] = b[i]; }
     __syncthreads();
-    const int t = threadIdx.y * 32 + threadIdx.x, g = t >> 3, k = t & 7, cgo = blockIdx.x * 32 + g;
+    const int g = t >> 3, k = t & 7, cgo = blockIdx.x * 32 + g;
     const long long wi = ((long long)n * C + cgo * 4 + (k & 3)) * 2 + (k >> 2);
-    if (cgo < C4) {
+    if (g < LX) {
         float s = 0.f;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) s += sm[i][g][k];
+        for (int i = 0; i < RY; ++i) s += sm[(i * LX + g) * 9 + k];
         if (gridDim.z > 1) atomicAdd(ws + wi, s); else ws[wi] = s;
     }
     if (!last_cta_of_group(cnt + (long long)n * gridDim.x + blockIdx.x, gridDim.z)) return;
-    if (cgo < C4) { work[wi] = __ldcg(ws + wi); ws[wi] = 0.f; }
+    if (g < LX) { work[wi] = __ldcg(ws + wi); ws[wi] = 0.f; }
 }
 
 template <typename TY, typename T>
